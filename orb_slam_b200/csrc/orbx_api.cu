@@ -1,0 +1,367 @@
+// C-ABI layer of the extractor (include/orbx.h): handle, device memory, chunked / pipelined execution.
+// Host glue only — all arithmetic is in orbx_kernels.cu.  No CPU fallback: without a CUDA device orbx_create fails.
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+
+#include "orbx_kernels.cuh"
+
+using namespace orbx;
+
+struct orbx_handle {
+  orbx_params p;
+  HostPlan hp;
+  int plan_w = 0, plan_h = 0;
+  BlurTiles tiles;
+  std::string err;
+  // device memory (sized once for max_batch frames of max_width x max_height)
+  uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_in[2] = {nullptr, nullptr};
+  Cand *d_cand = nullptr, *d_list = nullptr, *d_kp = nullptr;
+  int32_t *d_n_total = nullptr, *d_n_retain = nullptr, *d_kp_count = nullptr, *d_err = nullptr;
+  DevicePlan* d_plan = nullptr;
+  CellPlan* d_cells = nullptr;
+  ResizeX* d_rx = nullptr;
+  ResizeY* d_ry = nullptr;
+  orbx_keypoint* d_out_kps[2] = {nullptr, nullptr};
+  uint8_t* d_out_desc[2] = {nullptr, nullptr};
+  int32_t* d_out_n[2] = {nullptr, nullptr};
+  size_t cap_cells = 0, cap_rx = 0, cap_ry = 0;
+  int64_t cap_pyr = 0, cap_cand = 0, cap_list = 0, cap_cells_frame = 0;
+  int in_pitch = 0;
+  int64_t in_frame_bytes = 0;
+  cudaStream_t s_compute = nullptr, s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2], ev_compute[2], ev_out[2], ev_stage[ORBX_STAGE_COUNT + 1];
+  bool profiling = false;
+  float prof_ms[ORBX_STAGE_COUNT] = {0};
+  int64_t prof_launch[ORBX_STAGE_COUNT] = {0};
+  int64_t launches = 0;
+  // last chunk (for the debug getters)
+  ChunkBuffers last{};
+  int last_frames = 0;
+};
+
+static thread_local std::string g_create_err;
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+      return ORBX_ERR_CUDA;                                                                        \
+    }                                                                                              \
+  } while (0)
+
+extern "C" int orbx_default_params(orbx_params* p) {
+  if (!p) return ORBX_ERR_ARG;
+  p->nfeatures = 1000; p->scale_factor = 1.2f; p->nlevels = 8; p->score_type = ORBX_FAST_SCORE; p->fast_th = 20;
+  p->max_width = 640; p->max_height = 480; p->max_batch = 256; p->device = 0;
+  p->blur_mode = ORBX_BLUR_CV24; p->retain_mode = ORBX_RETAIN_CV24;
+  return ORBX_OK;
+}
+
+// Minimal `%YAML:1.0` "key: value" reader for the five ORBextractor.* keys (the reference uses cv::FileStorage,
+// src/Tracking.cc:52,105-109).  Note the shipped file writes "Camera.k1:-0.4157" without a space; accepted.
+extern "C" int orbx_params_from_yaml(const char* path, orbx_params* p) {
+  if (!path || !p) return ORBX_ERR_ARG;
+  std::ifstream f(path);
+  if (!f) { g_create_err = std::string("cannot open ") + path; return ORBX_ERR_IO; }
+  std::string line;
+  int found = 0;
+  while (std::getline(f, line)) {
+    size_t hash = line.find('#');
+    if (hash != std::string::npos) line.resize(hash);
+    size_t colon = line.find(':');
+    if (colon == std::string::npos) continue;
+    std::string key = line.substr(0, colon), val = line.substr(colon + 1);
+    while (!key.empty() && isspace((unsigned char)key.back())) key.pop_back();
+    size_t k0 = 0;
+    while (k0 < key.size() && isspace((unsigned char)key[k0])) k0++;
+    key = key.substr(k0);
+    double v = atof(val.c_str());
+    if (key == "ORBextractor.nFeatures") { p->nfeatures = (int)v; found |= 1; }
+    else if (key == "ORBextractor.scaleFactor") { p->scale_factor = (float)v; found |= 2; }
+    else if (key == "ORBextractor.nLevels") { p->nlevels = (int)v; found |= 4; }
+    else if (key == "ORBextractor.fastTh") { p->fast_th = (int)v; found |= 8; }
+    else if (key == "ORBextractor.nScoreType") { p->score_type = (int)v; found |= 16; }
+  }
+  if (found != 31) { g_create_err = "Settings file lacks one of the ORBextractor.* keys"; return ORBX_ERR_IO; }
+  if (p->score_type != 0 && p->score_type != 1) {  // assert(Score==1 || Score==0), src/Tracking.cc:111
+    g_create_err = "ORBextractor.nScoreType must be 0 or 1";
+    return ORBX_ERR_ARG;
+  }
+  return ORBX_OK;
+}
+
+static int upload_plan(orbx_handle* h, int w, int hgt) {
+  if (h->plan_w == w && h->plan_h == hgt) return ORBX_OK;
+  int rc = build_plan(h->p, w, hgt, &h->hp, &h->err);
+  if (rc != ORBX_OK) return rc;
+  const DevicePlan& dp = h->hp.dp;
+  if (h->hp.cells.size() > h->cap_cells || h->hp.rx.size() > h->cap_rx || h->hp.ry.size() > h->cap_ry ||
+      dp.pyr_frame_bytes > h->cap_pyr || dp.cand_per_frame > h->cap_cand || dp.list_per_frame > h->cap_list ||
+      dp.total_cells > h->cap_cells_frame) {
+    h->err = "image larger than the max_width x max_height the handle was created for";
+    return ORBX_ERR_ARG;
+  }
+  if (fast_cells_smem_bytes(h->hp.max_cell_px) > 200 * 1024) {
+    h->err = "cell too large for the shared-memory FAST tile (cell area > ~100k px)";
+    return ORBX_ERR_UNSUPPORTED;
+  }
+  CK(cudaStreamSynchronize(h->s_compute));
+  CK(cudaMemcpy(h->d_plan, &dp, sizeof(dp), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h->d_cells, h->hp.cells.data(), h->hp.cells.size() * sizeof(CellPlan), cudaMemcpyHostToDevice));
+  if (!h->hp.rx.empty()) {
+    CK(cudaMemcpy(h->d_rx, h->hp.rx.data(), h->hp.rx.size() * sizeof(ResizeX), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->d_ry, h->hp.ry.data(), h->hp.ry.size() * sizeof(ResizeY), cudaMemcpyHostToDevice));
+  }
+  int base = 0;
+  for (int l = 0; l < dp.nlevels; l++) {
+    h->tiles.base[l] = base;
+    h->tiles.tiles_x[l] = (dp.lv[l].w + 63) / 64;
+    base += h->tiles.tiles_x[l] * ((dp.lv[l].h + 31) / 32);
+  }
+  h->tiles.base[dp.nlevels] = base;
+  h->plan_w = w; h->plan_h = hgt;
+  return ORBX_OK;
+}
+
+extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
+  if (!pp || !out) return ORBX_ERR_ARG;
+  *out = nullptr;
+  orbx_handle* h = new orbx_handle();
+  h->p = *pp;
+  auto fail = [&](int rc) { g_create_err = h->err; delete h; return rc; };
+  if (pp->max_batch < 1 || pp->max_width < 1 || pp->max_height < 1 || pp->fast_th < 1 || pp->fast_th > 254 ||
+      (pp->score_type != 0 && pp->score_type != 1) || pp->blur_mode < 0 || pp->blur_mode > 1 ||
+      pp->retain_mode < 0 || pp->retain_mode > 1 || !(pp->scale_factor > 1.0f)) {
+    h->err = "bad parameters";
+    return fail(ORBX_ERR_ARG);
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || pp->device < 0 || pp->device >= ndev) {
+    h->err = "no usable CUDA device (this library has no CPU fallback)";
+    return fail(ORBX_ERR_CUDA);
+  }
+  auto body = [&]() -> int {
+    CK(cudaSetDevice(pp->device));
+    HostPlan mp;  // plan of the largest frame sizes every buffer
+    int rc = build_plan(h->p, pp->max_width, pp->max_height, &mp, &h->err);
+    if (rc != ORBX_OK) return rc;
+    const DevicePlan& dp = mp.dp;
+    const int64_t B = pp->max_batch;
+    // smaller frames have fewer pixels but may have (slightly) different grids: keep generous slack
+    h->cap_cells = mp.cells.size() * 2 + 64; h->cap_rx = mp.rx.size() + 64; h->cap_ry = mp.ry.size() + 64;
+    h->cap_pyr = dp.pyr_frame_bytes; h->cap_cand = dp.cand_per_frame + 1024; h->cap_list = dp.list_per_frame * 2;
+    h->cap_cells_frame = dp.total_cells * 2 + 64;
+    h->in_pitch = (pp->max_width + 15) / 16 * 16;
+    h->in_frame_bytes = (int64_t)h->in_pitch * pp->max_height;
+    CK(cudaMalloc(&h->d_pyr, B * h->cap_pyr));
+    CK(cudaMalloc(&h->d_blur, B * h->cap_pyr));
+    CK(cudaMalloc(&h->d_cand, B * h->cap_cand * sizeof(Cand)));
+    CK(cudaMalloc(&h->d_list, B * h->cap_list * sizeof(Cand)));
+    CK(cudaMalloc(&h->d_kp, B * pp->nfeatures * sizeof(Cand)));
+    CK(cudaMalloc(&h->d_n_total, B * h->cap_cells_frame * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_n_retain, B * h->cap_cells_frame * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_kp_count, B * kMaxLevels * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_err, sizeof(int32_t)));
+    CK(cudaMemset(h->d_err, 0, sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_plan, sizeof(DevicePlan)));
+    CK(cudaMalloc(&h->d_cells, h->cap_cells * sizeof(CellPlan)));
+    CK(cudaMalloc(&h->d_rx, h->cap_rx * sizeof(ResizeX)));
+    CK(cudaMalloc(&h->d_ry, h->cap_ry * sizeof(ResizeY)));
+    for (int i = 0; i < 2; i++) {
+      CK(cudaMalloc(&h->d_in[i], B * h->in_frame_bytes));
+      CK(cudaMalloc(&h->d_out_kps[i], B * pp->nfeatures * sizeof(orbx_keypoint)));
+      CK(cudaMalloc(&h->d_out_desc[i], B * pp->nfeatures * 32));
+      CK(cudaMalloc(&h->d_out_n[i], B * sizeof(int32_t)));
+      CK(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->ev_compute[i], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming));
+    }
+    for (int i = 0; i <= ORBX_STAGE_COUNT; i++) CK(cudaEventCreate(&h->ev_stage[i]));
+    CK(cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    return upload_plan(h, pp->max_width, pp->max_height);
+  };
+  int rc = body();
+  if (rc != ORBX_OK) { std::string m = h->err; orbx_destroy(h); g_create_err = m; return rc; }
+  *out = h;
+  return ORBX_OK;
+}
+
+extern "C" void orbx_destroy(orbx_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->p.device);
+  cudaDeviceSynchronize();
+  void* ptrs[] = {h->d_pyr, h->d_blur, h->d_cand, h->d_list, h->d_kp, h->d_n_total, h->d_n_retain, h->d_kp_count,
+                  h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_in[0], h->d_in[1], h->d_out_kps[0],
+                  h->d_out_kps[1], h->d_out_desc[0], h->d_out_desc[1], h->d_out_n[0], h->d_out_n[1]};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (h->s_compute) {
+    cudaStreamDestroy(h->s_compute); cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
+    for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_compute[i]); cudaEventDestroy(h->ev_out[i]); }
+    for (int i = 0; i <= ORBX_STAGE_COUNT; i++) cudaEventDestroy(h->ev_stage[i]);
+  }
+  delete h;
+}
+
+extern "C" int orbx_get_levels(const orbx_handle* h) { return h ? h->p.nlevels : 0; }
+extern "C" float orbx_get_scale_factor(const orbx_handle* h) { return h ? (float)(double)h->p.scale_factor : 0.f; }
+extern "C" const char* orbx_last_error(const orbx_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+extern "C" int64_t orbx_kernel_launches(const orbx_handle* h) { return h ? h->launches : 0; }
+
+// One chunk (<= max_batch frames) on stream s: 7 resizes, FAST cells, select, blur, describe = nlevels + 3 launches.
+static int run_chunk(orbx_handle* h, const uint8_t* d_imgs, int n, size_t stride, size_t frame_stride,
+                     orbx_keypoint* d_kps, uint8_t* d_desc, int32_t* d_n, cudaStream_t s) {
+  const DevicePlan& dp = h->hp.dp;
+  ChunkBuffers b{};
+  b.lv0 = d_imgs; b.lv0_frame_stride = (int64_t)frame_stride; b.lv0_pitch = (int)stride;
+  b.pyr = h->d_pyr; b.blur = h->d_blur; b.cand = h->d_cand; b.n_total = h->d_n_total; b.n_retain = h->d_n_retain;
+  b.list = h->d_list; b.kp = h->d_kp; b.kp_count = h->d_kp_count; b.err_flag = h->d_err;
+  b.plan = h->d_plan; b.cells = h->d_cells; b.rx = h->d_rx; b.ry = h->d_ry;
+  const bool prof = h->profiling;
+  int st = 0;
+  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  for (int l = 1; l < dp.nlevels; l++) launch_resize_level(b, dp, l, n, s);
+  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  launch_fast_cells(b, dp, h->hp.max_cell_px, n, s);
+  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  launch_select(b, dp, n, s);
+  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  launch_blur(b, dp, h->tiles, n, s);
+  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  launch_describe(b, dp, n, d_kps, d_desc, d_n, s);
+  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  h->launches += dp.nlevels + 3;
+  CK(cudaGetLastError());
+  if (prof) {
+    CK(cudaEventSynchronize(h->ev_stage[ORBX_STAGE_COUNT]));
+    const int nl[ORBX_STAGE_COUNT] = {dp.nlevels - 1, 1, 1, 1, 1};
+    for (int i = 0; i < ORBX_STAGE_COUNT; i++) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, h->ev_stage[i], h->ev_stage[i + 1]);
+      h->prof_ms[i] += ms;
+      h->prof_launch[i] += nl[i];
+    }
+  }
+  h->last = b; h->last_frames = n;
+  return ORBX_OK;
+}
+
+static int check_args(orbx_handle* h, const void* img, int n, int w, int hgt, size_t stride, const void* kps,
+                      const void* desc, const void* n_out) {
+  if (!h) return ORBX_ERR_ARG;
+  if (!kps || !desc || !n_out || n < 0 || (img && (w < 0 || hgt < 0))) { h->err = "null output or negative size"; return ORBX_ERR_ARG; }
+  if (img && w > 0 && hgt > 0 && stride < (size_t)w) { h->err = "stride < width"; return ORBX_ERR_ARG; }
+  if (w > h->p.max_width || hgt > h->p.max_height) { h->err = "image larger than max_width x max_height"; return ORBX_ERR_ARG; }
+  return ORBX_OK;
+}
+
+extern "C" int orbx_synchronize(orbx_handle* h) {
+  if (!h) return ORBX_ERR_ARG;
+  CK(cudaSetDevice(h->p.device));
+  CK(cudaStreamSynchronize(h->s_in));
+  CK(cudaStreamSynchronize(h->s_compute));
+  CK(cudaStreamSynchronize(h->s_out));
+  int32_t flag = 0;
+  CK(cudaMemcpy(&flag, h->d_err, sizeof(flag), cudaMemcpyDeviceToHost));
+  if (flag) {
+    cudaMemset(h->d_err, 0, sizeof(flag));
+    h->err = flag == 1 ? "cell candidate list overflow" : "level list overflow";
+    return ORBX_ERR_OVERFLOW;
+  }
+  return ORBX_OK;
+}
+
+extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int nframes, int w, int hgt,
+                                         size_t stride, size_t frame_stride, orbx_keypoint* d_kps, uint8_t* d_desc,
+                                         int* d_n_out, void* stream) {
+  int rc = check_args(h, d_imgs, nframes, w, hgt, stride, d_kps, d_desc, d_n_out);
+  if (rc != ORBX_OK) return rc;
+  CK(cudaSetDevice(h->p.device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->s_compute;
+  if (!d_imgs || w == 0 || hgt == 0 || nframes == 0) {  // empty image: nothing extracted (:721-722)
+    if (nframes > 0) CK(cudaMemsetAsync(d_n_out, 0, sizeof(int) * nframes, s));
+    return ORBX_OK;
+  }
+  rc = upload_plan(h, w, hgt);
+  if (rc != ORBX_OK) return rc;
+  const int B = h->p.max_batch, nf = h->p.nfeatures;
+  for (int f0 = 0; f0 < nframes; f0 += B) {
+    const int n = std::min(B, nframes - f0);
+    rc = run_chunk(h, d_imgs + (size_t)f0 * frame_stride, n, stride, frame_stride, d_kps + (size_t)f0 * nf,
+                   d_desc + (size_t)f0 * nf * 32, d_n_out + f0, s);
+    if (rc != ORBX_OK) return rc;
+  }
+  return ORBX_OK;
+}
+
+// HOST buffers: chunk k's H2D (s_in), kernels (s_compute) and D2H (s_out) overlap with chunks k-1 / k+1 through two
+// staging slots.  Pinned caller memory makes the copies truly asynchronous; pageable memory still works.
+extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nframes, int w, int hgt, size_t stride,
+                                  size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int* n_out) {
+  int rc = check_args(h, imgs, nframes, w, hgt, stride, kps, desc, n_out);
+  if (rc != ORBX_OK) return rc;
+  if (!imgs || w == 0 || hgt == 0 || nframes == 0) {
+    for (int f = 0; f < nframes; f++) n_out[f] = 0;
+    return ORBX_OK;
+  }
+  CK(cudaSetDevice(h->p.device));
+  rc = upload_plan(h, w, hgt);
+  if (rc != ORBX_OK) return rc;
+  const int B = h->p.max_batch, nf = h->p.nfeatures;
+  const int pitch = (w + 15) / 16 * 16;
+  const size_t fbytes = (size_t)pitch * hgt;
+  int k = 0;
+  for (int f0 = 0; f0 < nframes; f0 += B, k++) {
+    const int n = std::min(B, nframes - f0), slot = k & 1;
+    if (k >= 2) CK(cudaStreamWaitEvent(h->s_in, h->ev_compute[slot], 0));  // slot's previous input consumed
+    const uint8_t* src = imgs + (size_t)f0 * frame_stride;
+    if (frame_stride == stride * (size_t)hgt) {
+      CK(cudaMemcpy2DAsync(h->d_in[slot], pitch, src, stride, w, (size_t)hgt * n, cudaMemcpyHostToDevice, h->s_in));
+    } else {
+      for (int f = 0; f < n; f++)
+        CK(cudaMemcpy2DAsync(h->d_in[slot] + f * fbytes, pitch, src + (size_t)f * frame_stride, stride, w, hgt,
+                             cudaMemcpyHostToDevice, h->s_in));
+    }
+    CK(cudaEventRecord(h->ev_in[slot], h->s_in));
+    CK(cudaStreamWaitEvent(h->s_compute, h->ev_in[slot], 0));
+    if (k >= 2) CK(cudaStreamWaitEvent(h->s_compute, h->ev_out[slot], 0));  // slot's previous output drained
+    rc = run_chunk(h, h->d_in[slot], n, pitch, fbytes, h->d_out_kps[slot], h->d_out_desc[slot], h->d_out_n[slot],
+                   h->s_compute);
+    if (rc != ORBX_OK) return rc;
+    CK(cudaEventRecord(h->ev_compute[slot], h->s_compute));
+    CK(cudaStreamWaitEvent(h->s_out, h->ev_compute[slot], 0));
+    CK(cudaMemcpyAsync(kps + (size_t)f0 * nf, h->d_out_kps[slot], sizeof(orbx_keypoint) * nf * n,
+                       cudaMemcpyDeviceToHost, h->s_out));
+    CK(cudaMemcpyAsync(desc + (size_t)f0 * nf * 32, h->d_out_desc[slot], (size_t)32 * nf * n, cudaMemcpyDeviceToHost,
+                       h->s_out));
+    CK(cudaMemcpyAsync(n_out + f0, h->d_out_n[slot], sizeof(int) * n, cudaMemcpyDeviceToHost, h->s_out));
+    CK(cudaEventRecord(h->ev_out[slot], h->s_out));
+  }
+  return orbx_synchronize(h);
+}
+
+extern "C" int orbx_extract(orbx_handle* h, const uint8_t* img, int w, int hgt, size_t stride, orbx_keypoint* kps,
+                            uint8_t* desc, int* n_out) {
+  return orbx_extract_batch(h, img, 1, w, hgt, stride, stride * (size_t)(hgt > 0 ? hgt : 0), kps, desc, n_out);
+}
+
+extern "C" int orbx_profile_enable(orbx_handle* h, int on) {
+  if (!h) return ORBX_ERR_ARG;
+  h->profiling = on != 0;
+  return ORBX_OK;
+}
+extern "C" int orbx_profile_read(orbx_handle* h, float ms[ORBX_STAGE_COUNT], int64_t launches[ORBX_STAGE_COUNT]) {
+  if (!h) return ORBX_ERR_ARG;
+  for (int i = 0; i < ORBX_STAGE_COUNT; i++) {
+    if (ms) ms[i] = h->prof_ms[i];
+    if (launches) launches[i] = h->prof_launch[i];
+    h->prof_ms[i] = 0; h->prof_launch[i] = 0;
+  }
+  return ORBX_OK;
+}
+
+#include "orbx_api_debug.inl"

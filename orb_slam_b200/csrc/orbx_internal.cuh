@@ -1,0 +1,85 @@
+// Internal structures shared by the extractor's host planner (orbx_plan.cu), kernels (orbx_kernels.cu) and
+// C-ABI layer (orbx_api.cu).  Not installed; the public surface is include/orbx.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/orbx.h"
+
+namespace orbx {
+
+constexpr int kMaxLevels = 16;
+constexpr int kEdge = 16;        // EDGE_THRESHOLD, reference src/ORBextractor.cc:77
+constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE :76
+constexpr int kPatch = 31;       // PATCH_SIZE :75
+constexpr int kRetryTh = 7;      // FAST retry threshold :613
+
+// One FAST candidate / keypoint record while it moves through cell + level selection (8 bytes, swapped as a unit
+// by the std::nth_element port).  xy = (y << 16) | x in level coordinates.
+struct __align__(8) Cand {
+  float resp;
+  uint32_t xy;
+};
+
+struct LevelPlan {
+  int w, h;              // level size: cvRound((float)cols * mvInvScaleFactor[l])            (:785-786)
+  int pitch;             // bytes between rows of this level inside the pyramid slabs (multiple of 16)
+  int64_t off;           // byte offset of the level inside one frame's pyramid slab (level 0 of the unblurred
+                         // pyramid lives in the caller's frame buffer instead)
+  int cols, rows;        // cell grid                                                          (:533-534)
+  int cellW, cellH;      //                                                                    (:543-544)
+  int nCells, quota;     // nCells = rows*cols, quota = nfeaturesCell                          (:546-547)
+  int nDesired;          // mnFeaturesPerLevel[l]                                              (:476-487)
+  int cell_base;         // index of the level's first cell in the per-frame cell arrays
+  int kp_base;           // first keypoint slot of the level = sum of nDesired of the levels below
+  int list_base, list_cap;  // per-frame level-list scratch (records) used between cell and level retention
+  float scale;           // mvScaleFactor[l]                                                   (:462-465)
+  float size;            // (float)(int)(PATCH_SIZE * mvScaleFactor[l])                        (:675)
+  int tab_x, tab_y;      // offsets of this level's resize tables (xofs/alpha, yofs/beta)
+};
+
+struct CellPlan {
+  int16_t level;
+  int16_t x0, y0;        // first scored pixel of the cell (= iniX + 3, iniY + 3) in level coordinates
+  int16_t rw, rh;        // scored region size; 0 when the reference skips the cell (hX <= 0 / hY <= 0 / < 7 px)
+  int16_t skipped;       // 1: the reference `continue`s over this cell (hX <= 0 or hY <= 0)
+  int32_t cand_off;      // offset of the cell's candidate list in the per-frame candidate array
+  int32_t cand_cap;      // ceil(rw/2)*ceil(rh/2): NMS survivors are pairwise non-adjacent, so this cannot overflow
+};
+
+struct ResizeX {  // per destination column: source column and the two 11-bit weights (cv::resize INTER_LINEAR)
+  int16_t sx, a0, a1, pad;
+};
+struct ResizeY {
+  int16_t sy0, sy1, b0, b1;
+};
+
+// Everything the kernels need to know about one (image size, knob set); lives in device global memory.
+struct DevicePlan {
+  int nlevels, nfeatures, fast_th, score_type, blur_mode, retain_mode;
+  int width, height;
+  int total_cells;           // cells per frame over all levels
+  int64_t pyr_frame_bytes;   // bytes of one frame's pyramid slab (levels 1.. for unblurred, 0.. for blurred)
+  int64_t blur_frame_bytes;
+  int64_t cand_per_frame;    // candidate records per frame
+  int list_per_frame;        // level-list scratch records per frame
+  int umax[16];              // :495-510
+  LevelPlan lv[kMaxLevels];
+};
+
+struct HostPlan {
+  DevicePlan dp;
+  std::vector<CellPlan> cells;
+  std::vector<ResizeX> rx;
+  std::vector<ResizeY> ry;
+  int max_cell_px;           // largest scored-region + halo area, for the FAST kernel's shared memory
+};
+
+// Builds the plan exactly as the reference's constructor and ComputeKeyPoints do (float/double mix preserved).
+// Returns ORBX_OK, ORBX_ERR_UNSUPPORTED (grid with 0 columns/rows, cell outside the level) or ORBX_ERR_ARG.
+int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::string* err);
+
+}  // namespace orbx

@@ -1,0 +1,42 @@
+// Kernel launch interface between orbx_api.cu and orbx_kernels.cu.
+#pragma once
+#include "orbx_internal.cuh"
+
+namespace orbx {
+
+// Device buffers of one chunk of frames (all sized at orbx_create for max_batch frames of max_w x max_h).
+struct ChunkBuffers {
+  const uint8_t* lv0;        // level 0 of the unblurred pyramid = the frames themselves
+  int64_t lv0_frame_stride;  // bytes between frames
+  int lv0_pitch;             // bytes between rows
+  uint8_t* pyr;              // unblurred levels >= 1, [frame][pyr_frame_bytes]
+  uint8_t* blur;             // blurred levels 0.., [frame][blur_frame_bytes]
+  Cand* cand;                // [frame][cand_per_frame]   per-cell FAST candidates, row-major inside a cell
+  int32_t* n_total;          // [frame][total_cells]      candidates per cell (after the th=7 retry rule)
+  int32_t* n_retain;         // [frame][total_cells]      quota after redistribution
+  Cand* list;                // [frame][list_per_frame]   level lists between cell and level retention
+  Cand* kp;                  // [frame][nfeatures]        selected keypoints, slot = kp_base[level] + i
+  int32_t* kp_count;         // [frame][kMaxLevels]
+  int32_t* err_flag;         // [1] sticky device-side overflow flag
+  const DevicePlan* plan;    // device copy
+  const CellPlan* cells;     // device copy [total_cells]
+  const ResizeX* rx;
+  const ResizeY* ry;
+};
+
+struct BlurTiles {            // tile ranges of the single all-level blur launch
+  int base[kMaxLevels + 1];   // prefix of tiles per level
+  int tiles_x[kMaxLevels];
+};
+
+void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
+void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int max_cell_px, int nframes, cudaStream_t s);
+void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s);
+void launch_blur(const ChunkBuffers& b, const DevicePlan& hp, const BlurTiles& t, int nframes, cudaStream_t s);
+void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, orbx_keypoint* d_kps, uint8_t* d_desc,
+                     int32_t* d_n_out, cudaStream_t s);
+void launch_synth(uint8_t* d_out, uint8_t* d_tmp, int nframes, int w, int h, size_t stride, size_t frame_stride,
+                  uint64_t seed0, cudaStream_t s);
+int fast_cells_smem_bytes(int max_cell_px);
+
+}  // namespace orbx

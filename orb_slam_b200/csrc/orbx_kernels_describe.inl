@@ -1,0 +1,149 @@
+// Included by orbx_kernels.cu.  E7 IC_Angle, E9 rotated BRIEF, E10 output assembly: one warp per keypoint slot.
+namespace orbx {
+
+__constant__ int8_t c_pattern[1024] = {
+#include "orb_pattern_31.inc"
+};
+
+// cv::fastAtan2(y, x): float32 polynomial, every operation individually rounded (reference :150)
+__device__ __forceinline__ float fast_atan2_dev(float y, float x) {
+  const float s = (float)(180.0 / 3.14159265358979323846);
+  const float p1 = 0.9997878412794807f * s, p3 = -0.3258083974640975f * s, p5 = 0.1555786518463281f * s,
+              p7 = -0.04432655554792128f * s;  // folded at compile time in float, like the host's statics
+  const float eps = (float)DBL_EPSILON;
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a, c, c2;
+  if (ax >= ay) {
+    c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3),
+                                                      c2), p1), c));
+  }
+  if (x < 0) a = __fsub_rn(180.f, a);
+  if (y < 0) a = __fsub_rn(360.f, a);
+  return a;
+}
+
+// glibc >= 2.28 sinf/cosf (ARM optimized-routines sincosf: double polynomial, rounded once to float), the functions
+// `(float)cos(angle)`, `(float)sin(angle)` resolve to at reference :159-160.  Verified over EVERY float in
+// [0, 2*pi*1.0001] against the host libm (tools/check_sincosf.c; tests/test_gpu_extract.py re-checks on the device).
+__device__ __forceinline__ void sincosf_glibc(float y, float* sn, float* cs) {
+  const double hpi_inv = 0x1.45F306DC9C883p+23, hpi = 0x1.921FB54442D18p0;
+  const double C0 = 0x1p0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10,
+               C4 = 0x1.99343027bf8c3p-16;
+  const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+  double x = (double)y;
+  const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ff;
+  int n = 0;
+  double sgn = 1.0, neg = 1.0;
+  if (top < ((__float_as_uint(0x1.921FB6p-1f) >> 20) & 0x7ff)) {
+    if (top < ((__float_as_uint(0x1p-12f) >> 20) & 0x7ff)) { *sn = y; *cs = 1.0f; return; }
+  } else {
+    const double r = x * hpi_inv;
+    n = ((int32_t)r + 0x800000) >> 24;
+    x = fma(-(double)n, hpi, x);
+    sgn = ((n + 1) & 2) ? -1.0 : 1.0;  // sign table {1,-1,-1,1}[n & 3]
+    neg = (n & 2) ? -1.0 : 1.0;        // second coefficient table = first with the cosine coefficients negated
+  }
+  const double xs = x * sgn, x2 = x * x;
+  // sine polynomial
+  double x3 = xs * x2, s1 = fma(x2, S3, S2), x7 = x3 * x2, s = fma(x3, S1, xs);
+  const float fs = (float)fma(x7, s1, s);
+  // cosine polynomial
+  double x4 = x2 * x2, c2 = fma(x2, neg * C4, neg * C3), c1 = fma(x2, neg * C1, neg * C0), x6 = x4 * x2,
+         c = fma(x4, neg * C2, c1);
+  const float fc = (float)fma(x6, c2, c);
+  if ((n & 1) == 0) { *sn = fs; *cs = fc; }
+  else { *sn = fc; *cs = fs; }
+}
+
+__global__ void __launch_bounds__(256) describe_kernel(ChunkBuffers b, orbx_keypoint* out_kps, uint8_t* out_desc,
+                                                       int32_t* out_n, int nslots_total) {
+  const DevicePlan* P = b.plan;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (gw >= nslots_total) return;
+  const int frame = gw / P->nfeatures, slot = gw - frame * P->nfeatures;
+  const int32_t* cnt = b.kp_count + frame * kMaxLevels;
+  int level = 0, out_off = 0;
+  while (level + 1 < P->nlevels && slot >= P->lv[level + 1].kp_base) { out_off += cnt[level]; level++; }
+  const LevelPlan& L = P->lv[level];
+  const int idx = slot - L.kp_base;
+  if (slot == 0 && lane == 0) {
+    int tot = 0;
+    for (int l = 0; l < P->nlevels; l++) tot += cnt[l];
+    out_n[frame] = tot;
+  }
+  if (idx >= cnt[level]) return;
+  const Cand kp = b.kp[(int64_t)frame * P->nfeatures + slot];
+  const int cx = kp.xy & 0xffff, cy = kp.xy >> 16;
+  int pitch;
+  const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
+
+  // ---- E7 IC_Angle (:124-151): m10 = sum u*I, m01 = sum v*I over the 749-px disc, UNBLURRED level; lane = row
+  int m10 = 0, m01 = 0;
+  if (lane < 31) {
+    const int v = lane - kHalfPatch;
+    const int d = P->umax[v < 0 ? -v : v];
+    const uint8_t* row = img + (int64_t)(cy + v) * pitch + cx;
+    int rs = 0;
+    for (int u = -d; u <= d; u++) { const int I = row[u]; m10 += u * I; rs += I; }
+    m01 = v * rs;
+  }
+  m10 = __reduce_add_sync(0xffffffffu, m10);
+  m01 = __reduce_add_sync(0xffffffffu, m01);
+  const float angle = fast_atan2_dev((float)m01, (float)m10);
+
+  // ---- E9 computeOrbDescriptor (:155-194): lane = descriptor byte, 8 comparisons of rotated pattern samples.
+  // In-image samples read the blurred level; the <= 2 px that fall outside read the UNBLURRED reflect-101 border,
+  // which the reference's in-place ROI blur leaves untouched (:759-760).
+  const float factorPI = (float)(3.14159265358979323846 / 180.f);
+  float sa, ca;
+  sincosf_glibc(__fmul_rn(angle, factorPI), &sa, &ca);
+  const uint8_t* blur = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
+  int val = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    int t[2];
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+      const float px = (float)c_pattern[lane * 32 + j * 4 + e * 2], py = (float)c_pattern[lane * 32 + j * 4 + e * 2 + 1];
+      const int ry = __float2int_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)));
+      const int rx = __float2int_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)));
+      const int x = cx + rx, y = cy + ry;
+      if (x >= 0 && x < L.w && y >= 0 && y < L.h) t[e] = blur[(int64_t)y * L.pitch + x];
+      else t[e] = img[(int64_t)reflect101(y, L.h) * pitch + reflect101(x, L.w)];
+    }
+    val |= (t[0] < t[1]) << j;
+  }
+  const int o = out_off + idx;
+  out_desc[((int64_t)frame * P->nfeatures + o) * 32 + lane] = (uint8_t)val;
+
+  // ---- E10 keypoint record (:687-694, :769-775)
+  if (lane < 7) {
+    float fx = (float)cx, fy = (float)cy;
+    if (level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+    uint32_t w;
+    switch (lane) {
+      case 0: w = __float_as_uint(fx); break;
+      case 1: w = __float_as_uint(fy); break;
+      case 2: w = __float_as_uint(L.size); break;
+      case 3: w = __float_as_uint(angle); break;
+      case 4: w = __float_as_uint(kp.resp); break;
+      case 5: w = (uint32_t)level; break;
+      default: w = 0xffffffffu; break;
+    }
+    reinterpret_cast<uint32_t*>(out_kps + (int64_t)frame * P->nfeatures + o)[lane] = w;
+  }
+}
+
+void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, orbx_keypoint* d_kps, uint8_t* d_desc,
+                     int32_t* d_n_out, cudaStream_t s) {
+  const int nslots = hp.nfeatures * nframes;
+  describe_kernel<<<(nslots + 7) / 8, 256, 0, s>>>(b, d_kps, d_desc, d_n_out, nslots);
+}
+
+}  // namespace orbx

@@ -1,0 +1,208 @@
+// Included by orbx_kernels_detect.inl.  E5 quota redistribution and E6 KeyPointsFilter::retainBest.
+namespace orbx {
+
+// ------------------------------------------------------------------------------------------------------------------
+// Functional port of libstdc++ 13 std::nth_element (bits/stl_algo.h __introselect / __unguarded_partition_pivot /
+// __move_median_to_first / __heap_select / __insertion_sort, bits/stl_heap.h __make_heap / __pop_heap /
+// __adjust_heap / __push_heap) on 8-byte Cand records with the comparator of OpenCV's KeypointResponseGreater
+// (a.response > b.response).  The reference truncates retainBest's result to n entries IN THE ORDER nth_element
+// left them (:683-685, :697-701), so the element order — not just the set — is part of the output.
+// tests/test_select.py checks this port against the real std::nth_element on random and tie-heavy lists.
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool cgt(const Cand& a, const Cand& b) { return a.resp > b.resp; }
+__device__ __forceinline__ void cswap(Cand* v, int i, int j) { Cand t = v[i]; v[i] = v[j]; v[j] = t; }
+
+__device__ void nth_push_heap(Cand* first, int hole, int top, Cand value) {
+  int parent = (hole - 1) / 2;
+  while (hole > top && cgt(first[parent], value)) {
+    first[hole] = first[parent];
+    hole = parent;
+    parent = (hole - 1) / 2;
+  }
+  first[hole] = value;
+}
+
+__device__ void nth_adjust_heap(Cand* first, int hole, int len, Cand value) {
+  const int top = hole;
+  int child = hole;
+  while (child < (len - 1) / 2) {
+    child = 2 * (child + 1);
+    if (cgt(first[child], first[child - 1])) child--;
+    first[hole] = first[child];
+    hole = child;
+  }
+  if ((len & 1) == 0 && child == (len - 2) / 2) {
+    child = 2 * (child + 1);
+    first[hole] = first[child - 1];
+    hole = child - 1;
+  }
+  nth_push_heap(first, hole, top, value);
+}
+
+__device__ void nth_heap_select(Cand* first, int middle, int last) {  // [0,middle) heap, scan [middle,last)
+  const int len = middle;
+  if (len >= 2) {  // __make_heap
+    int parent = (len - 2) / 2;
+    while (true) {
+      Cand value = first[parent];
+      nth_adjust_heap(first, parent, len, value);
+      if (parent == 0) break;
+      parent--;
+    }
+  }
+  for (int i = middle; i < last; ++i)
+    if (cgt(first[i], first[0])) {  // __pop_heap(first, middle, i)
+      Cand value = first[i];
+      first[i] = first[0];
+      nth_adjust_heap(first, 0, len, value);
+    }
+}
+
+__device__ void nth_element_port(Cand* v, int nth, int n) {
+  if (n == 0 || nth == n) return;
+  int first = 0, last = n;
+  int depth = 2 * (31 - __clz(n));  // std::__lg(n) * 2
+  while (last - first > 3) {
+    if (depth == 0) {
+      nth_heap_select(v + first, nth + 1 - first, last - first);
+      cswap(v, first, nth);
+      return;
+    }
+    --depth;
+    // __unguarded_partition_pivot
+    const int mid = first + (last - first) / 2;
+    {  // __move_median_to_first(first, first+1, mid, last-1)
+      const int a = first + 1, b = mid, c = last - 1;
+      if (cgt(v[a], v[b])) {
+        if (cgt(v[b], v[c])) cswap(v, first, b);
+        else if (cgt(v[a], v[c])) cswap(v, first, c);
+        else cswap(v, first, a);
+      } else if (cgt(v[a], v[c])) cswap(v, first, a);
+      else if (cgt(v[b], v[c])) cswap(v, first, c);
+      else cswap(v, first, b);
+    }
+    int lo = first + 1, hi = last;
+    const float pivot = v[first].resp;  // the pivot element itself never moves during the partition
+    while (true) {
+      while (v[lo].resp > pivot) ++lo;
+      --hi;
+      while (pivot > v[hi].resp) --hi;
+      if (!(lo < hi)) break;
+      cswap(v, lo, hi);
+      ++lo;
+    }
+    const int cut = lo;
+    if (cut <= nth) first = cut;
+    else last = cut;
+  }
+  // __insertion_sort(first, last)
+  for (int i = first + 1; i < last; ++i) {
+    Cand val = v[i];
+    if (cgt(val, v[first])) {
+      for (int k = i; k > first; --k) v[k] = v[k - 1];
+      v[first] = val;
+    } else {
+      int k = i;
+      while (cgt(val, v[k - 1])) { v[k] = v[k - 1]; --k; }
+      v[k] = val;
+    }
+  }
+}
+
+// retainBest(keys, n) followed by resize(n): the first min(n, size) entries survive            (:683-685)
+__device__ __forceinline__ void retain_best_port(Cand* v, int size, int n, int retain_mode) {
+  if (n > 0 && size > n) nth_element_port(v, retain_mode == ORBX_RETAIN_CV24 ? n : n - 1, size);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// One warp per (level, frame):
+//   lane 0   quota per cell + redistribution loop                                  (reference :622-636, :644-670)
+//   lanes    per-cell retainBest in place in the cell's candidate list             (:678-685)
+//   lanes    copy the survivors, cells in row-major order, into the level list     (:687-694)
+//   lane 0   level cap retainBest(keypoints, nDesired) + resize                     (:697-701)
+//   lanes    publish the level's keypoints into the frame's slots [kp_base, kp_base + count)
+// Serial sections are a few hundred steps; thousands of (level, frame) warps run concurrently.
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_total) {
+  const DevicePlan* P = b.plan;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (gw >= nwarps_total) return;
+  const int level = gw % P->nlevels, frame = gw / P->nlevels;
+  const LevelPlan& L = P->lv[level];
+  const int nCells = L.nCells, q = L.quota;
+  const int32_t* nTotal = b.n_total + (int64_t)frame * P->total_cells + L.cell_base;
+  int32_t* nToRetain = b.n_retain + (int64_t)frame * P->total_cells + L.cell_base;
+  Cand* cand = b.cand + (int64_t)frame * P->cand_per_frame;
+  Cand* list = b.list + (int64_t)frame * P->list_per_frame + L.list_base;
+
+  if (lane == 0) {
+    // bNoMore is kept in the sign bit of nToRetain while the loop runs (-(v)-1 encodes "no more")
+    int nNoMore = 0, nToDistribute = 0;
+    for (int c = 0; c < nCells; c++) {
+      const CellPlan& cp = b.cells[L.cell_base + c];
+      const int nKeys = nTotal[c];
+      // a cell the reference `continue`s over (:571, :595) keeps nToRetain = 0 / bNoMore = false and is NOT
+      // counted in nNoMore; it still takes part in the redistribution below with nTotal = 0
+      if (cp.skipped) { nToRetain[c] = 0; continue; }
+      if (nKeys > q) nToRetain[c] = q;
+      else { nToRetain[c] = -nKeys - 1; nToDistribute += q - nKeys; nNoMore++; }
+    }
+    while (nToDistribute > 0 && nNoMore < nCells) {
+      const int nNew = q + (int)ceilf(__fdiv_rn((float)nToDistribute, (float)(nCells - nNoMore)));
+      nToDistribute = 0;
+      for (int c = 0; c < nCells; c++) {
+        if (nToRetain[c] >= 0) {
+          if (nTotal[c] > nNew) nToRetain[c] = nNew;
+          else { nToRetain[c] = -nTotal[c] - 1; nToDistribute += nNew - nTotal[c]; nNoMore++; }
+        }
+      }
+    }
+    for (int c = 0; c < nCells; c++)
+      if (nToRetain[c] < 0) nToRetain[c] = -nToRetain[c] - 1;
+  }
+  __syncwarp();
+  for (int c = lane; c < nCells; c += 32) {
+    const CellPlan& cp = b.cells[L.cell_base + c];
+    retain_best_port(cand + cp.cand_off, nTotal[c], nToRetain[c], P->retain_mode);
+  }
+  __syncwarp();
+  // exclusive prefix of nToRetain over the cells (warp scan in chunks of 32)
+  int run = 0;
+  for (int c0 = 0; c0 < nCells; c0 += 32) {
+    const int c = c0 + lane;
+    const int n = c < nCells ? min(nToRetain[c], nTotal[c]) : 0;
+    int incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    const int off = run + incl - n;
+    if (c < nCells && off + n <= L.list_cap) {
+      const Cand* src = cand + b.cells[L.cell_base + c].cand_off;
+      for (int k = 0; k < n; k++) list[off + k] = src[k];
+    }
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (run > L.list_cap) {
+    if (lane == 0) { atomicExch(b.err_flag, 2); b.kp_count[frame * kMaxLevels + level] = 0; }
+    return;
+  }
+  __syncwarp();
+  int count = run;
+  if (run > L.nDesired) {
+    if (lane == 0) retain_best_port(list, run, L.nDesired, P->retain_mode);
+    count = L.nDesired;
+  }
+  __syncwarp();
+  Cand* kp = b.kp + (int64_t)frame * P->nfeatures + L.kp_base;
+  for (int k = lane; k < count; k += 32) kp[k] = list[k];
+  if (lane == 0) b.kp_count[frame * kMaxLevels + level] = count;
+}
+
+void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s) {
+  const int nwarps = hp.nlevels * nframes;
+  select_kernel<<<(nwarps * 32 + 127) / 128, 128, 0, s>>>(b, nwarps);
+}
+
+}  // namespace orbx

@@ -1,0 +1,161 @@
+"""Parity of the CUDA extractor (through the C ABI, include/orbx.h) with the CPU oracle, stage by stage and end to
+end.  Bit-exact everywhere: coordinates, octaves, responses, angles (raw bits), sizes, descriptors."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _ex(**kw):
+    from orb_slam_b200 import ORBextractor
+    return ORBextractor(**kw)
+
+
+def _cmp_final(k, d, ok, od):
+    assert len(k) == len(ok)
+    for f in ("octave", "x", "y", "response", "size", "class_id"):
+        assert np.array_equal(k[f], ok[f]), f
+    assert np.array_equal(k["angle"].view(np.uint32), ok["angle"].view(np.uint32))  # raw bits (contract: 1e-3 deg)
+    assert np.array_equal(d, od)
+
+
+CONFIGS = [
+    dict(w=640, h=480, nf=1000, nl=8, th=20, seed=0),     # BASELINE config 1
+    dict(w=1241, h=376, nf=2000, nl=8, th=20, seed=3),    # BASELINE config 3 (wide-image grid)
+    dict(w=640, h=480, nf=2000, nl=8, th=20, seed=1),     # the initialisation extractor (src/Tracking.cc:128)
+    dict(w=320, h=240, nf=500, nl=6, th=12, seed=2),
+    dict(w=333, h=251, nf=700, nl=5, th=5, seed=4),       # odd sizes, fastTh below the retry threshold
+]
+
+
+@pytest.mark.parametrize("cfg", CONFIGS)
+def test_stagewise_parity(oracle, cfg):
+    img = oracle.synth(cfg["h"], cfg["w"], cfg["seed"])
+    O = oracle.OracleExtractor(cfg["nf"], 1.2, cfg["nl"], 1, cfg["th"])
+    ok, od = O(img)
+    ex = _ex(nfeatures=cfg["nf"], scaleFactor=1.2, nlevels=cfg["nl"], scoreType=1, fastTh=cfg["th"],
+             max_width=cfg["w"], max_height=cfg["h"], max_batch=2)
+    k, d = ex(img)
+    for l in range(cfg["nl"]):
+        info = ex.debug_level_info(l)
+        g = O.level_grid(l)
+        assert (info["w"], info["h"]) == O.level_size(l)
+        assert (info["cols"], info["rows"], info["cellW"], info["cellH"], info["quota"]) == (
+            g["cols"], g["rows"], g["cellW"], g["cellH"], g["quota"])
+        assert np.array_equal(ex.debug_level_image(0, l, 0), O.level_image(l, 0)), f"pyramid level {l}"
+        if g["nkept"]:
+            assert np.array_equal(ex.debug_level_image(0, l, 1), O.level_image(l, 1)), f"blur level {l}"
+        nt, nr = ex.debug_level_cells(0, l)
+        ont, onr = O.level_cells(l)
+        assert np.array_equal(nt, ont), f"nTotal level {l}"
+        assert np.array_equal(nr, onr), f"nToRetain level {l}"
+    _cmp_final(k, d, ok, od)
+
+
+def test_cell_candidates_are_row_major(oracle):
+    """With a quota no cell can reach, the select kernel leaves the per-cell lists untouched: they must equal
+    cv::FAST's row-major output per cell (the order std::nth_element later depends on)."""
+    img = oracle.synth(240, 320, 9)
+    O = oracle.OracleExtractor(20000, 1.2, 2, 1, 20)
+    O(img)
+    ex = _ex(nfeatures=20000, scaleFactor=1.2, nlevels=2, scoreType=1, fastTh=20, max_width=320, max_height=240,
+             max_batch=1)
+    ex(img)
+    ncheck = 0
+    for l in range(2):
+        g = O.level_grid(l)
+        for c in range(g["cols"] * g["rows"]):
+            ox, oy, orr = O.cell_keys(l, c)
+            x, y, r = ex.debug_cell_candidates(0, l, c)
+            j, i = c % g["cols"], c // g["cols"]
+            ix, iy = 16 + j * g["cellW"] - 3, 16 + i * g["cellH"] - 3
+            assert np.array_equal(x - ix, ox) and np.array_equal(y - iy, oy) and np.array_equal(r, orr)
+            ncheck += len(x)
+    assert ncheck > 200
+
+
+@pytest.mark.parametrize("blur_mode,retain_mode,score", [(1, 0, 1), (0, 1, 1), (1, 1, 1), (0, 0, 0), (1, 1, 0)])
+def test_modes(oracle, blur_mode, retain_mode, score):
+    img = oracle.synth(480, 640, 21)
+    ok, od = oracle.OracleExtractor(1000, 1.2, 8, score, 20, blur_mode, retain_mode)(img)
+    k, d = _ex(nfeatures=1000, scoreType=score, blur_mode=blur_mode, retain_mode=retain_mode, max_batch=1)(img)
+    _cmp_final(k, d, ok, od)
+
+
+def test_texture_extremes(oracle):
+    """Noise (thousands of corners per cell -> deep nth_element recursion), flat (zero keypoints, th=7 retry
+    everywhere) and half/half images."""
+    rng = np.random.default_rng(5)
+    noise = rng.integers(0, 256, (480, 640), dtype=np.uint8)
+    flat = np.full((480, 640), 77, np.uint8)
+    half = flat.copy(); half[:, 320:] = noise[:, 320:]
+    ex = _ex(max_batch=1)
+    O = oracle.OracleExtractor()
+    for img in (noise, flat, half):
+        ok, od = O(img)
+        k, d = ex(img)
+        _cmp_final(k, d, ok, od)
+    assert len(ex(flat)[0]) == 0
+
+
+def test_batch_and_strides(oracle):
+    """Batch path (chunking across max_batch, pipelined copies) == per-frame oracle; strided input rows."""
+    F, H, W = 7, 240, 320
+    frames = np.stack([oracle.synth(H, W, 100 + s) for s in range(F)])
+    ex = _ex(nfeatures=500, nlevels=6, max_width=W, max_height=H, max_batch=3)
+    O = oracle.OracleExtractor(500, 1.2, 6, 1, 20)
+    kps, desc, n = ex.extract_batch(frames)
+    for f in range(F):
+        ok, od = O(frames[f])
+        _cmp_final(kps[f, :n[f]], desc[f, :n[f]], ok, od)
+    padded = np.zeros((H, W + 37), np.uint8)
+    padded[:, :W] = frames[2]
+    k, d = ex(padded[:, :W])
+    ok, od = O(frames[2])
+    _cmp_final(k, d, ok, od)
+
+
+def test_empty_and_errors():
+    from orb_slam_b200 import ORBextractor, OrbxError
+    ex = ORBextractor(max_batch=1)
+    k, d = ex(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    with pytest.raises(OrbxError):
+        ex(np.zeros((481, 640), np.uint8))          # larger than max_height
+    with pytest.raises(OrbxError):
+        ORBextractor(nfeatures=50, max_batch=1)     # zero-column grid: the reference divides by zero
+    assert ex.GetLevels() == 8 and abs(ex.GetScaleFactor() - 1.2) < 1e-6
+
+
+def test_synth_twin(oracle):
+    import torch
+    from orb_slam_b200 import synth_frames_device
+    F, H, W = 3, 120, 200
+    buf = torch.empty((F, H, W), dtype=torch.uint8, device="cuda")
+    synth_frames_device(buf.data_ptr(), F, W, H, W, H * W, seed0=40)
+    got = buf.cpu().numpy()
+    for f in range(F):
+        assert np.array_equal(got[f], oracle.synth(H, W, 40 + f))
+
+
+def test_device_path_matches_host_path(oracle):
+    import torch
+    from orb_slam_b200 import KP_DTYPE
+    F, H, W = 5, 240, 320
+    frames = np.stack([oracle.synth(H, W, 300 + s) for s in range(F)])
+    ex = _ex(nfeatures=500, nlevels=6, max_width=W, max_height=H, max_batch=2)
+    kps, desc, n = ex.extract_batch(frames)
+    d_img = torch.from_numpy(frames).cuda()
+    d_k = torch.zeros((F, 500, 28), dtype=torch.uint8, device="cuda")
+    d_d = torch.zeros((F, 500, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(F, dtype=torch.int32, device="cuda")
+    ex.extract_batch_device(d_img.data_ptr(), F, W, H, W, H * W, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(),
+                            torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ex.synchronize()
+    n2 = d_n.cpu().numpy()
+    assert np.array_equal(n2, n)
+    k2 = d_k.cpu().numpy().view(KP_DTYPE).reshape(F, 500)
+    for f in range(F):
+        assert np.array_equal(k2[f, :n[f]], kps[f, :n[f]])
+        assert np.array_equal(d_d[f, :n[f]].cpu().numpy(), desc[f, :n[f]])
