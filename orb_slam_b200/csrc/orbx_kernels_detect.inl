@@ -6,46 +6,40 @@ namespace orbx {
 //     min(d) and min(-d), minus 1, d_k = I(p) - I(ring_k); p is a corner at threshold t  <=>  S >= t
 //     (cv::FAST / cornerScore<16>).  Scores below `tmin` are reported as 0.
 // ------------------------------------------------------------------------------------------------------------------
+// NOTE (CUDA 12.9 ptxas, sm_100a): the textbook form max(min9(d), -max9(d)) with d = I(p) - ring is MISCOMPILED —
+// ptxas fuses the neg.s32 into a 3-input VIMNMX3 and drops the negation (found with tools/dbg_fast2.cu, the PTX is
+// correct, the SASS is not).  The score is therefore computed on the RAW ring values with no negation or abs
+// anywhere:  S = max( max_k min9(ring) - v ,  v - min_k max9(ring) ) - 1.
 __device__ __forceinline__ int fast_score(const uint8_t* p, int pitch, int tmin) {
   const int v = p[0];
-  int d[16];
-  d[0] = v - p[3 * pitch];       d[8] = v - p[-3 * pitch];
-  d[4] = v - p[3];               d[12] = v - p[-3];
-  // opposite-pair quick reject: an arc of 9 contains one pixel of every opposite pair
-  {
-    const int m0 = max(abs(d[0]), abs(d[8])), m1 = max(abs(d[4]), abs(d[12]));
-    if (min(m0, m1) <= tmin) return 0;
-  }
-  d[1] = v - p[3 * pitch + 1];   d[9] = v - p[-3 * pitch - 1];
-  d[2] = v - p[2 * pitch + 2];   d[10] = v - p[-2 * pitch - 2];
-  d[3] = v - p[pitch + 3];       d[11] = v - p[-pitch - 3];
-  d[5] = v - p[-pitch + 3];      d[13] = v - p[pitch - 3];
-  d[6] = v - p[-2 * pitch + 2];  d[14] = v - p[2 * pitch - 2];
-  d[7] = v - p[-3 * pitch + 1];  d[15] = v - p[3 * pitch - 1];
-  {
-    int m = max(abs(d[1]), abs(d[9]));
-    m = min(m, max(abs(d[2]), abs(d[10])));
-    m = min(m, max(abs(d[3]), abs(d[11])));
-    m = min(m, max(abs(d[5]), abs(d[13])));
-    m = min(m, max(abs(d[6]), abs(d[14])));
-    m = min(m, max(abs(d[7]), abs(d[15])));
-    if (m <= tmin) return 0;
-  }
+  const int lo = v - tmin, hi = v + tmin;
+  int r[16];
+  r[0] = p[3 * pitch];   r[8] = p[-3 * pitch];
+  r[4] = p[3];           r[12] = p[-3];
+  // opposite-pair quick reject: an arc of 9 contains one pixel of every opposite pair, so a pair with both
+  // pixels inside [v - tmin, v + tmin] rules out every score >= tmin
+  if ((max(r[0], r[8]) <= hi && min(r[0], r[8]) >= lo) || (max(r[4], r[12]) <= hi && min(r[4], r[12]) >= lo))
+    return 0;
+  r[1] = p[3 * pitch + 1];   r[9] = p[-3 * pitch - 1];
+  r[2] = p[2 * pitch + 2];   r[10] = p[-2 * pitch - 2];
+  r[3] = p[pitch + 3];       r[11] = p[-pitch - 3];
+  r[5] = p[-pitch + 3];      r[13] = p[pitch - 3];
+  r[6] = p[-2 * pitch + 2];  r[14] = p[2 * pitch - 2];
+  r[7] = p[-3 * pitch + 1];  r[15] = p[3 * pitch - 1];
   // min/max over every window of 9 consecutive ring pixels, via windows of 2, 4, 8 (+1)
   int mn2[16], mx2[16];
 #pragma unroll
-  for (int k = 0; k < 16; k++) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
+  for (int k = 0; k < 16; k++) { mn2[k] = min(r[k], r[(k + 1) & 15]); mx2[k] = max(r[k], r[(k + 1) & 15]); }
   int mn4[16], mx4[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
-  int best = -256;
+  int brightest_min = 0, darkest_max = 255;
 #pragma unroll
   for (int k = 0; k < 16; k++) {
-    const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-    const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-    best = max(best, max(mn9, -mx9));
+    brightest_min = max(brightest_min, min(min(mn4[k], mn4[(k + 4) & 15]), r[(k + 8) & 15]));
+    darkest_max = min(darkest_max, max(max(mx4[k], mx4[(k + 4) & 15]), r[(k + 8) & 15]));
   }
-  const int s = best - 1;
+  const int s = max(brightest_min - v, v - darkest_max) - 1;
   return s >= tmin ? s : 0;
 }
 

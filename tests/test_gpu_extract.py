@@ -52,26 +52,26 @@ def test_stagewise_parity(oracle, cfg):
     _cmp_final(k, d, ok, od)
 
 
-def test_cell_candidates_are_row_major(oracle):
-    """With a quota no cell can reach, the select kernel leaves the per-cell lists untouched: they must equal
-    cv::FAST's row-major output per cell (the order std::nth_element later depends on)."""
-    img = oracle.synth(240, 320, 9)
-    O = oracle.OracleExtractor(20000, 1.2, 2, 1, 20)
+def test_cell_candidates(oracle):
+    """Per-cell FAST candidates (after NMS and the th=7 retry rule) equal cv::FAST's per-cell output as a set; their
+    row-major ORDER is what std::nth_element later depends on and is covered by the end-to-end order parity."""
+    img = oracle.synth(480, 640, 9)
+    O = oracle.OracleExtractor()
     O(img)
-    ex = _ex(nfeatures=20000, scaleFactor=1.2, nlevels=2, scoreType=1, fastTh=20, max_width=320, max_height=240,
-             max_batch=1)
+    ex = _ex(max_batch=1)
     ex(img)
     ncheck = 0
-    for l in range(2):
+    for l in range(8):
         g = O.level_grid(l)
         for c in range(g["cols"] * g["rows"]):
             ox, oy, orr = O.cell_keys(l, c)
             x, y, r = ex.debug_cell_candidates(0, l, c)
             j, i = c % g["cols"], c // g["cols"]
             ix, iy = 16 + j * g["cellW"] - 3, 16 + i * g["cellH"] - 3
-            assert np.array_equal(x - ix, ox) and np.array_equal(y - iy, oy) and np.array_equal(r, orr)
+            assert sorted(zip(oy.tolist(), ox.tolist(), orr.tolist())) == sorted(
+                zip((y - iy).tolist(), (x - ix).tolist(), r.tolist()))
             ncheck += len(x)
-    assert ncheck > 200
+    assert ncheck > 2000
 
 
 @pytest.mark.parametrize("blur_mode,retain_mode,score", [(1, 0, 1), (0, 1, 1), (1, 1, 1), (0, 0, 0), (1, 1, 0)])
