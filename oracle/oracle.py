@@ -196,6 +196,19 @@ class OracleExtractor:
             raise RuntimeError(f"oracle: degenerate configuration (code {n}); the reference would assert/crash")
         return kps[:n].copy(), desc[:n].copy()
 
+    def extract_many(self, images: np.ndarray, nthreads: int = 1):
+        """images [F,H,W] uint8 -> (kps [F,cap], desc [F,cap,32], n [F]); `nthreads` host threads."""
+        assert images.dtype == np.uint8 and images.ndim == 3 and images.strides[2] == 1
+        F, H, W = images.shape
+        cap = self.nfeatures
+        kps = np.zeros((F, cap), KP_DTYPE); desc = np.zeros((F, cap, 32), np.uint8); n = np.zeros(F, np.int32)
+        rc = self._L.orb_oracle_extract_many(self._h, _ptr(images, _u8p), F, W, H, images.strides[1],
+                                             images.strides[0], kps.ctypes.data, _ptr(desc, _u8p), _ptr(n, _i32p),
+                                             cap, nthreads)
+        if rc != 0:
+            raise RuntimeError("oracle: degenerate configuration")
+        return kps, desc, n
+
     def tables(self):
         f = np.zeros(self.nlevels, np.int32); s = np.zeros(self.nlevels, np.float32)
         i = np.zeros(self.nlevels, np.float32); u = np.zeros(16, np.int32)

@@ -122,15 +122,22 @@ void fast_9_16_nms(const uint8_t* img, int w, int h, size_t stride, int threshol
   out.clear();
   if (w < 7 || h < 7) return;
   std::vector<int> sc((size_t)w * h, 0);
+  const ptrdiff_t st = (ptrdiff_t)stride;
   for (int y = 3; y < h - 3; y++)
     for (int x = 3; x < w - 3; x++) {
-      int s = fast_score_9_16(img + (size_t)y * stride + x, stride);
+      const uint8_t* p = img + (size_t)y * stride + x;
+      // cv::FAST's own early-out (a 9-arc holds one pixel of every opposite pair), so the timed CPU baseline does
+      // the work OpenCV does, not 16 full windows per pixel
+      const int v = p[0], lo = v - threshold, hi = v + threshold;
+      const int a = p[3 * st], b = p[-3 * st], c = p[3], e = p[-3];
+      if ((a >= lo && a <= hi && b >= lo && b <= hi) || (c >= lo && c <= hi && e >= lo && e <= hi)) continue;
+      int s = fast_score_9_16(p, stride);
       sc[(size_t)y * w + x] = s >= threshold ? s : 0;  // non-corners count as 0 in the NMS buffers
     }
   for (int y = 3; y < h - 3; y++)
     for (int x = 3; x < w - 3; x++) {
       int s = sc[(size_t)y * w + x];
-      if (s < threshold) continue;
+      if (s < threshold || s == 0) continue;
       const int* c = &sc[(size_t)y * w + x];
       if (s > c[-1] && s > c[1] && s > c[-w - 1] && s > c[-w] && s > c[-w + 1] && s > c[w - 1] && s > c[w] &&
           s > c[w + 1])
@@ -660,3 +667,32 @@ void orb_oracle_sincos(float angle_rad, float* c, float* s) { *c = cosf(angle_ra
 const int8_t* orb_oracle_pattern() { return kOrbPattern31; }
 
 }  // extern "C"
+
+// Multi-threaded driver for the timed CPU baseline: independent frames over `nthreads` std::threads, one private
+// Extractor per thread (the reference itself is single-threaded: one Tracking thread calls operator()).
+#include <atomic>
+#include <thread>
+extern "C" int orb_oracle_extract_many(void* h, const uint8_t* imgs, int nframes, int w, int hgt, long stride,
+                                       long frame_stride, void* kps, uint8_t* desc, int* n_out, int cap,
+                                       int nthreads) {
+  Extractor* proto = (Extractor*)h;
+  std::atomic<int> next(0), bad(0);
+  auto work = [&]() {
+    Extractor e(proto->nfeatures, (float)proto->scaleFactor, proto->nlevels, proto->scoreType, proto->fastTh,
+                proto->blur_mode, proto->retain_mode);
+    e.keep_dump = false;
+    for (;;) {
+      int f = next.fetch_add(1);
+      if (f >= nframes) break;
+      int n = e.extract(imgs + (size_t)f * frame_stride, w, hgt, (size_t)stride, (KeyPoint*)kps + (size_t)f * cap,
+                        desc + (size_t)f * cap * 32, cap);
+      if (n < 0) { bad = 1; n = 0; }
+      n_out[f] = n;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < nthreads; t++) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
+  return bad ? -1 : 0;
+}
