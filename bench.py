@@ -174,7 +174,9 @@ def main():
     h_kps = torch.empty((F, NFEAT, 28), dtype=torch.uint8, pin_memory=True)
     h_desc = torch.empty((F, NFEAT, 32), dtype=torch.uint8, pin_memory=True)
     h_n = torch.zeros(F, dtype=torch.int32, pin_memory=True)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: the library treats a NULL stream as "use the handle's own stream", and CUDA
+    # events must be recorded on the stream the kernels are launched on
+    stream = torch.cuda.Stream(device=dev)
 
     def step_device():
         ex.extract_batch_device(d_frames.data_ptr(), F, W, H, W, H * W, d_kps.data_ptr(), d_desc.data_ptr(),
