@@ -1,0 +1,183 @@
+/* orbm.h — C ABI of the B200-native ORB descriptor matcher (part of liborbx.so).
+ *
+ * Drop-in boundary for the data-parallel part of ORB_SLAM::ORBmatcher (reference include/ORBmatcher.h:37-107,
+ * src/ORBmatcher.cc) and the grid queries it calls (Frame::GetFeaturesInArea, src/Frame.cc:199-276;
+ * KeyFrame::GetFeaturesInArea, src/KeyFrame.cc:612-652).  The reference passes Frame / KeyFrame / MapPoint objects;
+ * here every routine takes flat arrays: the object graph (MapPoint pointers, isBad(), 3-D projection) stays with the
+ * caller and is folded into per-keypoint `valid` flags and per-point (u, v, radius, level window) records.
+ * There is NO CPU fallback: every entry point runs hand-written sm_100a kernels and returns ORBM_ERR_CUDA when no
+ * usable device exists.
+ *
+ * Execution model: frames are uploaded once into a device-resident `orbm_frameset` (the 64x48 keypoint grid of
+ * src/Frame.cc:108-122 is built on the device at upload); searches are BATCHED over lists of frame pairs, because a
+ * single 1000-keypoint pair cannot fill one SM, let alone 148.  Candidate distances are computed in parallel; the
+ * reference's loop-carried accept / steal / already-taken logic is replayed by an in-order commit pass, so results
+ * equal the sequential reference bit for bit.
+ *
+ * Error convention: 0 on success, negative ORBM_ERR_* otherwise, text via orbm_last_error().  The reference
+ * asserts (ROS_ASSERT, src/ORBmatcher.cc:240) instead.
+ */
+#ifndef ORBM_H_
+#define ORBM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { ORBM_TH_HIGH = 100, ORBM_TH_LOW = 50, ORBM_HISTO_LENGTH = 30 }; /* src/ORBmatcher.cc:40-42 */
+enum { ORBM_GRID_COLS = 64, ORBM_GRID_ROWS = 48 };                     /* include/Frame.h:35-36 */
+
+enum {
+  ORBM_OK = 0,
+  ORBM_ERR_ARG = -1,
+  ORBM_ERR_CUDA = -2,
+  ORBM_ERR_UNSUPPORTED = -3,
+  ORBM_ERR_OVERFLOW = -4,
+  ORBM_ERR_COMM = -6 /* NCCL unavailable / failed (orbm_knn2_sharded only) */
+};
+
+/* What the matcher reads from a Frame / KeyFrame (all HOST pointers; copied at orbm_frameset_create). */
+typedef struct orbm_frame {
+  int32_t n;             /* number of keypoints, <= 65535 */
+  const float* x;        /* mvKeysUn[i].pt.x */
+  const float* y;        /* mvKeysUn[i].pt.y */
+  const float* angle;    /* mvKeysUn[i].angle (degrees) */
+  const int32_t* octave; /* mvKeysUn[i].octave */
+  const uint8_t* desc;   /* mDescriptors: n x 32 bytes */
+  const uint8_t* valid;  /* per routine, usually "mvpMapPoints[i] != NULL && !isBad()"; NULL = all 0 */
+  float min_x, min_y;    /* Frame::mnMinX / mnMinY (src/Frame.cc:320-349) */
+  float inv_w, inv_h;    /* mfGridElementWidthInv / mfGridElementHeightInv (src/Frame.cc:75-76) */
+} orbm_frame;
+
+/* DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>, Thirdparty/DBoW2/DBoW2/FeatureVector.h:21-22)
+ * flattened: node ids strictly ascending; features of node k = items[start[k] .. start[k+1]). */
+typedef struct orbm_featvec {
+  int32_t nnodes;
+  const int32_t* node_id;
+  const int32_t* start; /* nnodes + 1 entries */
+  const int32_t* items;
+} orbm_featvec;
+
+/* Projected map points for the SearchByProjection family (HOST pointers). */
+typedef struct orbm_points {
+  int32_t n;
+  const float* u;            /* projection into the target image */
+  const float* v;
+  const float* radius;       /* search radius already scaled (e.g. r * mvScaleFactors[level], src/ORBmatcher.cc:72) */
+  const int32_t* min_level;  /* level window handed to GetFeaturesInArea */
+  const int32_t* max_level;
+  const uint8_t* desc;       /* n x 32: MapPoint::GetDescriptor() / LastFrame.mDescriptors.row(i) */
+  const float* angle;        /* keypoint angle of the point's source observation (rotation check); may be NULL */
+  const uint8_t* valid;      /* point takes part (mbTrackInView, !isBad(), inside image ...); NULL = all 1 */
+} orbm_points;
+
+typedef struct orbm_handle orbm_handle;
+typedef struct orbm_frameset orbm_frameset;
+
+int orbm_create(int device, orbm_handle** out);
+void orbm_destroy(orbm_handle* h);
+const char* orbm_last_error(const orbm_handle* h); /* h == NULL: last failed orbm_create on this thread */
+int64_t orbm_kernel_launches(const orbm_handle* h);
+/* GPU milliseconds (CUDA events on the handle's stream, kernels only) of the last search / knn2 call. */
+float orbm_last_kernel_ms(const orbm_handle* h);
+
+/* ---- M1  ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1794-1810; same code: DBoW2 FORB::distance) --------
+ * n independent pairs: dist[i] = Hamming(a + 32 i, b + 32 i).  HOST buffers. */
+int orbm_descriptor_distance(orbm_handle* h, const uint8_t* a, const uint8_t* b, int n, int32_t* dist);
+
+/* ---- frames on the device + M3 grid ------------------------------------------------------------------------- */
+/* fvs may be NULL when no BoW search will be run on the set. */
+int orbm_frameset_create(orbm_handle* h, const orbm_frame* frames, const orbm_featvec* fvs, int nframes,
+                         orbm_frameset** out);
+void orbm_frameset_destroy(orbm_frameset* s);
+/* Replaces the valid flags of one frame (MapPoint associations change between searches). */
+int orbm_frameset_set_valid(orbm_frameset* s, int frame, const uint8_t* valid);
+/* The device-built grid as CSR in the reference's visiting order: cell = ix * 48 + iy (src/Frame.cc:232-258),
+ * insertion order inside a cell.  cell_start: 3073 entries, items: n entries (count = cell_start[3072]). */
+int orbm_frameset_grid(orbm_frameset* s, int frame, int32_t* cell_start, int32_t* items);
+/* Frame::GetFeaturesInArea(x, y, r, minLevel, maxLevel) (src/Frame.cc:199-264) evaluated on the device;
+ * minLevel = maxLevel = -1 gives KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:612-652). */
+int orbm_features_in_area(orbm_frameset* s, int frame, float x, float y, float r, int min_level, int max_level,
+                          int32_t* out, int cap, int* n_out);
+
+/* ---- pair searches: pair p = (frame idx1[p] of set1, frame idx2[p] of set2) ----------------------------------
+ * Per-pair outputs are rows of `stride` int32 (stride >= the largest frame of the written side); unused tail
+ * entries are set to -1.  nmatches[p] = the routine's return value. */
+
+/* M2  SearchForInitialization (src/ORBmatcher.cc:598-713): prev_xy [npairs][stride][2] = vbPrevMatched (in/out),
+ * matches12 [npairs][stride] = vnMatches12. */
+int orbm_search_for_initialization(orbm_handle* h, const orbm_frameset* set1, const orbm_frameset* set2,
+                                   const int32_t* idx1, const int32_t* idx2, int npairs, float* prev_xy, int stride,
+                                   int window, float ratio, int check_ori, int32_t* matches12, int32_t* nmatches);
+
+/* M4  WindowSearch (src/ORBmatcher.cc:409-516): set1 valid = F1 keypoint has a good MapPoint.
+ * matches21[p][i2] = i1 whose MapPoint is assigned to F2 keypoint i2. */
+int orbm_window_search(orbm_handle* h, const orbm_frameset* set1, const orbm_frameset* set2, const int32_t* idx1,
+                       const int32_t* idx2, int npairs, int window, float ratio, int check_ori, int min_level,
+                       int max_level, int32_t* matches21, int stride, int32_t* nmatches);
+
+/* M4  SearchByProjection(Frame&, Frame&, windowSize, ...) (src/ORBmatcher.cc:519-594): uv [npairs][stride][2] =
+ * projection of F1's MapPoint i1 into F2; set1 valid = MapPoint present, good and not already found in F2;
+ * set2 valid = F2 keypoint already has a MapPoint.  matches21 = NEW assignments only. */
+int orbm_search_by_projection_frames(orbm_handle* h, const orbm_frameset* set1, const orbm_frameset* set2,
+                                     const int32_t* idx1, const int32_t* idx2, int npairs, const float* uv,
+                                     int stride, int window, float ratio, int32_t* matches21, int32_t* nmatches);
+
+/* M6  projected-point candidate scoring, problem p = (points[p], frame idx[p] of set).
+ *  variant ORBM_PROJ_LOCAL_MAP  src/ORBmatcher.cc:49-125: best + second with levels, <= TH_HIGH, ratio test only
+ *                               when best and second share a level (`best > ratio * second` rejects)
+ *  variant ORBM_PROJ_BEST       best only, accept iff best <= th_dist; rotation check when check_ori:
+ *                               :1507-1620 (last frame, TH_HIGH), :1622-1746 (relocalisation, ORBdist),
+ *                               :286-407 (Sim3, TH_LOW, no orientation), Fuse / SearchBySim3 inner loops
+ * set valid = keypoint already has a MapPoint (skipped as candidate).  match_out[p][idx] = point index. */
+enum { ORBM_PROJ_LOCAL_MAP = 0, ORBM_PROJ_BEST = 1 };
+int orbm_search_by_projection(orbm_handle* h, const orbm_frameset* set, const int32_t* idx,
+                              const orbm_points* points, int nproblems, int variant, int th_dist, float ratio,
+                              int check_ori, int32_t* match_out, int stride, int32_t* nmatches);
+
+/* M5  SearchByBoW.  ORBM_BOW_KF_F: (KeyFrame*, Frame&) src/ORBmatcher.cc:155-284, set1 = keyframes (valid = good
+ * MapPoint), match_out[p][idxF] = idxKF, accept best <= TH_LOW.  ORBM_BOW_KF_KF: (KeyFrame*, KeyFrame*) :715-850,
+ * valid = good MapPoint on both sides, match_out[p][idx1] = idx2, accept best < TH_LOW. */
+enum { ORBM_BOW_KF_F = 0, ORBM_BOW_KF_KF = 1 };
+int orbm_search_by_bow(orbm_handle* h, const orbm_frameset* set1, const orbm_frameset* set2, const int32_t* idx1,
+                       const int32_t* idx2, int npairs, int variant, float ratio, int check_ori, int32_t* match_out,
+                       int stride, int32_t* nmatches);
+
+/* M9  SearchForTriangulation (src/ORBmatcher.cc:852-1014) incl. CheckDistEpipolarLine (:136-153).
+ * valid = keypoint already has a MapPoint (skipped, both sides).  F12 [npairs][9] row-major, sigma2 [nlevels] =
+ * pKF2->GetSigma2(level).  match12[p][idx1] = idx2. */
+int orbm_search_for_triangulation(orbm_handle* h, const orbm_frameset* set1, const orbm_frameset* set2,
+                                  const int32_t* idx1, const int32_t* idx2, int npairs, const float* F12,
+                                  const float* sigma2, int nlevels, int check_ori, int32_t* match12, int stride,
+                                  int32_t* nmatches);
+
+/* ---- M8  all-pairs 2-NN over a descriptor database (BASELINE config 5) ---------------------------------------
+ * Semantics of the reference's shared inner loop (src/ORBmatcher.cc:201-222) without exclusions: strict `<`, the
+ * lowest index wins ties, the second best is the multiset second minimum.  top2[2 q], top2[2 q + 1] =
+ * (dist << 23) | (idx_base + index) keys of the best and second best (0xFFFFFFFF = none); idx_base + ndb <= 2^23. */
+#define ORBM_KEY_NONE 0xFFFFFFFFu
+#define ORBM_KEY_DIST(k) ((int)((k) >> 23))
+#define ORBM_KEY_INDEX(k) ((int)((k) & 0x7FFFFFu))
+int orbm_knn2(orbm_handle* h, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int64_t idx_base,
+              uint32_t* top2); /* HOST buffers */
+int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int64_t idx_base,
+                     uint32_t* d_top2, void* stream); /* DEVICE buffers, asynchronous */
+/* Merge of per-shard results d_gathered [nshards][nq][2] (the all-gather receive buffer) into d_top2 [nq][2], plus
+ * the accept rule of :224-226: d_match[q] = best index if best <= th_dist && (float)best < ratio * (float)second,
+ * else -1 (d_match may be NULL). */
+int orbm_merge_top2_device(orbm_handle* h, const uint32_t* d_gathered, int nshards, int nq, int th_dist, float ratio,
+                           uint32_t* d_top2, int32_t* d_match, void* stream);
+/* Database sharded over the ranks of an NCCL communicator (one process per GPU): local 2-NN over this rank's shard
+ * (global indices = idx_base + local), ncclAllGather of the [nq][2] keys, merge.  comm = ncclComm_t.  d_gathered is
+ * caller-provided scratch [nranks][nq][2].  NCCL is resolved at run time from the process (dlsym). */
+int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db_shard, int64_t ndb_shard,
+                      int64_t idx_base, int nranks, void* comm, uint32_t* d_gathered, int th_dist, float ratio,
+                      uint32_t* d_top2, int32_t* d_match, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBM_H_ */

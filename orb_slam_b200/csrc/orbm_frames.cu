@@ -1,0 +1,271 @@
+// Device-resident frame sets and the 64x48 keypoint grid (M3).  include/orbm.h.
+// Reference: grid binning src/Frame.cc:108-122 + PosInGrid :266-276; window query Frame::GetFeaturesInArea :199-264
+// and KeyFrame::GetFeaturesInArea src/KeyFrame.cc:612-652.
+#include <cstring>
+
+#include "orbm_match.cuh"
+
+using namespace orbm;
+
+// ------------------------------------------------------------------------------------------------------------------
+// grid_build: one warp per frame.  cell = ix * 48 + iy with ix = round((x - minX) * invW) (half away from zero, the
+// C `round` the reference calls), keypoints outside [0,64) x [0,48) are dropped (:272-273).  CSR items keep the
+// insertion order (ascending keypoint index) inside every cell; the CSR order over cells (ix outer, iy inner) is the
+// visiting order of GetFeaturesInArea, so "position in the CSR" reproduces the reference's candidate order.
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) grid_build_kernel(FrameSetView fs) {
+  __shared__ int s_cnt[kGridCells + 1];
+  const int f = blockIdx.x, lane = threadIdx.x;
+  const int base = fs.frame_off[f], n = fs.frame_off[f + 1] - base;
+  const float4 gp = fs.gridp[f];
+  for (int c = lane; c <= kGridCells; c += 32) s_cnt[c] = 0;
+  __syncwarp();
+  for (int i = lane; i < n; i += 32) {
+    const int c = grid_cell_of(fs.x[base + i], fs.y[base + i], gp);
+    if (c >= 0) atomicAdd(&s_cnt[c], 1);
+  }
+  __syncwarp();
+  // exclusive scan over 3072 cells: each lane owns 96 consecutive cells
+  constexpr int per = kGridCells / 32;
+  int sum = 0;
+  for (int k = 0; k < per; k++) sum += s_cnt[lane * per + k];
+  int incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  int run = incl - sum;
+  for (int k = 0; k < per; k++) {
+    const int c = lane * per + k, v = s_cnt[c];
+    s_cnt[c] = run;
+    run += v;
+  }
+  if (lane == 31) s_cnt[kGridCells] = run;
+  __syncwarp();
+  int32_t* cs = fs.cell_start + (int64_t)f * (kGridCells + 1);
+  for (int c = lane; c <= kGridCells; c += 32) cs[c] = s_cnt[c];
+  __syncwarp();
+  // stable placement: rounds of 32 keypoints in index order; inside a round, lanes of the same cell are ranked
+  // by lane (= index) with __match_any_sync, then the cell cursor advances by the group size
+  int32_t* items = fs.items + base;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    const int i = i0 + lane;
+    const int c = i < n ? grid_cell_of(fs.x[base + i], fs.y[base + i], gp) : -1;
+    const unsigned peers = __match_any_sync(0xffffffffu, c);
+    if (c >= 0) {
+      const int rank = __popc(peers & ((1u << lane) - 1));
+      items[s_cnt[c] + rank] = i;
+    }
+    __syncwarp();
+    if (c >= 0 && (peers & ((1u << lane) - 1)) == 0) s_cnt[c] += __popc(peers);  // group leader
+    __syncwarp();
+  }
+}
+
+// Frame::GetFeaturesInArea evaluated by one warp (test / introspection entry point)
+__global__ void __launch_bounds__(32) features_in_area_kernel(FrameSetView fs, int f, float x, float y, float r,
+                                                              int minl, int maxl, int32_t* out, int cap, int* n_out) {
+  const int lane = threadIdx.x;
+  const int base = fs.frame_off[f];
+  const float4 gp = fs.gridp[f];
+  const int32_t* cs = fs.cell_start + (int64_t)f * (kGridCells + 1);
+  int cx0, cx1, cy0, cy1;
+  int n = 0;
+  if (area_cells(x, y, r, gp, &cx0, &cx1, &cy0, &cy1)) {
+    for (int ix = cx0; ix <= cx1; ix++) {
+      const int s0 = cs[ix * kGridRows + cy0], s1 = cs[ix * kGridRows + cy1 + 1];
+      for (int sb = s0; sb < s1; sb += 32) {
+        const int s = sb + lane;
+        int k = -1;
+        bool on = false;
+        if (s < s1) {
+          k = fs.items[base + s];
+          on = area_accept(fs.x[base + k], fs.y[base + k], fs.octave[base + k], x, y, r, minl, maxl);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, on);
+        if (on) {
+          const int pos = n + __popc(bal & ((1u << lane) - 1));
+          if (pos < cap) out[pos] = k;
+        }
+        n += __popc(bal);
+      }
+    }
+  }
+  if (lane == 0) *n_out = n;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------------------------
+FrameSetView orbm::view_of(const orbm_frameset* s) {
+  FrameSetView v;
+  v.frame_off = s->d_frame_off; v.x = s->d_x; v.y = s->d_y; v.angle = s->d_angle; v.octave = s->d_octave;
+  v.desc = reinterpret_cast<const uint4*>(s->d_desc); v.valid = s->d_valid; v.gridp = s->d_gridp;
+  v.cell_start = s->d_cell_start; v.items = s->d_items;
+  v.node_off = s->d_node_off; v.fvitem_off = s->d_fvitem_off; v.node_id = s->d_node_id;
+  v.node_start = s->d_node_start; v.fv_items = s->d_fv_items;
+  return v;
+}
+
+template <class T>
+static cudaError_t upload(T** dptr, const std::vector<T>& v, cudaStream_t s) {
+  const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+  cudaError_t e = cudaMalloc((void**)dptr, bytes + 16);
+  if (e != cudaSuccess) return e;
+  if (!v.empty()) e = cudaMemcpyAsync(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+  return e;
+}
+
+extern "C" int orbm_frameset_create(orbm_handle* h, const orbm_frame* frames, const orbm_featvec* fvs, int nframes,
+                                    orbm_frameset** out) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!frames || !out || nframes < 1) { h->err = "null frames / nframes < 1"; return ORBM_ERR_ARG; }
+  *out = nullptr;
+  ORBM_CK(cudaSetDevice(h->device));
+  orbm_frameset* s = new orbm_frameset();
+  s->h = h; s->nframes = nframes; s->has_fv = fvs != nullptr;
+  s->frame_off.assign(nframes + 1, 0);
+  for (int f = 0; f < nframes; f++) {
+    const orbm_frame& F = frames[f];
+    if (F.n < 0 || F.n > 65535 || (F.n > 0 && (!F.x || !F.y || !F.angle || !F.octave || !F.desc))) {
+      h->err = "frame with null arrays or more than 65535 keypoints";
+      delete s;
+      return ORBM_ERR_ARG;
+    }
+    s->frame_off[f + 1] = s->frame_off[f] + F.n;
+    s->max_n = std::max(s->max_n, F.n);
+  }
+  const int64_t N = s->total_kp = s->frame_off[nframes];
+  std::vector<float> x(N), y(N), ang(N);
+  std::vector<int32_t> oct(N);
+  std::vector<uint8_t> desc((size_t)N * 32), valid(N, 0);
+  std::vector<float4> gp(nframes);
+  for (int f = 0; f < nframes; f++) {
+    const orbm_frame& F = frames[f];
+    const size_t o = s->frame_off[f], n = F.n;
+    if (n) {
+      memcpy(&x[o], F.x, n * 4); memcpy(&y[o], F.y, n * 4); memcpy(&ang[o], F.angle, n * 4);
+      memcpy(&oct[o], F.octave, n * 4); memcpy(&desc[o * 32], F.desc, n * 32);
+      if (F.valid) memcpy(&valid[o], F.valid, n);
+    }
+    gp[f] = make_float4(F.min_x, F.min_y, F.inv_w, F.inv_h);
+  }
+  std::vector<int32_t> node_id, node_start, fv_items;
+  if (fvs) {
+    s->node_off.assign(nframes + 1, 0);
+    s->fvitem_off.assign(nframes + 1, 0);
+    for (int f = 0; f < nframes; f++) {
+      const orbm_featvec& V = fvs[f];
+      const int nn = V.nnodes;
+      if (nn < 0 || (nn > 0 && (!V.node_id || !V.start || !V.items)) || (nn > 0 && V.start[0] != 0)) {
+        h->err = "malformed feature vector";
+        delete s;
+        return ORBM_ERR_ARG;
+      }
+      const int ni = nn ? V.start[nn] : 0;
+      for (int k = 0; k < nn; k++) {
+        if ((k && V.node_id[k] <= V.node_id[k - 1]) || V.start[k + 1] < V.start[k]) {
+          h->err = "feature vector node ids must be strictly ascending with monotone starts";
+          delete s;
+          return ORBM_ERR_ARG;
+        }
+        node_id.push_back(V.node_id[k]);
+      }
+      for (int k = 0; k <= nn; k++) node_start.push_back(nn ? V.start[k] : 0);
+      for (int k = 0; k < ni; k++) {
+        if (V.items[k] < 0 || V.items[k] >= frames[f].n) { h->err = "feature vector item out of range"; delete s; return ORBM_ERR_ARG; }
+        fv_items.push_back(V.items[k]);
+      }
+      s->node_off[f + 1] = s->node_off[f] + nn;
+      s->fvitem_off[f + 1] = s->fvitem_off[f] + ni;
+    }
+    s->total_nodes = s->node_off[nframes];
+    s->total_fv_items = s->fvitem_off[nframes];
+  }
+  auto fail = [&](cudaError_t e) {
+    h->err = std::string("frameset upload: ") + cudaGetErrorString(e);
+    orbm_frameset_destroy(s);
+    return ORBM_ERR_CUDA;
+  };
+  cudaError_t e;
+  cudaStream_t st = h->stream;
+  if ((e = upload(&s->d_frame_off, s->frame_off, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_x, x, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_y, y, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_angle, ang, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_octave, oct, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_desc, desc, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_valid, valid, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_gridp, gp, st)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_cell_start, (size_t)nframes * (kGridCells + 1) * 4)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_items, std::max<size_t>(N, 1) * 4)) != cudaSuccess) return fail(e);
+  if (fvs) {
+    if ((e = upload(&s->d_node_off, s->node_off, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(&s->d_fvitem_off, s->fvitem_off, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(&s->d_node_id, node_id, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(&s->d_node_start, node_start, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(&s->d_fv_items, fv_items, st)) != cudaSuccess) return fail(e);
+  }
+  grid_build_kernel<<<nframes, 32, 0, st>>>(view_of(s));
+  h->launches++;
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
+  if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return fail(e);  // host vectors die here
+  *out = s;
+  return ORBM_OK;
+}
+
+extern "C" void orbm_frameset_destroy(orbm_frameset* s) {
+  if (!s) return;
+  cudaSetDevice(s->h->device);
+  cudaStreamSynchronize(s->h->stream);
+  void* ptrs[] = {s->d_frame_off, s->d_x, s->d_y, s->d_angle, s->d_octave, s->d_desc, s->d_valid, s->d_gridp,
+                  s->d_cell_start, s->d_items, s->d_node_off, s->d_fvitem_off, s->d_node_id, s->d_node_start,
+                  s->d_fv_items};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  delete s;
+}
+
+extern "C" int orbm_frameset_set_valid(orbm_frameset* s, int frame, const uint8_t* valid) {
+  if (!s) return ORBM_ERR_ARG;
+  orbm_handle* h = s->h;
+  if (frame < 0 || frame >= s->nframes) { h->err = "frame index out of range"; return ORBM_ERR_ARG; }
+  ORBM_CK(cudaSetDevice(h->device));
+  const int o = s->frame_off[frame], n = s->frame_off[frame + 1] - o;
+  if (n == 0) return ORBM_OK;
+  if (valid) ORBM_CK(cudaMemcpyAsync(s->d_valid + o, valid, n, cudaMemcpyHostToDevice, h->stream));
+  else ORBM_CK(cudaMemsetAsync(s->d_valid + o, 0, n, h->stream));
+  ORBM_CK(cudaStreamSynchronize(h->stream));
+  return ORBM_OK;
+}
+
+extern "C" int orbm_frameset_grid(orbm_frameset* s, int frame, int32_t* cell_start, int32_t* items) {
+  if (!s) return ORBM_ERR_ARG;
+  orbm_handle* h = s->h;
+  if (frame < 0 || frame >= s->nframes || !cell_start || !items) { h->err = "bad grid query"; return ORBM_ERR_ARG; }
+  ORBM_CK(cudaSetDevice(h->device));
+  ORBM_CK(cudaMemcpy(cell_start, s->d_cell_start + (size_t)frame * (kGridCells + 1), (kGridCells + 1) * 4,
+                     cudaMemcpyDeviceToHost));
+  const int n = cell_start[kGridCells];
+  if (n) ORBM_CK(cudaMemcpy(items, s->d_items + s->frame_off[frame], (size_t)n * 4, cudaMemcpyDeviceToHost));
+  return ORBM_OK;
+}
+
+extern "C" int orbm_features_in_area(orbm_frameset* s, int frame, float x, float y, float r, int min_level,
+                                     int max_level, int32_t* out, int cap, int* n_out) {
+  if (!s) return ORBM_ERR_ARG;
+  orbm_handle* h = s->h;
+  if (frame < 0 || frame >= s->nframes || !out || !n_out || cap < 0) { h->err = "bad area query"; return ORBM_ERR_ARG; }
+  ORBM_CK(cudaSetDevice(h->device));
+  ORBM_CK(h->ws_io.reserve((size_t)cap * 4 + 64));
+  int32_t* d_out = h->ws_io.as<int32_t>() + 16;
+  int* d_n = h->ws_io.as<int>();
+  features_in_area_kernel<<<1, 32, 0, h->stream>>>(view_of(s), frame, x, y, r, min_level, max_level, d_out, cap, d_n);
+  h->launches++;
+  ORBM_CK(cudaGetLastError());
+  ORBM_CK(cudaMemcpyAsync(n_out, d_n, 4, cudaMemcpyDeviceToHost, h->stream));
+  ORBM_CK(cudaStreamSynchronize(h->stream));
+  if (*n_out > cap) { h->err = "output capacity too small"; return ORBM_ERR_OVERFLOW; }
+  if (*n_out) ORBM_CK(cudaMemcpy(out, d_out, (size_t)*n_out * 4, cudaMemcpyDeviceToHost));
+  return ORBM_OK;
+}

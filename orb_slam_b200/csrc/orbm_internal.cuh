@@ -1,0 +1,89 @@
+// Internal structures of the matcher (orbm_*.cu).  Public surface: include/orbm.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/orbm.h"
+
+namespace orbm {
+
+constexpr int kGridCols = ORBM_GRID_COLS, kGridRows = ORBM_GRID_ROWS, kGridCells = kGridCols * kGridRows;
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+// candidate list entry: (distance << 22) | target index;  per-query list position < 2^22 as well
+constexpr int kCandShift = 22;
+constexpr uint32_t kCandMask = (1u << kCandShift) - 1;
+
+// 256-bit Hamming distance (ORBmatcher::DescriptorDistance, reference src/ORBmatcher.cc:1794-1810: SWAR popcount of
+// eight 32-bit XORs == sum of __popc).
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// A growable device buffer owned by the handle (grown outside the timed path; never shrunk).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace orbm
+
+struct orbm_handle {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  int64_t launches = 0;
+  float last_ms = 0.f;
+  int num_sms = 148;
+  // workspaces
+  orbm::DevBuf knn_part;     // per-chunk partial top-2 keys
+  orbm::DevBuf stage_a, stage_b, stage_c;  // staging for host-pointer entry points
+  orbm::DevBuf ws_problem, ws_query, ws_target, ws_cand, ws_misc, ws_io;
+  void* pinned = nullptr;    // pinned host staging for small result read-backs
+  size_t pinned_cap = 0;
+};
+
+// Device-resident frames: concatenated SoA + per-frame offsets + grids (+ optional feature vectors).
+struct orbm_frameset {
+  orbm_handle* h = nullptr;
+  int nframes = 0, max_n = 0;
+  int64_t total_kp = 0, total_nodes = 0, total_fv_items = 0;
+  std::vector<int32_t> frame_off;   // host copy [nframes + 1]
+  std::vector<int32_t> node_off;    // host copy [nframes + 1] (empty when no feature vectors)
+  std::vector<int32_t> fvitem_off;  // host copy [nframes + 1]
+  // device arrays
+  int32_t* d_frame_off = nullptr;
+  float *d_x = nullptr, *d_y = nullptr, *d_angle = nullptr;
+  int32_t* d_octave = nullptr;
+  uint8_t *d_desc = nullptr, *d_valid = nullptr;
+  float4* d_gridp = nullptr;        // (min_x, min_y, inv_w, inv_h) per frame
+  int32_t* d_cell_start = nullptr;  // [nframes][kGridCells + 1]
+  int32_t* d_items = nullptr;       // [total_kp] grid CSR items (frame-local keypoint indices) at frame_off
+  int32_t *d_node_off = nullptr, *d_fvitem_off = nullptr, *d_node_id = nullptr, *d_node_start = nullptr,
+          *d_fv_items = nullptr;    // node_start has nnodes + 1 entries per frame, stored at node_off[f] + f
+  bool has_fv = false;
+};
+
+#define ORBM_CK(call)                                                          \
+  do {                                                                         \
+    cudaError_t e_ = (call);                                                   \
+    if (e_ != cudaSuccess) {                                                   \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);             \
+      return ORBM_ERR_CUDA;                                                    \
+    }                                                                          \
+  } while (0)

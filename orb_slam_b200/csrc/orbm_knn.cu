@@ -1,0 +1,218 @@
+// Matcher handle + M1 (DescriptorDistance) + M8 (all-pairs 2-NN) kernels and entry points.  include/orbm.h.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstring>
+
+#include "orbm_internal.cuh"
+
+using namespace orbm;
+
+static thread_local std::string g_orbm_create_err;
+
+// ------------------------------------------------------------------------------------------------------------------
+// handle
+// ------------------------------------------------------------------------------------------------------------------
+extern "C" int orbm_create(int device, orbm_handle** out) {
+  if (!out) return ORBM_ERR_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+    g_orbm_create_err = "no usable CUDA device (this library has no CPU fallback)";
+    return ORBM_ERR_CUDA;
+  }
+  orbm_handle* h = new orbm_handle();
+  h->device = device;
+  auto body = [&]() -> int {
+    ORBM_CK(cudaSetDevice(device));
+    ORBM_CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    ORBM_CK(cudaEventCreate(&h->ev0));
+    ORBM_CK(cudaEventCreate(&h->ev1));
+    cudaDeviceProp prop;
+    ORBM_CK(cudaGetDeviceProperties(&prop, device));
+    h->num_sms = prop.multiProcessorCount;
+    return ORBM_OK;
+  };
+  int rc = body();
+  if (rc != ORBM_OK) { g_orbm_create_err = h->err; orbm_destroy(h); return rc; }
+  *out = h;
+  return ORBM_OK;
+}
+
+extern "C" void orbm_destroy(orbm_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  DevBuf* bufs[] = {&h->knn_part, &h->stage_a, &h->stage_b, &h->stage_c, &h->ws_problem, &h->ws_query,
+                    &h->ws_target, &h->ws_cand, &h->ws_misc, &h->ws_io};
+  for (DevBuf* b : bufs) b->release();
+  if (h->pinned) cudaFreeHost(h->pinned);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+extern "C" const char* orbm_last_error(const orbm_handle* h) { return h ? h->err.c_str() : g_orbm_create_err.c_str(); }
+extern "C" int64_t orbm_kernel_launches(const orbm_handle* h) { return h ? h->launches : 0; }
+extern "C" float orbm_last_kernel_ms(const orbm_handle* h) { return h ? h->last_ms : 0.f; }
+
+// ------------------------------------------------------------------------------------------------------------------
+// M1  batched DescriptorDistance: one thread per pair, two 16-byte loads per descriptor
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) distance_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
+                                                       int32_t* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = hamming256(a[2 * i], a[2 * i + 1], b[2 * i], b[2 * i + 1]);
+}
+
+extern "C" int orbm_descriptor_distance(orbm_handle* h, const uint8_t* a, const uint8_t* b, int n, int32_t* dist) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!a || !b || !dist || n < 0) { h->err = "null pointer or negative n"; return ORBM_ERR_ARG; }
+  if (n == 0) return ORBM_OK;
+  ORBM_CK(cudaSetDevice(h->device));
+  const size_t bytes = (size_t)n * 32;
+  ORBM_CK(h->stage_a.reserve(bytes));
+  ORBM_CK(h->stage_b.reserve(bytes));
+  ORBM_CK(h->stage_c.reserve((size_t)n * 4));
+  ORBM_CK(cudaMemcpyAsync(h->stage_a.p, a, bytes, cudaMemcpyHostToDevice, h->stream));
+  ORBM_CK(cudaMemcpyAsync(h->stage_b.p, b, bytes, cudaMemcpyHostToDevice, h->stream));
+  distance_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(h->stage_a.as<uint4>(), h->stage_b.as<uint4>(), n,
+                                                         h->stage_c.as<int32_t>());
+  h->launches++;
+  ORBM_CK(cudaGetLastError());
+  ORBM_CK(cudaMemcpyAsync(dist, h->stage_c.p, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+  ORBM_CK(cudaStreamSynchronize(h->stream));
+  return ORBM_OK;
+}
+
+#include "orbm_knn_kernels.inl"
+
+namespace {
+
+int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int64_t idx_base,
+                uint32_t* d_top2, cudaStream_t s) {
+  if (!d_q || !d_db || !d_top2 || nq < 0 || ndb < 0 || idx_base < 0) {
+    h->err = "null pointer or negative size";
+    return ORBM_ERR_ARG;
+  }
+  if (idx_base + ndb > (1 << 23)) {
+    h->err = "idx_base + ndb exceeds the 2^23 index range of the packed keys";
+    return ORBM_ERR_UNSUPPORTED;
+  }
+  if (((uintptr_t)d_q | (uintptr_t)d_db) & 15) { h->err = "descriptor arrays must be 16-byte aligned"; return ORBM_ERR_ARG; }
+  ORBM_CK(h->ws_misc.reserve(256));
+  int* d_err = h->ws_misc.as<int>();
+  ORBM_CK(cudaMemsetAsync(d_err, 0, sizeof(int), s));
+  if (nq == 0) return ORBM_OK;
+  if (ndb == 0) { ORBM_CK(cudaMemsetAsync(d_top2, 0xFF, (size_t)nq * 8, s)); return ORBM_OK; }
+  const int qpt = nq > 2 * kKnnThreads ? 4 : (nq > kKnnThreads ? 2 : 1);
+  const int qtiles = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
+  // chunks: about 2 CTAs per SM over the whole grid; each chunk a whole number of tiles and >= 8 tiles
+  int64_t want = std::max<int64_t>(1, (2 * (int64_t)h->num_sms + qtiles - 1) / qtiles);
+  int64_t chunk_len = (ndb + want - 1) / want;
+  chunk_len = std::max<int64_t>((chunk_len + kKnnTile - 1) / kKnnTile * kKnnTile, 8 * kKnnTile);
+  const int nchunks = (int)((ndb + chunk_len - 1) / chunk_len);
+  ORBM_CK(h->knn_part.reserve((size_t)nchunks * nq * 8 + 16));
+  dim3 grid(nchunks, qtiles);
+  const uint4* q4 = reinterpret_cast<const uint4*>(d_q);
+  const uint4* db4 = reinterpret_cast<const uint4*>(d_db);
+  uint32_t* part = h->knn_part.as<uint32_t>();
+  const int cl = (int)chunk_len;
+  const uint32_t ib = (uint32_t)idx_base;
+  if (qpt == 4) knn2_kernel<4><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  else if (qpt == 2) knn2_kernel<2><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  else knn2_kernel<1><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(part), nchunks, nq, 0, 0.f,
+                                                    reinterpret_cast<uint2*>(d_top2), nullptr);
+  h->launches += 2;
+  ORBM_CK(cudaGetLastError());
+  return ORBM_OK;
+}
+
+int knn_check_err(orbm_handle* h) {  // call after the stream has been synchronised
+  int flag = 0;
+  ORBM_CK(cudaMemcpy(&flag, h->ws_misc.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (flag) { h->err = "knn2: TMA tile never arrived (mbarrier wait timed out)"; return ORBM_ERR_CUDA; }
+  return ORBM_OK;
+}
+
+}  // namespace
+
+extern "C" int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                int64_t idx_base, uint32_t* d_top2, void* stream) {
+  if (!h) return ORBM_ERR_ARG;
+  ORBM_CK(cudaSetDevice(h->device));
+  return knn2_launch(h, d_q, nq, d_db, ndb, idx_base, d_top2, stream ? (cudaStream_t)stream : h->stream);
+}
+
+extern "C" int orbm_knn2(orbm_handle* h, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int64_t idx_base,
+                         uint32_t* top2) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!q || !db || !top2 || nq < 0 || ndb < 0) { h->err = "null pointer or negative size"; return ORBM_ERR_ARG; }
+  if (nq == 0) return ORBM_OK;
+  ORBM_CK(cudaSetDevice(h->device));
+  ORBM_CK(h->stage_a.reserve((size_t)nq * 32 + 16));
+  ORBM_CK(h->stage_b.reserve((size_t)ndb * 32 + 16));
+  ORBM_CK(h->stage_c.reserve((size_t)nq * 8 + 16));
+  ORBM_CK(cudaMemcpyAsync(h->stage_a.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, h->stream));
+  if (ndb) ORBM_CK(cudaMemcpyAsync(h->stage_b.p, db, (size_t)ndb * 32, cudaMemcpyHostToDevice, h->stream));
+  ORBM_CK(cudaEventRecord(h->ev0, h->stream));
+  int rc = knn2_launch(h, h->stage_a.as<uint8_t>(), nq, h->stage_b.as<uint8_t>(), ndb, idx_base,
+                       h->stage_c.as<uint32_t>(), h->stream);
+  if (rc != ORBM_OK) return rc;
+  ORBM_CK(cudaEventRecord(h->ev1, h->stream));
+  ORBM_CK(cudaMemcpyAsync(top2, h->stage_c.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, h->stream));
+  ORBM_CK(cudaStreamSynchronize(h->stream));
+  cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+  return knn_check_err(h);
+}
+
+extern "C" int orbm_merge_top2_device(orbm_handle* h, const uint32_t* d_gathered, int nshards, int nq, int th_dist,
+                                      float ratio, uint32_t* d_top2, int32_t* d_match, void* stream) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!d_gathered || nshards < 1 || nq < 0 || (!d_top2 && !d_match)) { h->err = "bad merge arguments"; return ORBM_ERR_ARG; }
+  if (nq == 0) return ORBM_OK;
+  ORBM_CK(cudaSetDevice(h->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(d_gathered), nshards, nq, th_dist,
+                                                    ratio, reinterpret_cast<uint2*>(d_top2), d_match);
+  h->launches++;
+  ORBM_CK(cudaGetLastError());
+  return ORBM_OK;
+}
+
+// NCCL is resolved from the process at run time so that liborbx.so has no link-time NCCL dependency and shares the
+// NCCL instance of whoever created the communicator (e.g. the one bundled with PyTorch).
+typedef int (*nccl_allgather_fn)(const void*, void*, size_t, int, void*, cudaStream_t);
+static nccl_allgather_fn resolve_allgather() {
+  static nccl_allgather_fn fn = nullptr;
+  if (fn) return fn;
+  void* sym = dlsym(RTLD_DEFAULT, "ncclAllGather");
+  if (!sym) {
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (lib) sym = dlsym(lib, "ncclAllGather");
+  }
+  fn = reinterpret_cast<nccl_allgather_fn>(sym);
+  return fn;
+}
+
+extern "C" int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db_shard,
+                                 int64_t ndb_shard, int64_t idx_base, int nranks, void* comm, uint32_t* d_gathered,
+                                 int th_dist, float ratio, uint32_t* d_top2, int32_t* d_match, void* stream) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!comm || !d_gathered || nranks < 1) { h->err = "bad communicator / gather buffer"; return ORBM_ERR_ARG; }
+  nccl_allgather_fn allgather = resolve_allgather();
+  if (!allgather) { h->err = "ncclAllGather not found in the process and libnccl.so.2 not loadable"; return ORBM_ERR_COMM; }
+  ORBM_CK(cudaSetDevice(h->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  ORBM_CK(h->stage_c.reserve((size_t)nq * 8 + 16));
+  uint32_t* d_local = h->stage_c.as<uint32_t>();
+  int rc = knn2_launch(h, d_q, nq, d_db_shard, ndb_shard, idx_base, d_local, s);
+  if (rc != ORBM_OK) return rc;
+  const int ncclUint32 = 3;
+  const int nrc = allgather(d_local, d_gathered, (size_t)nq * 2, ncclUint32, comm, s);
+  if (nrc != 0) { h->err = "ncclAllGather failed with code " + std::to_string(nrc); return ORBM_ERR_COMM; }
+  return orbm_merge_top2_device(h, d_gathered, nranks, nq, th_dist, ratio, d_top2, d_match, s);
+}

@@ -1,0 +1,481 @@
+// Included by orbm_match.cu: kernels of the search routines (M2, M4, M5, M6, M7, M9).
+//
+// Every routine of the reference is "for each query in order: ordered candidate list -> Hamming distances ->
+// best / second -> thresholds, with a loop-carried already-taken / steal dependence" (SURVEY H3).  Here:
+//   prep    (parallel)  query records + an upper bound of each candidate list
+//   offsets (warp/problem) scan -> candidate block of the problem inside one shared arena
+//   fill    (warp/query) candidates in the REFERENCE'S VISITING ORDER with their distances, (dist << 22) | target
+//   commit  (warp/problem) in-order replay of the accept / steal / taken logic; lanes share one query's list and
+//           reduce packed (dist, position) keys, whose order equals the sequential scan with strict `<`
+//   emit    output rows in the layout of include/orbm.h
+namespace {
+
+enum Kind { K_INIT = 0, K_WINDOW, K_PROJ_FF, K_PROJ_LOCAL, K_PROJ_BEST, K_BOW_KF_F, K_BOW_KF_KF, K_TRIANG };
+
+struct Problem {
+  int nq, nt;          // queries (may be rewritten by bow_prep), target keypoints
+  int qstart, tstart;  // offsets into the per-query / per-target workspaces
+  int qsrc;            // index of source element 0 in the query source arrays (set1 keypoints or points)
+  int nsrc;            // number of source elements (rows of the per-source output)
+  int tbase;           // set2.frame_off[target frame]
+  int tframe;          // target frame in set2
+  int f1;              // source frame in set1 (-1 for point problems)
+  int cand_base;       // written by offsets_kernel
+  int cand_total;
+  int nmatches;        // written by commit_kernel
+};
+
+struct __align__(16) QRec {
+  float x, y, r;  // window query
+  int lv;         // (minLevel & 0xffff) | (maxLevel << 16)
+  int cells;      // cx0 | cx1 << 8 | cy0 << 16 | cy1 << 24, -1 = empty window
+  int src;        // source index: keypoint of F1 / point / feature-vector item
+  int active;
+  int cnt;        // upper bound after prep, exact after fill
+  int off;        // offset inside the problem's candidate block
+  int match;      // matched target (-1 none)
+  int bin;        // rotation-histogram bin of the accepted match (-1 none)
+  int list2;      // BoW: absolute start of the shared node's target list in set2.fv_items
+};
+
+struct QuerySrc {  // where query descriptors / angles / positions come from
+  const uint4* desc;
+  const float *angle, *x, *y;
+  const int32_t* octave;
+  const uint8_t* valid;
+};
+
+struct SearchArgs {
+  int kind, nproblems;
+  Problem* prob;
+  QRec* q;
+  int2* tstate;      // per target: (owner source index: -1 free, -2 taken on entry ; matched distance)
+  uint32_t* cand;
+  int64_t cand_cap;
+  unsigned long long* cursor;  // [0] arena cursor, [1] overflow flag
+  QuerySrc src;
+  FrameSetView s1, s2;
+  const float* qxy;  // K_INIT: prev_xy rows, K_PROJ_FF: uv rows  [problem][stride][2]
+  const float* pu; const float* pv; const float* pr; const int32_t* pminl; const int32_t* pmaxl;  // point problems
+  int stride;
+  int window, min_level, max_level, check_ori, th_dist;
+  float ratio;
+  const float* F12;     // K_TRIANG [problem][9]
+  const float* sigma2;  // K_TRIANG [nlevels]
+  int nlevels;
+  int32_t* out;         // [problem][stride]
+  float* out_xy;        // K_INIT: prev_xy (same buffer as qxy)
+  int32_t* nmatches;    // [problem]
+};
+
+__device__ __forceinline__ int pack_lv(int a, int b) { return (a & 0xffff) | (b << 16); }
+__device__ __forceinline__ int lv_min(int lv) { return (int)(short)(lv & 0xffff); }
+__device__ __forceinline__ int lv_max(int lv) { return lv >> 16; }
+
+__device__ __forceinline__ int find_problem(const Problem* prob, int np, int idx, bool by_target) {
+  int lo = 0, hi = np - 1;  // last problem whose start <= idx
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    const int st = by_target ? prob[mid].tstart : prob[mid].qstart;
+    if (st <= idx) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+// per-target state on entry
+__global__ void __launch_bounds__(256) target_init_kernel(SearchArgs a, int ttotal) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ttotal) return;
+  const Problem& P = a.prob[find_problem(a.prob, a.nproblems, i, true)];
+  const int t = i - P.tstart;
+  const bool v = a.s2.valid[P.tbase + t] != 0;
+  bool taken = false;
+  switch (a.kind) {
+    case K_PROJ_FF: case K_PROJ_LOCAL: case K_PROJ_BEST: case K_TRIANG: taken = v; break;  // already has a MapPoint
+    case K_BOW_KF_KF: taken = !v; break;                                                  // :763-767
+    default: break;
+  }
+  a.tstate[i] = make_int2(taken ? -2 : -1, INT_MAX);
+}
+
+// grid family: query record + candidate upper bound (sum of the CSR column ranges of the cell window)
+__global__ void __launch_bounds__(256) grid_prep_kernel(SearchArgs a, int qtotal) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= qtotal) return;
+  const int p = find_problem(a.prob, a.nproblems, i, false);
+  const Problem& P = a.prob[p];
+  const int q = i - P.qstart, g = P.qsrc + q;
+  QRec r;
+  r.src = q; r.match = -1; r.bin = -1; r.list2 = 0; r.off = 0;
+  switch (a.kind) {
+    case K_INIT: {  // :611-618
+      const int level1 = a.src.octave[g];
+      r.active = !(level1 > 0);
+      r.x = a.qxy[((int64_t)p * a.stride + q) * 2]; r.y = a.qxy[((int64_t)p * a.stride + q) * 2 + 1];
+      r.r = (float)a.window; r.lv = pack_lv(level1, level1);
+      break;
+    }
+    case K_WINDOW: {  // :425-443
+      const int level1 = a.src.octave[g];
+      r.active = a.src.valid[g] != 0;
+      if (a.min_level > 0 && level1 < a.min_level) r.active = 0;
+      if (a.max_level < INT_MAX && level1 > a.max_level) r.active = 0;
+      r.x = a.src.x[g]; r.y = a.src.y[g]; r.r = (float)a.window; r.lv = pack_lv(level1, level1);
+      break;
+    }
+    case K_PROJ_FF: {  // :532-553
+      const int level1 = a.src.octave[g];
+      r.active = a.src.valid[g] != 0;
+      r.x = a.qxy[((int64_t)p * a.stride + q) * 2]; r.y = a.qxy[((int64_t)p * a.stride + q) * 2 + 1];
+      r.r = (float)a.window; r.lv = pack_lv(level1, level1);
+      break;
+    }
+    default: {  // K_PROJ_LOCAL / K_PROJ_BEST: points
+      r.active = a.src.valid ? a.src.valid[g] != 0 : 1;
+      r.x = a.pu[g]; r.y = a.pv[g]; r.r = a.pr[g]; r.lv = pack_lv(a.pminl[g], a.pmaxl[g]);
+      break;
+    }
+  }
+  int ub = 0;
+  r.cells = -1;
+  if (r.active) {
+    int cx0, cx1, cy0, cy1;
+    if (area_cells(r.x, r.y, r.r, a.s2.gridp[P.tframe], &cx0, &cx1, &cy0, &cy1)) {
+      r.cells = cx0 | (cx1 << 8) | (cy0 << 16) | (cy1 << 24);
+      const int32_t* cs = a.s2.cell_start + (int64_t)P.tframe * (kGridCells + 1);
+      for (int ix = cx0; ix <= cx1; ix++) ub += cs[ix * kGridRows + cy1 + 1] - cs[ix * kGridRows + cy0];
+    }
+  }
+  r.cnt = ub;
+  a.q[i] = r;
+}
+
+// one warp per problem: exclusive scan of the per-query bounds, block allocation in the shared candidate arena
+__global__ void __launch_bounds__(128) offsets_kernel(SearchArgs a) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= a.nproblems) return;
+  Problem& P = a.prob[p];
+  QRec* q = a.q + P.qstart;
+  int run = 0;
+  for (int i0 = 0; i0 < P.nq; i0 += 32) {
+    const int i = i0 + lane;
+    const int n = i < P.nq ? q[i].cnt : 0;
+    int incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (i < P.nq) q[i].off = run + incl - n;
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) {
+    const unsigned long long base = atomicAdd(a.cursor, (unsigned long long)run);
+    P.cand_total = run;
+    if (base + run > (unsigned long long)a.cand_cap) { a.cursor[1] = 1; P.cand_base = -1; }
+    else P.cand_base = (int)base;
+  }
+}
+
+// grid family: one warp per query walks the cell window column by column (each column is ONE contiguous CSR range),
+// keeps what Frame::GetFeaturesInArea keeps, in its order, and attaches the Hamming distance
+__global__ void __launch_bounds__(256) grid_fill_kernel(SearchArgs a, int qtotal) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (i >= qtotal) return;
+  QRec& r = a.q[i];
+  if (r.cnt == 0) return;  // inactive query or empty window: the bound is already 0
+  const Problem& P = a.prob[find_problem(a.prob, a.nproblems, i, false)];
+  if (P.cand_base < 0) return;
+  const int g = P.qsrc + r.src;
+  const uint4 d0 = a.src.desc[2 * (int64_t)g], d1 = a.src.desc[2 * (int64_t)g + 1];
+  const int cx0 = r.cells & 255, cx1 = (r.cells >> 8) & 255, cy0 = (r.cells >> 16) & 255, cy1 = (r.cells >> 24) & 255;
+  const int minl = lv_min(r.lv), maxl = lv_max(r.lv);
+  const float x = r.x, y = r.y, rad = r.r;
+  const int32_t* cs = a.s2.cell_start + (int64_t)P.tframe * (kGridCells + 1);
+  const int32_t* items = a.s2.items + P.tbase;
+  uint32_t* out = a.cand + P.cand_base + r.off;
+  int n = 0;
+  for (int ix = cx0; ix <= cx1; ix++) {
+    const int s0 = cs[ix * kGridRows + cy0], s1 = cs[ix * kGridRows + cy1 + 1];
+    for (int sb = s0; sb < s1; sb += 32) {
+      const int s = sb + lane;
+      bool on = false;
+      int t = 0;
+      if (s < s1) {
+        t = items[s];
+        const int gt = P.tbase + t;
+        on = area_accept(a.s2.x[gt], a.s2.y[gt], a.s2.octave[gt], x, y, rad, minl, maxl);
+      }
+      const unsigned bal = __ballot_sync(0xffffffffu, on);
+      if (on) {
+        const int gt = P.tbase + t;
+        const int dist = hamming256(d0, d1, a.s2.desc[2 * (int64_t)gt], a.s2.desc[2 * (int64_t)gt + 1]);
+        out[n + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)dist << kCandShift) | (uint32_t)t;
+      }
+      n += __popc(bal);
+    }
+  }
+  __syncwarp();
+  if (lane == 0) r.cnt = n;
+}
+
+// BoW family: one warp per problem.  Shared vocabulary nodes in ascending id order (the merge-join of
+// src/ORBmatcher.cc:176-259 visits exactly these); queries = the source features of every shared node, in order.
+__global__ void __launch_bounds__(128) bow_prep_kernel(SearchArgs a) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= a.nproblems) return;
+  Problem& P = a.prob[p];
+  const int f1 = P.f1, f2 = P.tframe;
+  const int nn1 = a.s1.node_off[f1 + 1] - a.s1.node_off[f1], nn2 = a.s2.node_off[f2 + 1] - a.s2.node_off[f2];
+  const int32_t* id1 = a.s1.node_id + a.s1.node_off[f1];
+  const int32_t* id2 = a.s2.node_id + a.s2.node_off[f2];
+  const int32_t* st1 = a.s1.node_start + a.s1.node_off[f1] + f1;
+  const int32_t* st2 = a.s2.node_start + a.s2.node_off[f2] + f2;
+  const int32_t* it1 = a.s1.fv_items + a.s1.fvitem_off[f1];
+  const int list2_base = a.s2.fvitem_off[f2];
+  QRec* q = a.q + P.qstart;
+  int run = 0;
+  for (int k0 = 0; k0 < nn1; k0 += 32) {
+    const int k1 = k0 + lane;
+    int k2 = -1, len = 0;
+    if (k1 < nn1) {
+      const int id = id1[k1];
+      int lo = 0, hi = nn2;  // lower_bound
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (id2[mid] < id) lo = mid + 1; else hi = mid; }
+      if (lo < nn2 && id2[lo] == id) { k2 = lo; len = st1[k1 + 1] - st1[k1]; }
+    }
+    int incl = len;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    const int off = run + incl - len;
+    for (int j = 0; j < len; j++) {
+      const int idx1 = it1[st1[k1] + j];
+      const bool v = a.src.valid[P.qsrc + idx1] != 0;
+      QRec r;
+      r.x = r.y = r.r = 0.f; r.lv = 0; r.cells = -1; r.off = 0;
+      r.src = idx1; r.match = -1; r.bin = -1;
+      r.active = a.kind == K_TRIANG ? !v : v;  // :191-195, :750-754 / :891-895
+      r.list2 = list2_base + st2[k2];
+      r.cnt = r.active ? st2[k2 + 1] - st2[k2] : 0;
+      q[off + j] = r;
+    }
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) P.nq = run;
+}
+
+__global__ void __launch_bounds__(256) bow_fill_kernel(SearchArgs a, int qtotal) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (i >= qtotal) return;
+  const Problem& P = a.prob[find_problem(a.prob, a.nproblems, i, false)];
+  if (i - P.qstart >= P.nq || P.cand_base < 0) return;
+  const QRec& r = a.q[i];
+  if (r.cnt == 0) return;
+  const int g = P.qsrc + r.src;
+  const uint4 d0 = a.src.desc[2 * (int64_t)g], d1 = a.src.desc[2 * (int64_t)g + 1];
+  uint32_t* out = a.cand + P.cand_base + r.off;
+  for (int j = lane; j < r.cnt; j += 32) {
+    const int t = a.s2.fv_items[r.list2 + j];
+    const int gt = P.tbase + t;
+    const int dist = hamming256(d0, d1, a.s2.desc[2 * (int64_t)gt], a.s2.desc[2 * (int64_t)gt + 1]);
+    out[j] = ((uint32_t)dist << kCandShift) | (uint32_t)t;
+  }
+}
+
+// rotation bin (e.g. src/ORBmatcher.cc:234-241): factor = 1/HISTO_LENGTH, round() half away from zero
+__device__ __forceinline__ int rot_bin(float a1, float a2) {
+  const float factor = 1.0f / ORBM_HISTO_LENGTH;
+  float rot = __fsub_rn(a1, a2);
+  if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+  int bin = (int)roundf(__fmul_rn(rot, factor));
+  if (bin == ORBM_HISTO_LENGTH) bin = 0;
+  return bin;
+}
+
+__device__ __forceinline__ void warp_top2(uint32_t& b, uint32_t& s) {
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) {
+    const uint32_t ob = __shfl_xor_sync(0xffffffffu, b, d), os = __shfl_xor_sync(0xffffffffu, s, d);
+    s = min(min(s, os), max(b, ob));
+    b = min(b, ob);
+  }
+}
+
+// ORBmatcher::CheckDistEpipolarLine (src/ORBmatcher.cc:136-153), individually rounded float ops in source order
+__device__ __forceinline__ bool epipolar_ok(float x1, float y1, float x2, float y2, const float* F, float sigma2) {
+  const float ea = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[0]), __fmul_rn(y1, F[3])), F[6]);
+  const float eb = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[1]), __fmul_rn(y1, F[4])), F[7]);
+  const float ec = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[2]), __fmul_rn(y1, F[5])), F[8]);
+  const float num = __fadd_rn(__fadd_rn(__fmul_rn(ea, x2), __fmul_rn(eb, y2)), ec);
+  const float den = __fadd_rn(__fmul_rn(ea, ea), __fmul_rn(eb, eb));
+  if (den == 0) return false;
+  const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+  return (double)dsqr < __dmul_rn(3.84, (double)sigma2);
+}
+
+
+// ------------------------------------------------------------------------------------------------------------------
+// commit: one warp per problem replays the reference's query loop IN ORDER.  For one query the 32 lanes share the
+// candidate list: each evaluates the skip rule against the current state, keeps its own (best, second) packed
+// (dist << 22 | list position) keys and a butterfly merges them.  Packed-key order = (distance, position) order,
+// which is what `if (dist < best) {second = best; best = dist} else if (dist < second) second = dist` computes.
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) commit_kernel(SearchArgs a) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= a.nproblems) return;
+  Problem& P = a.prob[p];
+  if (P.cand_base < 0) return;  // arena overflow: the host grows the arena and reruns
+  QRec* qr = a.q + P.qstart;
+  int2* ts = a.tstate + P.tstart;
+  const uint32_t* cand = a.cand + P.cand_base;
+  const int kind = a.kind;
+  const float ratio = a.ratio;
+  const float kIntMaxF = 2147483648.0f;  // (float)INT_MAX
+  int hist = 0;                           // lane b (< 30) counts rotHist[b].size()
+  const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL);
+  float F[9];
+  if (kind == K_TRIANG)
+    for (int k = 0; k < 9; k++) F[k] = a.F12[(int64_t)p * 9 + k];
+
+  for (int q = 0; q < P.nq; q++) {
+    const int cnt = qr[q].cnt;
+    if (cnt == 0) continue;  // inactive query, empty window (`vIndices.empty()`), or empty node list
+    const int off = qr[q].off, src = qr[q].src;
+    int accept_t = -1, accept_d = 0;
+    if (kind != K_TRIANG) {
+      uint32_t b = kNone, s = kNone;
+      for (int j = lane; j < cnt; j += 32) {
+        const uint32_t e = cand[off + j];
+        const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+        const int2 st = ts[t];
+        const bool skip = kind == K_INIT ? st.y <= d : st.x != -1;  // :637 / `if (taken) continue`
+        if (!skip) {
+          const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
+          s = min(s, max(b, key));
+          b = min(b, key);
+        }
+      }
+      warp_top2(b, s);
+      if (b != kNone) {
+        const int bd = (int)(b >> kCandShift);
+        const int bt = (int)(cand[off + (b & kCandMask)] & kCandMask);
+        const float sdf = s == kNone ? kIntMaxF : (float)(int)(s >> kCandShift);
+        bool ok = false;
+        switch (kind) {
+          case K_INIT: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(sdf, ratio); break;            // :652-654
+          case K_WINDOW: case K_PROJ_FF: ok = (float)bd <= __fmul_rn(sdf, ratio) && bd <= ORBM_TH_HIGH; break;  // :476, :585
+          case K_PROJ_LOCAL: {                                                                          // :112-117
+            if (bd <= ORBM_TH_HIGH) {
+              const int l1 = a.s2.octave[P.tbase + bt];
+              const int l2 = s == kNone ? -1 : a.s2.octave[P.tbase + (int)(cand[off + (s & kCandMask)] & kCandMask)];
+              ok = !(l1 == l2 && (float)bd > __fmul_rn(ratio, sdf));
+            }
+            break;
+          }
+          case K_PROJ_BEST: ok = bd <= a.th_dist; break;                                               // :1576, :1702, :398
+          case K_BOW_KF_F: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;          // :224-226
+          default: ok = bd < ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;                   // :791-793
+        }
+        if (ok) { accept_t = bt; accept_d = bd; }
+      }
+    } else {
+      // SearchForTriangulation :896-958: candidates with dist <= TH_LOW sorted by (dist, idx2); walk while
+      // dist <= 2 * best; the first one passing the epipolar test wins.  Entries already are (dist << 22) | idx2.
+      uint32_t last = 0;
+      bool first = true;
+      int dist_th = 0;
+      const float x1 = a.src.x[P.qsrc + src], y1 = a.src.y[P.qsrc + src];
+      while (true) {
+        uint32_t m = kNone;
+        for (int j = lane; j < cnt; j += 32) {
+          const uint32_t e = cand[off + j];
+          const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+          if (d <= ORBM_TH_LOW && ts[t].x == -1 && (first || e > last)) m = min(m, e);
+        }
+        m = __reduce_min_sync(0xffffffffu, m);
+        if (m == kNone) break;
+        const int d = (int)(m >> kCandShift), t = (int)(m & kCandMask);
+        if (first) { dist_th = 2 * d; first = false; }
+        if (d > dist_th) break;
+        const int gt = P.tbase + t;
+        int lvl = a.s2.octave[gt];
+        lvl = min(max(lvl, 0), a.nlevels - 1);
+        if (epipolar_ok(x1, y1, a.s2.x[gt], a.s2.y[gt], F, a.sigma2[lvl])) { accept_t = t; accept_d = d; break; }
+        last = m;
+      }
+    }
+    if (accept_t >= 0) {
+      int bin = -1;
+      if (use_hist) {
+        bin = rot_bin(a.src.angle[P.qsrc + src], a.s2.angle[P.tbase + accept_t]);
+        if (lane == bin) hist++;
+      }
+      if (lane == 0) {
+        if (kind == K_INIT) {  // steal :656-663
+          const int prev = ts[accept_t].x;
+          if (prev >= 0) qr[prev].match = -1;
+        }
+        ts[accept_t] = make_int2(src, accept_d);
+        qr[q].match = accept_t;
+        qr[q].bin = bin;
+      }
+    }
+    __syncwarp();
+  }
+
+  // rotation consistency (ComputeThreeMaxima, src/ORBmatcher.cc:1748-1789) + removal of the other bins
+  if (a.check_ori && use_hist) {
+    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+    for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+      const int sz = __shfl_sync(0xffffffffu, hist, i);
+      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+      else if (sz > max3) { max3 = sz; ind3 = i; }
+    }
+    if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+    for (int q = lane; q < P.nq; q += 32) {
+      const int bin = qr[q].bin;
+      if (bin >= 0 && bin != ind1 && bin != ind2 && bin != ind3 && qr[q].match >= 0) {
+        ts[qr[q].match].x = -1;
+        qr[q].match = -1;
+      }
+    }
+    __syncwarp();
+  }
+  int n = 0;
+  for (int q = lane; q < P.nq; q += 32) n += qr[q].match >= 0;
+  n = __reduce_add_sync(0xffffffffu, n);
+  if (lane == 0) { P.nmatches = n; a.nmatches[p] = n; }
+}
+
+// output rows (include/orbm.h): per-source for K_INIT / K_BOW_KF_KF / K_TRIANG, per-target otherwise
+__global__ void __launch_bounds__(128) emit_kernel(SearchArgs a) {
+  const int p = blockIdx.x;
+  const Problem& P = a.prob[p];
+  int32_t* out = a.out + (int64_t)p * a.stride;
+  const QRec* qr = a.q + P.qstart;
+  const int2* ts = a.tstate + P.tstart;
+  const bool per_source = a.kind == K_INIT || a.kind == K_BOW_KF_KF || a.kind == K_TRIANG;
+  if (per_source) {
+    for (int i = threadIdx.x; i < a.stride; i += blockDim.x) out[i] = -1;
+    __syncthreads();
+    for (int q = threadIdx.x; q < P.nq; q += blockDim.x) {
+      const int m = qr[q].match;
+      if (m >= 0) {
+        out[qr[q].src] = m;
+        if (a.kind == K_INIT) {  // update of vbPrevMatched, :708-710
+          a.out_xy[((int64_t)p * a.stride + q) * 2] = a.s2.x[P.tbase + m];
+          a.out_xy[((int64_t)p * a.stride + q) * 2 + 1] = a.s2.y[P.tbase + m];
+        }
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < a.stride; i += blockDim.x) out[i] = i < P.nt ? max(ts[i].x, -1) : -1;
+  }
+}
+
+}  // namespace

@@ -1,0 +1,376 @@
+"""Host-side mirror of ORB_SLAM::ORBmatcher (reference include/ORBmatcher.h:37-107) on top of the C ABI of
+include/orbm.h.  Same constructor (nnratio, checkOri), same method names and argument meaning; Frame / KeyFrame objects
+are replaced by :class:`MatchFrame` (flat numpy arrays) uploaded into a device-resident :class:`FrameSet`.
+numpy only owns memory: every distance and every match decision comes from the CUDA kernels.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from ._lib import lib
+
+TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30      # reference src/ORBmatcher.cc:40-42
+FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48        # reference include/Frame.h:35-36
+KEY_NONE = 0xFFFFFFFF
+
+
+class OrbmError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"orbm error {code}: {msg}")
+        self.code = code
+
+
+class _Frame(C.Structure):
+    _fields_ = [("n", C.c_int32), ("x", C.c_void_p), ("y", C.c_void_p), ("angle", C.c_void_p), ("octave", C.c_void_p),
+                ("desc", C.c_void_p), ("valid", C.c_void_p), ("min_x", C.c_float), ("min_y", C.c_float),
+                ("inv_w", C.c_float), ("inv_h", C.c_float)]
+
+
+class _FeatVec(C.Structure):
+    _fields_ = [("nnodes", C.c_int32), ("node_id", C.c_void_p), ("start", C.c_void_p), ("items", C.c_void_p)]
+
+
+class _Points(C.Structure):
+    _fields_ = [("n", C.c_int32), ("u", C.c_void_p), ("v", C.c_void_p), ("radius", C.c_void_p),
+                ("min_level", C.c_void_p), ("max_level", C.c_void_p), ("desc", C.c_void_p), ("angle", C.c_void_p),
+                ("valid", C.c_void_p)]
+
+
+def _bind(L):
+    if getattr(L, "_orbm_bound", False):
+        return L
+    vp, i32, f32 = C.c_void_p, C.c_int32, C.c_float
+    L.orbm_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.orbm_destroy.argtypes = [vp]; L.orbm_destroy.restype = None
+    L.orbm_last_error.argtypes = [vp]; L.orbm_last_error.restype = C.c_char_p
+    L.orbm_kernel_launches.argtypes = [vp]; L.orbm_kernel_launches.restype = C.c_int64
+    L.orbm_last_kernel_ms.argtypes = [vp]; L.orbm_last_kernel_ms.restype = C.c_float
+    L.orbm_descriptor_distance.argtypes = [vp, vp, vp, C.c_int, vp]
+    L.orbm_frameset_create.argtypes = [vp, vp, vp, C.c_int, C.POINTER(vp)]
+    L.orbm_frameset_destroy.argtypes = [vp]; L.orbm_frameset_destroy.restype = None
+    L.orbm_frameset_set_valid.argtypes = [vp, C.c_int, vp]
+    L.orbm_frameset_grid.argtypes = [vp, C.c_int, vp, vp]
+    L.orbm_features_in_area.argtypes = [vp, C.c_int, f32, f32, f32, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
+    L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, C.c_int, vp, vp]
+    L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
+    L.orbm_search_by_projection_frames.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, vp, vp]
+    L.orbm_search_by_projection.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, f32, C.c_int, vp, C.c_int, vp]
+    L.orbm_search_by_bow.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, vp, C.c_int, vp]
+    L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
+    L.orbm_knn2.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp]
+    L.orbm_knn2_device.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp, vp]
+    L.orbm_merge_top2_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, f32, vp, vp, vp]
+    L.orbm_knn2_sharded.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, C.c_int, vp, vp, C.c_int, f32, vp, vp, vp]
+    L._orbm_bound = True
+    return L
+
+
+@dataclass
+class MatchFrame:
+    """What the matcher reads from a Frame / KeyFrame (reference include/Frame.h, include/KeyFrame.h)."""
+    x: np.ndarray            # mvKeysUn[i].pt.x
+    y: np.ndarray
+    angle: np.ndarray        # mvKeysUn[i].angle
+    octave: np.ndarray
+    desc: np.ndarray         # mDescriptors [n,32] uint8
+    valid: np.ndarray | None = None   # per routine: keypoint has a good MapPoint
+    min_x: float = 0.0       # mnMinX, mnMinY, mnMaxX, mnMaxY (Frame::ComputeImageBounds)
+    min_y: float = 0.0
+    max_x: float = 640.0
+    max_y: float = 480.0
+    featvec: tuple | None = None      # (node_id[nn], start[nn+1], items[]) = DBoW2::FeatureVector flattened
+    _keep: list = field(default_factory=list, repr=False)
+
+    def __post_init__(self):
+        self.x = np.ascontiguousarray(self.x, np.float32); self.y = np.ascontiguousarray(self.y, np.float32)
+        self.angle = np.ascontiguousarray(self.angle, np.float32)
+        self.octave = np.ascontiguousarray(self.octave, np.int32)
+        self.desc = np.ascontiguousarray(self.desc, np.uint8).reshape(-1, 32)
+        if self.valid is not None:
+            self.valid = np.ascontiguousarray(self.valid, np.uint8)
+        if self.featvec is not None:
+            self.featvec = tuple(np.ascontiguousarray(a, np.int32) for a in self.featvec)
+
+    @property
+    def n(self):
+        return len(self.x)
+
+    @classmethod
+    def from_keypoints(cls, kps, desc, width, height, **kw):
+        """From the extractor's output (no undistortion: k1 == 0, src/Frame.cc:290-294; bounds :338-344)."""
+        return cls(kps["x"], kps["y"], kps["angle"], kps["octave"], desc, max_x=float(width), max_y=float(height), **kw)
+
+    def grid_inv(self):
+        # mfGridElementWidthInv = (float)FRAME_GRID_COLS / (float)(mnMaxX - mnMinX)   (src/Frame.cc:75-76)
+        iw = np.float32(FRAME_GRID_COLS) / np.float32(np.float32(self.max_x) - np.float32(self.min_x))
+        ih = np.float32(FRAME_GRID_ROWS) / np.float32(np.float32(self.max_y) - np.float32(self.min_y))
+        return float(iw), float(ih)
+
+    def c_struct(self):
+        iw, ih = self.grid_inv()
+        v = self.valid.ctypes.data if self.valid is not None and self.n else None
+        p = lambda a: a.ctypes.data if self.n else None
+        return _Frame(self.n, p(self.x), p(self.y), p(self.angle), p(self.octave), p(self.desc), v, self.min_x,
+                      self.min_y, iw, ih)
+
+    def c_featvec(self):
+        nid, st, it = self.featvec
+        return _FeatVec(len(nid), nid.ctypes.data if len(nid) else None, st.ctypes.data, it.ctypes.data if len(it) else None)
+
+
+class Matcher:
+    """Owns the orbm handle (device, stream, workspaces).  One per host thread."""
+
+    def __init__(self, device=0):
+        self._L = _bind(lib())
+        self._h = C.c_void_p()
+        rc = self._L.orbm_create(device, C.byref(self._h))
+        if rc != 0:
+            self._h = None
+            raise OrbmError(rc, (self._L.orbm_last_error(None) or b"").decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbm_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc != 0:
+            raise OrbmError(rc, (self._L.orbm_last_error(self._h) or b"").decode())
+
+    def kernel_launches(self):
+        return int(self._L.orbm_kernel_launches(self._h))
+
+    def last_kernel_ms(self):
+        return float(self._L.orbm_last_kernel_ms(self._h))
+
+    def upload(self, frames):
+        return FrameSet(self, frames)
+
+    # M1
+    def descriptor_distance(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32); b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+        assert a.shape == b.shape
+        out = np.empty(len(a), np.int32)
+        self._check(self._L.orbm_descriptor_distance(self._h, a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data))
+        return out
+
+    # M8
+    def knn2(self, q, db, idx_base=0):
+        q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32); db = np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
+        out = np.empty((len(q), 2), np.uint32)
+        self._check(self._L.orbm_knn2(self._h, q.ctypes.data, len(q), db.ctypes.data, len(db), idx_base, out.ctypes.data))
+        return out
+
+    def knn2_device(self, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream=None):
+        self._check(self._L.orbm_knn2_device(self._h, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream))
+
+    def merge_top2_device(self, gathered_ptr, nshards, nq, th_dist, ratio, top2_ptr, match_ptr, stream=None):
+        self._check(self._L.orbm_merge_top2_device(self._h, gathered_ptr, nshards, nq, th_dist, ratio, top2_ptr,
+                                                   match_ptr, stream))
+
+
+class FrameSet:
+    """Frames resident on the device with their 64x48 grids (reference src/Frame.cc:108-122)."""
+
+    def __init__(self, matcher: Matcher, frames):
+        self.m = matcher
+        self.frames = list(frames)
+        self._L = matcher._L
+        arr = (_Frame * len(self.frames))(*[f.c_struct() for f in self.frames])
+        fvs = None
+        if all(f.featvec is not None for f in self.frames):
+            fvs = (_FeatVec * len(self.frames))(*[f.c_featvec() for f in self.frames])
+        self._s = C.c_void_p()
+        matcher._check(self._L.orbm_frameset_create(matcher._h, arr, fvs, len(self.frames), C.byref(self._s)))
+        self.max_n = max(f.n for f in self.frames)
+
+    def close(self):
+        if getattr(self, "_s", None) and getattr(self.m, "_h", None):
+            self._L.orbm_frameset_destroy(self._s)
+        self._s = None
+
+    __del__ = close
+
+    def set_valid(self, frame, valid):
+        v = None if valid is None else np.ascontiguousarray(valid, np.uint8)
+        self.m._check(self._L.orbm_frameset_set_valid(self._s, frame, None if v is None else v.ctypes.data))
+
+    def grid(self, frame):
+        cs = np.zeros(FRAME_GRID_COLS * FRAME_GRID_ROWS + 1, np.int32)
+        items = np.zeros(max(self.frames[frame].n, 1), np.int32)
+        self.m._check(self._L.orbm_frameset_grid(self._s, frame, cs.ctypes.data, items.ctypes.data))
+        return cs, items[: cs[-1]]
+
+    def features_in_area(self, frame, x, y, r, min_level=-1, max_level=-1):
+        cap = max(self.frames[frame].n, 1)
+        out = np.zeros(cap, np.int32)
+        n = C.c_int(0)
+        self.m._check(self._L.orbm_features_in_area(self._s, frame, x, y, r, min_level, max_level, out.ctypes.data, cap,
+                                                    C.byref(n)))
+        return out[: n.value].copy()
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, np.int32)
+
+
+@dataclass
+class ProjectedPoints:
+    """Map points projected into a target frame (the SearchByProjection family)."""
+    u: np.ndarray
+    v: np.ndarray
+    radius: np.ndarray
+    min_level: np.ndarray
+    max_level: np.ndarray
+    desc: np.ndarray
+    angle: np.ndarray | None = None
+    valid: np.ndarray | None = None
+
+    def __post_init__(self):
+        f = lambda a: np.ascontiguousarray(a, np.float32)
+        self.u, self.v, self.radius = f(self.u), f(self.v), f(self.radius)
+        self.min_level, self.max_level = _i32(self.min_level), _i32(self.max_level)
+        self.desc = np.ascontiguousarray(self.desc, np.uint8).reshape(-1, 32)
+        if self.angle is not None:
+            self.angle = f(self.angle)
+        if self.valid is not None:
+            self.valid = np.ascontiguousarray(self.valid, np.uint8)
+
+    @property
+    def n(self):
+        return len(self.u)
+
+    def c_struct(self):
+        p = lambda a: a.ctypes.data if a is not None and self.n else None
+        return _Points(self.n, p(self.u), p(self.v), p(self.radius), p(self.min_level), p(self.max_level), p(self.desc),
+                       p(self.angle), p(self.valid))
+
+    @classmethod
+    def for_local_map(cls, proj_x, proj_y, view_cos, level, desc, scale_factors, th=1.0, valid=None):
+        """Radius and level window of SearchByProjection(Frame&, vector<MapPoint*>&, th), src/ORBmatcher.cc:53-73,
+        RadiusByViewingCos :127-133."""
+        view_cos = np.asarray(view_cos, np.float32)
+        level = _i32(level)
+        r = np.where(view_cos.astype(np.float64) > 0.998, np.float32(2.5), np.float32(4.0)).astype(np.float32)
+        if th != 1.0:
+            r = (r * np.float32(th)).astype(np.float32)
+        radius = (r * np.asarray(scale_factors, np.float32)[level]).astype(np.float32)
+        return cls(proj_x, proj_y, radius, level - 1, level, desc, None, valid)
+
+    @classmethod
+    def for_last_frame(cls, u, v, octave, desc, angle, scale_factors, th, valid=None):
+        """SearchByProjection(CurrentFrame, LastFrame, th), src/ORBmatcher.cc:1545-1550."""
+        octave = _i32(octave)
+        radius = (np.float32(th) * np.asarray(scale_factors, np.float32)[octave]).astype(np.float32)
+        return cls(u, v, radius, octave - 1, octave + 1, desc, angle, valid)
+
+
+class ORBmatcher:
+    """ORB_SLAM::ORBmatcher(nnratio = 0.6, checkOri = true), include/ORBmatcher.h:41.  Every Search* method takes
+    frame sets and lists of frame pairs (batched); a single pair is a list of length one."""
+
+    TH_HIGH, TH_LOW, HISTO_LENGTH = TH_HIGH, TH_LOW, HISTO_LENGTH
+
+    def __init__(self, nnratio=0.6, checkOri=True, *, matcher: Matcher | None = None, device=0):
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self.m = matcher or Matcher(device)
+        self._L = self.m._L
+
+    def upload(self, frames):
+        return self.m.upload(frames)
+
+    # static int DescriptorDistance(const cv::Mat&, const cv::Mat&), include/ORBmatcher.h:44
+    def DescriptorDistance(self, a, b):
+        d = self.m.descriptor_distance(a, b)
+        return int(d[0]) if len(d) == 1 else d
+
+    def _pairs(self, idx1, idx2):
+        i1, i2 = _i32(np.atleast_1d(idx1)), _i32(np.atleast_1d(idx2))
+        assert i1.shape == i2.shape
+        return i1, i2
+
+    def SearchForInitialization(self, set1: FrameSet, set2: FrameSet, idx1, idx2, vbPrevMatched, windowSize=10):
+        """src/ORBmatcher.cc:598-713.  vbPrevMatched: list (per pair) of [n1,2] float arrays, updated in place.
+        Returns (nmatches[np], vnMatches12 rows [np, stride])."""
+        i1, i2 = self._pairs(idx1, idx2)
+        stride = max(set1.max_n, 1)
+        xy = np.zeros((len(i1), stride, 2), np.float32)
+        for p, a in enumerate(vbPrevMatched):
+            xy[p, : len(a)] = a
+        out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
+        self.m._check(self._L.orbm_search_for_initialization(self.m._h, set1._s, set2._s, i1.ctypes.data, i2.ctypes.data,
+                                                             len(i1), xy.ctypes.data, stride, int(windowSize),
+                                                             self.mfNNratio, int(self.mbCheckOrientation),
+                                                             out.ctypes.data, nm.ctypes.data))
+        for p, a in enumerate(vbPrevMatched):
+            a[...] = xy[p, : len(a)]
+        return nm, out
+
+    def WindowSearch(self, set1, set2, idx1, idx2, windowSize, minScaleLevel=0, maxScaleLevel=2**31 - 1):
+        """src/ORBmatcher.cc:409-516.  Returns (nmatches, rows[i2] = i1)."""
+        i1, i2 = self._pairs(idx1, idx2)
+        stride = max(set2.max_n, 1)
+        out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
+        self.m._check(self._L.orbm_window_search(self.m._h, set1._s, set2._s, i1.ctypes.data, i2.ctypes.data, len(i1),
+                                                 int(windowSize), self.mfNNratio, int(self.mbCheckOrientation),
+                                                 int(minScaleLevel), int(maxScaleLevel), out.ctypes.data, stride,
+                                                 nm.ctypes.data))
+        return nm, out
+
+    def SearchByProjectionFrames(self, set1, set2, idx1, idx2, uv, windowSize):
+        """SearchByProjection(Frame&, Frame&, windowSize, ...), src/ORBmatcher.cc:519-594; uv: per pair [n1,2]."""
+        i1, i2 = self._pairs(idx1, idx2)
+        stride = max(set1.max_n, set2.max_n, 1)
+        xy = np.zeros((len(i1), stride, 2), np.float32)
+        for p, a in enumerate(uv):
+            xy[p, : len(a)] = a
+        out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
+        self.m._check(self._L.orbm_search_by_projection_frames(self.m._h, set1._s, set2._s, i1.ctypes.data,
+                                                               i2.ctypes.data, len(i1), xy.ctypes.data, stride,
+                                                               int(windowSize), self.mfNNratio, out.ctypes.data,
+                                                               nm.ctypes.data))
+        return nm, out
+
+    def SearchByProjection(self, fset, idx, points, variant="local_map", th_dist=TH_HIGH):
+        """Projected-point scoring: variant 'local_map' (src/ORBmatcher.cc:49-125) or 'best' (:1507-1620, :1622-1746,
+        :286-407).  points: list of ProjectedPoints, one per problem.  Returns (nmatches, rows[idx] = point)."""
+        ii = _i32(np.atleast_1d(idx))
+        arr = (_Points * len(points))(*[p.c_struct() for p in points])
+        stride = max(fset.max_n, 1)
+        out = np.empty((len(ii), stride), np.int32); nm = np.empty(len(ii), np.int32)
+        v = 0 if variant == "local_map" else 1
+        self.m._check(self._L.orbm_search_by_projection(self.m._h, fset._s, ii.ctypes.data, arr, len(ii), v,
+                                                        int(th_dist), self.mfNNratio, int(self.mbCheckOrientation),
+                                                        out.ctypes.data, stride, nm.ctypes.data))
+        return nm, out
+
+    def SearchByBoW(self, set1, set2, idx1, idx2, variant="kf_f"):
+        """'kf_f': SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:155-284, rows[idxF] = idxKF;
+        'kf_kf': SearchByBoW(KeyFrame*, KeyFrame*, ...) :715-850, rows[idx1] = idx2."""
+        i1, i2 = self._pairs(idx1, idx2)
+        stride = max(set1.max_n, set2.max_n, 1)
+        out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
+        self.m._check(self._L.orbm_search_by_bow(self.m._h, set1._s, set2._s, i1.ctypes.data, i2.ctypes.data, len(i1),
+                                                 0 if variant == "kf_f" else 1, self.mfNNratio,
+                                                 int(self.mbCheckOrientation), out.ctypes.data, stride, nm.ctypes.data))
+        return nm, out
+
+    def SearchForTriangulation(self, set1, set2, idx1, idx2, F12, sigma2):
+        """src/ORBmatcher.cc:852-1014; F12: [np,3,3] float32, sigma2: per-level.  rows[idx1] = idx2."""
+        i1, i2 = self._pairs(idx1, idx2)
+        F = np.ascontiguousarray(F12, np.float32).reshape(len(i1), 9)
+        s2 = np.ascontiguousarray(sigma2, np.float32)
+        stride = max(set1.max_n, 1)
+        out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
+        self.m._check(self._L.orbm_search_for_triangulation(self.m._h, set1._s, set2._s, i1.ctypes.data, i2.ctypes.data,
+                                                            len(i1), F.ctypes.data, s2.ctypes.data, len(s2),
+                                                            int(self.mbCheckOrientation), out.ctypes.data, stride,
+                                                            nm.ctypes.data))
+        return nm, out

@@ -1,0 +1,220 @@
+"""Parity of the CUDA matcher (through the C ABI, include/orbm.h) with the CPU oracle.  Everything is integer / index
+work, so every comparison is bit-exact (match indices, counts, updated vbPrevMatched, packed 2-NN keys)."""
+import numpy as np
+import pytest
+
+import matchdata as MD
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def M(oracle):
+    from oracle import match_oracle
+    match_oracle.lib()
+    return match_oracle
+
+
+@pytest.fixture(scope="module")
+def matcher():
+    from orb_slam_b200 import Matcher
+    return Matcher(0)
+
+
+@pytest.fixture(scope="module")
+def pairs(oracle):
+    """6 frame pairs: 640x480/1000 kp, the 2000-kp initialisation extractor, a small odd size."""
+    out = [MD.make_pair(oracle, s) for s in (0, 1, 2)]
+    out.append(MD.make_pair(oracle, 3, 640, 480, 2000))
+    out.append(MD.make_pair(oracle, 4, 333, 251, 700))
+    out.append(MD.make_pair(oracle, 5, 640, 480, 1000, shift=(0, 0)))
+    return out
+
+
+def _rows_equal(row, ref):
+    return np.array_equal(row[: len(ref)], ref) and np.all(row[len(ref):] == -1)
+
+
+def test_descriptor_distance(M, matcher):
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (5000, 32), dtype=np.uint8); b = rng.integers(0, 256, (5000, 32), dtype=np.uint8)
+    b[:10] = a[:10]; b[10] = ~a[10]
+    got = matcher.descriptor_distance(a, b)
+    ref = np.unpackbits(a ^ b, axis=1).sum(1)
+    assert np.array_equal(got, ref) and got[10] == 256 and got[0] == 0
+    assert all(int(got[i]) == M.descriptor_distance(a[i], b[i]) for i in range(0, 5000, 97))
+
+
+def test_grid_and_area(M, matcher, pairs):
+    frames = [p[1] for p in pairs]
+    fs = matcher.upload([MD.to_matchframe(f) for f in frames])
+    rng = np.random.default_rng(1)
+    for k, f in enumerate(frames):
+        cs, items = fs.grid(k)
+        ocs, oitems = M.grid_csr(f)
+        assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
+        for _ in range(40):
+            x, y, r = float(rng.uniform(-30, f.max_x + 30)), float(rng.uniform(-30, f.max_y + 30)), float(rng.uniform(0.5, 120))
+            mode = int(rng.integers(0, 3))
+            lv = (-1, -1) if mode == 0 else ((1, 1) if mode == 1 else (int(rng.integers(-1, 3)), int(rng.integers(3, 7))))
+            assert np.array_equal(fs.features_in_area(k, x, y, r, *lv), M.features_in_area(f, x, y, r, *lv))
+
+
+@pytest.mark.parametrize("ori", [True, False])
+def test_search_for_initialization(M, matcher, pairs, ori):
+    from orb_slam_b200 import ORBmatcher
+    om = ORBmatcher(0.9, ori, matcher=matcher)
+    s1 = om.upload([MD.to_matchframe(p[0]) for p in pairs]); s2 = om.upload([MD.to_matchframe(p[1]) for p in pairs])
+    idx = list(range(len(pairs)))
+    prev = [np.stack([p[0].x, p[0].y], 1).astype(np.float32) for p in pairs]
+    oprev = [a.copy() for a in prev]
+    nm, rows = om.SearchForInitialization(s1, s2, idx, idx, prev, 100)
+    total = 0
+    for k, (f1, f2, _) in enumerate(pairs):
+        on, om12 = M.search_for_initialization(f1, f2, oprev[k], 100, 0.9, ori)
+        assert nm[k] == on and _rows_equal(rows[k], om12), f"pair {k}"
+        assert np.array_equal(prev[k], oprev[k])
+        total += on
+    assert total > 300
+    # second call continues from the updated vbPrevMatched with a smaller window (as the tracker would)
+    nm2, rows2 = om.SearchForInitialization(s1, s2, idx, idx, prev, 20)
+    for k, (f1, f2, _) in enumerate(pairs):
+        on, om12 = M.search_for_initialization(f1, f2, oprev[k], 20, 0.9, ori)
+        assert nm2[k] == on and _rows_equal(rows2[k], om12) and np.array_equal(prev[k], oprev[k])
+
+
+def test_window_search_and_projection_frames(M, matcher, pairs):
+    from orb_slam_b200 import ORBmatcher
+    fr1 = [MD.with_valid(p[0], MD.random_valid(p[0].n, 0.6, 10 + k)) for k, p in enumerate(pairs)]
+    fr2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.2, 20 + k)) for k, p in enumerate(pairs)]
+    s1 = matcher.upload([MD.to_matchframe(f) for f in fr1]); s2 = matcher.upload([MD.to_matchframe(f) for f in fr2])
+    idx = list(range(len(pairs)))
+    for (win, ratio, ori, lo, hi) in [(200, 0.8, True, 0, 2**31 - 1), (100, 0.9, False, 1, 3), (50, 0.7, True, 0, 0)]:
+        om = ORBmatcher(ratio, ori, matcher=matcher)
+        nm, rows = om.WindowSearch(s1, s2, idx, idx, win, lo, hi)
+        for k in idx:
+            on, orow = M.window_search(fr1[k], fr2[k], win, ratio, ori, lo, hi)
+            assert nm[k] == on and _rows_equal(rows[k], orow), (win, k)
+        assert nm.sum() > 100
+    om = ORBmatcher(0.9, True, matcher=matcher)
+    for win in (15, 50):
+        uv = [np.stack([f.x + np.float32(p[2][0] * -1.0) + 1.5, f.y - np.float32(p[2][1]) - 0.75], 1).astype(np.float32)
+              for f, p in zip(fr1, pairs)]
+        nm, rows = om.SearchByProjectionFrames(s1, s2, idx, idx, uv, win)
+        for k in idx:
+            on, orow = M.search_by_projection_ff(fr1[k], fr2[k], uv[k], win, 0.9)
+            assert nm[k] == on and _rows_equal(rows[k], orow), (win, k)
+        assert nm.sum() > 100
+
+
+def _points_from(f1, shift, rng, kind, scale_factors):
+    from orb_slam_b200 import ProjectedPoints
+    n = f1.n
+    u = (f1.x - np.float32(shift[0]) + rng.uniform(-2, 2, n)).astype(np.float32)
+    v = (f1.y - np.float32(shift[1]) + rng.uniform(-2, 2, n)).astype(np.float32)
+    valid = (rng.random(n) < 0.8).astype(np.uint8)
+    if kind == "local_map":
+        cos = rng.uniform(0.99, 1.0, n).astype(np.float32)
+        return ProjectedPoints.for_local_map(u, v, cos, f1.octave, f1.desc, scale_factors, th=float(rng.choice([1.0, 5.0])),
+                                             valid=valid)
+    return ProjectedPoints.for_last_frame(u, v, f1.octave, f1.desc, f1.angle, scale_factors, 15.0, valid=valid)
+
+
+@pytest.mark.parametrize("variant,ratio,ori,th", [("local_map", 0.8, False, 100), ("best", 0.9, True, 100),
+                                                  ("best", 0.9, False, 50)])
+def test_search_by_projection(M, matcher, pairs, variant, ratio, ori, th):
+    from orb_slam_b200 import ORBmatcher
+    sf = np.cumprod(np.concatenate([[1.0], np.full(7, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    rng = np.random.default_rng(5)
+    fr2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.15, 30 + k)) for k, p in enumerate(pairs)]
+    s2 = matcher.upload([MD.to_matchframe(f) for f in fr2])
+    pts = [_points_from(p[0], p[2], rng, variant, sf) for p in pairs]
+    om = ORBmatcher(ratio, ori, matcher=matcher)
+    idx = list(range(len(pairs)))
+    nm, rows = om.SearchByProjection(s2, idx, pts, variant, th)
+    for k in idx:
+        on, orow = M.search_by_projection(fr2[k], pts[k], variant, th, ratio, ori)
+        assert nm[k] == on and _rows_equal(rows[k], orow), k
+    assert nm.sum() > 200
+
+
+@pytest.mark.parametrize("variant,ratio,ori", [("kf_f", 0.75, True), ("kf_f", 0.6, False), ("kf_kf", 0.75, True)])
+def test_search_by_bow(M, matcher, pairs, variant, ratio, ori):
+    from orb_slam_b200 import ORBmatcher
+    fr1 = [MD.with_valid(p[0], MD.random_valid(p[0].n, 0.7, 40 + k)) for k, p in enumerate(pairs)]
+    fr2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.8, 50 + k)) for k, p in enumerate(pairs)]
+    s1 = matcher.upload([MD.to_matchframe(f) for f in fr1]); s2 = matcher.upload([MD.to_matchframe(f) for f in fr2])
+    om = ORBmatcher(ratio, ori, matcher=matcher)
+    # also cross pairs (k, k+1): mostly non-matching content
+    i1 = list(range(len(pairs))) + [0, 1]
+    i2 = list(range(len(pairs))) + [1, 2]
+    nm, rows = om.SearchByBoW(s1, s2, i1, i2, variant)
+    for p, (a, b) in enumerate(zip(i1, i2)):
+        on, orow = M.search_by_bow(fr1[a], fr2[b], variant, ratio, ori)
+        assert nm[p] == on and _rows_equal(rows[p], orow), (variant, p)
+    assert nm[: len(pairs)].sum() > 100
+
+
+@pytest.mark.parametrize("ori", [True, False])
+def test_search_for_triangulation(M, matcher, pairs, ori):
+    from orb_slam_b200 import ORBmatcher
+    fr1 = [MD.with_valid(p[0], MD.random_valid(p[0].n, 0.3, 60 + k)) for k, p in enumerate(pairs)]
+    fr2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.3, 70 + k)) for k, p in enumerate(pairs)]
+    s1 = matcher.upload([MD.to_matchframe(f) for f in fr1]); s2 = matcher.upload([MD.to_matchframe(f) for f in fr2])
+    sf = np.cumprod(np.concatenate([[1.0], np.full(7, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    sigma2 = (sf * sf).astype(np.float32)
+    # fundamental matrix of a pure image translation (dx, dy): the epipolar line of x1 passes through x1 - shift
+    F12 = []
+    for p in pairs:
+        dx, dy = p[2]
+        t = np.array([dx, dy, 0.0]) + 1e-3
+        F12.append(np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]], np.float32) * np.float32(0.05))
+    om = ORBmatcher(0.6, ori, matcher=matcher)
+    idx = list(range(len(pairs)))
+    nm, rows = om.SearchForTriangulation(s1, s2, idx, idx, np.stack(F12), sigma2)
+    for k in idx:
+        on, orow = M.search_for_triangulation(fr1[k], fr2[k], F12[k], sigma2, ori)
+        assert nm[k] == on and _rows_equal(rows[k], orow), k
+    assert nm.sum() > 50
+
+
+def test_knn2(M, matcher):
+    rng = np.random.default_rng(11)
+    for nq, ndb in [(1000, 20000), (300, 5000), (37, 129), (600, 1), (5, 4097)]:
+        db = rng.integers(0, 256, (ndb, 32), dtype=np.uint8)
+        q = db[rng.integers(0, ndb, nq)].copy()
+        flip = rng.random((nq, 256)) < 0.1
+        q ^= np.packbits(flip, axis=1)
+        if ndb > 100:
+            db[77] = db[33]; q[0] = db[33]  # duplicate: lowest index wins, duplicate is the second best
+        got = matcher.knn2(q, db, idx_base=1000)
+        ref = M.knn2(q, db, idx_base=1000, threads=8)
+        assert np.array_equal(got, ref), (nq, ndb)
+    assert matcher.last_kernel_ms() > 0
+
+
+def test_knn2_sharded_merge_single_gpu(M, matcher):
+    """The multi-GPU merge path on one device: 4 database shards searched separately, results laid out like the
+    all-gather receive buffer, merged by orbm_merge_top2_device == one search over the whole database."""
+    import torch
+    rng = np.random.default_rng(12)
+    ndb, nq, shards = 40000, 1000, 4
+    db = rng.integers(0, 256, (ndb, 32), dtype=np.uint8)
+    q = db[rng.integers(0, ndb, nq)].copy()
+    q ^= np.packbits(rng.random((nq, 256)) < 0.08, axis=1)
+    d_db = torch.from_numpy(db).cuda(); d_q = torch.from_numpy(q).cuda()
+    gathered = torch.empty((shards, nq, 2), dtype=torch.int32, device="cuda")
+    per = ndb // shards
+    s = torch.cuda.current_stream().cuda_stream
+    for r in range(shards):
+        matcher.knn2_device(d_q.data_ptr(), nq, d_db[r * per:].data_ptr(), per, r * per, gathered[r].data_ptr(), s)
+    top2 = torch.empty((nq, 2), dtype=torch.int32, device="cuda"); match = torch.empty(nq, dtype=torch.int32, device="cuda")
+    matcher.merge_top2_device(gathered.data_ptr(), shards, nq, 50, 0.75, top2.data_ptr(), match.data_ptr(), s)
+    torch.cuda.synchronize()
+    ref = M.knn2(q, db, threads=8)
+    got = top2.cpu().numpy().view(np.uint32)
+    assert np.array_equal(got, ref)
+    bd, sd = (ref[:, 0] >> 23).astype(np.int64), (ref[:, 1] >> 23).astype(np.int64)
+    ok = (bd <= 50) & (bd.astype(np.float32) < np.float32(0.75) * sd.astype(np.float32))
+    exp = np.where(ok, (ref[:, 0] & 0x7FFFFF).astype(np.int64), -1)
+    assert np.array_equal(match.cpu().numpy(), exp) and ok.sum() > 500
