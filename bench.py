@@ -142,6 +142,9 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=0, help="cpu_baseline sample (0 = auto ~15 s)")
     ap.add_argument("--ref-frames", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-matching", action="store_true", help="skip the Hamming-matching legs")
+    ap.add_argument("--query-keyframes", type=int, default=8, help="config 5: query keyframes (x1000 descriptors) per step")
+    ap.add_argument("--match-pairs", type=int, default=256, help="config 4: frame pairs per GPU per step")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -260,6 +263,26 @@ def main():
         threads = os.cpu_count() or 1
         ncpu = args.cpu_frames or max(64, min(F, 8 * threads * 4))
         cpu = cpu_baseline(min(ncpu, F), threads, h_frames.numpy())
+    matching = None
+    if not args.no_matching:
+        import bench_matching as BM
+        from orb_slam_b200 import Matcher
+        del d_kps, d_desc, h_kps, h_desc
+        mt = Matcher(local)
+        s2 = ClockSampler(local) if rank == 0 else None
+        tk0 = time.time()
+        knn = BM.bench_knn2(args, rank, world, dev, mt, None)
+        tk1 = time.time()
+        kclk = s2.stop(tk0, tk1) if s2 else None
+        if kclk and kclk.get("sm_mhz"):
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            peak = sms * BM.POPC_PER_CLK_PER_SM * kclk["sm_mhz"] * 1e6 * world
+            knn["roofline"].update({"peak": peak / 1e12, "frac": knn["value"] * 8 / peak, "clock_mhz_assumed": kclk["sm_mhz"]})
+            knn["clocks"] = kclk
+        init = BM.bench_init_search(args, rank, world, dev, local, mt)
+        if rank == 0 and not args.no_cpu:
+            knn["cpu_baseline"] = BM.bench_knn2_cpu(args)
+        matching = {"knn2_all_pairs": knn, "search_for_initialization": init}
     if world > 1:
         dist.barrier()
     if rank == 0:
@@ -277,7 +300,8 @@ def main():
             "e2e": {"value": total / (e2e_ms * 1e-3), "unit": "frames/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": F * H * W, "d2h_bytes_per_step": F * (NFEAT * 60 + 4),
                     "api": "orbx_extract_batch (C ABI, pinned host buffers), wall clock between device syncs"},
-            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks}))
+            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+            "matching": matching}))
     if world > 1:
         dist.destroy_process_group()
 

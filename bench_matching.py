@@ -1,0 +1,195 @@
+"""Matching legs of bench.py (BASELINE.json metric, second half: "Hamming matches/s").
+
+config 5  all-pairs 2-NN: 5,000 keyframes x 1,000 descriptors (5 M x 256 bit), database sharded by keyframe over the
+          ranks (STRONG scaling: the database is fixed), queries replicated, one ncclAllGather of the packed per-shard
+          top-2 keys + merge kernel per query batch (orbm_knn2_sharded).
+config 4  SearchForInitialization (window 100, ratio 0.9, orientation check) on 1000-keypoint frame pairs cut from
+          shifted synthetic images and extracted by the CUDA extractor; batched over all pairs.
+Returns a dict that bench.py embeds under "matching" in its single JSON line.
+"""
+from __future__ import annotations
+
+import os
+import time
+
+import numpy as np
+
+DB_KEYFRAMES, KP_PER_KF = 5000, 1000
+# 8 x XOR32 + 8 x POPC32 per descriptor pair; POPC issues 16 lanes/clk/SM on sm_100
+# (tools/popc_microbench.cu, measured on this pool's B200: 0.50 warp-POPC/clk/SM)
+POPC_PER_CLK_PER_SM = 16.0
+
+
+def bench_knn2(args, rank, world, dev, matcher, clocks_mhz):
+    import torch
+    import torch.distributed as dist
+    from orb_slam_b200 import ShardedKnn2, shard_range
+
+    kf0, kf1 = shard_range(DB_KEYFRAMES, rank, world)
+    ndb = (kf1 - kf0) * KP_PER_KF
+    g = torch.Generator(device=dev); g.manual_seed(12345 + rank)
+    db = torch.randint(0, 256, (ndb, 32), dtype=torch.uint8, device=dev, generator=g)
+    nq = args.query_keyframes * KP_PER_KF
+    # queries: descriptors of the (replicated) first keyframes of rank 0's shard + 10 % bit flips; same on all ranks
+    gq = torch.Generator(device=dev); gq.manual_seed(999)
+    q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=gq)
+    if world > 1:
+        dist.broadcast(q, 0)
+    gathered = torch.empty((world, nq, 2), dtype=torch.int32, device=dev)
+    top2 = torch.empty((nq, 2), dtype=torch.int32, device=dev)
+    match = torch.empty(nq, dtype=torch.int32, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    sh = ShardedKnn2.from_torch_distributed(matcher, dev) if world > 1 else None
+
+    def step():
+        if sh is not None:
+            sh.search(q.data_ptr(), nq, db.data_ptr(), ndb, kf0 * KP_PER_KF, gathered.data_ptr(), top2.data_ptr(),
+                      match.data_ptr(), 50, 0.75, stream.cuda_stream)
+        else:
+            matcher.knn2_device(q.data_ptr(), nq, db.data_ptr(), ndb, 0, gathered.data_ptr(), stream.cuda_stream)
+            matcher.merge_top2_device(gathered.data_ptr(), 1, nq, 50, 0.75, top2.data_ptr(), match.data_ptr(),
+                                      stream.cuda_stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    l0 = matcher.kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    launches = matcher.kernel_launches() - l0
+    pairs = float(nq) * DB_KEYFRAMES * KP_PER_KF
+    pps = pairs / (ms * 1e-3)
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    mhz = clocks_mhz or 1965.0
+    popc_peak = sms * POPC_PER_CLK_PER_SM * mhz * 1e6 * world
+    out = {"metric": "Hamming distance evaluations/s (all-pairs 2-NN, 5k keyframes x 1000 descriptors)",
+           "value": pps, "unit": "pairs/s", "ms_per_step": ms, "queries_per_step": nq, "db_descriptors": DB_KEYFRAMES * KP_PER_KF,
+           "scaling": "strong", "shard_descriptors_per_gpu": ndb, "gpu_launches": launches,
+           "collective": "ncclAllGather of [nq,2] u32 keys per step" if world > 1 else "none (1 GPU)",
+           "roofline": {"bound": "popc issue rate", "achieved": pps * 8 / 1e12, "peak": popc_peak / 1e12,
+                        "unit": "T popc32/s (8 per pair, algorithmic; the kernel issues 5 after carry-save compression)",
+                        "frac": pps * 8 / popc_peak, "clock_mhz_assumed": mhz,
+                        "peak_source": "16 POPC lanes/clk/SM measured by tools/popc_microbench.cu x SMs x SM clock under load"},
+           "db_bytes_read_per_step": float(ndb) * 32 * ((nq + 1023) // 1024)}
+    if sh is not None:
+        sh.close()
+    return out
+
+
+def make_pairs(npairs, dev, local):
+    """Frame pairs for config 4: two 640x480 windows of one 704x544 synthetic image, offset by (dx, dy)."""
+    import torch
+    from orb_slam_b200 import MatchFrame, ORBextractor, synth_frames_device
+    W, H, BW, BH = 640, 480, 704, 544
+    big = torch.empty((npairs, BH, BW), dtype=torch.uint8, device=dev)
+    synth_frames_device(big.data_ptr(), npairs, BW, BH, BW, BH * BW, seed0=50_000)
+    torch.cuda.synchronize()
+    rng = np.random.default_rng(4)
+    sh = rng.integers(-30, 31, (npairs, 2))
+    a = big[:, 32:32 + H, 32:32 + W].contiguous()
+    b = torch.stack([big[p, 32 + sh[p, 1]:32 + sh[p, 1] + H, 32 + sh[p, 0]:32 + sh[p, 0] + W] for p in range(npairs)]).contiguous()
+    ex = ORBextractor(1000, 1.2, 8, 1, 20, max_width=W, max_height=H, max_batch=min(npairs, 128), device=local)
+    ka, da, na = ex.extract_batch(a.cpu().numpy())
+    kb, db, nb = ex.extract_batch(b.cpu().numpy())
+    f1 = [MatchFrame.from_keypoints(ka[p, :na[p]], da[p, :na[p]], W, H) for p in range(npairs)]
+    f2 = [MatchFrame.from_keypoints(kb[p, :nb[p]], db[p, :nb[p]], W, H) for p in range(npairs)]
+    ex.close()
+    return f1, f2
+
+
+def bench_init_search(args, rank, world, dev, local, matcher):
+    import torch
+    import torch.distributed as dist
+    from orb_slam_b200 import ORBmatcher
+    npairs = args.match_pairs
+    f1, f2 = make_pairs(npairs, dev, local)
+    om = ORBmatcher(0.9, True, matcher=matcher)
+    s1, s2 = om.upload(f1), om.upload(f2)
+    idx = np.arange(npairs, dtype=np.int32)
+    prev0 = [np.stack([f.x, f.y], 1).astype(np.float32) for f in f1]  # vbPrevMatched = F1 keypoints (Tracking.cc:334-336)
+
+    def step():
+        prev = [p.copy() for p in prev0]
+        return om.SearchForInitialization(s1, s2, idx, idx, prev, 100)
+
+    for _ in range(3):
+        nm, rows = step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t = time.perf_counter(); kms = 0.0
+    for _ in range(args.steps):
+        nm, rows = step()
+        kms += matcher.last_kernel_ms()
+    e2e_ms = (time.perf_counter() - t) * 1e3 / args.steps
+    kms /= args.steps
+    if world > 1:
+        tt = torch.tensor([e2e_ms, kms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms, kms = float(tt[0].item()), float(tt[1].item())
+    out = {"metric": "SearchForInitialization frame pairs/s (1000-kp pairs, window 100, ratio 0.9)",
+           "value": npairs * world / (kms * 1e-3), "unit": "pairs/s", "kernel_ms_per_step": kms,
+           "e2e": {"value": npairs * world / (e2e_ms * 1e-3), "unit": "pairs/s", "ms_per_step": e2e_ms,
+                   "note": "host prev_xy in, matches out through the C ABI; frame sets resident"},
+           "pairs_per_gpu": npairs, "mean_matches_per_pair": float(nm.mean()), "scaling": "weak"}
+    if rank == 0 and not args.no_cpu:
+        from oracle import match_oracle as MO
+        import ctypes as C
+        L = MO.lib(True)
+        n = min(npairs, 64)
+        h1 = [MO.frame_struct(f) for f in f1[:n]]; h2 = [MO.frame_struct(f) for f in f2[:n]]
+        A1 = (MO._Frame * n)(*[h.s for h in h1]); A2 = (MO._Frame * n)(*[h.s for h in h2])
+        stride = max(f.n for f in f1[:n])
+        threads = os.cpu_count() or 1
+
+        def cpu(nthreads):
+            xy = np.zeros((n, stride, 2), np.float32)
+            for p in range(n):
+                xy[p, :f1[p].n] = prev0[p]
+            m = np.empty((n, stride), np.int32); cnt = np.empty(n, np.int32)
+            t0 = time.perf_counter()
+            L.mo_search_for_initialization_many(A1, A2, n, xy.ctypes.data, stride, 100, 0.9, 1, m.ctypes.data,
+                                                cnt.ctypes.data, nthreads)
+            return n / (time.perf_counter() - t0), m, cnt
+
+        cpu(threads)
+        v, m, cnt = cpu(threads)
+        v1, _, _ = cpu(1)
+        ok = all(np.array_equal(rows[p, :f1[p].n], m[p, :f1[p].n]) and nm[p] == cnt[p] for p in range(n))
+        out["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": threads, "kind": "port", "single_thread_value": v1,
+                               "sample": f"{n} of the same pairs, oracle/liborb_oracle_fast.so", "gpu_equals_cpu": bool(ok)}
+    return out
+
+
+def bench_knn2_cpu(args):
+    """Bounded CPU sample of config 5: 64 queries against a 200k-descriptor slice, all host threads."""
+    from oracle import match_oracle as MO
+    rng = np.random.default_rng(12345)
+    db = rng.integers(0, 256, (200_000, 32), dtype=np.uint8)
+    threads = os.cpu_count() or 1
+    q = rng.integers(0, 256, (max(64, 4 * threads), 32), dtype=np.uint8)
+    MO.knn2(q[:threads], db[:1000], fast=True, threads=threads)
+    t = time.perf_counter()
+    MO.knn2(q, db, fast=True, threads=threads)
+    dt = time.perf_counter() - t
+    t1 = time.perf_counter()
+    MO.knn2(q[:4], db, fast=True, threads=1)
+    dt1 = time.perf_counter() - t1
+    return {"value": len(q) * len(db) / dt, "unit": "pairs/s", "cores": threads, "kind": "port",
+            "single_thread_value": 4 * len(db) / dt1,
+            "sample": f"{len(q)} queries x 200,000 database descriptors, oracle SWAR popcount (-O3 -march=native)"}

@@ -173,6 +173,12 @@ int orbm_merge_top2_device(orbm_handle* h, const uint32_t* d_gathered, int nshar
 /* Database sharded over the ranks of an NCCL communicator (one process per GPU): local 2-NN over this rank's shard
  * (global indices = idx_base + local), ncclAllGather of the [nq][2] keys, merge.  comm = ncclComm_t.  d_gathered is
  * caller-provided scratch [nranks][nq][2].  NCCL is resolved at run time from the process (dlsym). */
+/* Communicator helpers for callers without an NCCL dependency of their own: rank 0 creates the id, every rank
+ * receives it out of band (e.g. one broadcast over the launcher's control channel) and joins. */
+#define ORBM_COMM_ID_BYTES 128
+int orbm_comm_unique_id(uint8_t id[ORBM_COMM_ID_BYTES]);
+int orbm_comm_init_rank(orbm_handle* h, int nranks, const uint8_t id[ORBM_COMM_ID_BYTES], int rank, void** comm);
+void orbm_comm_destroy(void* comm);
 int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db_shard, int64_t ndb_shard,
                       int64_t idx_base, int nranks, void* comm, uint32_t* d_gathered, int th_dist, float ratio,
                       uint32_t* d_top2, int32_t* d_match, void* stream);

@@ -2,6 +2,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "orbm_internal.cuh"
@@ -121,9 +122,12 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
   uint32_t* part = h->knn_part.as<uint32_t>();
   const int cl = (int)chunk_len;
   const uint32_t ib = (uint32_t)idx_base;
-  if (qpt == 4) knn2_kernel<4><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
-  else if (qpt == 2) knn2_kernel<2><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
-  else knn2_kernel<1><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  static const int dv = [] { const char* e = getenv("ORBM_KNN_VARIANT"); return e ? atoi(e) : 2; }();
+#define ORBM_KNN_LAUNCH(Q, D) knn2_kernel<Q, D><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err)
+#define ORBM_KNN_DV(Q) (dv == 0 ? ORBM_KNN_LAUNCH(Q, 0) : dv == 1 ? ORBM_KNN_LAUNCH(Q, 1) : ORBM_KNN_LAUNCH(Q, 2))
+  if (qpt == 4) ORBM_KNN_DV(4);
+  else if (qpt == 2) ORBM_KNN_DV(2);
+  else ORBM_KNN_DV(1);
   merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(part), nchunks, nq, 0, 0.f,
                                                     reinterpret_cast<uint2*>(d_top2), nullptr);
   h->launches += 2;
@@ -184,18 +188,67 @@ extern "C" int orbm_merge_top2_device(orbm_handle* h, const uint32_t* d_gathered
 }
 
 // NCCL is resolved from the process at run time so that liborbx.so has no link-time NCCL dependency and shares the
-// NCCL instance of whoever created the communicator (e.g. the one bundled with PyTorch).
-typedef int (*nccl_allgather_fn)(const void*, void*, size_t, int, void*, cudaStream_t);
-static nccl_allgather_fn resolve_allgather() {
-  static nccl_allgather_fn fn = nullptr;
-  if (fn) return fn;
-  void* sym = dlsym(RTLD_DEFAULT, "ncclAllGather");
-  if (!sym) {
-    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-    if (lib) sym = dlsym(lib, "ncclAllGather");
+// NCCL instance already loaded in the process (e.g. the one bundled with PyTorch), else the system libnccl.so.2.
+namespace {
+struct NcclUid { char b[128]; };  // ncclUniqueId, passed by value
+struct NcclApi {
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, NcclUid, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok = false;
+};
+NcclApi* nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api.ok ? &api : nullptr;
+  tried = true;
+  void* lib = nullptr;
+  auto sym = [&](const char* name) -> void* {
+    void* p = dlsym(RTLD_DEFAULT, name);
+    if (!p) {
+      if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+      if (lib) p = dlsym(lib, name);
+    }
+    return p;
+  };
+  *(void**)&api.AllGather = sym("ncclAllGather");
+  *(void**)&api.GetUniqueId = sym("ncclGetUniqueId");
+  *(void**)&api.CommInitRank = sym("ncclCommInitRank");
+  *(void**)&api.CommDestroy = sym("ncclCommDestroy");
+  *(void**)&api.GetErrorString = sym("ncclGetErrorString");
+  api.ok = api.AllGather && api.GetUniqueId && api.CommInitRank && api.CommDestroy;
+  return api.ok ? &api : nullptr;
+}
+}  // namespace
+
+extern "C" int orbm_comm_unique_id(uint8_t id[ORBM_COMM_ID_BYTES]) {
+  NcclApi* n = nccl_api();
+  if (!n || !id) return ORBM_ERR_COMM;
+  return n->GetUniqueId(id) == 0 ? ORBM_OK : ORBM_ERR_COMM;
+}
+
+extern "C" int orbm_comm_init_rank(orbm_handle* h, int nranks, const uint8_t id[ORBM_COMM_ID_BYTES], int rank,
+                                   void** comm) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!id || !comm || nranks < 1 || rank < 0 || rank >= nranks) { h->err = "bad communicator arguments"; return ORBM_ERR_ARG; }
+  NcclApi* n = nccl_api();
+  if (!n) { h->err = "NCCL not found in the process and libnccl.so.2 not loadable"; return ORBM_ERR_COMM; }
+  ORBM_CK(cudaSetDevice(h->device));
+  NcclUid uid;
+  memcpy(uid.b, id, sizeof(uid.b));
+  const int rc = n->CommInitRank(comm, nranks, uid, rank);
+  if (rc != 0) {
+    h->err = std::string("ncclCommInitRank: ") + (n->GetErrorString ? n->GetErrorString(rc) : "error");
+    return ORBM_ERR_COMM;
   }
-  fn = reinterpret_cast<nccl_allgather_fn>(sym);
-  return fn;
+  return ORBM_OK;
+}
+
+extern "C" void orbm_comm_destroy(void* comm) {
+  NcclApi* n = nccl_api();
+  if (n && comm) n->CommDestroy(comm);
 }
 
 extern "C" int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db_shard,
@@ -203,8 +256,8 @@ extern "C" int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, con
                                  int th_dist, float ratio, uint32_t* d_top2, int32_t* d_match, void* stream) {
   if (!h) return ORBM_ERR_ARG;
   if (!comm || !d_gathered || nranks < 1) { h->err = "bad communicator / gather buffer"; return ORBM_ERR_ARG; }
-  nccl_allgather_fn allgather = resolve_allgather();
-  if (!allgather) { h->err = "ncclAllGather not found in the process and libnccl.so.2 not loadable"; return ORBM_ERR_COMM; }
+  NcclApi* nccl = nccl_api();
+  if (!nccl) { h->err = "NCCL not found in the process and libnccl.so.2 not loadable"; return ORBM_ERR_COMM; }
   ORBM_CK(cudaSetDevice(h->device));
   cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
   ORBM_CK(h->stage_c.reserve((size_t)nq * 8 + 16));
@@ -212,7 +265,7 @@ extern "C" int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, con
   int rc = knn2_launch(h, d_q, nq, d_db_shard, ndb_shard, idx_base, d_local, s);
   if (rc != ORBM_OK) return rc;
   const int ncclUint32 = 3;
-  const int nrc = allgather(d_local, d_gathered, (size_t)nq * 2, ncclUint32, comm, s);
+  const int nrc = nccl->AllGather(d_local, d_gathered, (size_t)nq * 2, ncclUint32, comm, s);
   if (nrc != 0) { h->err = "ncclAllGather failed with code " + std::to_string(nrc); return ORBM_ERR_COMM; }
   return orbm_merge_top2_device(h, d_gathered, nranks, nq, th_dist, ratio, d_top2, d_match, s);
 }

@@ -53,7 +53,43 @@ __device__ __forceinline__ void top2_insert(uint32_t& best, uint32_t& second, ui
   best = min(best, key);
 }
 
-template <int QPT>
+// Hamming distance of one 256-bit pair, three instruction mixes (all exact):
+//   DV 0  8 XOR + 8 POPC                          POPC-pipe bound: POPC issues 16 lanes/clk/SM on sm_100
+//                                                 (tools/popc_microbench.cu), XOR/IADD3 64 lanes/clk/SM
+//   DV 1  two 3:2 carry-save adders  -> 6 POPC    sum = a^b^c, carry = maj(a,b,c): one LOP3 each
+//   DV 2  three carry-save adders    -> 5 POPC    balances the POPC pipe (5/16 clk) against the ALU pipe
+// dist = popc(ones) + 2 * popc(twos).
+// lop3 through inline PTX: ptxas otherwise re-derives its own (longer) LOP3 decomposition of the adder tree
+__device__ __forceinline__ uint32_t lop3_xor3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t lop3_maj(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+
+template <int DV>
+__device__ __forceinline__ uint32_t hamming_dv(const uint4& qa, const uint4& qb, const uint4& d0, const uint4& d1) {
+  const uint32_t x0 = qa.x ^ d0.x, x1 = qa.y ^ d0.y, x2 = qa.z ^ d0.z, x3 = qa.w ^ d0.w;
+  const uint32_t x4 = qb.x ^ d1.x, x5 = qb.y ^ d1.y, x6 = qb.z ^ d1.z, x7 = qb.w ^ d1.w;
+  if (DV == 0) {
+    return __popc(x0) + __popc(x1) + __popc(x2) + __popc(x3) + __popc(x4) + __popc(x5) + __popc(x6) + __popc(x7);
+  } else {
+    const uint32_t sa = lop3_xor3(x0, x1, x2), ca = lop3_maj(x0, x1, x2);
+    const uint32_t sb = lop3_xor3(x3, x4, x5), cb = lop3_maj(x3, x4, x5);
+    if (DV == 1) {
+      return __popc(sa) + __popc(sb) + __popc(x6) + __popc(x7) + 2 * (__popc(ca) + __popc(cb));
+    } else {
+      const uint32_t sc = lop3_xor3(sa, sb, x6), cc = lop3_maj(sa, sb, x6);
+      return __popc(sc) + __popc(x7) + 2 * (__popc(ca) + __popc(cb) + __popc(cc));
+    }
+  }
+}
+
+template <int QPT, int DV>
 __global__ void __launch_bounds__(kKnnThreads) knn2_kernel(const uint4* __restrict__ q, int nq,
                                                            const uint4* __restrict__ db, int64_t ndb, int chunk_len,
                                                            uint32_t idx_base, uint32_t* __restrict__ part,
@@ -107,7 +143,7 @@ __global__ void __launch_bounds__(kKnnThreads) knn2_kernel(const uint4* __restri
       const uint4 d0 = t[2 * j], d1 = t[2 * j + 1];
 #pragma unroll
       for (int k = 0; k < QPT; k++) {
-        const uint32_t dist = (uint32_t)hamming256(qa[k], qb[k], d0, d1);
+        const uint32_t dist = hamming_dv<DV>(qa[k], qb[k], d0, d1);
         top2_insert(best[k], second[k], (dist << 23) + (kb + j));
       }
     }

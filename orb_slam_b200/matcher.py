@@ -374,3 +374,55 @@ class ORBmatcher:
                                                             int(self.mbCheckOrientation), out.ctypes.data, stride,
                                                             nm.ctypes.data))
         return nm, out
+
+
+def shard_range(n_units, rank, world):
+    """Contiguous shard [a, b) of n_units keyframes owned by `rank` (database sharded by keyframe)."""
+    return n_units * rank // world, n_units * (rank + 1) // world
+
+
+class ShardedKnn2:
+    """All-pairs 2-NN with the database sharded over the ranks of one box (BASELINE config 5): every rank searches
+    its shard with global indices, ONE ncclAllGather exchanges the per-shard packed top-2 keys, a merge kernel applies
+    min / second-min and the accept rule.  The communicator is created through the C ABI (orbm_comm_*); the 128-byte
+    NCCL id travels over whatever control channel the launcher has (torch.distributed here)."""
+
+    def __init__(self, matcher: Matcher, rank: int, world: int, unique_id: bytes):
+        self.m, self.rank, self.world = matcher, rank, world
+        L = matcher._L
+        L.orbm_comm_init_rank.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.orbm_comm_destroy.argtypes = [C.c_void_p]; L.orbm_comm_destroy.restype = None
+        self._comm = C.c_void_p()
+        matcher._check(L.orbm_comm_init_rank(matcher._h, world, unique_id, rank, C.byref(self._comm)))
+
+    @staticmethod
+    def new_unique_id() -> bytes:
+        L = _bind(lib())
+        buf = C.create_string_buffer(128)
+        L.orbm_comm_unique_id.argtypes = [C.c_char_p]
+        rc = L.orbm_comm_unique_id(buf)
+        if rc != 0:
+            raise OrbmError(rc, "NCCL not available in this process")
+        return buf.raw
+
+    @classmethod
+    def from_torch_distributed(cls, matcher, device):
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        t = torch.zeros(128, dtype=torch.uint8, device=device)
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(cls.new_unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        return cls(matcher, rank, world, bytes(t.cpu().numpy().tobytes()))
+
+    def close(self):
+        if getattr(self, "_comm", None) and getattr(self.m, "_h", None):
+            self.m._L.orbm_comm_destroy(self._comm)
+        self._comm = None
+
+    def search(self, q_ptr, nq, db_shard_ptr, ndb_shard, idx_base, gathered_ptr, top2_ptr, match_ptr, th_dist=TH_LOW,
+               ratio=0.75, stream=None):
+        """Device pointers; asynchronous on `stream`.  gathered: [world, nq, 2] uint32 scratch."""
+        self.m._check(self.m._L.orbm_knn2_sharded(self.m._h, q_ptr, nq, db_shard_ptr, ndb_shard, idx_base, self.world,
+                                                  self._comm, gathered_ptr, th_dist, ratio, top2_ptr, match_ptr, stream))
