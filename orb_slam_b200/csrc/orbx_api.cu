@@ -104,7 +104,7 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     h->err = "image larger than the max_width x max_height the handle was created for";
     return ORBX_ERR_ARG;
   }
-  if (fast_cells_smem_bytes(h->hp.max_cell_px) > 200 * 1024) {
+  if (h->hp.fast_smem_bytes > 200 * 1024) {
     h->err = "cell too large for the shared-memory FAST tile (cell area > ~100k px)";
     return ORBX_ERR_UNSUPPORTED;
   }
@@ -226,7 +226,7 @@ static int run_chunk(orbx_handle* h, const uint8_t* d_imgs, int n, size_t stride
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   for (int l = 1; l < dp.nlevels; l++) launch_resize_level(b, dp, l, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
-  launch_fast_cells(b, dp, h->hp.max_cell_px, n, s);
+  launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   launch_select(b, dp, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);

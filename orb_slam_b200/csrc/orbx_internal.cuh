@@ -75,8 +75,18 @@ struct HostPlan {
   std::vector<CellPlan> cells;
   std::vector<ResizeX> rx;
   std::vector<ResizeY> ry;
-  int max_cell_px;           // largest scored-region + halo area, for the FAST kernel's shared memory
+  int fast_smem_bytes;       // dynamic shared memory of the FAST kernel: max over cells of fast_cell_smem()
 };
+
+// Shared-memory geometry of fast_cells_kernel for a cell sub-image of cw x ch pixels (scored region (cw-6) x (ch-6)):
+// the sub-image is staged as zero-extended u16 (two pixels per 32-bit word for the packed VIMNMX3.U16x2 ladder),
+// sub-image column c at halfword c + 5 so that scored column 0 sits on a 16-byte boundary.
+inline __host__ __device__ int fast_sp16(int cw) { return (cw + 12 + 7) & ~7; }          // halfwords per row
+inline __host__ __device__ int fast_scp(int rw) { return ((rw + 3) & ~3) + 8; }        // score-map bytes per row
+inline __host__ __device__ int fast_img_bytes(int cw, int ch) { return (ch * fast_sp16(cw) * 2 + 15) & ~15; }
+inline __host__ __device__ int fast_cell_smem(int cw, int ch) {
+  return fast_img_bytes(cw, ch) + (((ch - 4) * fast_scp(cw - 6) + 15) & ~15);
+}
 
 // Builds the plan exactly as the reference's constructor and ComputeKeyPoints do (float/double mix preserved).
 // Returns ORBX_OK, ORBX_ERR_UNSUPPORTED (grid with 0 columns/rows, cell outside the level) or ORBX_ERR_ARG.

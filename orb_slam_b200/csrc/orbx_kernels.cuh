@@ -30,13 +30,12 @@ struct BlurTiles {            // tile ranges of the single all-level blur launch
 };
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
-void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int max_cell_px, int nframes, cudaStream_t s);
+void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s);
 void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s);
 void launch_blur(const ChunkBuffers& b, const DevicePlan& hp, const BlurTiles& t, int nframes, cudaStream_t s);
 void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, orbx_keypoint* d_kps, uint8_t* d_desc,
                      int32_t* d_n_out, cudaStream_t s);
 void launch_synth(uint8_t* d_out, uint8_t* d_tmp, int nframes, int w, int h, size_t stride, size_t frame_stride,
                   uint64_t seed0, cudaStream_t s);
-int fast_cells_smem_bytes(int max_cell_px);
 
 }  // namespace orbx

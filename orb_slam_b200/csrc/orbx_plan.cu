@@ -95,7 +95,7 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
   const float imageRatio = (float)width / height;  // :527
   int64_t pyr_off = 0, blur_off = 0, cand_off = 0;
   int cell_base = 0, kp_base = 0, list_base = 0;
-  hp.max_cell_px = 0;
+  hp.fast_smem_bytes = 0;
   for (int level = 0; level < nlevels; level++) {
     LevelPlan& L = dp.lv[level];
     float scale = mvInvScaleFactor[level];
@@ -176,7 +176,7 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
             c.x0 = (int16_t)(cx0 + 3); c.y0 = (int16_t)(cy0 + 3);
             c.rw = (int16_t)(cw - 6); c.rh = (int16_t)(ch - 6);
             c.cand_cap = ((c.rw + 1) / 2) * ((c.rh + 1) / 2);
-            hp.max_cell_px = std::max(hp.max_cell_px, ch * ((cw + 3) & ~3));
+            hp.fast_smem_bytes = std::max(hp.fast_smem_bytes, fast_cell_smem(cw, ch));
           }
         }
         cand_off += c.cand_cap;
