@@ -14,34 +14,6 @@ namespace orbx {
 // computed on the RAW ring values with no negation anywhere:
 //     S = max( max_k min9(ring) - v ,  v - min_k max9(ring) ) - 1.
 // ------------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void fast_score_x2(const uint32_t (&r)[16], uint32_t v2, int tmin, int* s0, int* s1) {
-  uint32_t mn3[16], mx3[16];
-#pragma unroll
-  for (int k = 0; k < 16; k++) {
-    mn3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-    mx3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-  }
-  uint32_t mn9[16], mx9[16];
-#pragma unroll
-  for (int k = 0; k < 16; k++) {
-    mn9[k] = __vimin3_u16x2(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
-    mx9[k] = __vimax3_u16x2(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
-  }
-  uint32_t b = __vimax3_u16x2(mn9[0], mn9[1], mn9[2]), d = __vimin3_u16x2(mx9[0], mx9[1], mx9[2]);
-#pragma unroll
-  for (int k = 3; k < 15; k += 2) {
-    b = __vimax3_u16x2(b, mn9[k], mn9[k + 1]);
-    d = __vimin3_u16x2(d, mx9[k], mx9[k + 1]);
-  }
-  b = __vmaxu2(b, mn9[15]);
-  d = __vminu2(d, mx9[15]);
-  const int v0 = v2 & 0xffff, v1 = v2 >> 16;
-  const int a0 = max((int)(b & 0xffff) - v0, v0 - (int)(d & 0xffff)) - 1;
-  const int a1 = max((int)(b >> 16) - v1, v1 - (int)(d >> 16)) - 1;
-  *s0 = a0 >= tmin ? a0 : 0;
-  *s1 = a1 >= tmin ? a1 : 0;
-}
-
 // E4  HarrisResponses(cellImage, kps, 7, 0.04f)   (reference :79-120); p = level image at the keypoint
 __device__ float harris_response(const uint8_t* p, int step) {
   int a = 0, b = 0, c = 0;
@@ -64,40 +36,109 @@ __device__ float harris_response(const uint8_t* p, int step) {
 // ------------------------------------------------------------------------------------------------------------------
 // One CTA per (cell, frame): FAST score of the cell's scored region, 3x3 strict NMS that never looks outside the
 // region (the reference runs cv::FAST per cell sub-image, :599-607), the "<= 3 corners -> redo with threshold 7"
-// rule (:609-614) on the same score map, then an ORDER-PRESERVING compaction (row-major, the input order of
+// rule (:609-614) on the same score map, then an ORDER-PRESERVING emission (row-major, the input order of
 // retainBest's nth_element) into the cell's candidate list.
 //
 // Shared memory: the cell sub-image as zero-extended u16 (sub-image column c at halfword c + 5, so scored column 0
-// is 16-byte aligned), and the u8 score map with a zero ring.  A thread scores GROUPS of 4 adjacent pixels: per ring
-// row it loads 12 halfwords (3 x LDS.64); ring values of the two pixel pairs are whole registers (even dx) or one
-// PRMT of two neighbouring registers (odd dx).
+// is 16-byte aligned), the u8 score map with a zero ring, two survivor bitmaps (threshold fastTh / 7).
+// Work is split DENSE-CHEAP / SPARSE-HEAVY with warp-local queues so that the heavy code always runs on full warps:
+//   1  every 4-pixel group: opposite-pair reject  min(max(|r0-v|,|r8-v|), max(|r4-v|,|r12-v|)) > tmin  (an arc of 9
+//      contains a pixel of every opposite pair) on packed pixel PAIRS; surviving pairs are queued
+//   2  queued pairs, 32 at a time: the full VIMNMX3.U16x2 ladder -> score bytes
+//   3  every score word: pixels with S >= tmin are queued; queued pixels, 32 at a time: strict 3x3 NMS -> bitmaps
+//   4  popcount prefix over the bitmap words -> survivors in row-major order
+// Pixels failing the reject keep score 0 instead of their true S < tmin: harmless, a neighbour below tmin can never
+// suppress a survivor (S_c >= t >= tmin > S_n), which is also why one threshold-free map serves both thresholds.
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kFastThreads = 256;
+constexpr int kFastThreads = 256, kFastWarps = kFastThreads / 32, kFastQueue = 160;
 
 __device__ __forceinline__ uint32_t hw_mid(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }
+__device__ __forceinline__ uint32_t absdiff_u16x2(uint32_t a, uint32_t v) { return __vmaxu2(a, v) - __vminu2(a, v); }
 
-__global__ void __launch_bounds__(kFastThreads) fast_cells_kernel(ChunkBuffers b) {
+// Full score of the pixel pair at scored position (x even, y): loads the 16 ring values of both pixels as packed
+// halfwords straight from the staged sub-image (row pitch sp32 words).
+__device__ __forceinline__ uint32_t fast_pair_score(const uint32_t* s_img32, int sp32, int x, int y) {
+  const uint32_t* c0 = s_img32 + (y + 3) * sp32 + ((x + 8) >> 1);  // word holding the pair's centre pixels
+#define L(dy, dw) c0[(dy) * sp32 + (dw)]
+  uint32_t r[16];
+  {
+    const uint32_t a = L(3, -1), bq = L(3, 0), cq = L(3, 1);
+    r[0] = bq; r[1] = hw_mid(bq, cq); r[15] = hw_mid(a, bq);
+  }
+  r[2] = L(2, 1); r[14] = L(2, -1);
+  {
+    const uint32_t a = L(1, -2), bq = L(1, -1), cq = L(1, 1), dq = L(1, 2);
+    r[13] = hw_mid(a, bq); r[3] = hw_mid(cq, dq);
+  }
+  uint32_t v2;
+  {
+    const uint32_t a = L(0, -2), bq = L(0, -1), cq = L(0, 1), dq = L(0, 2);
+    v2 = L(0, 0);
+    r[12] = hw_mid(a, bq); r[4] = hw_mid(cq, dq);
+  }
+  {
+    const uint32_t a = L(-1, -2), bq = L(-1, -1), cq = L(-1, 1), dq = L(-1, 2);
+    r[11] = hw_mid(a, bq); r[5] = hw_mid(cq, dq);
+  }
+  r[6] = L(-2, 1); r[10] = L(-2, -1);
+  {
+    const uint32_t a = L(-3, -1), bq = L(-3, 0), cq = L(-3, 1);
+    r[8] = bq; r[7] = hw_mid(bq, cq); r[9] = hw_mid(a, bq);
+  }
+#undef L
+  uint32_t mn3[16], mx3[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    mn3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+    mx3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+  }
+  uint32_t mn9[16], mx9[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    mn9[k] = __vimin3_u16x2(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
+    mx9[k] = __vimax3_u16x2(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
+  }
+  uint32_t bb = __vimax3_u16x2(mn9[0], mn9[1], mn9[2]), dd = __vimin3_u16x2(mx9[0], mx9[1], mx9[2]);
+#pragma unroll
+  for (int k = 3; k < 15; k += 2) {
+    bb = __vimax3_u16x2(bb, mn9[k], mn9[k + 1]);
+    dd = __vimin3_u16x2(dd, mx9[k], mx9[k + 1]);
+  }
+  bb = __vmaxu2(bb, mn9[15]);
+  dd = __vminu2(dd, mx9[15]);
+  // S = max(bright - v, v - dark) - 1 per halfword (signed 16-bit lanes, |values| <= 255), clamped at 0
+  const uint32_t m = __vmaxs2(__vsub2(bb, v2), __vsub2(v2, dd));
+  return __vmaxs2(__vsub2(m, 0x00010001u), 0u);
+}
+
+__global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffers b) {
   extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ uint32_t s_queue[kFastWarps][kFastQueue];
+  __shared__ int s_cnt[2];
+  __shared__ int s_warp[kFastWarps];
   const DevicePlan* P = b.plan;
   const int cell = blockIdx.x, frame = blockIdx.y;
   const CellPlan c = b.cells[cell];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned lt_mask = (1u << lane) - 1;
   int32_t* n_total = b.n_total + (int64_t)frame * P->total_cells + cell;
   if (c.rw <= 0) {
     if (tid == 0) *n_total = 0;
     return;
   }
-  __shared__ int s_cnt[2];
-  __shared__ int s_warp[kFastThreads / 32];
   int pitch;
   const uint8_t* img = level_ptr(b, P, c.level, frame, &pitch);
   const int rw = c.rw, rh = c.rh, cw = rw + 6, ch = rh + 6;   // cw x ch = the sub-image handed to cv::FAST
-  const int sp16 = fast_sp16(cw), scp = fast_scp(rw);
+  const int sp16 = fast_sp16(cw), sp32 = sp16 >> 1, scp = fast_scp(rw);
+  const int npx = rw * rh, nbw = (npx + 31) >> 5;
   uint16_t* s_img = reinterpret_cast<uint16_t*>(smem);          // [ch][sp16]
   uint8_t* s_sc = smem + fast_img_bytes(cw, ch);                // [rh + 2][scp], scored column x at byte 4 + x
+  uint32_t* s_bmA = reinterpret_cast<uint32_t*>(s_sc + fast_sc_bytes(rw, rh));  // survivors with S >= fastTh
+  uint32_t* s_bmB = s_bmA + nbw;                                                // survivors with S >= 7
   const int G = (rw + 3) >> 2;                                  // 4-pixel groups per scored row
+  const int ngroups = G * rh;
 
-  // ---- stage the sub-image: aligned 32-bit global loads, four u16 stores -------------------------------------------
+  // ---- 0  stage the sub-image: aligned 32-bit global loads, four u16 stores ------------------------------------------
   {
     const int wpr = (cw + 3 + 3) >> 2;  // aligned words covering one sub-image row (any misalignment 0..3)
     for (int i = tid; i < ch * wpr; i += kFastThreads) {
@@ -109,77 +150,122 @@ __global__ void __launch_bounds__(kFastThreads) fast_cells_kernel(ChunkBuffers b
       uint16_t* dst = s_img + r * sp16 + 5 + 4 * j - mis;       // >= 2; bytes outside the sub-image land in padding
       dst[0] = w & 0xff; dst[1] = (w >> 8) & 0xff; dst[2] = (w >> 16) & 0xff; dst[3] = w >> 24;
     }
-    for (int i = tid; i < ((rh + 2) * scp) >> 2; i += kFastThreads) reinterpret_cast<uint32_t*>(s_sc)[i] = 0;
+    const int nz = (fast_sc_bytes(rw, rh) >> 2) + 2 * nbw;       // score map + both bitmaps are contiguous
+    for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint32_t*>(s_sc)[i] = 0;
     if (tid < 2) s_cnt[tid] = 0;
   }
   __syncthreads();
 
-  // ---- scores -----------------------------------------------------------------------------------------------------
   const int tA = P->fast_th, tB = kRetryTh, tmin = max(min(tA, tB), 1);
-  const int ngroups = G * rh;
-  for (int i = tid; i < ngroups; i += kFastThreads) {
-    const int y = i / G, g = i - y * G;
-    // W[dy + 3][j] = halfwords 4g + 4 + 2j, 4g + 5 + 2j of sub-image row y + 3 + dy
-    uint32_t W[7][6];
-#pragma unroll
-    for (int dy = 0; dy < 7; dy++) {
-      const uint2* src = reinterpret_cast<const uint2*>(s_img + (y + dy) * sp16 + 4 * g + 4);
-      const uint2 a0 = src[0], a1 = src[1], a2 = src[2];
-      W[dy][0] = a0.x; W[dy][1] = a0.y; W[dy][2] = a1.x; W[dy][3] = a1.y; W[dy][4] = a2.x; W[dy][5] = a2.y;
+  uint32_t* q = s_queue[warp];
+  const uint32_t* s_img32 = reinterpret_cast<const uint32_t*>(s_img);
+  const int gstep_y = kFastThreads / G, gstep_g = kFastThreads - gstep_y * G;
+
+  // ---- 1 + 2  scores ---------------------------------------------------------------------------------------------------
+  {
+    auto heavy = [&](uint32_t e) {
+      const int x = e & 0xffff, y = e >> 16;
+      const uint32_t s2 = fast_pair_score(s_img32, sp32, x, y);
+      uint32_t two = __byte_perm(s2, 0, 0x4420);               // (S(x), S(x+1)) as two bytes
+      if (x + 1 >= rw) two &= 0xff;
+      *reinterpret_cast<uint16_t*>(s_sc + (y + 1) * scp + 4 + x) = (uint16_t)two;
+    };
+    const uint32_t bias = (0x8000u - (uint32_t)(tmin + 1)) * 0x00010001u;  // bit 15 of (q + bias) <=> q > tmin
+    int qlen = 0;
+    int y = (warp * 32 + lane) / G, g = (warp * 32 + lane) - y * G;
+    for (int i0 = warp * 32; i0 < ngroups; i0 += kFastThreads) {
+      uint32_t flags = 0;
+      if (i0 + lane < ngroups) {
+        const uint2* mid = reinterpret_cast<const uint2*>(s_img + (y + 3) * sp16 + 4 * g + 4);
+        const uint2 a0 = mid[0], a1 = mid[1], a2 = mid[2];     // halfwords 4g+4 .. 4g+15 of the centre row
+        const uint2 up = *reinterpret_cast<const uint2*>(s_img + y * sp16 + 4 * g + 8);        // dy = -3, dx = 0
+        const uint2 dn = *reinterpret_cast<const uint2*>(s_img + (y + 6) * sp16 + 4 * g + 8);  // dy = +3
+        // pair 0: centre a1.x, left = hw(4g+5,4g+6), right = hw(4g+11,4g+12); pair 1: one word to the right
+        const uint32_t qa = __vminu2(__vmaxu2(absdiff_u16x2(up.x, a1.x), absdiff_u16x2(dn.x, a1.x)),
+                                     __vmaxu2(absdiff_u16x2(hw_mid(a0.x, a0.y), a1.x),
+                                              absdiff_u16x2(hw_mid(a1.y, a2.x), a1.x)));
+        const uint32_t qb = __vminu2(__vmaxu2(absdiff_u16x2(up.y, a1.y), absdiff_u16x2(dn.y, a1.y)),
+                                     __vmaxu2(absdiff_u16x2(hw_mid(a0.y, a1.x), a1.y),
+                                              absdiff_u16x2(hw_mid(a2.x, a2.y), a1.y)));
+        if ((qa + bias) & 0x80008000u) flags |= 1;
+        if (((qb + bias) & 0x80008000u) && 4 * g + 2 < rw) flags |= 2;
+      }
+      const unsigned b0 = __ballot_sync(0xffffffffu, flags & 1), b1 = __ballot_sync(0xffffffffu, flags & 2);
+      if (b0 | b1) {
+        // queue order is irrelevant: all "pair 0" entries first, then all "pair 1" entries
+        if (flags & 1) q[qlen + __popc(b0 & lt_mask)] = ((uint32_t)y << 16) | (uint32_t)(4 * g);
+        if (flags & 2) q[qlen + __popc(b0) + __popc(b1 & lt_mask)] = ((uint32_t)y << 16) | (uint32_t)(4 * g + 2);
+        qlen += __popc(b0) + __popc(b1);
+        __syncwarp();
+        while (qlen >= 32) {
+          qlen -= 32;
+          heavy(q[qlen + lane]);
+        }
+        __syncwarp();
+      }
+      y += gstep_y; g += gstep_g;
+      if (g >= G) { g -= G; y++; }
     }
-    int sc[4];
-#pragma unroll
-    for (int h = 0; h < 2; h++) {  // pixel pair h: pixels 2h, 2h + 1 of the group
-      // value at ring offset (dx, dy) for the pair = halfwords (4g + 8 + 2h + dx, +1) of row dy
-#define RV(dx, dy) (((dx) & 1) ? hw_mid(W[(dy) + 3][(3 + (dx)) / 2 + h], W[(dy) + 3][(3 + (dx)) / 2 + h + 1]) \
-                               : W[(dy) + 3][2 + (dx) / 2 + h])
-      uint32_t r[16];
-      r[0] = RV(0, 3);   r[1] = RV(1, 3);   r[2] = RV(2, 2);    r[3] = RV(3, 1);
-      r[4] = RV(3, 0);   r[5] = RV(3, -1);  r[6] = RV(2, -2);   r[7] = RV(1, -3);
-      r[8] = RV(0, -3);  r[9] = RV(-1, -3); r[10] = RV(-2, -2); r[11] = RV(-3, -1);
-      r[12] = RV(-3, 0); r[13] = RV(-3, 1); r[14] = RV(-2, 2);  r[15] = RV(-1, 3);
-      const uint32_t v2 = RV(0, 0);
-#undef RV
-      fast_score_x2(r, v2, tmin, &sc[2 * h], &sc[2 * h + 1]);
-    }
-    const int x0 = 4 * g;
-    uint32_t packed = 0;
-#pragma unroll
-    for (int k = 0; k < 4; k++)
-      if (x0 + k < rw) packed |= (uint32_t)sc[k] << (8 * k);
-    if (packed) *reinterpret_cast<uint32_t*>(s_sc + (y + 1) * scp + 4 + x0) = packed;
+    if (lane < qlen) heavy(q[lane]);
   }
   __syncthreads();
 
-  // ---- NMS: survivors' scores into s_ks (aliases s_img), counts at both thresholds ------------------------------------
-  uint8_t* s_ks = smem;  // [rh][4 G]
+  // ---- 3  NMS of the pixels with S >= tmin -----------------------------------------------------------------------------
   int nA = 0, nB = 0;
-  for (int i = tid; i < ngroups; i += kFastThreads) {
-    const int y = i / G, g = i - y * G;
-    const uint8_t* q0 = s_sc + (y + 1) * scp + 4 + 4 * g;
-    const uint32_t cw4 = *reinterpret_cast<const uint32_t*>(q0);
-    uint32_t keep4 = 0;
-    if (cw4) {
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const int s = (cw4 >> (8 * k)) & 255;
-        if (s) {
-          const uint8_t* q = q0 + k;
-          const int m = max(max(max(q[-1], q[1]), max(q[-scp - 1], q[-scp])),
-                            max(max(q[-scp + 1], q[scp - 1]), max(q[scp], q[scp + 1])));
-          if (s > m) { keep4 |= (uint32_t)s << (8 * k); nA += s >= tA; nB += s >= tB; }
-        }
+  {
+    auto nms = [&](uint32_t e) {
+      const int x = e & 0xffff, y = e >> 16;
+      const uint8_t* p = s_sc + (y + 1) * scp + 4 + x;
+      const int s = p[0];
+      const int m = max(max(max(p[-1], p[1]), max(p[-scp - 1], p[-scp])),
+                        max(max(p[-scp + 1], p[scp - 1]), max(p[scp], p[scp + 1])));
+      if (s > m) {
+        const int idx = y * rw + x;
+        if (s >= tA) { atomicOr(&s_bmA[idx >> 5], 1u << (idx & 31)); nA++; }
+        if (s >= tB) { atomicOr(&s_bmB[idx >> 5], 1u << (idx & 31)); nB++; }
       }
+    };
+    int qlen = 0;
+    int y = (warp * 32 + lane) / G, g = (warp * 32 + lane) - y * G;
+    for (int i0 = warp * 32; i0 < ngroups; i0 += kFastThreads) {
+      uint32_t w4 = 0;
+      if (i0 + lane < ngroups) w4 = *reinterpret_cast<const uint32_t*>(s_sc + (y + 1) * scp + 4 + 4 * g);
+      int flags = 0;
+      if (w4) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) flags |= ((int)((w4 >> (8 * k)) & 255) >= tmin) << k;
+      }
+      if (__any_sync(0xffffffffu, flags)) {
+        int cnt = __popc(flags), incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int o = __shfl_up_sync(0xffffffffu, incl, d);
+          if (lane >= d) incl += o;
+        }
+        int off = qlen + incl - cnt;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+          if (flags & (1 << k)) q[off++] = ((uint32_t)y << 16) | (uint32_t)(4 * g + k);
+        qlen += __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();
+        while (qlen >= 32) {
+          qlen -= 32;
+          nms(q[qlen + lane]);
+        }
+        __syncwarp();
+      }
+      y += gstep_y; g += gstep_g;
+      if (g >= G) { g -= G; y++; }
     }
-    reinterpret_cast<uint32_t*>(s_ks)[i] = keep4;
+    if (lane < qlen) nms(q[lane]);
   }
-  // (s_ks aliases s_img, which is dead since the barrier after the score phase; the loop above reads only s_sc)
   nA = __reduce_add_sync(0xffffffffu, nA);
   nB = __reduce_add_sync(0xffffffffu, nB);
   if (lane == 0) { atomicAdd(&s_cnt[0], nA); atomicAdd(&s_cnt[1], nB); }
   __syncthreads();
-  const int t = s_cnt[0] > 3 ? tA : tB;          // :609-614
-  const int total = s_cnt[0] > 3 ? s_cnt[0] : s_cnt[1];
+  const bool useA = s_cnt[0] > 3;                 // :609-614
+  const int total = useA ? s_cnt[0] : s_cnt[1];
+  const uint32_t* bm = useA ? s_bmA : s_bmB;
   if (tid == 0) *n_total = total;
   if (total > c.cand_cap) {                       // cannot happen (NMS survivors are non-adjacent); never truncate
     if (tid == 0) atomicExch(b.err_flag, 1);
@@ -187,15 +273,13 @@ __global__ void __launch_bounds__(kFastThreads) fast_cells_kernel(ChunkBuffers b
   }
   if (total == 0) return;
 
-  // ---- ordered compaction: rounds of 256 groups (1024 row-major pixels) ---------------------------------------------
+  // ---- 4  ordered emission: popcount prefix over the bitmap words (bit index = y * rw + x, row-major) --------------------
   Cand* out = b.cand + (int64_t)frame * P->cand_per_frame + c.cand_off;
   int base = 0;
-  for (int i0 = 0; i0 < ngroups; i0 += kFastThreads) {
+  for (int i0 = 0; i0 < nbw; i0 += kFastThreads) {
     const int i = i0 + tid;
-    uint32_t k4 = i < ngroups ? reinterpret_cast<const uint32_t*>(s_ks)[i] : 0;
-    int cnt = 0;
-#pragma unroll
-    for (int k = 0; k < 4; k++) cnt += (int)((k4 >> (8 * k)) & 255) >= t && ((k4 >> (8 * k)) & 255) != 0;
+    uint32_t bits = i < nbw ? bm[i] : 0;
+    const int cnt = __popc(bits);
     int incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -206,25 +290,21 @@ __global__ void __launch_bounds__(kFastThreads) fast_cells_kernel(ChunkBuffers b
     __syncthreads();
     int off = base + incl - cnt, round_total = 0;
 #pragma unroll
-    for (int wq = 0; wq < kFastThreads / 32; wq++) {
+    for (int wq = 0; wq < kFastWarps; wq++) {
       const int v = s_warp[wq];
       if (wq < warp) off += v;
       round_total += v;
     }
-    if (cnt) {
-      const int y = i / G, g = i - y * G;
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const int s = (k4 >> (8 * k)) & 255;
-        if (s >= t && s != 0) {
-          const int lx = c.x0 + 4 * g + k, ly = c.y0 + y;
-          Cand r;
-          r.resp = P->score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
-                                                      : (float)s;
-          r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
-          out[off++] = r;
-        }
-      }
+    while (bits) {
+      const int bit = __ffs(bits) - 1;
+      bits &= bits - 1;
+      const int idx = 32 * i + bit, y = idx / rw, x = idx - y * rw;
+      const int lx = c.x0 + x, ly = c.y0 + y;
+      Cand r;
+      r.resp = P->score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
+                                                  : (float)s_sc[(y + 1) * scp + 4 + x];
+      r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
+      out[off++] = r;
     }
     base += round_total;
     __syncthreads();
@@ -232,8 +312,9 @@ __global__ void __launch_bounds__(kFastThreads) fast_cells_kernel(ChunkBuffers b
 }
 
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s) {
-  if (smem_bytes > 48 * 1024)
-    cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  // per-device attributes; a few microseconds per chunk of up to max_batch frames
+  cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   dim3 grid(hp.total_cells, nframes);
   fast_cells_kernel<<<grid, kFastThreads, smem_bytes, s>>>(b);
 }
