@@ -1,7 +1,7 @@
 // Included by orbx_kernels.cu.  E7 IC_Angle, E9 rotated BRIEF, E10 output assembly: one warp per keypoint slot.
 namespace orbx {
 
-__constant__ int8_t c_pattern[1024] = {
+__device__ __align__(16) int8_t d_pattern[1024] = {
 #include "orb_pattern_31.inc"
 };
 
@@ -61,10 +61,27 @@ __device__ __forceinline__ void sincosf_glibc(float y, float* sn, float* cs) {
   else { *sn = fc; *cs = fs; }
 }
 
-__global__ void __launch_bounds__(256) describe_kernel(ChunkBuffers b, orbx_keypoint* out_kps, uint8_t* out_desc,
-                                                       int32_t* out_n, int nslots_total) {
+// umax of the 31-px disc (reference :495-510); build_plan() verifies that the table it computes with the reference's
+// code equals this one.
+__device__ constexpr int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+constexpr int kDescWarps = 8, kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchWords = 11, kPatchPitch = 4 * kPatchWords;
+
+// One warp per keypoint slot.
+//  E7  lane = COLUMN u of the 31-px disc: 31 row loads, each one coalesced 31-byte segment (the former lane = row
+//      layout cost 31 scattered sectors per load instruction and made the kernel L1-wavefront bound).
+//  E9  the 37x37 window of the BLURRED level that the rotated pattern can reach (|offset| <= 18) is staged into
+//      shared memory by aligned 32-bit loads (2 rows per instruction) and the 512 samples are read from there;
+//      the pattern lives in registers (two 16-byte loads per lane) instead of 32-way divergent __constant__ reads.
+//      Windows touching the image border take the per-sample path: in-image samples read the blurred level, the
+//      <= 2 px outside read the UNBLURRED reflect-101 border, which the reference's in-place ROI blur leaves
+//      untouched (:759-760).
+__global__ void __launch_bounds__(32 * kDescWarps) describe_kernel(ChunkBuffers b, orbx_keypoint* out_kps,
+                                                                  uint8_t* out_desc, int32_t* out_n,
+                                                                  int nslots_total) {
+  __shared__ __align__(16) uint8_t s_patch[kDescWarps][kPatchRows * kPatchPitch];
   const DevicePlan* P = b.plan;
-  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (gw >= nslots_total) return;
   const int frame = gw / P->nfeatures, slot = gw - frame * P->nfeatures;
   const int32_t* cnt = b.kp_count + frame * kMaxLevels;
@@ -82,40 +99,75 @@ __global__ void __launch_bounds__(256) describe_kernel(ChunkBuffers b, orbx_keyp
   const int cx = kp.xy & 0xffff, cy = kp.xy >> 16;
   int pitch;
   const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
+  const int lw = L.w, lh = L.h, lpitch = L.pitch;
+  const uint8_t* blur = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
 
-  // ---- E7 IC_Angle (:124-151): m10 = sum u*I, m01 = sum v*I over the 749-px disc, UNBLURRED level; lane = row
+  // pattern of this lane's descriptor byte: 16 points x (x, y) int8
+  const uint4 pa = reinterpret_cast<const uint4*>(d_pattern)[2 * lane], pb = reinterpret_cast<const uint4*>(d_pattern)[2 * lane + 1];
+  const uint32_t pat[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
+
+  // ---- E9 staging first (independent of the angle): the loads overlap the orientation arithmetic
+  const bool fast_path = cx >= kPatchR + 3 && cx + kPatchR + 8 <= lpitch && cx + kPatchR < lw && cy >= kPatchR &&
+                         cy + kPatchR < lh;
+  int mis = 0;
+  if (fast_path) {
+    const uint8_t* w0 = blur + (int64_t)(cy - kPatchR) * lpitch + (cx - kPatchR);
+    mis = (int)((uintptr_t)w0 & 3);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(w0 - mis);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(s_patch[warp]);
+    const int half = lane >> 4, j = lane & 15, wpitch = lpitch >> 2;
+    if (j < kPatchWords) {
+#pragma unroll 5
+      for (int r0 = 0; r0 < kPatchRows; r0 += 2) {
+        const int r = r0 + half;
+        if (r < kPatchRows) dst[r * kPatchWords + j] = src[r * wpitch + j];
+      }
+    }
+  }
+
+  // ---- E7 IC_Angle (:124-151): m10 = sum u*I, m01 = sum v*I over the 749-px disc, UNBLURRED level
   int m10 = 0, m01 = 0;
   if (lane < 31) {
-    const int v = lane - kHalfPatch;
-    const int d = P->umax[v < 0 ? -v : v];
-    const uint8_t* row = img + (int64_t)(cy + v) * pitch + cx;
-    int rs = 0;
-    for (int u = -d; u <= d; u++) { const int I = row[u]; m10 += u * I; rs += I; }
-    m01 = v * rs;
+    const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+    const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
+    int colsum = 0;
+#pragma unroll
+    for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+      if (au <= kUmax[v < 0 ? -v : v]) {
+        const int I = c[v * pitch];
+        colsum += I;
+        m01 += v * I;
+      }
+    }
+    m10 = u * colsum;
   }
   m10 = __reduce_add_sync(0xffffffffu, m10);
   m01 = __reduce_add_sync(0xffffffffu, m01);
   const float angle = fast_atan2_dev((float)m01, (float)m10);
 
-  // ---- E9 computeOrbDescriptor (:155-194): lane = descriptor byte, 8 comparisons of rotated pattern samples.
-  // In-image samples read the blurred level; the <= 2 px that fall outside read the UNBLURRED reflect-101 border,
-  // which the reference's in-place ROI blur leaves untouched (:759-760).
+  // ---- E9 computeOrbDescriptor (:155-194): lane = descriptor byte, 8 comparisons of rotated pattern samples
   const float factorPI = (float)(3.14159265358979323846 / 180.f);
   float sa, ca;
   sincosf_glibc(__fmul_rn(angle, factorPI), &sa, &ca);
-  const uint8_t* blur = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
+  __syncwarp();
+  const uint8_t* sp = s_patch[warp] + kPatchR * kPatchPitch + kPatchR + mis;
   int val = 0;
 #pragma unroll
   for (int j = 0; j < 8; j++) {
     int t[2];
 #pragma unroll
     for (int e = 0; e < 2; e++) {
-      const float px = (float)c_pattern[lane * 32 + j * 4 + e * 2], py = (float)c_pattern[lane * 32 + j * 4 + e * 2 + 1];
+      const uint32_t w = pat[j] >> (16 * e);
+      const float px = (float)(int8_t)(w & 0xff), py = (float)(int8_t)((w >> 8) & 0xff);
       const int ry = __float2int_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)));
       const int rx = __float2int_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)));
-      const int x = cx + rx, y = cy + ry;
-      if (x >= 0 && x < L.w && y >= 0 && y < L.h) t[e] = blur[(int64_t)y * L.pitch + x];
-      else t[e] = img[(int64_t)reflect101(y, L.h) * pitch + reflect101(x, L.w)];
+      if (fast_path) {
+        t[e] = sp[ry * kPatchPitch + rx];
+      } else {
+        const int x = cx + rx, y = cy + ry;
+        if (x >= 0 && x < lw && y >= 0 && y < lh) t[e] = blur[(int64_t)y * lpitch + x];
+        else t[e] = img[(int64_t)reflect101(y, lh) * pitch + reflect101(x, lw)];
+      }
     }
     val |= (t[0] < t[1]) << j;
   }
@@ -143,7 +195,7 @@ __global__ void __launch_bounds__(256) describe_kernel(ChunkBuffers b, orbx_keyp
 void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, orbx_keypoint* d_kps, uint8_t* d_desc,
                      int32_t* d_n_out, cudaStream_t s) {
   const int nslots = hp.nfeatures * nframes;
-  describe_kernel<<<(nslots + 7) / 8, 256, 0, s>>>(b, d_kps, d_desc, d_n_out, nslots);
+  describe_kernel<<<(nslots + kDescWarps - 1) / kDescWarps, 32 * kDescWarps, 0, s>>>(b, d_kps, d_desc, d_n_out, nslots);
 }
 
 }  // namespace orbx

@@ -90,6 +90,9 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
       ++v0;
     }
     for (int i = 0; i < 16; i++) dp.umax[i] = umax[i];
+    static const int kExpect[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};  // describe kernel's table
+    for (int i = 0; i < 16; i++)
+      if (umax[i] != kExpect[i]) { *err = "umax table differs from the kernel's constant"; return ORBX_ERR_UNSUPPORTED; }
   }
 
   const float imageRatio = (float)width / height;  // :527
