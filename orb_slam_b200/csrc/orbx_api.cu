@@ -119,7 +119,7 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
   for (int l = 0; l < dp.nlevels; l++) {
     h->tiles.base[l] = base;
     h->tiles.tiles_x[l] = (dp.lv[l].w + 63) / 64;
-    base += h->tiles.tiles_x[l] * ((dp.lv[l].h + 31) / 32);
+    base += h->tiles.tiles_x[l] * ((dp.lv[l].h + 63) / 64);
   }
   h->tiles.base[dp.nlevels] = base;
   h->plan_w = w; h->plan_h = hgt;

@@ -74,9 +74,18 @@ void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level,
 // Separable integer taps, dst = (sum_j k_j sum_i k_i p + 32768) >> 16  (SURVEY §0.3 P3).  The reference blurs in
 // place and keeps the unblurred border; here the blurred image goes to its own slab and the unblurred level stays
 // intact (the descriptor kernel reads the unblurred reflect for the <= 2 px of patch overhang).
-// One CTA = 64x32 output tile of one level of one frame; all levels in one launch.
+// One CTA = 64x64 output tile of one level of one frame; all levels in one launch.
+//
+// Both passes run on PACKED u16x2 lanes, two pixels per IMAD:
+//   horizontal  pixels (x, x+2) share a register (even / odd bytes of a word are one AND away from that form);
+//               h = k0 (S[-3] + S[3]) + k1 (S[-2] + S[2]) + k2 (S[-1] + S[1]) + k3 S[0] <= 255 * 257 = 65535 fits a lane
+//   vertical    sum_j k_j h_j needs 25 bits, so h is split into its low and high BYTE planes at the end of the
+//               horizontal pass: sum_j k_j hL_j and sum_j k_j hH_j each fit a lane again, and
+//               v = 256 * VH + VL is rebuilt per pixel only for the final (v + 32768) >> 16.
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kBlurTW = 64, kBlurTH = 32;
+constexpr int kBlurT = 64, kBlurRows = kBlurT + 6, kBlurWords = 18;  // staged row = image columns x0-4 .. x0+67
+
+__device__ __forceinline__ uint32_t packed_mid(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }
 
 __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles tiles) {
   const DevicePlan* P = b.plan;
@@ -86,42 +95,66 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
   const int t = blockIdx.x - tiles.base[level];
   const int tx = t % tiles.tiles_x[level], ty = t / tiles.tiles_x[level];
   const int frame = blockIdx.y;
-  const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
+  const int x0 = tx * kBlurT, y0 = ty * kBlurT;
+  const int lw = L.w, lh = L.h;
   int spitch;
   const uint8_t* src = level_ptr(b, P, level, frame, &spitch);
   uint8_t* dst = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
 
-  __shared__ uint8_t s_in[kBlurTH + 6][kBlurTW + 8];
-  __shared__ uint16_t s_h[kBlurTH + 6][kBlurTW];
+  __shared__ uint32_t s_in[kBlurRows][kBlurWords];
+  __shared__ uint4 s_h[kBlurRows][kBlurT / 4];  // per 4 output columns: {L(o0,o2), L(o1,o3), H(o0,o2), H(o1,o3)}
   const int tid = threadIdx.x;
-  for (int i = tid; i < (kBlurTH + 6) * (kBlurTW + 6); i += 256) {
-    const int r = i / (kBlurTW + 6), c = i % (kBlurTW + 6);
-    const int yy = reflect101(min(y0 + r - 3, L.h + 2), L.h), xx = reflect101(min(x0 + c - 3, L.w + 2), L.w);
-    s_in[r][c] = src[(int64_t)yy * spitch + xx];
-  }
-  __syncthreads();
-  const int k0 = 18, k1 = 34, k2 = P->blur_mode == 0 ? 49 : 48, k3 = P->blur_mode == 0 ? 55 : 56;
-  for (int i = tid; i < (kBlurTH + 6) * kBlurTW; i += 256) {
-    const int r = i / kBlurTW, c = i % kBlurTW;
-    const uint8_t* p = &s_in[r][c];
-    const int v = k0 * (p[0] + p[6]) + k1 * (p[1] + p[5]) + k2 * (p[2] + p[4]) + k3 * p[3];
-    s_h[r][c] = (uint16_t)v;  // <= 255*257 = 65535
-  }
-  __syncthreads();
-  // each thread: 4 adjacent columns of 2 rows -> 32-bit stores
-  for (int i = tid; i < kBlurTH * (kBlurTW / 4); i += 256) {
-    const int r = i / (kBlurTW / 4), c4 = (i % (kBlurTW / 4)) * 4;
-    const int y = y0 + r;
-    if (y >= L.h || x0 + c4 >= L.w) continue;
-    uint32_t packed = 0;
+  const bool words_ok = ((spitch & 3) == 0) && (((uintptr_t)src & 3) == 0);
+  for (int i = tid; i < kBlurRows * kBlurWords; i += 256) {
+    const int r = i / kBlurWords, j = i - r * kBlurWords;
+    const int yy = reflect101(min(y0 + r - 3, lh + 2), lh);
+    const int xs = x0 - 4 + 4 * j;
+    const uint8_t* row = src + (int64_t)yy * spitch;
+    uint32_t w;
+    if (words_ok && xs >= 0 && xs + 3 < lw) {
+      w = *reinterpret_cast<const uint32_t*>(row + xs);
+    } else {
+      w = 0;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int c = c4 + k;
-      const int v = k0 * (s_h[r][c] + s_h[r + 6][c]) + k1 * (s_h[r + 1][c] + s_h[r + 5][c]) +
-                    k2 * (s_h[r + 2][c] + s_h[r + 4][c]) + k3 * s_h[r + 3][c];
-      packed |= (uint32_t)min((v + 32768) >> 16, 255) << (8 * k);
+      for (int k = 0; k < 4; k++) w |= (uint32_t)row[reflect101(min(max(xs + k, -3), lw + 2), lw)] << (8 * k);
     }
-    *reinterpret_cast<uint32_t*>(dst + (int64_t)y * L.pitch + x0 + c4) = packed;  // padding columns are scratch
+    s_in[r][j] = w;
+  }
+  __syncthreads();
+  const uint32_t k0 = 18, k1 = 34, k2 = P->blur_mode == 0 ? 49 : 48, k3 = P->blur_mode == 0 ? 55 : 56;
+  const uint32_t M = 0x00FF00FFu;
+  for (int i = tid; i < kBlurRows * (kBlurT / 4); i += 256) {
+    const int r = i >> 4, k = i & 15;
+    const uint32_t w0 = s_in[r][k], w1 = s_in[r][k + 1], w2 = s_in[r][k + 2];
+    // S_i = (B_i, B_{i+2}) with B_i = staged byte 4k + i; output o_j is centred on B_{4+j}
+    const uint32_t E0 = w0 & M, E1 = w1 & M, E2 = w2 & M, O0 = (w0 >> 8) & M, O1 = (w1 >> 8) & M, O2 = (w2 >> 8) & M;
+    const uint32_t S1 = O0, S2 = packed_mid(E0, E1), S3 = packed_mid(O0, O1), S4 = E1, S5 = O1,
+                   S6 = packed_mid(E1, E2), S7 = packed_mid(O1, O2), S8 = E2;
+    const uint32_t hA = k0 * (S1 + S7) + k1 * (S2 + S6) + k2 * (S3 + S5) + k3 * S4;  // (o0, o2)
+    const uint32_t hB = k0 * (S2 + S8) + k1 * (S3 + S7) + k2 * (S4 + S6) + k3 * S5;  // (o1, o3)
+    s_h[r][k] = make_uint4(hA & M, hB & M, (hA >> 8) & M, (hB >> 8) & M);
+  }
+  __syncthreads();
+  {
+    const int k = tid & 15, strip = tid >> 4;  // 4 columns x 4 rows per thread
+    const int x = x0 + 4 * k;
+    if (x >= lw || y0 + 4 * strip >= lh) return;
+    uint4 a[10];
+#pragma unroll
+    for (int q = 0; q < 10; q++) a[q] = s_h[4 * strip + q][k];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int y = y0 + 4 * strip + q;
+      if (y >= lh) break;
+#define BLURV(c) (k0 * (a[q].c + a[q + 6].c) + k1 * (a[q + 1].c + a[q + 5].c) + k2 * (a[q + 2].c + a[q + 4].c) + k3 * a[q + 3].c)
+      const uint32_t AL = BLURV(x), BL = BLURV(y), AH = BLURV(z), BH = BLURV(w);
+#undef BLURV
+      const uint32_t r0 = min((((AH & 0xffff) << 8) + (AL & 0xffff) + 32768u) >> 16, 255u);
+      const uint32_t r2 = min((((AH >> 16) << 8) + (AL >> 16) + 32768u) >> 16, 255u);
+      const uint32_t r1 = min((((BH & 0xffff) << 8) + (BL & 0xffff) + 32768u) >> 16, 255u);
+      const uint32_t r3 = min((((BH >> 16) << 8) + (BL >> 16) + 32768u) >> 16, 255u);
+      *reinterpret_cast<uint32_t*>(dst + (int64_t)y * L.pitch + x) = r0 | (r1 << 8) | (r2 << 16) | (r3 << 24);
+    }
   }
 }
 
