@@ -51,7 +51,7 @@ struct CellPlan {
 };
 
 struct ResizeX {  // per destination column: source column and the two 11-bit weights (cv::resize INTER_LINEAR)
-  int16_t sx, a0, a1, pad;
+  int16_t sx, pad, a0, a1;  // (a0, a1) form one 32-bit word: the s16x2 operand of DP2A
 };
 struct ResizeY {
   int16_t sy0, sy1, b0, b1;

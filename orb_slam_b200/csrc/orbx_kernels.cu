@@ -33,6 +33,10 @@ __device__ __forceinline__ const uint8_t* level_ptr(const ChunkBuffers& b, const
 // The 16-px reflect border of the reference (copyMakeBorder :806/:814) is never materialised: consumers reflect
 // indices instead.
 // ------------------------------------------------------------------------------------------------------------------
+// Fast path (aligned source rows, scale < ~2.3): the thread's 4 destination pixels read source columns
+// sx0 .. sx3 + 1, at most 8 bytes, so each of the two source rows is fetched as three aligned 32-bit words, shifted
+// once to start at sx0, and every pixel's (S0[sx], S0[sx+1], S1[sx], S1[sx+1]) quadruple is three PRMTs away; the two
+// horizontal interpolations are then ONE DP2A each (u8 pair . s16 weight pair).
 __global__ void __launch_bounds__(256) resize_level_kernel(ChunkBuffers b, int level) {
   const DevicePlan* P = b.plan;
   const LevelPlan& L = P->lv[level];
@@ -47,15 +51,37 @@ __global__ void __launch_bounds__(256) resize_level_kernel(ChunkBuffers b, int l
   const uint8_t* S0 = src + (int64_t)ry.sy0 * spitch;
   const uint8_t* S1 = src + (int64_t)ry.sy1 * spitch;
   const int sw = P->lv[level - 1].w;
-  uint32_t packed = 0;
+  uint2 rx[4];
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    const int dx = dx0 + k;
-    if (dx < L.w) {
-      const ResizeX rx = b.rx[L.tab_x + dx];
-      const int sx = rx.sx, sx1 = min(sx + 1, sw - 1);
-      const int h0 = S0[sx] * rx.a0 + S0[sx1] * rx.a1;
-      const int h1 = S1[sx] * rx.a0 + S1[sx1] * rx.a1;
+  for (int k = 0; k < 4; k++) rx[k] = reinterpret_cast<const uint2*>(b.rx)[L.tab_x + min(dx0 + k, L.w - 1)];
+  const int sx0 = rx[0].x & 0xffff, sx3 = rx[3].x & 0xffff;
+  const bool fast = ((spitch & 3) == 0) && (((uintptr_t)src & 3) == 0) && (sx3 + 1 - sx0 <= 7);
+  uint32_t packed = 0;
+  if (fast) {
+    const int base4 = sx0 & ~3, sh = (sx0 & 3) * 8;
+    const uint32_t* A = reinterpret_cast<const uint32_t*>(S0 + base4);
+    const uint32_t* B = reinterpret_cast<const uint32_t*>(S1 + base4);
+    const bool in1 = base4 + 4 < sw, in2 = base4 + 8 < sw;   // never start a load beyond the row
+    const uint32_t a0 = A[0], a1 = in1 ? A[1] : 0u, a2 = in2 ? A[2] : 0u;
+    const uint32_t c0 = B[0], c1 = in1 ? B[1] : 0u, c2 = in2 ? B[2] : 0u;
+    const uint32_t wa0 = __funnelshift_r(a0, a1, sh), wa1 = __funnelshift_r(a1, a2, sh);  // bytes sx0.. of row 0
+    const uint32_t wb0 = __funnelshift_r(c0, c1, sh), wb1 = __funnelshift_r(c1, c2, sh);  // ... of row 1
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int o = (int)(rx[k].x & 0xffff) - sx0;
+      const uint32_t sel = (uint32_t)o | ((uint32_t)(o + 1) << 4);
+      const uint32_t q = __byte_perm(__byte_perm(wa0, wa1, sel), __byte_perm(wb0, wb1, sel), 0x5410);
+      const uint32_t h0 = __dp2a_lo(rx[k].y, q, 0u), h1 = __dp2a_hi(rx[k].y, q, 0u);
+      const int v = (((ry.b0 * (int)(h0 >> 4)) >> 16) + ((ry.b1 * (int)(h1 >> 4)) >> 16) + 2) >> 2;
+      packed |= (uint32_t)(v & 255) << (8 * k);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int sx = rx[k].x & 0xffff, sx1 = min(sx + 1, sw - 1);
+      const int ca0 = (int)(short)(rx[k].y & 0xffff), ca1 = (int)(short)(rx[k].y >> 16);
+      const int h0 = S0[sx] * ca0 + S0[sx1] * ca1;
+      const int h1 = S1[sx] * ca0 + S1[sx1] * ca1;
       const int v = (((ry.b0 * (h0 >> 4)) >> 16) + ((ry.b1 * (h1 >> 4)) >> 16) + 2) >> 2;
       packed |= (uint32_t)(v & 255) << (8 * k);
     }
