@@ -85,8 +85,8 @@ inline __host__ __device__ int fast_sp16(int cw) { return (cw + 12 + 7) & ~7; } 
 inline __host__ __device__ int fast_scp(int rw) { return ((rw + 3) & ~3) + 8; }        // score-map bytes per row
 inline __host__ __device__ int fast_img_bytes(int cw, int ch) { return (ch * fast_sp16(cw) * 2 + 15) & ~15; }
 inline __host__ __device__ int fast_sc_bytes(int rw, int rh) { return ((rh + 2) * fast_scp(rw) + 15) & ~15; }
-inline __host__ __device__ int fast_cell_smem(int cw, int ch) {  // image + score map + two survivor bitmaps
-  return fast_img_bytes(cw, ch) + fast_sc_bytes(cw - 6, ch - 6) + 8 * (((cw - 6) * (ch - 6) + 31) / 32) + 16;
+inline __host__ __device__ int fast_cell_smem(int cw, int ch) {  // image + score map + three pixel bitmaps
+  return fast_img_bytes(cw, ch) + fast_sc_bytes(cw - 6, ch - 6) + 12 * (((cw - 6) * (ch - 6) + 31) / 32) + 16;
 }
 
 // Builds the plan exactly as the reference's constructor and ComputeKeyPoints do (float/double mix preserved).

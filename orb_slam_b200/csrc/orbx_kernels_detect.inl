@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   uint8_t* s_sc = smem + fast_img_bytes(cw, ch);                // [rh + 2][scp], scored column x at byte 4 + x
   uint32_t* s_bmA = reinterpret_cast<uint32_t*>(s_sc + fast_sc_bytes(rw, rh));  // survivors with S >= fastTh
   uint32_t* s_bmB = s_bmA + nbw;                                                // survivors with S >= 7
+  uint32_t* s_bmC = s_bmB + nbw;                                                // pixels with S >= tmin (NMS inputs)
   const int G = (rw + 3) >> 2;                                  // 4-pixel groups per scored row
   const int ngroups = G * rh;
 
@@ -150,7 +151,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
       uint16_t* dst = s_img + r * sp16 + 5 + 4 * j - mis;       // >= 2; bytes outside the sub-image land in padding
       dst[0] = w & 0xff; dst[1] = (w >> 8) & 0xff; dst[2] = (w >> 16) & 0xff; dst[3] = w >> 24;
     }
-    const int nz = (fast_sc_bytes(rw, rh) >> 2) + 2 * nbw;       // score map + both bitmaps are contiguous
+    const int nz = (fast_sc_bytes(rw, rh) >> 2) + 3 * nbw;       // score map + the three bitmaps are contiguous
     for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint32_t*>(s_sc)[i] = 0;
     if (tid < 2) s_cnt[tid] = 0;
   }
@@ -160,6 +161,8 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   uint32_t* q = s_queue[warp];
   const uint32_t* s_img32 = reinterpret_cast<const uint32_t*>(s_img);
   const int gstep_y = kFastThreads / G, gstep_g = kFastThreads - gstep_y * G;
+  // floor(i / d) == umulhi(i, floor(2^32 / d) + 1) for i * d < 2^32 (all indices here are < 2^17)
+  const uint32_t rw_magic = 0xffffffffu / (uint32_t)rw + 1u, g_magic = 0xffffffffu / (uint32_t)G + 1u;
 
   // ---- 1 + 2  scores ---------------------------------------------------------------------------------------------------
   {
@@ -168,11 +171,16 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
       const uint32_t s2 = fast_pair_score(s_img32, sp32, x, y);
       uint32_t two = __byte_perm(s2, 0, 0x4420);               // (S(x), S(x+1)) as two bytes
       if (x + 1 >= rw) two &= 0xff;
-      *reinterpret_cast<uint16_t*>(s_sc + (y + 1) * scp + 4 + x) = (uint16_t)two;
+      if (two) {
+        *reinterpret_cast<uint16_t*>(s_sc + (y + 1) * scp + 4 + x) = (uint16_t)two;
+        const int idx = y * rw + x;                             // row-major pixel index = bitmap bit
+        if ((int)(two & 0xff) >= tmin) atomicOr(&s_bmC[idx >> 5], 1u << (idx & 31));
+        if ((int)(two >> 8) >= tmin) atomicOr(&s_bmC[(idx + 1) >> 5], 1u << ((idx + 1) & 31));
+      }
     };
     const uint32_t bias = (0x8000u - (uint32_t)(tmin + 1)) * 0x00010001u;  // bit 15 of (q + bias) <=> q > tmin
     int qlen = 0;
-    int y = (warp * 32 + lane) / G, g = (warp * 32 + lane) - y * G;
+    int y = __umulhi((uint32_t)(warp * 32 + lane), g_magic), g = (warp * 32 + lane) - y * G;
     for (int i0 = warp * 32; i0 < ngroups; i0 += kFastThreads) {
       uint32_t flags = 0;
       if (i0 + lane < ngroups) {
@@ -225,37 +233,44 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
         if (s >= tB) { atomicOr(&s_bmB[idx >> 5], 1u << (idx & 31)); nB++; }
       }
     };
+    // candidates come from the bitmap written by phase 2: 32 words (1024 pixels) per warp round
     int qlen = 0;
-    int y = (warp * 32 + lane) / G, g = (warp * 32 + lane) - y * G;
-    for (int i0 = warp * 32; i0 < ngroups; i0 += kFastThreads) {
-      uint32_t w4 = 0;
-      if (i0 + lane < ngroups) w4 = *reinterpret_cast<const uint32_t*>(s_sc + (y + 1) * scp + 4 + 4 * g);
-      int flags = 0;
-      if (w4) {
+    for (int i0 = warp * 32; i0 < nbw; i0 += kFastThreads) {
+      const int i = i0 + lane;
+      uint32_t bits = i < nbw ? s_bmC[i] : 0u;
+      const int cnt = __popc(bits);
+      if (!__any_sync(0xffffffffu, cnt)) continue;
+      int incl = cnt;
 #pragma unroll
-        for (int k = 0; k < 4; k++) flags |= ((int)((w4 >> (8 * k)) & 255) >= tmin) << k;
+      for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
       }
-      if (__any_sync(0xffffffffu, flags)) {
-        int cnt = __popc(flags), incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const int o = __shfl_up_sync(0xffffffffu, incl, d);
-          if (lane >= d) incl += o;
+      const int round_total = __shfl_sync(0xffffffffu, incl, 31);
+      if (qlen + round_total > kFastQueue) {
+        // dense textures (e.g. noise): more candidates than the queue holds; each lane walks its own word
+        while (bits) {
+          const int idx = 32 * i + __ffs(bits) - 1;
+          bits &= bits - 1;
+          const int yy = __umulhi((uint32_t)idx, rw_magic);
+          nms(((uint32_t)yy << 16) | (uint32_t)(idx - yy * rw));
         }
-        int off = qlen + incl - cnt;
-#pragma unroll
-        for (int k = 0; k < 4; k++)
-          if (flags & (1 << k)) q[off++] = ((uint32_t)y << 16) | (uint32_t)(4 * g + k);
-        qlen += __shfl_sync(0xffffffffu, incl, 31);
-        __syncwarp();
-        while (qlen >= 32) {
-          qlen -= 32;
-          nms(q[qlen + lane]);
-        }
-        __syncwarp();
+        continue;
       }
-      y += gstep_y; g += gstep_g;
-      if (g >= G) { g -= G; y++; }
+      int off = qlen + incl - cnt;
+      while (bits) {
+        const int idx = 32 * i + __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int yy = __umulhi((uint32_t)idx, rw_magic);
+        q[off++] = ((uint32_t)yy << 16) | (uint32_t)(idx - yy * rw);
+      }
+      qlen += round_total;
+      __syncwarp();
+      while (qlen >= 32) {
+        qlen -= 32;
+        nms(q[qlen + lane]);
+      }
+      __syncwarp();
     }
     if (lane < qlen) nms(q[lane]);
   }
@@ -298,7 +313,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
     while (bits) {
       const int bit = __ffs(bits) - 1;
       bits &= bits - 1;
-      const int idx = 32 * i + bit, y = idx / rw, x = idx - y * rw;
+      const int idx = 32 * i + bit, y = __umulhi((uint32_t)idx, rw_magic), x = idx - y * rw;
       const int lx = c.x0 + x, ly = c.y0 + y;
       Cand r;
       r.resp = P->score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
