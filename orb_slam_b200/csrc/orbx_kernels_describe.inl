@@ -84,17 +84,21 @@ __global__ void __launch_bounds__(32 * kDescWarps) describe_kernel(ChunkBuffers 
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (gw >= nslots_total) return;
   const int frame = gw / P->nfeatures, slot = gw - frame * P->nfeatures;
+  // level of the slot and output offset = sum of the lower levels' counts: one parallel round of loads (lane = level)
+  // instead of a chain of dependent ones
   const int32_t* cnt = b.kp_count + frame * kMaxLevels;
-  int level = 0, out_off = 0;
-  while (level + 1 < P->nlevels && slot >= P->lv[level + 1].kp_base) { out_off += cnt[level]; level++; }
+  const int my_cnt = lane < P->nlevels ? cnt[lane] : 0;
+  const int my_base = lane < P->nlevels ? P->lv[lane].kp_base : 0x7fffffff;
+  const int level = __popc(__ballot_sync(0xffffffffu, lane >= 1 && slot >= my_base));
+  const int out_off = __reduce_add_sync(0xffffffffu, lane < level ? my_cnt : 0);
+  const int level_cnt = __shfl_sync(0xffffffffu, my_cnt, level);
   const LevelPlan& L = P->lv[level];
   const int idx = slot - L.kp_base;
-  if (slot == 0 && lane == 0) {
-    int tot = 0;
-    for (int l = 0; l < P->nlevels; l++) tot += cnt[l];
-    out_n[frame] = tot;
+  {
+    const int tot = __reduce_add_sync(0xffffffffu, my_cnt);
+    if (slot == 0 && lane == 0) out_n[frame] = tot;
   }
-  if (idx >= cnt[level]) return;
+  if (idx >= level_cnt) return;
   const Cand kp = b.kp[(int64_t)frame * P->nfeatures + slot];
   const int cx = kp.xy & 0xffff, cy = kp.xy >> 16;
   int pitch;
@@ -117,7 +121,7 @@ __global__ void __launch_bounds__(32 * kDescWarps) describe_kernel(ChunkBuffers 
     uint32_t* dst = reinterpret_cast<uint32_t*>(s_patch[warp]);
     const int half = lane >> 4, j = lane & 15, wpitch = lpitch >> 2;
     if (j < kPatchWords) {
-#pragma unroll 5
+#pragma unroll
       for (int r0 = 0; r0 < kPatchRows; r0 += 2) {
         const int r = r0 + half;
         if (r < kPatchRows) dst[r * kPatchWords + j] = src[r * wpitch + j];
@@ -158,9 +162,12 @@ __global__ void __launch_bounds__(32 * kDescWarps) describe_kernel(ChunkBuffers 
 #pragma unroll
     for (int e = 0; e < 2; e++) {
       const uint32_t w = pat[j] >> (16 * e);
-      const float px = (float)(int8_t)(w & 0xff), py = (float)(int8_t)((w >> 8) & 0xff);
-      const int ry = __float2int_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)));
-      const int rx = __float2int_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)));
+      // exact small-integer <-> float conversions through the 1.5 * 2^23 trick (FADD/IADD instead of the XU pipe's
+      // I2F / F2I); float -> int rounds half to even exactly like cvRound
+      const float px = __fsub_rn(__int_as_float(0x4B400000 + (int)(int8_t)(w & 0xff)), 12582912.f);
+      const float py = __fsub_rn(__int_as_float(0x4B400000 + (int)(int8_t)((w >> 8) & 0xff)), 12582912.f);
+      const int ry = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)), 12582912.f)) - 0x4B400000;
+      const int rx = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)), 12582912.f)) - 0x4B400000;
       if (fast_path) {
         t[e] = sp[ry * kPatchPitch + rx];
       } else {
