@@ -48,6 +48,10 @@ struct CellPlan {
   int16_t skipped;       // 1: the reference `continue`s over this cell (hX <= 0 or hY <= 0)
   int32_t cand_off;      // offset of the cell's candidate list in the per-frame candidate array
   int32_t cand_cap;      // ceil(rw/2)*ceil(rh/2): NMS survivors are pairwise non-adjacent, so this cannot overflow
+  // reciprocal multipliers (fast_magic) of the three row lengths fast_cells_kernel splits flat indices by
+  uint32_t m_grp;        // staging groups (4 px) per sub-image row      = fast_ngrp(rw + 6)
+  uint32_t m_g8;         // reject groups (8 px) per scored row          = (rw + 7) / 8
+  uint32_t m_wpr;        // bitmap words (32 px) per scored row          = (rw + 31) / 32
 };
 
 struct ResizeX {  // per destination column: source column and the two 11-bit weights (cv::resize INTER_LINEAR)
@@ -79,15 +83,25 @@ struct HostPlan {
 };
 
 // Shared-memory geometry of fast_cells_kernel for a cell sub-image of cw x ch pixels (scored region (cw-6) x (ch-6)):
-// the sub-image is staged as zero-extended u16 (two pixels per 32-bit word for the packed VIMNMX3.U16x2 ladder),
-// sub-image column c at halfword c + 5 so that scored column 0 sits on a 16-byte boundary.
+//   u16 image   zero-extended pixels, two per 32-bit word, for the packed VIMNMX3.U16x2 ladder; sub-image column c at
+//               halfword c + 5 so that scored column 0 sits on a 16-byte boundary
+//   u8 image    the same pixels >> 1 (7 bits) at byte c + 5, for the byte-SIMD (VABSDIFF4) reject
+//   score map   u8, one zero ring
+//   4 bitmaps   one bit per scored pixel, rows padded to 32-pixel words (row-major word order = row-major pixel order)
+inline __host__ __device__ int fast_ngrp(int cw) { return (cw + 5 + 3) >> 2; }           // 4-pixel staging groups/row
 inline __host__ __device__ int fast_sp16(int cw) { return (cw + 12 + 7) & ~7; }          // halfwords per row
-inline __host__ __device__ int fast_scp(int rw) { return ((rw + 3) & ~3) + 8; }        // score-map bytes per row
+inline __host__ __device__ int fast_bp(int rw) { return 8 * ((rw + 7) >> 3) + 16; }      // u8-image bytes per row
+inline __host__ __device__ int fast_scp(int rw) { return ((rw + 3) & ~3) + 8; }          // score-map bytes per row
 inline __host__ __device__ int fast_img_bytes(int cw, int ch) { return (ch * fast_sp16(cw) * 2 + 15) & ~15; }
+inline __host__ __device__ int fast_h8_bytes(int cw, int ch) { return (ch * fast_bp(cw - 6) + 15) & ~15; }
 inline __host__ __device__ int fast_sc_bytes(int rw, int rh) { return ((rh + 2) * fast_scp(rw) + 15) & ~15; }
-inline __host__ __device__ int fast_cell_smem(int cw, int ch) {  // image + score map + three pixel bitmaps
-  return fast_img_bytes(cw, ch) + fast_sc_bytes(cw - 6, ch - 6) + 12 * (((cw - 6) * (ch - 6) + 31) / 32) + 16;
+inline __host__ __device__ int fast_bm_words(int rw, int rh) { return rh * ((rw + 31) >> 5); }
+inline __host__ __device__ int fast_cell_smem(int cw, int ch) {
+  return fast_img_bytes(cw, ch) + fast_h8_bytes(cw, ch) + fast_sc_bytes(cw - 6, ch - 6) +
+         16 * fast_bm_words(cw - 6, ch - 6) + 16;
 }
+// floor(i / d) == umulhi(i, fast_magic(d)) for i * d < 2^32; d == 1 gives 0, which magic_div() reads as "i itself"
+inline uint32_t fast_magic(uint32_t d) { return 0xffffffffu / d + 1u; }
 
 // Builds the plan exactly as the reference's constructor and ComputeKeyPoints do (float/double mix preserved).
 // Returns ORBX_OK, ORBX_ERR_UNSUPPORTED (grid with 0 columns/rows, cell outside the level) or ORBX_ERR_ARG.

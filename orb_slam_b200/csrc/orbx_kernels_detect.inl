@@ -39,21 +39,75 @@ __device__ float harris_response(const uint8_t* p, int step) {
 // rule (:609-614) on the same score map, then an ORDER-PRESERVING emission (row-major, the input order of
 // retainBest's nth_element) into the cell's candidate list.
 //
-// Shared memory: the cell sub-image as zero-extended u16 (sub-image column c at halfword c + 5, so scored column 0
-// is 16-byte aligned), the u8 score map with a zero ring, two survivor bitmaps (threshold fastTh / 7).
-// Work is split DENSE-CHEAP / SPARSE-HEAVY with warp-local queues so that the heavy code always runs on full warps:
-//   1  every 4-pixel group: opposite-pair reject  min(max(|r0-v|,|r8-v|), max(|r4-v|,|r12-v|)) > tmin  (an arc of 9
-//      contains a pixel of every opposite pair) on packed pixel PAIRS; surviving pairs are queued
-//   2  queued pairs, 32 at a time: the full VIMNMX3.U16x2 ladder -> score bytes
-//   3  every score word: pixels with S >= tmin are queued; queued pixels, 32 at a time: strict 3x3 NMS -> bitmaps
+// Work is split DENSE-CHEAP / SPARSE-HEAVY; the sparse stages run from per-warp queues so that the heavy code always
+// executes on full warps:
+//   0  stage the sub-image twice: zero-extended u16 (ladder operand) and u8 >> 1 (reject operand)
+//   1  byte-SIMD reject, 8 pixels per thread: an arc of 9 ring pixels contains one pixel of every opposite pair, so a
+//      corner at threshold t needs (|up-v| > t or |down-v| > t) and (|left-v| > t or |right-v| > t).  On the halved
+//      image |a'-v'| >= ceil(t/2) is implied by |a-v| > t, differences fit 7 bits, and adding (0x80 - ceil(t/2)) to a
+//      VABSDIFF4 result raises bit 7 of each byte exactly when the halved test passes: 2 instructions per 4 pixels
+//      per ring direction.  The 8 pass bits go to a bitmap byte.  (Conservative: never drops a corner.)
+//   2  flagged pixel PAIRS, 32 at a time: the full VIMNMX3.U16x2 ladder -> score bytes, bitmap C = (S >= tmin)
+//   3  bitmap C pixels, 32 at a time: strict 3x3 NMS -> bitmaps A (S >= fastTh) and B (S >= 7)
 //   4  popcount prefix over the bitmap words -> survivors in row-major order
 // Pixels failing the reject keep score 0 instead of their true S < tmin: harmless, a neighbour below tmin can never
 // suppress a survivor (S_c >= t >= tmin > S_n), which is also why one threshold-free map serves both thresholds.
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kFastThreads = 256, kFastWarps = kFastThreads / 32, kFastQueue = 160;
+constexpr int kFastThreads = 256, kFastWarps = kFastThreads / 32, kFastQueue = 160, kFastSub = 4;
 
 __device__ __forceinline__ uint32_t hw_mid(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }
-__device__ __forceinline__ uint32_t absdiff_u16x2(uint32_t a, uint32_t v) { return __vmaxu2(a, v) - __vminu2(a, v); }
+// floor(i / d) with m = fast_magic(d) (orbx_internal.cuh); m == 0 encodes d == 1
+__device__ __forceinline__ int magic_div(int i, uint32_t m) { return m ? (int)__umulhi((uint32_t)i, m) : i; }
+
+// Appends base + b for every set bit b of every lane's `bits` to the warp's queue (lane order, then bit order) and
+// runs fn on each full group of 32 entries.  A round that would overflow the queue is split into sub-rounds of
+// kFastSub lanes (<= 32 * kFastSub = 128 new entries on top of <= 31 left over).  Must be called by all 32 lanes.
+template <class F>
+__device__ __forceinline__ void queue_bits(uint32_t* q, int& qlen, uint32_t bits, uint32_t base, int lane, F&& fn) {
+  const int cnt = __popc(bits);
+  if (!__any_sync(0xffffffffu, cnt)) return;
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  const int excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
+  if (qlen + total <= kFastQueue) {
+    int off = qlen + excl;
+    while (bits) {
+      q[off++] = base + (uint32_t)(__ffs(bits) - 1);
+      bits &= bits - 1;
+    }
+    qlen += total;
+    __syncwarp();
+    while (qlen >= 32) {
+      qlen -= 32;
+      fn(q[qlen + lane]);
+    }
+    __syncwarp();
+    return;
+  }
+#pragma unroll 1
+  for (int k = 0; k < 32; k += kFastSub) {
+    const int lo = __shfl_sync(0xffffffffu, excl, k), hi = __shfl_sync(0xffffffffu, incl, k + kFastSub - 1);
+    if (hi == lo) continue;
+    if (lane >= k && lane < k + kFastSub) {
+      int off = qlen + excl - lo;
+      while (bits) {
+        q[off++] = base + (uint32_t)(__ffs(bits) - 1);
+        bits &= bits - 1;
+      }
+    }
+    qlen += hi - lo;
+    __syncwarp();
+    while (qlen >= 32) {
+      qlen -= 32;
+      fn(q[qlen + lane]);
+    }
+    __syncwarp();
+  }
+}
 
 // Full score of the pixel pair at scored position (x even, y): loads the 16 ring values of both pixels as packed
 // halfwords straight from the staged sub-image (row pitch sp32 words).
@@ -120,7 +174,6 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   const int cell = blockIdx.x, frame = blockIdx.y;
   const CellPlan c = b.cells[cell];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const unsigned lt_mask = (1u << lane) - 1;
   int32_t* n_total = b.n_total + (int64_t)frame * P->total_cells + cell;
   if (c.rw <= 0) {
     if (tid == 0) *n_total = 0;
@@ -129,29 +182,51 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   int pitch;
   const uint8_t* img = level_ptr(b, P, c.level, frame, &pitch);
   const int rw = c.rw, rh = c.rh, cw = rw + 6, ch = rh + 6;   // cw x ch = the sub-image handed to cv::FAST
-  const int sp16 = fast_sp16(cw), sp32 = sp16 >> 1, scp = fast_scp(rw);
-  const int npx = rw * rh, nbw = (npx + 31) >> 5;
+  const int sp16 = fast_sp16(cw), sp32 = sp16 >> 1, bp = fast_bp(rw), scp = fast_scp(rw);
+  const int wpr = (rw + 31) >> 5, nbw = wpr * rh;               // bitmap words per scored row / per bitmap
   uint16_t* s_img = reinterpret_cast<uint16_t*>(smem);          // [ch][sp16]
-  uint8_t* s_sc = smem + fast_img_bytes(cw, ch);                // [rh + 2][scp], scored column x at byte 4 + x
+  uint8_t* s_h8 = smem + fast_img_bytes(cw, ch);                // [ch][bp]
+  uint8_t* s_sc = s_h8 + fast_h8_bytes(cw, ch);                 // [rh + 2][scp], scored column x at byte 4 + x
   uint32_t* s_bmA = reinterpret_cast<uint32_t*>(s_sc + fast_sc_bytes(rw, rh));  // survivors with S >= fastTh
   uint32_t* s_bmB = s_bmA + nbw;                                                // survivors with S >= 7
   uint32_t* s_bmC = s_bmB + nbw;                                                // pixels with S >= tmin (NMS inputs)
-  const int G = (rw + 3) >> 2;                                  // 4-pixel groups per scored row
-  const int ngroups = G * rh;
+  uint32_t* s_bmF = s_bmC + nbw;                                                // pixels passing the reject
 
-  // ---- 0  stage the sub-image: aligned 32-bit global loads, four u16 stores ------------------------------------------
+  // ---- 0  stage the sub-image: 4 pixels per thread from two aligned 32-bit global loads ------------------------------
+  // group u of row r = sub-image columns 4u-5 .. 4u-2 (the first group starts left of the sub-image, inside the level:
+  // cells start at column >= 13) -> halfwords / bytes 4u .. 4u+3 of the staged rows
   {
-    const int wpr = (cw + 3 + 3) >> 2;  // aligned words covering one sub-image row (any misalignment 0..3)
-    for (int i = tid; i < ch * wpr; i += kFastThreads) {
-      const int r = i / wpr, j = i - r * wpr;
-      const uint8_t* row = img + (int64_t)(c.y0 - 3 + r) * pitch + (c.x0 - 3);
-      const int mis = (int)((uintptr_t)row & 3);
-      if (4 * j >= mis + cw) continue;                          // this row needs one word less
-      const uint32_t w = *reinterpret_cast<const uint32_t*>(row - mis + 4 * j);
-      uint16_t* dst = s_img + r * sp16 + 5 + 4 * j - mis;       // >= 2; bytes outside the sub-image land in padding
-      dst[0] = w & 0xff; dst[1] = (w >> 8) & 0xff; dst[2] = (w >> 16) & 0xff; dst[3] = w >> 24;
+    const int ngrp = fast_ngrp(cw);
+    const uint8_t* img0 = img + (int64_t)(c.y0 - 3) * pitch + (c.x0 - 3) - 5;
+    const int sr = magic_div(kFastThreads, c.m_grp), su = kFastThreads - sr * ngrp;
+    int r = magic_div(tid, c.m_grp), u = tid - r * ngrp;
+    // four groups per thread per round, all eight loads issued before the first use
+    for (int i = tid; i < ch * ngrp; i += 4 * kFastThreads) {
+      uint32_t lo[4], hi[4], sh[4];
+      int o[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        o[k] = -1;
+        if (i + k * kFastThreads < ch * ngrp) {
+          const uintptr_t p = reinterpret_cast<uintptr_t>(img0 + r * pitch + 4 * u);
+          const uint32_t* a = reinterpret_cast<const uint32_t*>(p & ~(uintptr_t)3);
+          lo[k] = a[0]; hi[k] = a[1]; sh[k] = ((uint32_t)p & 3u) * 8u;
+          o[k] = (r << 16) | u;
+        }
+        r += sr; u += su;
+        if (u >= ngrp) { u -= ngrp; r++; }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        if (o[k] < 0) continue;
+        const int rr = o[k] >> 16, uu = o[k] & 0xffff;
+        const uint32_t b4 = __funnelshift_r(lo[k], hi[k], sh[k]);
+        *reinterpret_cast<uint2*>(s_img + rr * sp16 + 4 * uu) =
+            make_uint2(__byte_perm(b4, 0, 0x4140), __byte_perm(b4, 0, 0x4342));
+        *reinterpret_cast<uint32_t*>(s_h8 + rr * bp + 4 * uu) = (b4 >> 1) & 0x7f7f7f7fu;
+      }
     }
-    const int nz = (fast_sc_bytes(rw, rh) >> 2) + 3 * nbw;       // score map + the three bitmaps are contiguous
+    const int nz = (fast_sc_bytes(rw, rh) >> 2) + 3 * nbw;       // score map + bitmaps A, B, C are contiguous
     for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint32_t*>(s_sc)[i] = 0;
     if (tid < 2) s_cnt[tid] = 0;
   }
@@ -160,11 +235,34 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   const int tA = P->fast_th, tB = kRetryTh, tmin = max(min(tA, tB), 1);
   uint32_t* q = s_queue[warp];
   const uint32_t* s_img32 = reinterpret_cast<const uint32_t*>(s_img);
-  const int gstep_y = kFastThreads / G, gstep_g = kFastThreads - gstep_y * G;
-  // floor(i / d) == umulhi(i, floor(2^32 / d) + 1) for i * d < 2^32 (all indices here are < 2^17)
-  const uint32_t rw_magic = 0xffffffffu / (uint32_t)rw + 1u, g_magic = 0xffffffffu / (uint32_t)G + 1u;
 
-  // ---- 1 + 2  scores ---------------------------------------------------------------------------------------------------
+  // ---- 1  reject: 8 pixels per thread on the halved u8 image -----------------------------------------------------------
+  {
+    const int G8 = (rw + 7) >> 3, n8 = G8 * rh;
+    const uint32_t bias4 = (0x80u - (uint32_t)((tmin + 1) >> 1)) * 0x01010101u;
+    const int sy = magic_div(kFastThreads, c.m_g8), sg = kFastThreads - sy * G8;
+    int y = magic_div(tid, c.m_g8), g = tid - y * G8;
+    uint8_t* s_flag = reinterpret_cast<uint8_t*>(s_bmF);
+    for (int i = tid; i < n8; i += kFastThreads) {
+      const uint8_t* ctr = s_h8 + (y + 3) * bp + 8 * g + 8;     // centre bytes of scored pixels 8g .. 8g+7
+      const uint2 C = *reinterpret_cast<const uint2*>(ctr);
+      const uint2 U = *reinterpret_cast<const uint2*>(ctr - 3 * bp), D = *reinterpret_cast<const uint2*>(ctr + 3 * bp);
+      const uint32_t W0 = *reinterpret_cast<const uint32_t*>(ctr - 4), W3 = *reinterpret_cast<const uint32_t*>(ctr + 8);
+      const uint32_t Lx = __byte_perm(W0, C.x, 0x4321), Ly = __byte_perm(C.x, C.y, 0x4321);   // columns x - 3
+      const uint32_t Rx = __byte_perm(C.x, C.y, 0x6543), Ry = __byte_perm(C.y, W3, 0x6543);   // columns x + 3
+      const uint32_t mx = ((__vabsdiffu4(U.x, C.x) + bias4) | (__vabsdiffu4(D.x, C.x) + bias4)) &
+                          ((__vabsdiffu4(Lx, C.x) + bias4) | (__vabsdiffu4(Rx, C.x) + bias4)) & 0x80808080u;
+      const uint32_t my = ((__vabsdiffu4(U.y, C.y) + bias4) | (__vabsdiffu4(D.y, C.y) + bias4)) &
+                          ((__vabsdiffu4(Ly, C.y) + bias4) | (__vabsdiffu4(Ry, C.y) + bias4)) & 0x80808080u;
+      // bits 7/15/23/31 -> one nibble: the products of 0x00204081 land them on bits 28..31 without collisions
+      s_flag[y * (4 * wpr) + g] = (uint8_t)(((mx * 0x00204081u) >> 28) | (((my * 0x00204081u) >> 24) & 0xf0u));
+      y += sy; g += sg;
+      if (g >= G8) { g -= G8; y++; }
+    }
+  }
+  __syncthreads();
+
+  // ---- 2  full score of the flagged pixel pairs -----------------------------------------------------------------------
   {
     auto heavy = [&](uint32_t e) {
       const int x = e & 0xffff, y = e >> 16;
@@ -173,46 +271,24 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
       if (x + 1 >= rw) two &= 0xff;
       if (two) {
         *reinterpret_cast<uint16_t*>(s_sc + (y + 1) * scp + 4 + x) = (uint16_t)two;
-        const int idx = y * rw + x;                             // row-major pixel index = bitmap bit
-        if ((int)(two & 0xff) >= tmin) atomicOr(&s_bmC[idx >> 5], 1u << (idx & 31));
-        if ((int)(two >> 8) >= tmin) atomicOr(&s_bmC[(idx + 1) >> 5], 1u << ((idx + 1) & 31));
+        const uint32_t m = ((int)(two & 0xff) >= tmin ? 1u : 0u) | ((int)(two >> 8) >= tmin ? 2u : 0u);
+        if (m) atomicOr(&s_bmC[y * wpr + (x >> 5)], m << (x & 31));   // x is even: both bits in one word
       }
     };
-    const uint32_t bias = (0x8000u - (uint32_t)(tmin + 1)) * 0x00010001u;  // bit 15 of (q + bias) <=> q > tmin
     int qlen = 0;
-    int y = __umulhi((uint32_t)(warp * 32 + lane), g_magic), g = (warp * 32 + lane) - y * G;
-    for (int i0 = warp * 32; i0 < ngroups; i0 += kFastThreads) {
-      uint32_t flags = 0;
-      if (i0 + lane < ngroups) {
-        const uint2* mid = reinterpret_cast<const uint2*>(s_img + (y + 3) * sp16 + 4 * g + 4);
-        const uint2 a0 = mid[0], a1 = mid[1], a2 = mid[2];     // halfwords 4g+4 .. 4g+15 of the centre row
-        const uint2 up = *reinterpret_cast<const uint2*>(s_img + y * sp16 + 4 * g + 8);        // dy = -3, dx = 0
-        const uint2 dn = *reinterpret_cast<const uint2*>(s_img + (y + 6) * sp16 + 4 * g + 8);  // dy = +3
-        // pair 0: centre a1.x, left = hw(4g+5,4g+6), right = hw(4g+11,4g+12); pair 1: one word to the right
-        const uint32_t qa = __vminu2(__vmaxu2(absdiff_u16x2(up.x, a1.x), absdiff_u16x2(dn.x, a1.x)),
-                                     __vmaxu2(absdiff_u16x2(hw_mid(a0.x, a0.y), a1.x),
-                                              absdiff_u16x2(hw_mid(a1.y, a2.x), a1.x)));
-        const uint32_t qb = __vminu2(__vmaxu2(absdiff_u16x2(up.y, a1.y), absdiff_u16x2(dn.y, a1.y)),
-                                     __vmaxu2(absdiff_u16x2(hw_mid(a0.y, a1.x), a1.y),
-                                              absdiff_u16x2(hw_mid(a2.x, a2.y), a1.y)));
-        if ((qa + bias) & 0x80008000u) flags |= 1;
-        if (((qb + bias) & 0x80008000u) && 4 * g + 2 < rw) flags |= 2;
+    // word i = (round * 32 + lane) * 8 + warp: every warp samples the whole cell, so the sparse work is balanced
+    for (int i0 = 0; i0 < nbw; i0 += kFastThreads) {
+      const int i = i0 + lane * kFastWarps + warp;
+      uint32_t bits = 0, base = 0;
+      if (i < nbw) {
+        const int y = magic_div(i, c.m_wpr), wx = i - y * wpr;
+        uint32_t f = s_bmF[i];
+        const int nv = rw - 32 * wx;                            // columns >= rw were computed from padding
+        if (nv < 32) f &= (1u << nv) - 1u;
+        bits = (f | (f >> 1)) & 0x55555555u;                    // pair (x, x+1), x even, when either pixel passed
+        base = ((uint32_t)y << 16) | (uint32_t)(32 * wx);
       }
-      const unsigned b0 = __ballot_sync(0xffffffffu, flags & 1), b1 = __ballot_sync(0xffffffffu, flags & 2);
-      if (b0 | b1) {
-        // queue order is irrelevant: all "pair 0" entries first, then all "pair 1" entries
-        if (flags & 1) q[qlen + __popc(b0 & lt_mask)] = ((uint32_t)y << 16) | (uint32_t)(4 * g);
-        if (flags & 2) q[qlen + __popc(b0) + __popc(b1 & lt_mask)] = ((uint32_t)y << 16) | (uint32_t)(4 * g + 2);
-        qlen += __popc(b0) + __popc(b1);
-        __syncwarp();
-        while (qlen >= 32) {
-          qlen -= 32;
-          heavy(q[qlen + lane]);
-        }
-        __syncwarp();
-      }
-      y += gstep_y; g += gstep_g;
-      if (g >= G) { g -= G; y++; }
+      queue_bits(q, qlen, bits, base, lane, heavy);
     }
     if (lane < qlen) heavy(q[lane]);
   }
@@ -228,49 +304,21 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
       const int m = max(max(max(p[-1], p[1]), max(p[-scp - 1], p[-scp])),
                         max(max(p[-scp + 1], p[scp - 1]), max(p[scp], p[scp + 1])));
       if (s > m) {
-        const int idx = y * rw + x;
-        if (s >= tA) { atomicOr(&s_bmA[idx >> 5], 1u << (idx & 31)); nA++; }
-        if (s >= tB) { atomicOr(&s_bmB[idx >> 5], 1u << (idx & 31)); nB++; }
+        const int w = y * wpr + (x >> 5);
+        if (s >= tA) { atomicOr(&s_bmA[w], 1u << (x & 31)); nA++; }
+        if (s >= tB) { atomicOr(&s_bmB[w], 1u << (x & 31)); nB++; }
       }
     };
-    // candidates come from the bitmap written by phase 2: 32 words (1024 pixels) per warp round
     int qlen = 0;
-    for (int i0 = warp * 32; i0 < nbw; i0 += kFastThreads) {
-      const int i = i0 + lane;
-      uint32_t bits = i < nbw ? s_bmC[i] : 0u;
-      const int cnt = __popc(bits);
-      if (!__any_sync(0xffffffffu, cnt)) continue;
-      int incl = cnt;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += o;
+    for (int i0 = 0; i0 < nbw; i0 += kFastThreads) {
+      const int i = i0 + lane * kFastWarps + warp;
+      uint32_t bits = 0, base = 0;
+      if (i < nbw) {
+        const int y = magic_div(i, c.m_wpr);
+        bits = s_bmC[i];
+        base = ((uint32_t)y << 16) | (uint32_t)(32 * (i - y * wpr));
       }
-      const int round_total = __shfl_sync(0xffffffffu, incl, 31);
-      if (qlen + round_total > kFastQueue) {
-        // dense textures (e.g. noise): more candidates than the queue holds; each lane walks its own word
-        while (bits) {
-          const int idx = 32 * i + __ffs(bits) - 1;
-          bits &= bits - 1;
-          const int yy = __umulhi((uint32_t)idx, rw_magic);
-          nms(((uint32_t)yy << 16) | (uint32_t)(idx - yy * rw));
-        }
-        continue;
-      }
-      int off = qlen + incl - cnt;
-      while (bits) {
-        const int idx = 32 * i + __ffs(bits) - 1;
-        bits &= bits - 1;
-        const int yy = __umulhi((uint32_t)idx, rw_magic);
-        q[off++] = ((uint32_t)yy << 16) | (uint32_t)(idx - yy * rw);
-      }
-      qlen += round_total;
-      __syncwarp();
-      while (qlen >= 32) {
-        qlen -= 32;
-        nms(q[qlen + lane]);
-      }
-      __syncwarp();
+      queue_bits(q, qlen, bits, base, lane, nms);
     }
     if (lane < qlen) nms(q[lane]);
   }
@@ -288,7 +336,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   }
   if (total == 0) return;
 
-  // ---- 4  ordered emission: popcount prefix over the bitmap words (bit index = y * rw + x, row-major) --------------------
+  // ---- 4  ordered emission: popcount prefix over the bitmap words (row-major) ------------------------------------------
   Cand* out = b.cand + (int64_t)frame * P->cand_per_frame + c.cand_off;
   int base = 0;
   for (int i0 = 0; i0 < nbw; i0 += kFastThreads) {
@@ -310,16 +358,19 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
       if (wq < warp) off += v;
       round_total += v;
     }
-    while (bits) {
-      const int bit = __ffs(bits) - 1;
-      bits &= bits - 1;
-      const int idx = 32 * i + bit, y = __umulhi((uint32_t)idx, rw_magic), x = idx - y * rw;
-      const int lx = c.x0 + x, ly = c.y0 + y;
-      Cand r;
-      r.resp = P->score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
-                                                  : (float)s_sc[(y + 1) * scp + 4 + x];
-      r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
-      out[off++] = r;
+    if (bits) {
+      const int y = magic_div(i, c.m_wpr), xb = 32 * (i - y * wpr);
+      const int ly = c.y0 + y;
+      while (bits) {
+        const int x = xb + __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int lx = c.x0 + x;
+        Cand r;
+        r.resp = P->score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
+                                                    : (float)s_sc[(y + 1) * scp + 4 + x];
+        r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
+        out[off++] = r;
+      }
     }
     base += round_total;
     __syncthreads();

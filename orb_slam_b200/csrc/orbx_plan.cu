@@ -179,6 +179,9 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
             c.x0 = (int16_t)(cx0 + 3); c.y0 = (int16_t)(cy0 + 3);
             c.rw = (int16_t)(cw - 6); c.rh = (int16_t)(ch - 6);
             c.cand_cap = ((c.rw + 1) / 2) * ((c.rh + 1) / 2);
+            c.m_grp = fast_magic(fast_ngrp(cw));
+            c.m_g8 = fast_magic((c.rw + 7) / 8);
+            c.m_wpr = fast_magic((c.rw + 31) / 32);
             hp.fast_smem_bytes = std::max(hp.fast_smem_bytes, fast_cell_smem(cw, ch));
           }
         }
