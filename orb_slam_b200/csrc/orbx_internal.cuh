@@ -49,7 +49,7 @@ struct CellPlan {
   int32_t cand_off;      // offset of the cell's candidate list in the per-frame candidate array
   int32_t cand_cap;      // ceil(rw/2)*ceil(rh/2): NMS survivors are pairwise non-adjacent, so this cannot overflow
   // reciprocal multipliers (fast_magic) of the three row lengths fast_cells_kernel splits flat indices by
-  uint32_t m_grp;        // staging groups (4 px) per sub-image row      = fast_ngrp(rw + 6)
+  uint32_t m_grp;        // staging groups (8 px) per sub-image row      = fast_ngrp(rw + 6)
   uint32_t m_g8;         // reject groups (8 px) per scored row          = (rw + 7) / 8
   uint32_t m_wpr;        // bitmap words (32 px) per scored row          = (rw + 31) / 32
 };
@@ -88,7 +88,7 @@ struct HostPlan {
 //   u8 image    the same pixels >> 1 (7 bits) at byte c + 5, for the byte-SIMD (VABSDIFF4) reject
 //   score map   u8, one zero ring
 //   4 bitmaps   one bit per scored pixel, rows padded to 32-pixel words (row-major word order = row-major pixel order)
-inline __host__ __device__ int fast_ngrp(int cw) { return (cw + 5 + 3) >> 2; }           // 4-pixel staging groups/row
+inline __host__ __device__ int fast_ngrp(int cw) { return (cw + 5 + 7) >> 3; }           // 8-pixel staging groups/row
 inline __host__ __device__ int fast_sp16(int cw) { return (cw + 12 + 7) & ~7; }          // halfwords per row
 inline __host__ __device__ int fast_bp(int rw) { return 8 * ((rw + 7) >> 3) + 16; }      // u8-image bytes per row
 inline __host__ __device__ int fast_scp(int rw) { return ((rw + 3) & ~3) + 8; }          // score-map bytes per row

@@ -181,6 +181,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   }
   int pitch;
   const uint8_t* img = level_ptr(b, P, c.level, frame, &pitch);
+  const int tA = P->fast_th;
   const int rw = c.rw, rh = c.rh, cw = rw + 6, ch = rh + 6;   // cw x ch = the sub-image handed to cv::FAST
   const int sp16 = fast_sp16(cw), sp32 = sp16 >> 1, bp = fast_bp(rw), scp = fast_scp(rw);
   const int wpr = (rw + 31) >> 5, nbw = wpr * rh;               // bitmap words per scored row / per bitmap
@@ -192,47 +193,53 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   uint32_t* s_bmC = s_bmB + nbw;                                                // pixels with S >= tmin (NMS inputs)
   uint32_t* s_bmF = s_bmC + nbw;                                                // pixels passing the reject
 
-  // ---- 0  stage the sub-image: 4 pixels per thread from two aligned 32-bit global loads ------------------------------
-  // group u of row r = sub-image columns 4u-5 .. 4u-2 (the first group starts left of the sub-image, inside the level:
-  // cells start at column >= 13) -> halfwords / bytes 4u .. 4u+3 of the staged rows
+  // ---- 0  stage the sub-image: 8 pixels per thread from three aligned 32-bit global loads -----------------------------
+  // group u of row r = sub-image columns 8u-5 .. 8u+2 (the first group starts left of the sub-image, inside the level:
+  // cells start at column >= 13) -> halfwords / bytes 8u .. 8u+7 of the staged rows
   {
-    const int ngrp = fast_ngrp(cw);
+    const int ngrp = fast_ngrp(cw), ntot = ch * ngrp;
     const uint8_t* img0 = img + (int64_t)(c.y0 - 3) * pitch + (c.x0 - 3) - 5;
+    const int mis0 = (int)(reinterpret_cast<uintptr_t>(img0) & 3);
+    const uint8_t* base0 = img0 - mis0;                          // 4-byte aligned
     const int sr = magic_div(kFastThreads, c.m_grp), su = kFastThreads - sr * ngrp;
     int r = magic_div(tid, c.m_grp), u = tid - r * ngrp;
-    // four groups per thread per round, all eight loads issued before the first use
-    for (int i = tid; i < ch * ngrp; i += 4 * kFastThreads) {
-      uint32_t lo[4], hi[4], sh[4];
-      int o[4];
+    // three groups per thread per round, all nine loads issued before the first use
+    for (int i = tid; i < ntot; i += 3 * kFastThreads) {
+      uint32_t w[3][3];
+      int o[3], sh[3];
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+      for (int k = 0; k < 3; k++) {
         o[k] = -1;
-        if (i + k * kFastThreads < ch * ngrp) {
-          const uintptr_t p = reinterpret_cast<uintptr_t>(img0 + r * pitch + 4 * u);
-          const uint32_t* a = reinterpret_cast<const uint32_t*>(p & ~(uintptr_t)3);
-          lo[k] = a[0]; hi[k] = a[1]; sh[k] = ((uint32_t)p & 3u) * 8u;
+        if (i + k * kFastThreads < ntot) {
+          const int off = r * pitch + 8 * u + mis0;
+          const uint32_t* a = reinterpret_cast<const uint32_t*>(base0 + (off & ~3));
+          w[k][0] = a[0]; w[k][1] = a[1]; w[k][2] = a[2];
+          sh[k] = (off & 3) * 8;
           o[k] = (r << 16) | u;
         }
         r += sr; u += su;
         if (u >= ngrp) { u -= ngrp; r++; }
       }
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+      for (int k = 0; k < 3; k++) {
         if (o[k] < 0) continue;
         const int rr = o[k] >> 16, uu = o[k] & 0xffff;
-        const uint32_t b4 = __funnelshift_r(lo[k], hi[k], sh[k]);
-        *reinterpret_cast<uint2*>(s_img + rr * sp16 + 4 * uu) =
-            make_uint2(__byte_perm(b4, 0, 0x4140), __byte_perm(b4, 0, 0x4342));
-        *reinterpret_cast<uint32_t*>(s_h8 + rr * bp + 4 * uu) = (b4 >> 1) & 0x7f7f7f7fu;
+        const uint32_t b0 = __funnelshift_r(w[k][0], w[k][1], sh[k]), b1 = __funnelshift_r(w[k][1], w[k][2], sh[k]);
+        *reinterpret_cast<uint4*>(s_img + rr * sp16 + 8 * uu) =
+            make_uint4(__byte_perm(b0, 0, 0x4140), __byte_perm(b0, 0, 0x4342), __byte_perm(b1, 0, 0x4140),
+                       __byte_perm(b1, 0, 0x4342));
+        *reinterpret_cast<uint2*>(s_h8 + rr * bp + 8 * uu) =
+            make_uint2((b0 >> 1) & 0x7f7f7f7fu, (b1 >> 1) & 0x7f7f7f7fu);
       }
     }
-    const int nz = (fast_sc_bytes(rw, rh) >> 2) + 3 * nbw;       // score map + bitmaps A, B, C are contiguous
-    for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint32_t*>(s_sc)[i] = 0;
+    // score map + bitmaps A, B, C are contiguous; the rounding to 16 bytes may run into bitmap F (written in phase 1)
+    const int nz = ((fast_sc_bytes(rw, rh) >> 2) + 3 * nbw + 3) >> 2;
+    for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
     if (tid < 2) s_cnt[tid] = 0;
   }
   __syncthreads();
 
-  const int tA = P->fast_th, tB = kRetryTh, tmin = max(min(tA, tB), 1);
+  const int tB = kRetryTh, tmin = max(min(tA, tB), 1);
   uint32_t* q = s_queue[warp];
   const uint32_t* s_img32 = reinterpret_cast<const uint32_t*>(s_img);
 
