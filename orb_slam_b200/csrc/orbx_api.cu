@@ -118,8 +118,9 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
   int base = 0;
   for (int l = 0; l < dp.nlevels; l++) {
     h->tiles.base[l] = base;
-    h->tiles.tiles_x[l] = (dp.lv[l].w + 63) / 64;
-    base += h->tiles.tiles_x[l] * ((dp.lv[l].h + 63) / 64);
+    h->tiles.tiles_x[l] = (dp.lv[l].w + 63) / 64;          // blur7_kernel tiles: 64 columns x 58 rows
+    h->tiles.magic_x[l] = fast_magic(h->tiles.tiles_x[l]);
+    base += h->tiles.tiles_x[l] * ((dp.lv[l].h + 57) / 58);
   }
   h->tiles.base[dp.nlevels] = base;
   h->plan_w = w; h->plan_h = hgt;

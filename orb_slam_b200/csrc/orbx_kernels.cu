@@ -16,6 +16,9 @@ __device__ __forceinline__ int reflect101(int i, int n) {  // copyMakeBorder(BOR
   return i >= n ? 2 * (n - 1) - i : i;
 }
 
+// floor(i / d) with m = fast_magic(d) (orbx_internal.cuh); m == 0 encodes d == 1
+__device__ __forceinline__ int magic_div(int i, uint32_t m) { return m ? (int)__umulhi((uint32_t)i, m) : i; }
+
 __device__ __forceinline__ const uint8_t* level_ptr(const ChunkBuffers& b, const DevicePlan* P, int level, int frame,
                                                     int* pitch) {
   if (level == 0) {
@@ -97,21 +100,20 @@ void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level,
 
 // ------------------------------------------------------------------------------------------------------------------
 // E8  7x7 Gaussian blur, sigma 2, BORDER_REFLECT_101                                            (reference :760)
-// Separable integer taps, dst = (sum_j k_j sum_i k_i p + 32768) >> 16  (SURVEY §0.3 P3).  The reference blurs in
-// place and keeps the unblurred border; here the blurred image goes to its own slab and the unblurred level stays
+// Separable integer taps, dst = min((sum_j k_j sum_i k_i p + 32768) >> 16, 255)  (SURVEY §0.3 P3).  The reference blurs
+// in place and keeps the unblurred border; here the blurred image goes to its own slab and the unblurred level stays
 // intact (the descriptor kernel reads the unblurred reflect for the <= 2 px of patch overhang).
-// One CTA = 64x64 output tile of one level of one frame; all levels in one launch.
+// One CTA = 64 x 58 output tile (64 staged rows) of one level of one frame; all levels in one launch.
 //
-// Both passes run on PACKED u16x2 lanes, two pixels per IMAD:
-//   horizontal  pixels (x, x+2) share a register (even / odd bytes of a word are one AND away from that form);
-//               h = k0 (S[-3] + S[3]) + k1 (S[-2] + S[2]) + k2 (S[-1] + S[1]) + k3 S[0] <= 255 * 257 = 65535 fits a lane
-//   vertical    sum_j k_j h_j needs 25 bits, so h is split into its low and high BYTE planes at the end of the
-//               horizontal pass: sum_j k_j hL_j and sum_j k_j hH_j each fit a lane again, and
-//               v = 256 * VH + VL is rebuilt per pixel only for the final (v + 32768) >> 16.
+// Both passes are integer dot products on the IDP pipe (measured 2 warp-inst/clk/SM, tools/int_ops_microbench.cu),
+// which runs beside the ALU pipe that does the byte shuffles:
+//   horizontal  h(x) = dp4a(bytes x-4..x-1, (0,k0,k1,k2)) + dp4a(bytes x..x+3, (k3,k4,k5,k6)); the 12 byte windows of 8
+//               consecutive outputs are 3 aligned words and 9 funnel shifts.  h <= 255 * 257 fits 16 bits; a thread
+//               does the same 8 columns of two consecutive rows and stores (h[2r], h[2r+1]) as one u16x2 word
+//   vertical    v(y) = four dp2a over those row-pair words; odd rows use the SAME words with the taps shifted by one
+//               ((0,k0),(k1,k2),(k3,k4),(k5,k6)), so no re-pairing is needed.  v needs 25 bits: a plain 32-bit sum.
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kBlurT = 64, kBlurRows = kBlurT + 6, kBlurWords = 18;  // staged row = image columns x0-4 .. x0+67
-
-__device__ __forceinline__ uint32_t packed_mid(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }
+constexpr int kBlurTW = 64, kBlurTH = 58, kBlurRows = 64, kBlurInW = 20;  // staged row = image columns x0-8 .. x0+71
 
 __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles tiles) {
   const DevicePlan* P = b.plan;
@@ -119,67 +121,108 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
   while (level + 1 < P->nlevels && (int)blockIdx.x >= tiles.base[level + 1]) level++;
   const LevelPlan& L = P->lv[level];
   const int t = blockIdx.x - tiles.base[level];
-  const int tx = t % tiles.tiles_x[level], ty = t / tiles.tiles_x[level];
+  const int ty = magic_div(t, tiles.magic_x[level]), tx = t - ty * tiles.tiles_x[level];
   const int frame = blockIdx.y;
-  const int x0 = tx * kBlurT, y0 = ty * kBlurT;
+  const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
   const int lw = L.w, lh = L.h;
   int spitch;
   const uint8_t* src = level_ptr(b, P, level, frame, &spitch);
   uint8_t* dst = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
-
-  __shared__ uint32_t s_in[kBlurRows][kBlurWords];
-  __shared__ uint4 s_h[kBlurRows][kBlurT / 4];  // per 4 output columns: {L(o0,o2), L(o1,o3), H(o0,o2), H(o1,o3)}
-  const int tid = threadIdx.x;
-  const bool words_ok = ((spitch & 3) == 0) && (((uintptr_t)src & 3) == 0);
-  for (int i = tid; i < kBlurRows * kBlurWords; i += 256) {
-    const int r = i / kBlurWords, j = i - r * kBlurWords;
-    const int yy = reflect101(min(y0 + r - 3, lh + 2), lh);
-    const int xs = x0 - 4 + 4 * j;
-    const uint8_t* row = src + (int64_t)yy * spitch;
-    uint32_t w;
-    if (words_ok && xs >= 0 && xs + 3 < lw) {
-      w = *reinterpret_cast<const uint32_t*>(row + xs);
-    } else {
-      w = 0;
-#pragma unroll
-      for (int k = 0; k < 4; k++) w |= (uint32_t)row[reflect101(min(max(xs + k, -3), lw + 2), lw)] << (8 * k);
-    }
-    s_in[r][j] = w;
-  }
-  __syncthreads();
   const uint32_t k0 = 18, k1 = 34, k2 = P->blur_mode == 0 ? 49 : 48, k3 = P->blur_mode == 0 ? 55 : 56;
-  const uint32_t M = 0x00FF00FFu;
-  for (int i = tid; i < kBlurRows * (kBlurT / 4); i += 256) {
-    const int r = i >> 4, k = i & 15;
-    const uint32_t w0 = s_in[r][k], w1 = s_in[r][k + 1], w2 = s_in[r][k + 2];
-    // S_i = (B_i, B_{i+2}) with B_i = staged byte 4k + i; output o_j is centred on B_{4+j}
-    const uint32_t E0 = w0 & M, E1 = w1 & M, E2 = w2 & M, O0 = (w0 >> 8) & M, O1 = (w1 >> 8) & M, O2 = (w2 >> 8) & M;
-    const uint32_t S1 = O0, S2 = packed_mid(E0, E1), S3 = packed_mid(O0, O1), S4 = E1, S5 = O1,
-                   S6 = packed_mid(E1, E2), S7 = packed_mid(O1, O2), S8 = E2;
-    const uint32_t hA = k0 * (S1 + S7) + k1 * (S2 + S6) + k2 * (S3 + S5) + k3 * S4;  // (o0, o2)
-    const uint32_t hB = k0 * (S2 + S8) + k1 * (S3 + S7) + k2 * (S4 + S6) + k3 * S5;  // (o1, o3)
-    s_h[r][k] = make_uint4(hA & M, hB & M, (hA >> 8) & M, (hB >> 8) & M);
+
+  __shared__ __align__(16) uint32_t s_in[kBlurRows][kBlurInW];
+  __shared__ __align__(16) uint32_t s_v[kBlurRows / 2][kBlurTW];  // (h[2r][x], h[2r+1][x])
+  const int tid = threadIdx.x;
+  // ---- stage 64 rows x 80 bytes, 8 bytes per load ---------------------------------------------------------------------
+  {
+    const bool vec_ok = ((spitch & 7) == 0) && ((reinterpret_cast<uintptr_t>(src) & 7) == 0);
+    uint2 v[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const int i = tid + 256 * k;
+      if (i >= kBlurRows * (kBlurInW / 2)) break;
+      const int r = i / (kBlurInW / 2), j = i - r * (kBlurInW / 2);
+      const int yy = reflect101(min(y0 + r - 3, lh + 2), lh);
+      const int xs = x0 - 8 + 8 * j;
+      const uint8_t* row = src + (int64_t)yy * spitch;
+      if (vec_ok && xs >= 0 && xs + 7 < lw) {
+        v[k] = *reinterpret_cast<const uint2*>(row + xs);
+      } else {
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          lo |= (uint32_t)row[reflect101(min(max(xs + q, -3), lw + 2), lw)] << (8 * q);
+          hi |= (uint32_t)row[reflect101(min(max(xs + 4 + q, -3), lw + 2), lw)] << (8 * q);
+        }
+        v[k] = make_uint2(lo, hi);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const int i = tid + 256 * k;
+      if (i >= kBlurRows * (kBlurInW / 2)) break;
+      reinterpret_cast<uint2*>(&s_in[0][0])[i] = v[k];
+    }
   }
   __syncthreads();
+  // ---- horizontal: one thread = 8 columns x 2 rows --------------------------------------------------------------------
   {
-    const int k = tid & 15, strip = tid >> 4;  // 4 columns x 4 rows per thread
-    const int x = x0 + 4 * k;
-    if (x >= lw || y0 + 4 * strip >= lh) return;
-    uint4 a[10];
+    const int tc = tid & 7, rp = tid >> 3;
+    const uint32_t cA = (k0 << 8) | (k1 << 16) | (k2 << 24), cB = k3 | (k2 << 8) | (k1 << 16) | (k0 << 24);
+    uint32_t h[2][8];
 #pragma unroll
-    for (int q = 0; q < 10; q++) a[q] = s_h[4 * strip + q][k];
+    for (int rr = 0; rr < 2; rr++) {
+      const uint32_t* in = &s_in[2 * rp + rr][2 * tc];       // byte 8 tc of the staged row = image column x0 + 8 tc - 8
+      const uint32_t w1 = in[1], w4 = in[4];
+      const uint2 w23 = *reinterpret_cast<const uint2*>(in + 2);
+      uint32_t win[12];                                       // win[s] = staged bytes 8 tc + 4 + s .. + 3
+      win[0] = w1; win[4] = w23.x; win[8] = w23.y;
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const int y = y0 + 4 * strip + q;
-      if (y >= lh) break;
-#define BLURV(c) (k0 * (a[q].c + a[q + 6].c) + k1 * (a[q + 1].c + a[q + 5].c) + k2 * (a[q + 2].c + a[q + 4].c) + k3 * a[q + 3].c)
-      const uint32_t AL = BLURV(x), BL = BLURV(y), AH = BLURV(z), BH = BLURV(w);
+      for (int q = 1; q < 4; q++) {
+        win[q] = __funnelshift_r(w1, w23.x, 8 * q);
+        win[4 + q] = __funnelshift_r(w23.x, w23.y, 8 * q);
+        win[8 + q] = __funnelshift_r(w23.y, w4, 8 * q);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) h[rr][i] = __dp4a(win[i], cA, __dp4a(win[i + 4], cB, 0u));
+    }
+    uint4* out = reinterpret_cast<uint4*>(&s_v[rp][8 * tc]);
+#define PAIR(i) __byte_perm(h[0][i], h[1][i], 0x5410)
+    out[0] = make_uint4(PAIR(0), PAIR(1), PAIR(2), PAIR(3));
+    out[1] = make_uint4(PAIR(4), PAIR(5), PAIR(6), PAIR(7));
+#undef PAIR
+  }
+  __syncthreads();
+  // ---- vertical: one thread = 4 columns x 4 rows ----------------------------------------------------------------------
+  {
+    const int cg = tid & 15, strip = tid >> 4;
+    const int x = x0 + 4 * cg, ys = y0 + 4 * strip;
+    if (x >= lw || ys >= lh || 4 * strip >= kBlurTH) return;
+    // tap pairs for dp2a_lo (low half) / dp2a_hi (high half): even output rows start on a row pair, odd rows do not
+    const uint32_t cE0 = (k0 | (k1 << 8)) | ((k2 | (k3 << 8)) << 16);   // (k0,k1) (k2,k3)
+    const uint32_t cE1 = (k2 | (k1 << 8)) | (k0 << 16);                 // (k4,k5) (k6,0)
+    const uint32_t cO0 = (k0 << 8) | ((k1 | (k2 << 8)) << 16);          // (0,k0) (k1,k2)
+    const uint32_t cO1 = (k3 | (k2 << 8)) | ((k1 | (k0 << 8)) << 16);   // (k3,k4) (k5,k6)
+    uint4 a[5];
+#pragma unroll
+    for (int m = 0; m < 5; m++) a[m] = *reinterpret_cast<const uint4*>(&s_v[min(2 * strip + m, kBlurRows / 2 - 1)][4 * cg]);
+    const int nrows = min(min(4, kBlurTH - 4 * strip), lh - ys);
+#pragma unroll
+    for (int d = 0; d < 4; d++) {
+      if (d >= nrows) break;
+      const int m0 = d >> 1;
+      uint32_t acc[4];
+#define BLURV(c, i)                                                                                        \
+      acc[i] = (d & 1) ? __dp2a_hi(a[m0 + 3].c, cO1, __dp2a_lo(a[m0 + 2].c, cO1, __dp2a_hi(a[m0 + 1].c, cO0,     \
+                             __dp2a_lo(a[m0].c, cO0, 32768u))))                                                 \
+                       : __dp2a_hi(a[m0 + 3].c, cE1, __dp2a_lo(a[m0 + 2].c, cE1, __dp2a_hi(a[m0 + 1].c, cE0,     \
+                             __dp2a_lo(a[m0].c, cE0, 32768u))));
+      BLURV(x, 0) BLURV(y, 1) BLURV(z, 2) BLURV(w, 3)
 #undef BLURV
-      const uint32_t r0 = min((((AH & 0xffff) << 8) + (AL & 0xffff) + 32768u) >> 16, 255u);
-      const uint32_t r2 = min((((AH >> 16) << 8) + (AL >> 16) + 32768u) >> 16, 255u);
-      const uint32_t r1 = min((((BH & 0xffff) << 8) + (BL & 0xffff) + 32768u) >> 16, 255u);
-      const uint32_t r3 = min((((BH >> 16) << 8) + (BL >> 16) + 32768u) >> 16, 255u);
-      *reinterpret_cast<uint32_t*>(dst + (int64_t)y * L.pitch + x) = r0 | (r1 << 8) | (r2 << 16) | (r3 << 24);
+      // bits 16..24 of each sum, clamped to 255 on u16x2 lanes, then packed to four bytes
+      const uint32_t p01 = __vminu2(__byte_perm(acc[0], acc[1], 0x7632), 0x00ff00ffu);
+      const uint32_t p23 = __vminu2(__byte_perm(acc[2], acc[3], 0x7632), 0x00ff00ffu);
+      *reinterpret_cast<uint32_t*>(dst + (int64_t)(ys + d) * L.pitch + x) = __byte_perm(p01, p23, 0x6420);
     }
   }
 }

@@ -27,6 +27,7 @@ struct ChunkBuffers {
 struct BlurTiles {            // tile ranges of the single all-level blur launch
   int base[kMaxLevels + 1];   // prefix of tiles per level
   int tiles_x[kMaxLevels];
+  uint32_t magic_x[kMaxLevels];  // fast_magic(tiles_x): tile row = magic_div(tile, magic_x)
 };
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);

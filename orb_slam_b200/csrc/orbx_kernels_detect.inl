@@ -56,8 +56,6 @@ __device__ float harris_response(const uint8_t* p, int step) {
 constexpr int kFastThreads = 256, kFastWarps = kFastThreads / 32, kFastQueue = 160, kFastSub = 4;
 
 __device__ __forceinline__ uint32_t hw_mid(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }
-// floor(i / d) with m = fast_magic(d) (orbx_internal.cuh); m == 0 encodes d == 1
-__device__ __forceinline__ int magic_div(int i, uint32_t m) { return m ? (int)__umulhi((uint32_t)i, m) : i; }
 
 // Appends base + b for every set bit b of every lane's `bits` to the warp's queue (lane order, then bit order) and
 // runs fn on each full group of 32 entries.  A round that would overflow the queue is split into sub-rounds of
