@@ -116,7 +116,11 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     CK(cudaMemcpy(h->d_ry, h->hp.ry.data(), h->hp.ry.size() * sizeof(ResizeY), cudaMemcpyHostToDevice));
   }
   int base = 0;
+  memset(&h->tiles, 0, sizeof(h->tiles));
+  h->tiles.nlevels = dp.nlevels; h->tiles.blur_mode = dp.blur_mode; h->tiles.frame_bytes = dp.pyr_frame_bytes;
   for (int l = 0; l < dp.nlevels; l++) {
+    h->tiles.w[l] = dp.lv[l].w; h->tiles.h[l] = dp.lv[l].h; h->tiles.pitch[l] = dp.lv[l].pitch;
+    h->tiles.off[l] = dp.lv[l].off;
     h->tiles.base[l] = base;
     h->tiles.tiles_x[l] = (dp.lv[l].w + 63) / 64;          // blur7_kernel tiles: 64 columns x 58 rows
     h->tiles.magic_x[l] = fast_magic(h->tiles.tiles_x[l]);

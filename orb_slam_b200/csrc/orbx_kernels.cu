@@ -116,26 +116,28 @@ void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level,
 constexpr int kBlurTW = 64, kBlurTH = 58, kBlurRows = 64, kBlurInW = 20;  // staged row = image columns x0-8 .. x0+71
 
 __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles tiles) {
-  const DevicePlan* P = b.plan;
   int level = 0;
-  while (level + 1 < P->nlevels && (int)blockIdx.x >= tiles.base[level + 1]) level++;
-  const LevelPlan& L = P->lv[level];
+  while (level + 1 < tiles.nlevels && (int)blockIdx.x >= tiles.base[level + 1]) level++;
   const int t = blockIdx.x - tiles.base[level];
   const int ty = magic_div(t, tiles.magic_x[level]), tx = t - ty * tiles.tiles_x[level];
   const int frame = blockIdx.y;
   const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
-  const int lw = L.w, lh = L.h;
-  int spitch;
-  const uint8_t* src = level_ptr(b, P, level, frame, &spitch);
-  uint8_t* dst = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
-  const uint32_t k0 = 18, k1 = 34, k2 = P->blur_mode == 0 ? 49 : 48, k3 = P->blur_mode == 0 ? 55 : 56;
+  const int lw = tiles.w[level], lh = tiles.h[level], dpitch = tiles.pitch[level];
+  const int spitch = level == 0 ? b.lv0_pitch : dpitch;
+  const uint8_t* src = level == 0 ? b.lv0 + (int64_t)frame * b.lv0_frame_stride
+                                  : b.pyr + (int64_t)frame * tiles.frame_bytes + tiles.off[level];
+  uint8_t* dst = b.blur + (int64_t)frame * tiles.frame_bytes + tiles.off[level];
+  const uint32_t k0 = 18, k1 = 34, k2 = tiles.blur_mode == 0 ? 49 : 48, k3 = tiles.blur_mode == 0 ? 55 : 56;
 
   __shared__ __align__(16) uint32_t s_in[kBlurRows][kBlurInW];
   __shared__ __align__(16) uint32_t s_v[kBlurRows / 2][kBlurTW];  // (h[2r][x], h[2r+1][x])
   const int tid = threadIdx.x;
   // ---- stage 64 rows x 80 bytes, 8 bytes per load ---------------------------------------------------------------------
+  // Rows reflect through the address.  Columns: whole 8-byte groups are loaded wherever they lie inside the row pitch
+  // (bytes at columns >= lw are padding), and the <= 3 reflected columns on either side of the image are patched in
+  // shared memory afterwards - no per-byte path in the common case.
+  const bool vec_ok = ((spitch & 7) == 0) && ((reinterpret_cast<uintptr_t>(src) & 7) == 0);
   {
-    const bool vec_ok = ((spitch & 7) == 0) && ((reinterpret_cast<uintptr_t>(src) & 7) == 0);
     uint2 v[3];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
@@ -145,11 +147,10 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
       const int yy = reflect101(min(y0 + r - 3, lh + 2), lh);
       const int xs = x0 - 8 + 8 * j;
       const uint8_t* row = src + (int64_t)yy * spitch;
-      if (vec_ok && xs >= 0 && xs + 7 < lw) {
-        v[k] = *reinterpret_cast<const uint2*>(row + xs);
-      } else {
+      if (vec_ok) {
+        v[k] = (xs >= 0 && xs + 8 <= spitch) ? *reinterpret_cast<const uint2*>(row + xs) : make_uint2(0u, 0u);
+      } else {                                               // caller's level-0 buffer with an odd base or stride
         uint32_t lo = 0, hi = 0;
-#pragma unroll
         for (int q = 0; q < 4; q++) {
           lo |= (uint32_t)row[reflect101(min(max(xs + q, -3), lw + 2), lw)] << (8 * q);
           hi |= (uint32_t)row[reflect101(min(max(xs + 4 + q, -3), lw + 2), lw)] << (8 * q);
@@ -165,6 +166,17 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
     }
   }
   __syncthreads();
+  if (vec_ok && (x0 == 0 || x0 + kBlurTW + 3 > lw)) {         // CTA-uniform: this tile touches an image side
+    if (tid < kBlurRows) {
+      uint8_t* rowb = reinterpret_cast<uint8_t*>(&s_in[tid][0]);  // byte i = column x0 - 8 + i
+      if (x0 == 0) { rowb[5] = rowb[11]; rowb[6] = rowb[10]; rowb[7] = rowb[9]; }
+      for (int k = 0; k < 3; k++) {                           // column lw + k <- column lw - 2 - k
+        const int i = lw + k - x0 + 8;
+        if (i >= 8 && i < 4 * kBlurInW) rowb[i] = rowb[lw - 2 - k - x0 + 8];
+      }
+    }
+    __syncthreads();
+  }
   // ---- horizontal: one thread = 8 columns x 2 rows --------------------------------------------------------------------
   {
     const int tc = tid & 7, rp = tid >> 3;
@@ -207,6 +219,7 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
 #pragma unroll
     for (int m = 0; m < 5; m++) a[m] = *reinterpret_cast<const uint4*>(&s_v[min(2 * strip + m, kBlurRows / 2 - 1)][4 * cg]);
     const int nrows = min(min(4, kBlurTH - 4 * strip), lh - ys);
+    uint8_t* orow = dst + (int64_t)ys * dpitch + x;
 #pragma unroll
     for (int d = 0; d < 4; d++) {
       if (d >= nrows) break;
@@ -222,7 +235,8 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
       // bits 16..24 of each sum, clamped to 255 on u16x2 lanes, then packed to four bytes
       const uint32_t p01 = __vminu2(__byte_perm(acc[0], acc[1], 0x7632), 0x00ff00ffu);
       const uint32_t p23 = __vminu2(__byte_perm(acc[2], acc[3], 0x7632), 0x00ff00ffu);
-      *reinterpret_cast<uint32_t*>(dst + (int64_t)(ys + d) * L.pitch + x) = __byte_perm(p01, p23, 0x6420);
+      *reinterpret_cast<uint32_t*>(orow) = __byte_perm(p01, p23, 0x6420);
+      orow += dpitch;
     }
   }
 }

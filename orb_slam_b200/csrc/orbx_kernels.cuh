@@ -24,10 +24,14 @@ struct ChunkBuffers {
   const ResizeY* ry;
 };
 
-struct BlurTiles {            // tile ranges of the single all-level blur launch
+struct BlurTiles {            // everything blur7_kernel needs per level, passed by value (constant bank, no global loads)
+  int nlevels, blur_mode;
   int base[kMaxLevels + 1];   // prefix of tiles per level
   int tiles_x[kMaxLevels];
   uint32_t magic_x[kMaxLevels];  // fast_magic(tiles_x): tile row = magic_div(tile, magic_x)
+  int w[kMaxLevels], h[kMaxLevels], pitch[kMaxLevels];
+  int64_t off[kMaxLevels];    // LevelPlan::off
+  int64_t frame_bytes;        // DevicePlan::pyr_frame_bytes == blur_frame_bytes
 };
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
