@@ -36,65 +36,122 @@ __device__ __forceinline__ const uint8_t* level_ptr(const ChunkBuffers& b, const
 // The 16-px reflect border of the reference (copyMakeBorder :806/:814) is never materialised: consumers reflect
 // indices instead.
 // ------------------------------------------------------------------------------------------------------------------
+// One thread = 4 destination columns x kResizeRows destination rows; one warp = 128 columns of those rows.
+// The column set-up (table loads, byte selectors) is paid once per thread.  The source rows a warp needs form one
+// contiguous range [sy0(first row), sy1(last row)]: all of them are fetched up front (one memory round trip), each
+// gets ONE horizontal pass, and a destination row is emitted when the walk reaches its lower source row - consecutive
+// destination rows share a source row (sy1(dy) == sy0(dy + 1) for scale < 2), so ~1.3 horizontal passes per
+// destination row instead of 2.
 // Fast path (aligned source rows, scale < ~2.3): the thread's 4 destination pixels read source columns
-// sx0 .. sx3 + 1, at most 8 bytes, so each of the two source rows is fetched as three aligned 32-bit words, shifted
-// once to start at sx0, and every pixel's (S0[sx], S0[sx+1], S1[sx], S1[sx+1]) quadruple is three PRMTs away; the two
-// horizontal interpolations are then ONE DP2A each (u8 pair . s16 weight pair).
+// sx0 .. sx3 + 1, at most 8 bytes, so a source row is fetched as three aligned 32-bit words, shifted once to start
+// at sx0; every pixel's (S[sx], S[sx+1]) pair is one PRMT away and its horizontal interpolation is ONE DP2A
+// (u8 pair . s16 weight pair).
+constexpr int kResizeRows = 6, kResizeSrcMax = 10;
+
 __global__ void __launch_bounds__(256) resize_level_kernel(ChunkBuffers b, int level) {
   const DevicePlan* P = b.plan;
   const LevelPlan& L = P->lv[level];
-  const int frame = blockIdx.z;
-  const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-  const int dy = blockIdx.y * 8 + threadIdx.y;
-  if (dx0 >= L.w || dy >= L.h) return;
+  const int frame = blockIdx.z, lane = threadIdx.x;
+  const int lw = L.w, lh = L.h, dpitch = L.pitch;
+  const int dx_raw = (blockIdx.x * 32 + lane) * 4;
+  const int dy0 = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+  if (dy0 >= lh) return;                                      // whole warp
+  const bool col_ok = dx_raw < lw;                            // lanes past the row keep computing (shuffles), never store
+  const int dx0 = min(dx_raw, (lw - 1) & ~3);
   int spitch;
   const uint8_t* src = level_ptr(b, P, level - 1, frame, &spitch);
-  uint8_t* dst = b.pyr + (int64_t)frame * P->pyr_frame_bytes + L.off;
-  const ResizeY ry = b.ry[L.tab_y + dy];
-  const uint8_t* S0 = src + (int64_t)ry.sy0 * spitch;
-  const uint8_t* S1 = src + (int64_t)ry.sy1 * spitch;
+  uint8_t* drow = b.pyr + (int64_t)frame * P->pyr_frame_bytes + L.off + (int64_t)dy0 * dpitch + dx0;
+  const int nrows = min(kResizeRows, lh - dy0);
+  const uint2 myry = reinterpret_cast<const uint2*>(b.ry)[L.tab_y + dy0 + min(lane, nrows - 1)];  // lane r: row dy0 + r
   const int sw = P->lv[level - 1].w;
   uint2 rx[4];
 #pragma unroll
-  for (int k = 0; k < 4; k++) rx[k] = reinterpret_cast<const uint2*>(b.rx)[L.tab_x + min(dx0 + k, L.w - 1)];
+  for (int k = 0; k < 4; k++) rx[k] = reinterpret_cast<const uint2*>(b.rx)[L.tab_x + min(dx0 + k, lw - 1)];
   const int sx0 = rx[0].x & 0xffff, sx3 = rx[3].x & 0xffff;
-  const bool fast = ((spitch & 3) == 0) && (((uintptr_t)src & 3) == 0) && (sx3 + 1 - sx0 <= 7);
-  uint32_t packed = 0;
+  const int s_first = (int)(short)(__shfl_sync(0xffffffffu, myry.x, 0) & 0xffff);
+  const int s_last = (int)(short)(__shfl_sync(0xffffffffu, myry.x, nrows - 1) >> 16);
+  const int ns = s_last - s_first + 1;
+  const bool fast = __all_sync(0xffffffffu, ((spitch & 3) == 0) && (((uintptr_t)src & 3) == 0) && (sx3 + 1 - sx0 <= 7)) &&
+                    ns >= 1 && ns <= kResizeSrcMax;
   if (fast) {
     const int base4 = sx0 & ~3, sh = (sx0 & 3) * 8;
-    const uint32_t* A = reinterpret_cast<const uint32_t*>(S0 + base4);
-    const uint32_t* B = reinterpret_cast<const uint32_t*>(S1 + base4);
     const bool in1 = base4 + 4 < sw, in2 = base4 + 8 < sw;   // never start a load beyond the row
-    const uint32_t a0 = A[0], a1 = in1 ? A[1] : 0u, a2 = in2 ? A[2] : 0u;
-    const uint32_t c0 = B[0], c1 = in1 ? B[1] : 0u, c2 = in2 ? B[2] : 0u;
-    const uint32_t wa0 = __funnelshift_r(a0, a1, sh), wa1 = __funnelshift_r(a1, a2, sh);  // bytes sx0.. of row 0
-    const uint32_t wb0 = __funnelshift_r(c0, c1, sh), wb1 = __funnelshift_r(c1, c2, sh);  // ... of row 1
+    uint32_t raw[kResizeSrcMax][3];
+    const uint8_t* scol = src + (int64_t)s_first * spitch + base4;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int o = (int)(rx[k].x & 0xffff) - sx0;
-      const uint32_t sel = (uint32_t)o | ((uint32_t)(o + 1) << 4);
-      const uint32_t q = __byte_perm(__byte_perm(wa0, wa1, sel), __byte_perm(wb0, wb1, sel), 0x5410);
-      const uint32_t h0 = __dp2a_lo(rx[k].y, q, 0u), h1 = __dp2a_hi(rx[k].y, q, 0u);
-      const int v = (((ry.b0 * (int)(h0 >> 4)) >> 16) + ((ry.b1 * (int)(h1 >> 4)) >> 16) + 2) >> 2;
-      packed |= (uint32_t)(v & 255) << (8 * k);
+    for (int j = 0; j < kResizeSrcMax; j++) {
+      if (j < ns) {
+        const uint32_t* A = reinterpret_cast<const uint32_t*>(scol + (int64_t)j * spitch);
+        raw[j][0] = A[0]; raw[j][1] = in1 ? A[1] : 0u; raw[j][2] = in2 ? A[2] : 0u;
+      }
     }
-  } else {
+    uint32_t sel[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-      const int sx = rx[k].x & 0xffff, sx1 = min(sx + 1, sw - 1);
-      const int ca0 = (int)(short)(rx[k].y & 0xffff), ca1 = (int)(short)(rx[k].y >> 16);
-      const int h0 = S0[sx] * ca0 + S0[sx1] * ca1;
-      const int h1 = S1[sx] * ca0 + S1[sx1] * ca1;
-      const int v = (((ry.b0 * (h0 >> 4)) >> 16) + ((ry.b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-      packed |= (uint32_t)(v & 255) << (8 * k);
+      const uint32_t o = (rx[k].x & 0xffff) - (uint32_t)sx0;
+      sel[k] = o | ((o + 1) << 4);                            // bytes (S[sx], S[sx+1], -, -): dp2a_lo reads two
+    }
+    // H[k] = (S[sx_k] * a0 + S[sx_k + 1] * a1) >> 4 of one source row
+    auto hrow = [&](const uint32_t (&a)[3], uint32_t (&H)[4]) {
+      const uint32_t w0 = __funnelshift_r(a[0], a[1], sh), w1 = __funnelshift_r(a[1], a[2], sh);
+#pragma unroll
+      for (int k = 0; k < 4; k++) H[k] = __dp2a_lo(rx[k].y, __byte_perm(w0, w1, sel[k]), 0u) >> 4;
+    };
+    // emits every destination row whose LOWER source row is s_first + j (upper row = Hp unless the row is clamped)
+    int r = 0;
+    auto emit = [&](int j, const uint32_t (&Hp)[4], const uint32_t (&Hq)[4]) {
+      while (r < nrows) {
+        const uint32_t yx = __shfl_sync(0xffffffffu, myry.x, r), yy = __shfl_sync(0xffffffffu, myry.y, r);
+        const int sy0 = (int)(short)(yx & 0xffff), sy1 = (int)(short)(yx >> 16);
+        if (sy1 != s_first + j) break;
+        const int b0 = (int)(short)(yy & 0xffff), b1 = (int)(short)(yy >> 16);
+        uint32_t packed = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const int h0 = (int)(sy0 == sy1 ? Hq[k] : Hp[k]);
+          const int v = (((b0 * h0) >> 16) + ((b1 * (int)Hq[k]) >> 16) + 2) >> 2;
+          packed |= (uint32_t)(v & 255) << (8 * k);
+        }
+        if (col_ok) *reinterpret_cast<uint32_t*>(drow) = packed;   // pitch % 16 == 0, dx0 % 4 == 0
+        drow += dpitch;
+        r++;
+      }
+    };
+    uint32_t Hp[4], Hq[4];
+    hrow(raw[0], Hp);
+    emit(0, Hp, Hp);
+#pragma unroll
+    for (int j = 1; j < kResizeSrcMax; j++) {
+      if (j >= ns) break;
+      hrow(raw[j], Hq);
+      emit(j, Hp, Hq);
+#pragma unroll
+      for (int k = 0; k < 4; k++) Hp[k] = Hq[k];
+    }
+  } else if (col_ok) {
+    for (int r = 0; r < nrows; r++) {
+      const ResizeY ry = b.ry[L.tab_y + dy0 + r];
+      const uint8_t* S0 = src + (int64_t)ry.sy0 * spitch;
+      const uint8_t* S1 = src + (int64_t)ry.sy1 * spitch;
+      uint32_t packed = 0;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int sx = rx[k].x & 0xffff, sx1 = min(sx + 1, sw - 1);
+        const int ca0 = (int)(short)(rx[k].y & 0xffff), ca1 = (int)(short)(rx[k].y >> 16);
+        const int h0 = S0[sx] * ca0 + S0[sx1] * ca1;
+        const int h1 = S1[sx] * ca0 + S1[sx1] * ca1;
+        const int v = (((ry.b0 * (h0 >> 4)) >> 16) + ((ry.b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+        packed |= (uint32_t)(v & 255) << (8 * k);
+      }
+      *reinterpret_cast<uint32_t*>(drow) = packed;
+      drow += dpitch;
     }
   }
-  *reinterpret_cast<uint32_t*>(dst + (int64_t)dy * L.pitch + dx0) = packed;  // pitch % 16 == 0, dx0 % 4 == 0
 }
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s) {
   const LevelPlan& L = hp.lv[level];
-  dim3 block(32, 8), grid((L.w + 127) / 128, (L.h + 7) / 8, nframes);
+  dim3 block(32, 8), grid((L.w + 127) / 128, (L.h + 8 * kResizeRows - 1) / (8 * kResizeRows), nframes);
   resize_level_kernel<<<grid, block, 0, s>>>(b, level);
 }
 

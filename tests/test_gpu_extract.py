@@ -159,3 +159,31 @@ def test_device_path_matches_host_path(oracle):
     for f in range(F):
         assert np.array_equal(k2[f, :n[f]], kps[f, :n[f]])
         assert np.array_equal(d_d[f, :n[f]].cpu().numpy(), desc[f, :n[f]])
+
+
+def test_device_input_unaligned(oracle):
+    """Caller-owned device frames with an odd base address and odd row stride: every kernel's unaligned path
+    (resize slow path, FAST funnel-shift staging, blur byte staging, describe) must give the aligned result."""
+    import torch
+    from orb_slam_b200 import KP_DTYPE
+    F, H, W = 3, 251, 333
+    frames = np.stack([oracle.synth(H, W, 300 + s) for s in range(F)])
+    ex = _ex(nfeatures=600, nlevels=6, max_width=W, max_height=H, max_batch=2)
+    kps, desc, n = ex.extract_batch(frames)
+    stride, fstride, base = W + 5, H * (W + 5) + 11, 3
+    buf = torch.zeros(base + F * fstride + 64, dtype=torch.uint8, device="cuda")
+    for f in range(F):
+        view = buf[base + f * fstride: base + f * fstride + H * stride].view(H, stride)
+        view[:, :W] = torch.from_numpy(frames[f]).cuda()
+    d_k = torch.zeros((F, 600, 28), dtype=torch.uint8, device="cuda")
+    d_d = torch.zeros((F, 600, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(F, dtype=torch.int32, device="cuda")
+    ex.extract_batch_device(buf.data_ptr() + base, F, W, H, stride, fstride, d_k.data_ptr(), d_d.data_ptr(),
+                            d_n.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ex.synchronize()
+    assert np.array_equal(d_n.cpu().numpy(), n)
+    k2 = d_k.cpu().numpy().view(KP_DTYPE).reshape(F, 600)
+    for f in range(F):
+        assert np.array_equal(k2[f, :n[f]], kps[f, :n[f]])
+        assert np.array_equal(d_d[f, :n[f]].cpu().numpy(), desc[f, :n[f]])
