@@ -67,142 +67,272 @@ __device__ constexpr int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11
 
 constexpr int kDescWarps = 8, kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchWords = 11, kPatchPitch = 4 * kPatchWords;
 
-// One warp per keypoint slot.
-//  E7  lane = COLUMN u of the 31-px disc: 31 row loads, each one coalesced 31-byte segment (the former lane = row
-//      layout cost 31 scattered sectors per load instruction and made the kernel L1-wavefront bound).
-//  E9  the 37x37 window of the BLURRED level that the rotated pattern can reach (|offset| <= 18) is staged into
-//      shared memory by aligned 32-bit loads (2 rows per instruction) and the 512 samples are read from there;
-//      the pattern lives in registers (two 16-byte loads per lane) instead of 32-way divergent __constant__ reads.
-//      Windows touching the image border take the per-sample path: in-image samples read the blurred level, the
-//      <= 2 px outside read the UNBLURRED reflect-101 border, which the reference's in-place ROI blur leaves
-//      untouched (:759-760).
-__global__ void __launch_bounds__(32 * kDescWarps) describe_kernel(ChunkBuffers b, orbx_keypoint* out_kps,
-                                                                  uint8_t* out_desc, int32_t* out_n,
-                                                                  int nslots_total) {
-  __shared__ __align__(16) uint8_t s_patch[kDescWarps][kPatchRows * kPatchPitch];
+// Persistent warps, one keypoint slot per warp per iteration, software-pipelined three deep so that no global-memory
+// latency sits on a warp's critical path:
+//   stage A (slot i+3)  plain loads of the slot's record (Cand) and of its frame's per-level counts
+//   stage B (slot i+2)  decode (level, output index, centre), then cp.async of BOTH windows the slot needs into the
+//                       warp's double-buffered shared memory: the 37x37 window of the BLURRED level the rotated
+//                       pattern can reach (|offset| <= 18) and the 31x31 window of the UNBLURRED level for IC_Angle
+//   stage C (slot i)    everything else, from shared memory only
+//  E7  lane = COLUMN u of the 31-px disc, 31 byte reads per lane.
+//  E9  lane = descriptor byte; the pattern sits in shared memory as float pairs (transposed, conflict-free), the 16
+//      rotated samples are read from the staged window.  Windows touching the image border take the per-sample path:
+//      in-image samples read the blurred level, the <= 2 px outside read the UNBLURRED reflect-101 border, which the
+//      reference's in-place ROI blur leaves untouched (:759-760).
+constexpr int kRawRows = 31, kRawWords = 9, kRawPitch = 4 * kRawWords;
+constexpr int kBlurBufBytes = (kPatchRows * kPatchPitch + 15) & ~15, kRawBufBytes = (kRawRows * kRawPitch + 15) & ~15;
+constexpr int kDescBufBytes = kBlurBufBytes + kRawBufBytes;
+constexpr float kMagic = 12582912.f;          // 1.5 * 2^23: float(int) and cvRound(float) through FADD only
+constexpr int kMagicBits = 0x4B400000;
+
+struct DescRaw {   // stage A
+  Cand kp;
+  int my_cnt, frame, slot;   // slot < 0: past the end
+};
+struct DescRec {   // stage B -> C
+  int frame, level, cx, cy, o, flags, mis;   // flags: 1 valid, 2 blurred window staged, 4 raw window staged
+  float resp;
+};
+
+__device__ __forceinline__ void cp_async4(uint32_t dst_smem, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(__cvta_generic_to_global(src)) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(32 * kDescWarps, 4) describe_kernel(ChunkBuffers b, orbx_keypoint* out_kps,
+                                                                     uint8_t* out_desc, int32_t* out_n,
+                                                                     int nslots_total) {
+  __shared__ __align__(16) uint8_t s_buf[kDescWarps][2][kDescBufBytes];
+  __shared__ float2 s_pat[16 * 32];            // [j][lane] = pattern point 16 * lane + j
   const DevicePlan* P = b.plan;
-  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (gw >= nslots_total) return;
-  const int frame = gw / P->nfeatures, slot = gw - frame * P->nfeatures;
-  // level of the slot and output offset = sum of the lower levels' counts: one parallel round of loads (lane = level)
-  // instead of a chain of dependent ones
-  const int32_t* cnt = b.kp_count + frame * kMaxLevels;
-  const int my_cnt = lane < P->nlevels ? cnt[lane] : 0;
-  const int my_base = lane < P->nlevels ? P->lv[lane].kp_base : 0x7fffffff;
-  const int level = __popc(__ballot_sync(0xffffffffu, lane >= 1 && slot >= my_base));
-  const int out_off = __reduce_add_sync(0xffffffffu, lane < level ? my_cnt : 0);
-  const int level_cnt = __shfl_sync(0xffffffffu, my_cnt, level);
-  const LevelPlan& L = P->lv[level];
-  const int idx = slot - L.kp_base;
-  {
-    const int tot = __reduce_add_sync(0xffffffffu, my_cnt);
-    if (slot == 0 && lane == 0) out_n[frame] = tot;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int t = threadIdx.x; t < 512; t += 32 * kDescWarps) {
+    const int pl = t & 31, pj = t >> 5, pt = 16 * pl + pj;
+    s_pat[t] = make_float2((float)d_pattern[2 * pt], (float)d_pattern[2 * pt + 1]);
   }
-  if (idx >= level_cnt) return;
-  const Cand kp = b.kp[(int64_t)frame * P->nfeatures + slot];
-  const int cx = kp.xy & 0xffff, cy = kp.xy >> 16;
-  int pitch;
-  const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
-  const int lw = L.w, lh = L.h, lpitch = L.pitch;
-  const uint8_t* blur = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
+  __syncthreads();
+  const int nfeatures = P->nfeatures, nlevels = P->nlevels;
+  const int my_base = lane < nlevels ? P->lv[lane].kp_base : 0x7fffffff;
+  const int stride = gridDim.x * kDescWarps;
+  const int stride_f = stride / nfeatures, stride_s = stride - stride_f * nfeatures;
+  // stage A cursor: global slot gA = frameA * nfeatures + slotA, advanced by `stride` per iteration
+  int gA = blockIdx.x * kDescWarps + warp;
+  int frameA = gA / nfeatures, slotA = gA - frameA * nfeatures;
 
-  // pattern of this lane's descriptor byte: 16 points x (x, y) int8
-  const uint4 pa = reinterpret_cast<const uint4*>(d_pattern)[2 * lane], pb = reinterpret_cast<const uint4*>(d_pattern)[2 * lane + 1];
-  const uint32_t pat[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
+  const int bl_half = lane / kPatchWords, bl_j4 = 4 * (lane - bl_half * kPatchWords);   // blurred-window copy role
+  const int rw_third = lane / kRawWords, rw_j4 = 4 * (lane - rw_third * kRawWords);     // raw-window copy role
 
-  // ---- E9 staging first (independent of the angle): the loads overlap the orientation arithmetic
-  const bool fast_path = cx >= kPatchR + 3 && cx + kPatchR + 8 <= lpitch && cx + kPatchR < lw && cy >= kPatchR &&
-                         cy + kPatchR < lh;
-  int mis = 0;
-  if (fast_path) {
-    const uint8_t* w0 = blur + (int64_t)(cy - kPatchR) * lpitch + (cx - kPatchR);
-    mis = (int)((uintptr_t)w0 & 3);
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(w0 - mis);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(s_patch[warp]);
-    const int half = lane >> 4, j = lane & 15, wpitch = lpitch >> 2;
-    if (j < kPatchWords) {
+  auto load_raw = [&]() {
+    DescRaw r;
+    r.kp.resp = 0.f; r.kp.xy = 0; r.my_cnt = 0; r.frame = frameA; r.slot = -1;
+    if (gA < nslots_total) {
+      r.slot = slotA;
+      r.kp = b.kp[gA];                                        // slot gA of the [frame][nfeatures] array
+      if (lane < nlevels) r.my_cnt = b.kp_count[frameA * kMaxLevels + lane];
+    }
+    gA += stride; frameA += stride_f; slotA += stride_s;
+    if (slotA >= nfeatures) { slotA -= nfeatures; frameA++; }
+    return r;
+  };
+  // stage B: decode the slot and start the asynchronous copies of its two windows into `buf`
+  auto decode_issue = [&](const DescRaw& raw, uint8_t* buf) {
+    DescRec r;
+    r.flags = 0; r.frame = 0; r.level = 0; r.cx = 0; r.cy = 0; r.o = 0; r.mis = 0; r.resp = raw.kp.resp;
+    if (raw.slot >= 0) {
+      const int frame = raw.frame, slot = raw.slot;
+      // level of the slot and output offset = sum of the lower levels' counts (lane = level)
+      const int level = __popc(__ballot_sync(0xffffffffu, lane >= 1 && slot >= my_base));
+      const int out_off = __reduce_add_sync(0xffffffffu, lane < level ? raw.my_cnt : 0);
+      const int level_cnt = __shfl_sync(0xffffffffu, raw.my_cnt, level);
+      const int idx = slot - __shfl_sync(0xffffffffu, my_base, level);
+      if (slot == 0) {
+        const int tot = __reduce_add_sync(0xffffffffu, raw.my_cnt);
+        if (lane == 0) out_n[frame] = tot;
+      }
+      if (idx < level_cnt) {
+        const LevelPlan& L = P->lv[level];
+        const int cx = raw.kp.xy & 0xffff, cy = raw.kp.xy >> 16;
+        const int lw = L.w, lh = L.h, lpitch = L.pitch;
+        r.frame = frame; r.level = level; r.cx = cx; r.cy = cy; r.o = out_off + idx; r.flags = 1;
+        const uint32_t sdst = (uint32_t)__cvta_generic_to_shared(buf);
+        if (cx >= kPatchR + 3 && cx + kPatchR + 8 <= lpitch && cx + kPatchR < lw && cy >= kPatchR && cy + kPatchR < lh) {
+          const uint8_t* w0 = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off + (int64_t)(cy - kPatchR) * lpitch +
+                              (cx - kPatchR);
+          const int mis = (int)((uintptr_t)w0 & 3);
+          const uint8_t* src = w0 - mis;
+          r.mis = mis; r.flags |= 2;
+          // two window rows per round: lanes 0-10 one row, lanes 11-21 the next
+          if (bl_half < 2) {
+            const uint8_t* p = src + bl_half * lpitch + bl_j4;
+            const uint32_t d = sdst + bl_half * kPatchPitch + bl_j4;
 #pragma unroll
-      for (int r0 = 0; r0 < kPatchRows; r0 += 2) {
-        const int r = r0 + half;
-        if (r < kPatchRows) dst[r * kPatchWords + j] = src[r * wpitch + j];
+            for (int r0 = 0; r0 < kPatchRows; r0 += 2) {
+              if (r0 + bl_half < kPatchRows) cp_async4(d + r0 * kPatchPitch, p);
+              p += 2 * lpitch;
+            }
+          }
+        }
+        int pitch;
+        const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
+        if ((pitch & 3) == 0) {     // the window's misalignment is then the same on every row
+          const uint8_t* w0 = img + (int64_t)(cy - kHalfPatch) * pitch + (cx - kHalfPatch);
+          const int mis = (int)((uintptr_t)w0 & 3);
+          const uint8_t* src = w0 - mis;
+          r.mis |= mis << 8; r.flags |= 4;
+          // three window rows per round: lanes 0-8, 9-17, 18-26
+          if (rw_third < 3) {
+            const uint8_t* p = src + rw_third * pitch + rw_j4;
+            const uint32_t d = sdst + kBlurBufBytes + rw_third * kRawPitch + rw_j4;
+#pragma unroll
+            for (int r0 = 0; r0 < kRawRows; r0 += 3) {
+              if (r0 + rw_third < kRawRows) cp_async4(d + r0 * kRawPitch, p);
+              p += 3 * pitch;
+            }
+          }
+        }
       }
     }
-  }
-
-  // ---- E7 IC_Angle (:124-151): m10 = sum u*I, m01 = sum v*I over the 749-px disc, UNBLURRED level
-  int m10 = 0, m01 = 0;
-  if (lane < 31) {
-    const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
-    const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
-    int colsum = 0;
+    cp_async_commit();            // one group per slot, empty or not, so that wait_group counts slots
+    return r;
+  };
+  // stage C: orientation, descriptor, keypoint record
+  auto compute = [&](const DescRec& r, const uint8_t* buf) {
+    if (!(r.flags & 1)) return;
+    const int frame = r.frame, level = r.level, cx = r.cx, cy = r.cy;
+    const LevelPlan& L = P->lv[level];
+    // ---- E7 IC_Angle (:124-151): m10 = sum u*I, m01 = sum v*I over the 749-px disc, UNBLURRED level
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+      const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+      int colsum = 0;
+      if (r.flags & 4) {
+        const uint8_t* c = buf + kBlurBufBytes + kHalfPatch * kRawPitch + ((r.mis >> 8) & 3) + lane;
 #pragma unroll
-    for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-      if (au <= kUmax[v < 0 ? -v : v]) {
-        const int I = c[v * pitch];
-        colsum += I;
-        m01 += v * I;
-      }
-    }
-    m10 = u * colsum;
-  }
-  m10 = __reduce_add_sync(0xffffffffu, m10);
-  m01 = __reduce_add_sync(0xffffffffu, m01);
-  const float angle = fast_atan2_dev((float)m01, (float)m10);
-
-  // ---- E9 computeOrbDescriptor (:155-194): lane = descriptor byte, 8 comparisons of rotated pattern samples
-  const float factorPI = (float)(3.14159265358979323846 / 180.f);
-  float sa, ca;
-  sincosf_glibc(__fmul_rn(angle, factorPI), &sa, &ca);
-  __syncwarp();
-  const uint8_t* sp = s_patch[warp] + kPatchR * kPatchPitch + kPatchR + mis;
-  int val = 0;
-#pragma unroll
-  for (int j = 0; j < 8; j++) {
-    int t[2];
-#pragma unroll
-    for (int e = 0; e < 2; e++) {
-      const uint32_t w = pat[j] >> (16 * e);
-      // exact small-integer <-> float conversions through the 1.5 * 2^23 trick (FADD/IADD instead of the XU pipe's
-      // I2F / F2I); float -> int rounds half to even exactly like cvRound
-      const float px = __fsub_rn(__int_as_float(0x4B400000 + (int)(int8_t)(w & 0xff)), 12582912.f);
-      const float py = __fsub_rn(__int_as_float(0x4B400000 + (int)(int8_t)((w >> 8) & 0xff)), 12582912.f);
-      const int ry = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)), 12582912.f)) - 0x4B400000;
-      const int rx = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)), 12582912.f)) - 0x4B400000;
-      if (fast_path) {
-        t[e] = sp[ry * kPatchPitch + rx];
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+          if (au <= kUmax[v < 0 ? -v : v]) {
+            const int I = c[v * kRawPitch];
+            colsum += I;
+            m01 += v * I;
+          }
+        }
       } else {
-        const int x = cx + rx, y = cy + ry;
-        if (x >= 0 && x < lw && y >= 0 && y < lh) t[e] = blur[(int64_t)y * lpitch + x];
-        else t[e] = img[(int64_t)reflect101(y, lh) * pitch + reflect101(x, lw)];
+        int pitch;
+        const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
+        const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
+#pragma unroll
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+          if (au <= kUmax[v < 0 ? -v : v]) {
+            const int I = c[v * pitch];
+            colsum += I;
+            m01 += v * I;
+          }
+        }
+      }
+      m10 = u * colsum;
+    }
+    m10 = __reduce_add_sync(0xffffffffu, m10);
+    m01 = __reduce_add_sync(0xffffffffu, m01);
+    const float angle = fast_atan2_dev((float)m01, (float)m10);
+
+    // ---- E9 computeOrbDescriptor (:155-194): lane = descriptor byte, 8 comparisons of rotated pattern samples
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float sa, ca;
+    sincosf_glibc(__fmul_rn(angle, factorPI), &sa, &ca);
+    int val = 0;
+    if (r.flags & 2) {
+      // sample (rx, ry) sits at window byte (ry + 18) * 44 + rx + 18 + mis >= 0; rx, ry come out of the magic-number
+      // rounding as kMagicBits + value, so the constant part of the index is folded into the offset (mod 2^32)
+      const uint32_t base_off = (uint32_t)(kPatchR * kPatchPitch + kPatchR + (r.mis & 3)) -
+                                (uint32_t)(kPatchPitch + 1) * (uint32_t)kMagicBits;
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        int t[2];
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          const float2 p = s_pat[(2 * j + e) * 32 + lane];
+          // float -> int rounds half to even exactly like cvRound; every product and sum individually rounded (:165)
+          const int ryb = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)), kMagic));
+          const int rxb = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)), kMagic));
+          t[e] = buf[(uint32_t)ryb * (uint32_t)kPatchPitch + (uint32_t)rxb + base_off];
+        }
+        val |= (t[0] < t[1]) << j;
+      }
+    } else {
+      int pitch;
+      const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
+      const int lw = L.w, lh = L.h, lpitch = L.pitch;
+      const uint8_t* blur = b.blur + (int64_t)frame * P->blur_frame_bytes + L.off;
+#pragma unroll 1
+      for (int j = 0; j < 8; j++) {
+        int t[2];
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          const float2 p = s_pat[(2 * j + e) * 32 + lane];
+          const int ry = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)), kMagic)) - kMagicBits;
+          const int rx = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)), kMagic)) - kMagicBits;
+          const int x = cx + rx, y = cy + ry;
+          if (x >= 0 && x < lw && y >= 0 && y < lh) t[e] = blur[(int64_t)y * lpitch + x];
+          else t[e] = img[(int64_t)reflect101(y, lh) * pitch + reflect101(x, lw)];
+        }
+        val |= (t[0] < t[1]) << j;
       }
     }
-    val |= (t[0] < t[1]) << j;
-  }
-  const int o = out_off + idx;
-  out_desc[((int64_t)frame * P->nfeatures + o) * 32 + lane] = (uint8_t)val;
+    out_desc[((int64_t)frame * nfeatures + r.o) * 32 + lane] = (uint8_t)val;
 
-  // ---- E10 keypoint record (:687-694, :769-775)
-  if (lane < 7) {
-    float fx = (float)cx, fy = (float)cy;
-    if (level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
-    uint32_t w;
-    switch (lane) {
-      case 0: w = __float_as_uint(fx); break;
-      case 1: w = __float_as_uint(fy); break;
-      case 2: w = __float_as_uint(L.size); break;
-      case 3: w = __float_as_uint(angle); break;
-      case 4: w = __float_as_uint(kp.resp); break;
-      case 5: w = (uint32_t)level; break;
-      default: w = 0xffffffffu; break;
+    // ---- E10 keypoint record (:687-694, :769-775)
+    if (lane < 7) {
+      float fx = (float)cx, fy = (float)cy;
+      if (level != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+      uint32_t w;
+      switch (lane) {
+        case 0: w = __float_as_uint(fx); break;
+        case 1: w = __float_as_uint(fy); break;
+        case 2: w = __float_as_uint(L.size); break;
+        case 3: w = __float_as_uint(angle); break;
+        case 4: w = __float_as_uint(r.resp); break;
+        case 5: w = (uint32_t)level; break;
+        default: w = 0xffffffffu; break;
+      }
+      reinterpret_cast<uint32_t*>(out_kps + (int64_t)frame * nfeatures + r.o)[lane] = w;
     }
-    reinterpret_cast<uint32_t*>(out_kps + (int64_t)frame * P->nfeatures + o)[lane] = w;
+  };
+
+  // ---- pipeline ---------------------------------------------------------------------------------------------------------
+  uint8_t* buf0 = s_buf[warp][0];
+  uint8_t* buf1 = s_buf[warp][1];
+  DescRaw raw = load_raw();
+  DescRec rec0 = decode_issue(raw, buf0);
+  raw = load_raw();
+  DescRec rec1 = decode_issue(raw, buf1);
+  raw = load_raw();
+  for (int g = blockIdx.x * kDescWarps + warp; g < nslots_total; g += stride) {
+    cp_async_wait<1>();           // every group but the newest has landed: this slot's windows are complete
+    __syncwarp();
+    compute(rec0, buf0);
+    __syncwarp();                 // all lanes are done reading buf0 before it is refilled
+    rec0 = rec1;
+    rec1 = decode_issue(raw, buf0);
+    raw = load_raw();
+    uint8_t* tmp = buf0; buf0 = buf1; buf1 = tmp;
   }
+  cp_async_wait<0>();
 }
 
 void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, orbx_keypoint* d_kps, uint8_t* d_desc,
                      int32_t* d_n_out, cudaStream_t s) {
   const int nslots = hp.nfeatures * nframes;
-  describe_kernel<<<(nslots + kDescWarps - 1) / kDescWarps, 32 * kDescWarps, 0, s>>>(b, d_kps, d_desc, d_n_out, nslots);
+  static int max_ctas = 0;
+  if (!max_ctas) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, describe_kernel, 32 * kDescWarps, 0);
+    max_ctas = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  const int ctas = (nslots + kDescWarps - 1) / kDescWarps;
+  describe_kernel<<<ctas < max_ctas ? ctas : max_ctas, 32 * kDescWarps, 0, s>>>(b, d_kps, d_desc, d_n_out, nslots);
 }
 
 }  // namespace orbx
