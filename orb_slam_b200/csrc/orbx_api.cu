@@ -30,7 +30,8 @@ struct orbx_handle {
   int64_t cap_pyr = 0, cap_cand = 0, cap_list = 0, cap_cells_frame = 0;
   int in_pitch = 0;
   int64_t in_frame_bytes = 0;
-  cudaStream_t s_compute = nullptr, s_in = nullptr, s_out = nullptr;
+  cudaStream_t s_compute = nullptr, s_in = nullptr, s_out = nullptr, s_aux = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // blur runs beside select on s_aux
   cudaEvent_t ev_in[2], ev_compute[2], ev_out[2], ev_stage[ORBX_STAGE_COUNT + 1];
   bool profiling = false;
   float prof_ms[ORBX_STAGE_COUNT] = {0};
@@ -188,6 +189,9 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     CK(cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->s_aux, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     return upload_plan(h, pp->max_width, pp->max_height);
   };
   int rc = body();
@@ -206,6 +210,9 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->s_compute) {
     cudaStreamDestroy(h->s_compute); cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
+    if (h->s_aux) cudaStreamDestroy(h->s_aux);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_compute[i]); cudaEventDestroy(h->ev_out[i]); }
     for (int i = 0; i <= ORBX_STAGE_COUNT; i++) cudaEventDestroy(h->ev_stage[i]);
   }
@@ -233,10 +240,21 @@ static int run_chunk(orbx_handle* h, const uint8_t* d_imgs, int n, size_t stride
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
-  launch_select(b, dp, n, s);
-  if (prof) cudaEventRecord(h->ev_stage[st++], s);
-  launch_blur(b, dp, h->tiles, n, s);
-  if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  if (prof) {                     // serial, so that the per-stage events mean something
+    launch_select(b, dp, n, s);
+    cudaEventRecord(h->ev_stage[st++], s);
+    launch_blur(b, dp, h->tiles, n, s);
+    cudaEventRecord(h->ev_stage[st++], s);
+  } else {
+    // select is a latency-bound kernel of a few thousand warps and blur does not depend on it: blur runs beside it
+    // on s_aux (fork after FAST, whose CTAs fill the SMs' shared memory; join before describe)
+    CK(cudaEventRecord(h->ev_fork, s));
+    launch_select(b, dp, n, s);
+    CK(cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
+    launch_blur(b, dp, h->tiles, n, h->s_aux);
+    CK(cudaEventRecord(h->ev_join, h->s_aux));
+    CK(cudaStreamWaitEvent(s, h->ev_join, 0));
+  }
   launch_describe(b, dp, n, d_kps, d_desc, d_n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   h->launches += dp.nlevels + 3;
