@@ -16,9 +16,17 @@ struct orbx_handle {
   BlurTiles tiles;
   std::string err;
   // device memory (sized once for max_batch frames of max_width x max_height)
-  uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_in[2] = {nullptr, nullptr};
-  Cand *d_cand = nullptr, *d_list = nullptr, *d_kp = nullptr;
-  int32_t *d_n_total = nullptr, *d_n_retain = nullptr, *d_kp_count = nullptr, *d_err = nullptr;
+  // Two complete scratch sets + streams: consecutive chunks have no data dependence, so chunk k+1's kernels run beside
+  // chunk k's and fill the SMs during its latency-bound stages (select) and kernel tails.
+  struct Lane {
+    uint8_t *d_pyr = nullptr, *d_blur = nullptr;
+    Cand *d_cand = nullptr, *d_list = nullptr, *d_kp = nullptr;
+    int32_t *d_n_total = nullptr, *d_n_retain = nullptr, *d_kp_count = nullptr;
+    cudaStream_t s_main = nullptr, s_aux = nullptr;                       // blur runs beside select on s_aux
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
+  } lane[2];
+  uint8_t* d_in[2] = {nullptr, nullptr};
+  int32_t* d_err = nullptr;
   DevicePlan* d_plan = nullptr;
   CellPlan* d_cells = nullptr;
   ResizeX* d_rx = nullptr;
@@ -30,8 +38,8 @@ struct orbx_handle {
   int64_t cap_pyr = 0, cap_cand = 0, cap_list = 0, cap_cells_frame = 0;
   int in_pitch = 0;
   int64_t in_frame_bytes = 0;
-  cudaStream_t s_compute = nullptr, s_in = nullptr, s_out = nullptr, s_aux = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // blur runs beside select on s_aux
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_user = nullptr;                      // fork point on a caller's stream (device-resident API)
   cudaEvent_t ev_in[2], ev_compute[2], ev_out[2], ev_stage[ORBX_STAGE_COUNT + 1];
   bool profiling = false;
   float prof_ms[ORBX_STAGE_COUNT] = {0};
@@ -109,7 +117,7 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     h->err = "cell too large for the shared-memory FAST tile (cell area > ~100k px)";
     return ORBX_ERR_UNSUPPORTED;
   }
-  CK(cudaStreamSynchronize(h->s_compute));
+  for (auto& ln : h->lane) CK(cudaStreamSynchronize(ln.s_main));
   CK(cudaMemcpy(h->d_plan, &dp, sizeof(dp), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(h->d_cells, h->hp.cells.data(), h->hp.cells.size() * sizeof(CellPlan), cudaMemcpyHostToDevice));
   if (!h->hp.rx.empty()) {
@@ -162,14 +170,21 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     h->cap_cells_frame = dp.total_cells * 2 + 64;
     h->in_pitch = (pp->max_width + 15) / 16 * 16;
     h->in_frame_bytes = (int64_t)h->in_pitch * pp->max_height;
-    CK(cudaMalloc(&h->d_pyr, B * h->cap_pyr));
-    CK(cudaMalloc(&h->d_blur, B * h->cap_pyr));
-    CK(cudaMalloc(&h->d_cand, B * h->cap_cand * sizeof(Cand)));
-    CK(cudaMalloc(&h->d_list, B * h->cap_list * sizeof(Cand)));
-    CK(cudaMalloc(&h->d_kp, B * pp->nfeatures * sizeof(Cand)));
-    CK(cudaMalloc(&h->d_n_total, B * h->cap_cells_frame * sizeof(int32_t)));
-    CK(cudaMalloc(&h->d_n_retain, B * h->cap_cells_frame * sizeof(int32_t)));
-    CK(cudaMalloc(&h->d_kp_count, B * kMaxLevels * sizeof(int32_t)));
+    for (auto& ln : h->lane) {
+      CK(cudaMalloc(&ln.d_pyr, B * h->cap_pyr));
+      CK(cudaMalloc(&ln.d_blur, B * h->cap_pyr));
+      CK(cudaMalloc(&ln.d_cand, B * h->cap_cand * sizeof(Cand)));
+      CK(cudaMalloc(&ln.d_list, B * h->cap_list * sizeof(Cand)));
+      CK(cudaMalloc(&ln.d_kp, B * pp->nfeatures * sizeof(Cand)));
+      CK(cudaMalloc(&ln.d_n_total, B * h->cap_cells_frame * sizeof(int32_t)));
+      CK(cudaMalloc(&ln.d_n_retain, B * h->cap_cells_frame * sizeof(int32_t)));
+      CK(cudaMalloc(&ln.d_kp_count, B * kMaxLevels * sizeof(int32_t)));
+      CK(cudaStreamCreateWithFlags(&ln.s_main, cudaStreamNonBlocking));
+      CK(cudaStreamCreateWithFlags(&ln.s_aux, cudaStreamNonBlocking));
+      CK(cudaEventCreateWithFlags(&ln.ev_fork, cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&ln.ev_join, cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&ln.ev_done, cudaEventDisableTiming));
+    }
     CK(cudaMalloc(&h->d_err, sizeof(int32_t)));
     CK(cudaMemset(h->d_err, 0, sizeof(int32_t)));
     CK(cudaMalloc(&h->d_plan, sizeof(DevicePlan)));
@@ -186,12 +201,9 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
       CK(cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming));
     }
     for (int i = 0; i <= ORBX_STAGE_COUNT; i++) CK(cudaEventCreate(&h->ev_stage[i]));
-    CK(cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&h->s_aux, cudaStreamNonBlocking));
-    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_user, cudaEventDisableTiming));
     return upload_plan(h, pp->max_width, pp->max_height);
   };
   int rc = body();
@@ -204,15 +216,21 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   if (!h) return;
   cudaSetDevice(h->p.device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->d_pyr, h->d_blur, h->d_cand, h->d_list, h->d_kp, h->d_n_total, h->d_n_retain, h->d_kp_count,
-                  h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_in[0], h->d_in[1], h->d_out_kps[0],
+  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_in[0], h->d_in[1], h->d_out_kps[0],
                   h->d_out_kps[1], h->d_out_desc[0], h->d_out_desc[1], h->d_out_n[0], h->d_out_n[1]};
   for (void* p : ptrs) if (p) cudaFree(p);
-  if (h->s_compute) {
-    cudaStreamDestroy(h->s_compute); cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
-    if (h->s_aux) cudaStreamDestroy(h->s_aux);
-    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-    if (h->ev_join) cudaEventDestroy(h->ev_join);
+  for (auto& ln : h->lane) {
+    void* lp[] = {ln.d_pyr, ln.d_blur, ln.d_cand, ln.d_list, ln.d_kp, ln.d_n_total, ln.d_n_retain, ln.d_kp_count};
+    for (void* p : lp) if (p) cudaFree(p);
+    if (ln.s_main) cudaStreamDestroy(ln.s_main);
+    if (ln.s_aux) cudaStreamDestroy(ln.s_aux);
+    if (ln.ev_fork) cudaEventDestroy(ln.ev_fork);
+    if (ln.ev_join) cudaEventDestroy(ln.ev_join);
+    if (ln.ev_done) cudaEventDestroy(ln.ev_done);
+  }
+  if (h->s_in) {
+    cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
+    if (h->ev_user) cudaEventDestroy(h->ev_user);
     for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_compute[i]); cudaEventDestroy(h->ev_out[i]); }
     for (int i = 0; i <= ORBX_STAGE_COUNT; i++) cudaEventDestroy(h->ev_stage[i]);
   }
@@ -225,13 +243,15 @@ extern "C" const char* orbx_last_error(const orbx_handle* h) { return h ? h->err
 extern "C" int64_t orbx_kernel_launches(const orbx_handle* h) { return h ? h->launches : 0; }
 
 // One chunk (<= max_batch frames) on stream s: 7 resizes, FAST cells, select, blur, describe = nlevels + 3 launches.
-static int run_chunk(orbx_handle* h, const uint8_t* d_imgs, int n, size_t stride, size_t frame_stride,
+// `li` selects the scratch set; s is the stream the chunk is ordered on (the lane's own s_main or a caller's stream).
+static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_t stride, size_t frame_stride,
                      orbx_keypoint* d_kps, uint8_t* d_desc, int32_t* d_n, cudaStream_t s) {
   const DevicePlan& dp = h->hp.dp;
+  orbx_handle::Lane& ln = h->lane[li];
   ChunkBuffers b{};
   b.lv0 = d_imgs; b.lv0_frame_stride = (int64_t)frame_stride; b.lv0_pitch = (int)stride;
-  b.pyr = h->d_pyr; b.blur = h->d_blur; b.cand = h->d_cand; b.n_total = h->d_n_total; b.n_retain = h->d_n_retain;
-  b.list = h->d_list; b.kp = h->d_kp; b.kp_count = h->d_kp_count; b.err_flag = h->d_err;
+  b.pyr = ln.d_pyr; b.blur = ln.d_blur; b.cand = ln.d_cand; b.n_total = ln.d_n_total; b.n_retain = ln.d_n_retain;
+  b.list = ln.d_list; b.kp = ln.d_kp; b.kp_count = ln.d_kp_count; b.err_flag = h->d_err;
   b.plan = h->d_plan; b.cells = h->d_cells; b.rx = h->d_rx; b.ry = h->d_ry;
   const bool prof = h->profiling;
   int st = 0;
@@ -248,12 +268,12 @@ static int run_chunk(orbx_handle* h, const uint8_t* d_imgs, int n, size_t stride
   } else {
     // select is a latency-bound kernel of a few thousand warps and blur does not depend on it: blur runs beside it
     // on s_aux (fork after FAST, whose CTAs fill the SMs' shared memory; join before describe)
-    CK(cudaEventRecord(h->ev_fork, s));
+    CK(cudaEventRecord(ln.ev_fork, s));
     launch_select(b, dp, n, s);
-    CK(cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
-    launch_blur(b, dp, h->tiles, n, h->s_aux);
-    CK(cudaEventRecord(h->ev_join, h->s_aux));
-    CK(cudaStreamWaitEvent(s, h->ev_join, 0));
+    CK(cudaStreamWaitEvent(ln.s_aux, ln.ev_fork, 0));
+    launch_blur(b, dp, h->tiles, n, ln.s_aux);
+    CK(cudaEventRecord(ln.ev_join, ln.s_aux));
+    CK(cudaStreamWaitEvent(s, ln.ev_join, 0));
   }
   launch_describe(b, dp, n, d_kps, d_desc, d_n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
@@ -286,7 +306,7 @@ extern "C" int orbx_synchronize(orbx_handle* h) {
   if (!h) return ORBX_ERR_ARG;
   CK(cudaSetDevice(h->p.device));
   CK(cudaStreamSynchronize(h->s_in));
-  CK(cudaStreamSynchronize(h->s_compute));
+  for (auto& ln : h->lane) CK(cudaStreamSynchronize(ln.s_main));
   CK(cudaStreamSynchronize(h->s_out));
   int32_t flag = 0;
   CK(cudaMemcpy(&flag, h->d_err, sizeof(flag), cudaMemcpyDeviceToHost));
@@ -304,7 +324,7 @@ extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, 
   int rc = check_args(h, d_imgs, nframes, w, hgt, stride, d_kps, d_desc, d_n_out);
   if (rc != ORBX_OK) return rc;
   CK(cudaSetDevice(h->p.device));
-  cudaStream_t s = stream ? (cudaStream_t)stream : h->s_compute;
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->lane[0].s_main;
   if (!d_imgs || w == 0 || hgt == 0 || nframes == 0) {  // empty image: nothing extracted (:721-722)
     if (nframes > 0) CK(cudaMemsetAsync(d_n_out, 0, sizeof(int) * nframes, s));
     return ORBX_OK;
@@ -312,16 +332,33 @@ extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, 
   rc = upload_plan(h, w, hgt);
   if (rc != ORBX_OK) return rc;
   const int B = h->p.max_batch, nf = h->p.nfeatures;
-  for (int f0 = 0; f0 < nframes; f0 += B) {
+  if (nframes <= B || h->profiling) {   // one chunk (or serial, timed stages): everything on the caller's stream
+    for (int f0 = 0; f0 < nframes; f0 += B) {
+      const int n = std::min(B, nframes - f0);
+      rc = run_chunk(h, 0, d_imgs + (size_t)f0 * frame_stride, n, stride, frame_stride, d_kps + (size_t)f0 * nf,
+                     d_desc + (size_t)f0 * nf * 32, d_n_out + f0, s);
+      if (rc != ORBX_OK) return rc;
+    }
+    return ORBX_OK;
+  }
+  // several chunks: fork the caller's stream into the two lanes, alternate chunks between them, join at the end
+  CK(cudaEventRecord(h->ev_user, s));
+  for (auto& ln : h->lane) CK(cudaStreamWaitEvent(ln.s_main, h->ev_user, 0));
+  int k = 0;
+  for (int f0 = 0; f0 < nframes; f0 += B, k++) {
     const int n = std::min(B, nframes - f0);
-    rc = run_chunk(h, d_imgs + (size_t)f0 * frame_stride, n, stride, frame_stride, d_kps + (size_t)f0 * nf,
-                   d_desc + (size_t)f0 * nf * 32, d_n_out + f0, s);
+    rc = run_chunk(h, k & 1, d_imgs + (size_t)f0 * frame_stride, n, stride, frame_stride, d_kps + (size_t)f0 * nf,
+                   d_desc + (size_t)f0 * nf * 32, d_n_out + f0, h->lane[k & 1].s_main);
     if (rc != ORBX_OK) return rc;
+  }
+  for (auto& ln : h->lane) {
+    CK(cudaEventRecord(ln.ev_done, ln.s_main));
+    CK(cudaStreamWaitEvent(s, ln.ev_done, 0));
   }
   return ORBX_OK;
 }
 
-// HOST buffers: chunk k's H2D (s_in), kernels (s_compute) and D2H (s_out) overlap with chunks k-1 / k+1 through two
+// HOST buffers: chunk k's H2D (s_in), kernels (lane k & 1) and D2H (s_out) overlap with chunks k-1 / k+1 through two
 // staging slots.  Pinned caller memory makes the copies truly asynchronous; pageable memory still works.
 extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nframes, int w, int hgt, size_t stride,
                                   size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int* n_out) {
@@ -350,12 +387,13 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nfram
                              cudaMemcpyHostToDevice, h->s_in));
     }
     CK(cudaEventRecord(h->ev_in[slot], h->s_in));
-    CK(cudaStreamWaitEvent(h->s_compute, h->ev_in[slot], 0));
-    if (k >= 2) CK(cudaStreamWaitEvent(h->s_compute, h->ev_out[slot], 0));  // slot's previous output drained
-    rc = run_chunk(h, h->d_in[slot], n, pitch, fbytes, h->d_out_kps[slot], h->d_out_desc[slot], h->d_out_n[slot],
-                   h->s_compute);
+    cudaStream_t sc = h->lane[h->profiling ? 0 : slot].s_main;
+    CK(cudaStreamWaitEvent(sc, h->ev_in[slot], 0));
+    if (k >= 2) CK(cudaStreamWaitEvent(sc, h->ev_out[slot], 0));  // slot's previous output drained
+    rc = run_chunk(h, h->profiling ? 0 : slot, h->d_in[slot], n, pitch, fbytes, h->d_out_kps[slot], h->d_out_desc[slot],
+                   h->d_out_n[slot], sc);
     if (rc != ORBX_OK) return rc;
-    CK(cudaEventRecord(h->ev_compute[slot], h->s_compute));
+    CK(cudaEventRecord(h->ev_compute[slot], sc));
     CK(cudaStreamWaitEvent(h->s_out, h->ev_compute[slot], 0));
     CK(cudaMemcpyAsync(kps + (size_t)f0 * nf, h->d_out_kps[slot], sizeof(orbx_keypoint) * nf * n,
                        cudaMemcpyDeviceToHost, h->s_out));

@@ -29,8 +29,8 @@ extern "C" int orbx_debug_level_cells(orbx_handle* h, int frame, int level, int3
   const DevicePlan& dp = h->hp.dp;
   const LevelPlan& L = dp.lv[level];
   const int64_t off = (int64_t)frame * dp.total_cells + L.cell_base;
-  if (n_total) CK(cudaMemcpy(n_total, h->d_n_total + off, sizeof(int32_t) * L.nCells, cudaMemcpyDeviceToHost));
-  if (n_retain) CK(cudaMemcpy(n_retain, h->d_n_retain + off, sizeof(int32_t) * L.nCells, cudaMemcpyDeviceToHost));
+  if (n_total) CK(cudaMemcpy(n_total, h->last.n_total + off, sizeof(int32_t) * L.nCells, cudaMemcpyDeviceToHost));
+  if (n_retain) CK(cudaMemcpy(n_retain, h->last.n_retain + off, sizeof(int32_t) * L.nCells, cudaMemcpyDeviceToHost));
   return ORBX_OK;
 }
 
@@ -46,12 +46,12 @@ extern "C" int orbx_debug_cell_candidates(orbx_handle* h, int frame, int level, 
   CK(cudaDeviceSynchronize());
   const CellPlan& c = h->hp.cells[L.cell_base + cell];
   int32_t cnt = 0;
-  CK(cudaMemcpy(&cnt, h->d_n_total + (int64_t)frame * dp.total_cells + L.cell_base + cell, sizeof(cnt),
+  CK(cudaMemcpy(&cnt, h->last.n_total + (int64_t)frame * dp.total_cells + L.cell_base + cell, sizeof(cnt),
                 cudaMemcpyDeviceToHost));
   *n = cnt;
   const int m = std::min(cnt, cap);
   std::vector<Cand> tmp(m);
-  if (m) CK(cudaMemcpy(tmp.data(), h->d_cand + (int64_t)frame * dp.cand_per_frame + c.cand_off, sizeof(Cand) * m,
+  if (m) CK(cudaMemcpy(tmp.data(), h->last.cand + (int64_t)frame * dp.cand_per_frame + c.cand_off, sizeof(Cand) * m,
                        cudaMemcpyDeviceToHost));
   for (int i = 0; i < m; i++) { xs[i] = tmp[i].xy & 0xffff; ys[i] = tmp[i].xy >> 16; resp[i] = tmp[i].resp; }
   return ORBX_OK;
