@@ -237,10 +237,15 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   }
   __syncthreads();
 
-  const int tB = kRetryTh, tmin = max(min(tA, tB), 1);
+  const int tB = kRetryTh;
   uint32_t* q = s_queue[warp];
   const uint32_t* s_img32 = reinterpret_cast<const uint32_t*>(s_img);
-
+  // Like the reference (:599-614) the cell is first searched at fastTh only; the sparse stages then see the few
+  // pixels with S >= fastTh instead of every pixel with S >= 7.  Only a cell with <= 3 survivors is searched again
+  // at 7 (everything below is CTA-uniform).  fastTh <= 7: one pass at fastTh serves both thresholds.
+  int tmin = max(tA > tB ? tA : min(tA, tB), 1);
+  bool useA;
+  for (;;) {
   // ---- 1  reject: 8 pixels per thread on the halved u8 image -----------------------------------------------------------
   {
     const int G8 = (rw + 7) >> 3, n8 = G8 * rh;
@@ -331,7 +336,18 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   nB = __reduce_add_sync(0xffffffffu, nB);
   if (lane == 0) { atomicAdd(&s_cnt[0], nA); atomicAdd(&s_cnt[1], nB); }
   __syncthreads();
-  const bool useA = s_cnt[0] > 3;                 // :609-614
+  useA = s_cnt[0] > 3;                            // :609-614
+  if (useA || tmin <= tB) break;
+  // retry at 7: forget this pass's scores and bitmaps
+  __syncthreads();                                // everyone has read s_cnt
+  {
+    const int nz = ((fast_sc_bytes(rw, rh) >> 2) + 3 * nbw + 3) >> 2;
+    for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+    if (tid < 2) s_cnt[tid] = 0;
+  }
+  tmin = tB;
+  __syncthreads();
+  }
   const int total = useA ? s_cnt[0] : s_cnt[1];
   const uint32_t* bm = useA ? s_bmA : s_bmB;
   if (tid == 0) *n_total = total;
