@@ -73,9 +73,10 @@ __device__ __forceinline__ void queue_bits(uint32_t* q, int& qlen, uint32_t bits
   const int excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
   if (qlen + total <= kFastQueue) {
     int off = qlen + excl;
-    while (bits) {
-      q[off++] = base + (uint32_t)(__ffs(bits) - 1);
-      bits &= bits - 1;
+    while (bits) {                                            // entry order is irrelevant: take the TOP bit, one FLO
+      const int bit = 31 - __clz(bits);                       // (ffs = BREV + FLO, both quarter-rate)
+      q[off++] = base + (uint32_t)bit;
+      bits ^= 1u << bit;
     }
     qlen += total;
     __syncwarp();
@@ -93,8 +94,9 @@ __device__ __forceinline__ void queue_bits(uint32_t* q, int& qlen, uint32_t bits
     if (lane >= k && lane < k + kFastSub) {
       int off = qlen + excl - lo;
       while (bits) {
-        q[off++] = base + (uint32_t)(__ffs(bits) - 1);
-        bits &= bits - 1;
+        const int bit = 31 - __clz(bits);
+        q[off++] = base + (uint32_t)bit;
+        bits ^= 1u << bit;
       }
     }
     qlen += hi - lo;

@@ -187,3 +187,21 @@ def test_device_input_unaligned(oracle):
     for f in range(F):
         assert np.array_equal(k2[f, :n[f]], kps[f, :n[f]])
         assert np.array_equal(d_d[f, :n[f]].cpu().numpy(), desc[f, :n[f]])
+
+
+@pytest.mark.parametrize("div,seed", [(3, 11), (6, 12)])
+def test_low_contrast_retry_path(oracle, div, seed):
+    """Low-contrast frames: most cells have <= 3 corners at fastTh = 20 and are searched again at 7 (:609-614) — the
+    second pass of fast_cells_kernel — while a few keep their fastTh result; per-cell counts and the final output
+    must match the oracle."""
+    img = (oracle.synth(480, 640, seed).astype(np.int32) // div + 90).astype(np.uint8)
+    O = oracle.OracleExtractor(1000, 1.2, 8, 1, 20)
+    ok, od = O(img)
+    ex = _ex(nfeatures=1000, nlevels=8, max_width=640, max_height=480, max_batch=1)
+    k, d = ex(img)
+    for l in range(8):
+        nt, nr = ex.debug_level_cells(0, l)
+        ont, onr = O.level_cells(l)
+        assert np.array_equal(nt, ont), f"nTotal level {l}"
+        assert np.array_equal(nr, onr), f"nToRetain level {l}"
+    _cmp_final(k, d, ok, od)
