@@ -165,23 +165,32 @@ __device__ __forceinline__ uint32_t fast_pair_score(const uint32_t* s_img32, int
   return __vmaxs2(__vsub2(m, 0x00010001u), 0u);
 }
 
-__global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffers b) {
+// Per-level constants of the launch, passed by value: they sit in the constant bank, so the only global round trip
+// before the image loads is the CellPlan record.
+struct FastLevels {
+  int fast_th, score_type, total_cells;
+  int64_t cand_per_frame, frame_bytes;
+  int pitch[kMaxLevels];
+  int64_t off[kMaxLevels];
+};
+
+__global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffers b, FastLevels fl) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ uint32_t s_queue[kFastWarps][kFastQueue];
   __shared__ int s_cnt[2];
   __shared__ int s_warp[kFastWarps];
-  const DevicePlan* P = b.plan;
   const int cell = blockIdx.x, frame = blockIdx.y;
   const CellPlan c = b.cells[cell];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int32_t* n_total = b.n_total + (int64_t)frame * P->total_cells + cell;
+  int32_t* n_total = b.n_total + (int64_t)frame * fl.total_cells + cell;
   if (c.rw <= 0) {
     if (tid == 0) *n_total = 0;
     return;
   }
-  int pitch;
-  const uint8_t* img = level_ptr(b, P, c.level, frame, &pitch);
-  const int tA = P->fast_th;
+  const int pitch = c.level == 0 ? b.lv0_pitch : fl.pitch[c.level];
+  const uint8_t* img = c.level == 0 ? b.lv0 + (int64_t)frame * b.lv0_frame_stride
+                                    : b.pyr + (int64_t)frame * fl.frame_bytes + fl.off[c.level];
+  const int tA = fl.fast_th;
   const int rw = c.rw, rh = c.rh, cw = rw + 6, ch = rh + 6;   // cw x ch = the sub-image handed to cv::FAST
   const int sp16 = fast_sp16(cw), sp32 = sp16 >> 1, bp = fast_bp(rw), scp = fast_scp(rw);
   const int wpr = (rw + 31) >> 5, nbw = wpr * rh;               // bitmap words per scored row / per bitmap
@@ -195,41 +204,43 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
 
   // ---- 0  stage the sub-image: 8 pixels per thread from three aligned 32-bit global loads -----------------------------
   // group u of row r = sub-image columns 8u-5 .. 8u+2 (the first group starts left of the sub-image, inside the level:
-  // cells start at column >= 13) -> halfwords / bytes 8u .. 8u+7 of the staged rows
+  // cells start at column >= 13) -> halfwords / bytes 8u .. 8u+7 of the staged rows.  A thread keeps its column group
+  // and walks down the rows, `rpr` rows per round of the CTA, so the per-round address math is three additions.
   {
-    const int ngrp = fast_ngrp(cw), ntot = ch * ngrp;
-    const uint8_t* img0 = img + (int64_t)(c.y0 - 3) * pitch + (c.x0 - 3) - 5;
-    const int mis0 = (int)(reinterpret_cast<uintptr_t>(img0) & 3);
-    const uint8_t* base0 = img0 - mis0;                          // 4-byte aligned
-    const int sr = magic_div(kFastThreads, c.m_grp), su = kFastThreads - sr * ngrp;
-    int r = magic_div(tid, c.m_grp), u = tid - r * ngrp;
-    // three groups per thread per round, all nine loads issued before the first use
-    for (int i = tid; i < ntot; i += 3 * kFastThreads) {
-      uint32_t w[3][3];
-      int o[3], sh[3];
+    const int ngrp = fast_ngrp(cw);                              // <= kFastThreads (build_plan)
+    const int rpr = magic_div(kFastThreads, c.m_grp);            // rows per round
+    const int r0 = magic_div(tid, c.m_grp), u = tid - r0 * ngrp;
+    if (r0 < rpr) {
+      const uint8_t* img0 = img + (int64_t)(c.y0 - 3) * pitch + (c.x0 - 3) - 5;
+      const int mis0 = (int)(reinterpret_cast<uintptr_t>(img0) & 3);
+      const uint8_t* base0 = img0 - mis0;                        // 4-byte aligned
+      int off = r0 * pitch + 8 * u + mis0;                       // byte offset of the group from base0
+      uint8_t* d16 = reinterpret_cast<uint8_t*>(s_img) + r0 * (2 * sp16) + 16 * u;
+      uint8_t* d8 = s_h8 + r0 * bp + 8 * u;
+      const int s_off = rpr * pitch, s16 = rpr * 2 * sp16, s8 = rpr * bp;
+      // three rows per trip, all nine loads issued before the first use
+      for (int r = r0; r < ch; r += 3 * rpr) {
+        uint32_t w[3][3];
+        int sh[3];
 #pragma unroll
-      for (int k = 0; k < 3; k++) {
-        o[k] = -1;
-        if (i + k * kFastThreads < ntot) {
-          const int off = r * pitch + 8 * u + mis0;
-          const uint32_t* a = reinterpret_cast<const uint32_t*>(base0 + (off & ~3));
-          w[k][0] = a[0]; w[k][1] = a[1]; w[k][2] = a[2];
-          sh[k] = (off & 3) * 8;
-          o[k] = (r << 16) | u;
+        for (int k = 0; k < 3; k++) {
+          if (r + k * rpr < ch) {
+            const uint32_t* a = reinterpret_cast<const uint32_t*>(base0 + ((off + k * s_off) & ~3));
+            w[k][0] = a[0]; w[k][1] = a[1]; w[k][2] = a[2];
+            sh[k] = ((off + k * s_off) & 3) * 8;
+          }
         }
-        r += sr; u += su;
-        if (u >= ngrp) { u -= ngrp; r++; }
-      }
 #pragma unroll
-      for (int k = 0; k < 3; k++) {
-        if (o[k] < 0) continue;
-        const int rr = o[k] >> 16, uu = o[k] & 0xffff;
-        const uint32_t b0 = __funnelshift_r(w[k][0], w[k][1], sh[k]), b1 = __funnelshift_r(w[k][1], w[k][2], sh[k]);
-        *reinterpret_cast<uint4*>(s_img + rr * sp16 + 8 * uu) =
-            make_uint4(__byte_perm(b0, 0, 0x4140), __byte_perm(b0, 0, 0x4342), __byte_perm(b1, 0, 0x4140),
-                       __byte_perm(b1, 0, 0x4342));
-        *reinterpret_cast<uint2*>(s_h8 + rr * bp + 8 * uu) =
-            make_uint2((b0 >> 1) & 0x7f7f7f7fu, (b1 >> 1) & 0x7f7f7f7fu);
+        for (int k = 0; k < 3; k++) {
+          if (r + k * rpr < ch) {
+            const uint32_t b0 = __funnelshift_r(w[k][0], w[k][1], sh[k]), b1 = __funnelshift_r(w[k][1], w[k][2], sh[k]);
+            *reinterpret_cast<uint4*>(d16 + k * s16) =
+                make_uint4(__byte_perm(b0, 0, 0x4140), __byte_perm(b0, 0, 0x4342), __byte_perm(b1, 0, 0x4140),
+                           __byte_perm(b1, 0, 0x4342));
+            *reinterpret_cast<uint2*>(d8 + k * s8) = make_uint2((b0 >> 1) & 0x7f7f7f7fu, (b1 >> 1) & 0x7f7f7f7fu);
+          }
+        }
+        off += 3 * s_off; d16 += 3 * s16; d8 += 3 * s8;
       }
     }
     // score map + bitmaps A, B, C are contiguous; the rounding to 16 bytes may run into bitmap F (written in phase 1)
@@ -360,7 +371,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
   if (total == 0) return;
 
   // ---- 4  ordered emission: popcount prefix over the bitmap words (row-major) ------------------------------------------
-  Cand* out = b.cand + (int64_t)frame * P->cand_per_frame + c.cand_off;
+  Cand* out = b.cand + (int64_t)frame * fl.cand_per_frame + c.cand_off;
   int base = 0;
   for (int i0 = 0; i0 < nbw; i0 += kFastThreads) {
     const int i = i0 + tid;
@@ -389,7 +400,7 @@ __global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffer
         bits &= bits - 1;
         const int lx = c.x0 + x;
         Cand r;
-        r.resp = P->score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
+        r.resp = fl.score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
                                                     : (float)s_sc[(y + 1) * scp + 4 + x];
         r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
         out[off++] = r;
@@ -404,8 +415,12 @@ void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_byt
   // per-device attributes; a few microseconds per chunk of up to max_batch frames
   cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  FastLevels fl;
+  fl.fast_th = hp.fast_th; fl.score_type = hp.score_type; fl.total_cells = hp.total_cells;
+  fl.cand_per_frame = hp.cand_per_frame; fl.frame_bytes = hp.pyr_frame_bytes;
+  for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
   dim3 grid(hp.total_cells, nframes);
-  fast_cells_kernel<<<grid, kFastThreads, smem_bytes, s>>>(b);
+  fast_cells_kernel<<<grid, kFastThreads, smem_bytes, s>>>(b, fl);
 }
 
 }  // namespace orbx

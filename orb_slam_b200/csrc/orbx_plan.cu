@@ -175,6 +175,10 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
             *err = "cell sub-image outside the level (the reference's cv::Mat range assertion fails here)";
             return ORBX_ERR_UNSUPPORTED;
           }
+          if (fast_ngrp(cw) > 256) {
+            *err = "cell wider than 2040 px (fast_cells_kernel stages one 8-pixel group per thread and row)";
+            return ORBX_ERR_UNSUPPORTED;
+          }
           if (cw >= 7 && ch >= 7) {  // FAST scores nothing on a sub-image narrower than 7 px
             c.x0 = (int16_t)(cx0 + 3); c.y0 = (int16_t)(cy0 + 3);
             c.rw = (int16_t)(cw - 6); c.rh = (int16_t)(ch - 6);
