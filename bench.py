@@ -145,6 +145,7 @@ def main():
     ap.add_argument("--no-matching", action="store_true", help="skip the Hamming-matching legs")
     ap.add_argument("--query-keyframes", type=int, default=8, help="config 5: query keyframes (x1000 descriptors) per step")
     ap.add_argument("--match-pairs", type=int, default=256, help="config 4: frame pairs per GPU per step")
+    ap.add_argument("--all-configs", action="store_true", help="also time BASELINE configs 1 and 3 (rank 0, N=1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -283,6 +284,12 @@ def main():
         if rank == 0 and not args.no_cpu:
             knn["cpu_baseline"] = BM.bench_knn2_cpu(args)
         matching = {"knn2_all_pairs": knn, "search_for_initialization": init}
+    other = None
+    if args.all_configs and world == 1:
+        import bench_configs
+        del d_frames, h_frames
+        ex.close()
+        other = bench_configs.run()
     if world > 1:
         dist.barrier()
     if rank == 0:
@@ -301,7 +308,7 @@ def main():
                     "h2d_bytes_per_step": F * H * W, "d2h_bytes_per_step": F * (NFEAT * 60 + 4),
                     "api": "orbx_extract_batch (C ABI, pinned host buffers), wall clock between device syncs"},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "matching": matching}))
+            "matching": matching, "other_configs": other}))
     if world > 1:
         dist.destroy_process_group()
 

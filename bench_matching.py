@@ -122,10 +122,15 @@ def bench_init_search(args, rank, world, dev, local, matcher):
     s1, s2 = om.upload(f1), om.upload(f2)
     idx = np.arange(npairs, dtype=np.int32)
     prev0 = [np.stack([f.x, f.y], 1).astype(np.float32) for f in f1]  # vbPrevMatched = F1 keypoints (Tracking.cc:334-336)
+    stride1 = max(f.n for f in f1)
+    prev_packed0 = np.zeros((npairs, stride1, 2), np.float32)
+    for p in range(npairs):
+        prev_packed0[p, :f1[p].n] = prev0[p]
+    prev_packed = np.empty_like(prev_packed0)
 
     def step():
-        prev = [p.copy() for p in prev0]
-        return om.SearchForInitialization(s1, s2, idx, idx, prev, 100)
+        np.copyto(prev_packed, prev_packed0)          # the search updates vbPrevMatched in place
+        return om.SearchForInitialization(s1, s2, idx, idx, prev_packed, 100)
 
     for _ in range(3):
         nm, rows = step()

@@ -26,6 +26,7 @@ struct orbx_handle {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
   } lane[2];
   uint8_t* d_in[2] = {nullptr, nullptr};
+  uint8_t* d_raw[2] = {nullptr, nullptr};   // tightly packed host rows land here first (one contiguous H2D), then D2D repitch
   int32_t* d_err = nullptr;
   DevicePlan* d_plan = nullptr;
   CellPlan* d_cells = nullptr;
@@ -193,6 +194,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     CK(cudaMalloc(&h->d_ry, h->cap_ry * sizeof(ResizeY)));
     for (int i = 0; i < 2; i++) {
       CK(cudaMalloc(&h->d_in[i], B * h->in_frame_bytes));
+      CK(cudaMalloc(&h->d_raw[i], B * h->in_frame_bytes));
       CK(cudaMalloc(&h->d_out_kps[i], B * pp->nfeatures * sizeof(orbx_keypoint)));
       CK(cudaMalloc(&h->d_out_desc[i], B * pp->nfeatures * 32));
       CK(cudaMalloc(&h->d_out_n[i], B * sizeof(int32_t)));
@@ -216,7 +218,7 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   if (!h) return;
   cudaSetDevice(h->p.device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_in[0], h->d_in[1], h->d_out_kps[0],
+  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_in[0], h->d_in[1], h->d_raw[0], h->d_raw[1], h->d_out_kps[0],
                   h->d_out_kps[1], h->d_out_desc[0], h->d_out_desc[1], h->d_out_n[0], h->d_out_n[1]};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (auto& ln : h->lane) {
@@ -379,7 +381,15 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nfram
     const int n = std::min(B, nframes - f0), slot = k & 1;
     if (k >= 2) CK(cudaStreamWaitEvent(h->s_in, h->ev_compute[slot], 0));  // slot's previous input consumed
     const uint8_t* src = imgs + (size_t)f0 * frame_stride;
-    if (frame_stride == stride * (size_t)hgt) {
+    if (frame_stride == stride * (size_t)hgt && stride == (size_t)pitch) {
+      // rows already have the device pitch: one contiguous copy (a strided 2-D H2D costs a DMA descriptor per row)
+      CK(cudaMemcpyAsync(h->d_in[slot], src, fbytes * n, cudaMemcpyHostToDevice, h->s_in));
+    } else if (frame_stride == stride * (size_t)hgt && frame_stride <= (size_t)h->in_frame_bytes) {
+      // tightly packed rows: contiguous H2D into the raw slot, then re-pitch on the device at HBM speed
+      CK(cudaMemcpyAsync(h->d_raw[slot], src, frame_stride * n, cudaMemcpyHostToDevice, h->s_in));
+      CK(cudaMemcpy2DAsync(h->d_in[slot], pitch, h->d_raw[slot], stride, w, (size_t)hgt * n, cudaMemcpyDeviceToDevice,
+                           h->s_in));
+    } else if (frame_stride == stride * (size_t)hgt) {
       CK(cudaMemcpy2DAsync(h->d_in[slot], pitch, src, stride, w, (size_t)hgt * n, cudaMemcpyHostToDevice, h->s_in));
     } else {
       for (int f = 0; f < n; f++)

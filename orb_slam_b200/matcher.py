@@ -297,20 +297,27 @@ class ORBmatcher:
         return i1, i2
 
     def SearchForInitialization(self, set1: FrameSet, set2: FrameSet, idx1, idx2, vbPrevMatched, windowSize=10):
-        """src/ORBmatcher.cc:598-713.  vbPrevMatched: list (per pair) of [n1,2] float arrays, updated in place.
+        """src/ORBmatcher.cc:598-713.  vbPrevMatched: list (per pair) of [n1,2] float arrays, or one packed float32
+        array [pairs, set1.max_n, 2]; updated in place either way.
         Returns (nmatches[np], vnMatches12 rows [np, stride])."""
         i1, i2 = self._pairs(idx1, idx2)
         stride = max(set1.max_n, 1)
-        xy = np.zeros((len(i1), stride, 2), np.float32)
-        for p, a in enumerate(vbPrevMatched):
-            xy[p, : len(a)] = a
+        packed = (isinstance(vbPrevMatched, np.ndarray) and vbPrevMatched.dtype == np.float32
+                  and vbPrevMatched.shape == (len(i1), stride, 2) and vbPrevMatched.flags.c_contiguous)
+        if packed:      # the ABI's own layout [pair][stride][2]: used (and updated) in place, no per-pair copies
+            xy = vbPrevMatched
+        else:
+            xy = np.zeros((len(i1), stride, 2), np.float32)
+            for p, a in enumerate(vbPrevMatched):
+                xy[p, : len(a)] = a
         out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
         self.m._check(self._L.orbm_search_for_initialization(self.m._h, set1._s, set2._s, i1.ctypes.data, i2.ctypes.data,
                                                              len(i1), xy.ctypes.data, stride, int(windowSize),
                                                              self.mfNNratio, int(self.mbCheckOrientation),
                                                              out.ctypes.data, nm.ctypes.data))
-        for p, a in enumerate(vbPrevMatched):
-            a[...] = xy[p, : len(a)]
+        if not packed:
+            for p, a in enumerate(vbPrevMatched):
+                a[...] = xy[p, : len(a)]
         return nm, out
 
     def WindowSearch(self, set1, set2, idx1, idx2, windowSize, minScaleLevel=0, maxScaleLevel=2**31 - 1):
