@@ -322,110 +322,158 @@ __device__ __forceinline__ bool epipolar_ok(float x1, float y1, float x2, float 
 // candidate list: each evaluates the skip rule against the current state, keeps its own (best, second) packed
 // (dist << 22 | list position) keys and a butterfly merges them.  Packed-key order = (distance, position) order,
 // which is what `if (dist < best) {second = best; best = dist} else if (dist < second) second = dist` computes.
+// The replay is a serial chain, so everything on it is kept off global memory: the per-target state lives in shared
+// memory (copied in / out once), query records are fetched 32 at a time and broadcast by shuffles, the next query's
+// candidates are prefetched while the current one is resolved, the winners' targets travel with the keys (shuffle
+// from the owning lane instead of a reload), and the rotation bins are computed in parallel after the loop (the
+// histogram counts accept EVENTS, a later steal does not remove the entry: :656-663 leaves rotHist alone).
 // ------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) commit_kernel(SearchArgs a) {
-  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+constexpr int kCommitWarps = 2, kCommitSmemTargets = 2048;
+
+__global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a) {
+  __shared__ int2 s_ts[kCommitWarps][kCommitSmemTargets];
+  __shared__ int s_hist[kCommitWarps][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x * kCommitWarps + warp;
   if (p >= a.nproblems) return;
   Problem& P = a.prob[p];
   if (P.cand_base < 0) return;  // arena overflow: the host grows the arena and reruns
   QRec* qr = a.q + P.qstart;
-  int2* ts = a.tstate + P.tstart;
+  int2* gts = a.tstate + P.tstart;
+  const bool ts_in_smem = P.nt <= kCommitSmemTargets;
+  int2* ts = ts_in_smem ? s_ts[warp] : gts;
+  if (ts_in_smem) {
+    for (int i = lane; i < P.nt; i += 32) ts[i] = gts[i];
+    __syncwarp();
+  }
   const uint32_t* cand = a.cand + P.cand_base;
   const int kind = a.kind;
   const float ratio = a.ratio;
   const float kIntMaxF = 2147483648.0f;  // (float)INT_MAX
-  int hist = 0;                           // lane b (< 30) counts rotHist[b].size()
   const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL);
   float F[9];
   if (kind == K_TRIANG)
     for (int k = 0; k < 9; k++) F[k] = a.F12[(int64_t)p * 9 + k];
 
-  for (int q = 0; q < P.nq; q++) {
-    const int cnt = qr[q].cnt;
-    if (cnt == 0) continue;  // inactive query, empty window (`vIndices.empty()`), or empty node list
-    const int off = qr[q].off, src = qr[q].src;
-    int accept_t = -1, accept_d = 0;
-    if (kind != K_TRIANG) {
-      uint32_t b = kNone, s = kNone;
-      for (int j = lane; j < cnt; j += 32) {
-        const uint32_t e = cand[off + j];
-        const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
-        const int2 st = ts[t];
-        const bool skip = kind == K_INIT ? st.y <= d : st.x != -1;  // :637 / `if (taken) continue`
-        if (!skip) {
-          const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
-          s = min(s, max(b, key));
-          b = min(b, key);
-        }
-      }
-      warp_top2(b, s);
-      if (b != kNone) {
-        const int bd = (int)(b >> kCandShift);
-        const int bt = (int)(cand[off + (b & kCandMask)] & kCandMask);
-        const float sdf = s == kNone ? kIntMaxF : (float)(int)(s >> kCandShift);
-        bool ok = false;
-        switch (kind) {
-          case K_INIT: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(sdf, ratio); break;            // :652-654
-          case K_WINDOW: case K_PROJ_FF: ok = (float)bd <= __fmul_rn(sdf, ratio) && bd <= ORBM_TH_HIGH; break;  // :476, :585
-          case K_PROJ_LOCAL: {                                                                          // :112-117
-            if (bd <= ORBM_TH_HIGH) {
-              const int l1 = a.s2.octave[P.tbase + bt];
-              const int l2 = s == kNone ? -1 : a.s2.octave[P.tbase + (int)(cand[off + (s & kCandMask)] & kCandMask)];
-              ok = !(l1 == l2 && (float)bd > __fmul_rn(ratio, sdf));
-            }
-            break;
-          }
-          case K_PROJ_BEST: ok = bd <= a.th_dist; break;                                               // :1576, :1702, :398
-          case K_BOW_KF_F: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;          // :224-226
-          default: ok = bd < ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;                   // :791-793
-        }
-        if (ok) { accept_t = bt; accept_d = bd; }
-      }
-    } else {
-      // SearchForTriangulation :896-958: candidates with dist <= TH_LOW sorted by (dist, idx2); walk while
-      // dist <= 2 * best; the first one passing the epipolar test wins.  Entries already are (dist << 22) | idx2.
-      uint32_t last = 0;
-      bool first = true;
-      int dist_th = 0;
-      const float x1 = a.src.x[P.qsrc + src], y1 = a.src.y[P.qsrc + src];
-      while (true) {
-        uint32_t m = kNone;
-        for (int j = lane; j < cnt; j += 32) {
-          const uint32_t e = cand[off + j];
-          const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
-          if (d <= ORBM_TH_LOW && ts[t].x == -1 && (first || e > last)) m = min(m, e);
-        }
-        m = __reduce_min_sync(0xffffffffu, m);
-        if (m == kNone) break;
-        const int d = (int)(m >> kCandShift), t = (int)(m & kCandMask);
-        if (first) { dist_th = 2 * d; first = false; }
-        if (d > dist_th) break;
-        const int gt = P.tbase + t;
-        int lvl = a.s2.octave[gt];
-        lvl = min(max(lvl, 0), a.nlevels - 1);
-        if (epipolar_ok(x1, y1, a.s2.x[gt], a.s2.y[gt], F, a.sigma2[lvl])) { accept_t = t; accept_d = d; break; }
-        last = m;
-      }
+  for (int q0 = 0; q0 < P.nq; q0 += 32) {
+    // lane i holds the record of query q0 + i
+    int my_cnt = 0, my_off = 0, my_src = 0;
+    if (q0 + lane < P.nq) { my_cnt = qr[q0 + lane].cnt; my_off = qr[q0 + lane].off; my_src = qr[q0 + lane].src; }
+    unsigned todo = __ballot_sync(0xffffffffu, my_cnt != 0);  // inactive query / empty window / empty node list: skip
+    uint32_t e_next = 0;
+    if (todo && kind != K_TRIANG) {
+      const int i = __ffs(todo) - 1;
+      const int c = __shfl_sync(0xffffffffu, my_cnt, i), o = __shfl_sync(0xffffffffu, my_off, i);
+      if (lane < c) e_next = cand[o + lane];
     }
-    if (accept_t >= 0) {
-      int bin = -1;
-      if (use_hist) {
-        bin = rot_bin(a.src.angle[P.qsrc + src], a.s2.angle[P.tbase + accept_t]);
-        if (lane == bin) hist++;
+    while (todo) {
+      const int i = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int q = q0 + i;
+      const int cnt = __shfl_sync(0xffffffffu, my_cnt, i), off = __shfl_sync(0xffffffffu, my_off, i);
+      const int src = __shfl_sync(0xffffffffu, my_src, i);
+      int accept_t = -1, accept_d = 0;
+      if (kind != K_TRIANG) {
+        const uint32_t e0 = e_next;
+        if (todo) {                                            // prefetch the next query's first 32 candidates
+          const int i2 = __ffs(todo) - 1;
+          const int c2 = __shfl_sync(0xffffffffu, my_cnt, i2), o2 = __shfl_sync(0xffffffffu, my_off, i2);
+          if (lane < c2) e_next = cand[o2 + lane];
+        }
+        uint32_t b = kNone, s = kNone;
+        int tb = 0, tsec = 0;                                  // targets of this lane's best / second keys
+        for (int j = lane; j < cnt; j += 32) {
+          const uint32_t e = j < 32 ? e0 : cand[off + j];
+          const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+          const int2 st = ts[t];
+          const bool skip = kind == K_INIT ? st.y <= d : st.x != -1;  // :637 / `if (taken) continue`
+          if (!skip) {
+            const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
+            if (key < b) { s = b; tsec = tb; b = key; tb = t; }
+            else if (key < s) { s = key; tsec = t; }
+          }
+        }
+        uint32_t gb = b, gs = s;
+        warp_top2(gb, gs);
+        if (gb != kNone) {
+          const int bd = (int)(gb >> kCandShift);
+          const int bt = __shfl_sync(0xffffffffu, tb, (int)(gb & 31u));   // list position j lives on lane j % 32
+          const float sdf = gs == kNone ? kIntMaxF : (float)(int)(gs >> kCandShift);
+          bool ok = false;
+          switch (kind) {
+            case K_INIT: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(sdf, ratio); break;            // :652-654
+            case K_WINDOW: case K_PROJ_FF: ok = (float)bd <= __fmul_rn(sdf, ratio) && bd <= ORBM_TH_HIGH; break;  // :476, :585
+            case K_PROJ_LOCAL: {                                                                          // :112-117
+              // the second-best entry is either the best or the second key of the lane that owns its position
+              const int t2 = __shfl_sync(0xffffffffu, b == gs ? tb : tsec, (int)(gs & 31u));
+              if (bd <= ORBM_TH_HIGH) {
+                const int l1 = a.s2.octave[P.tbase + bt];
+                const int l2 = gs == kNone ? -1 : a.s2.octave[P.tbase + t2];
+                ok = !(l1 == l2 && (float)bd > __fmul_rn(ratio, sdf));
+              }
+              break;
+            }
+            case K_PROJ_BEST: ok = bd <= a.th_dist; break;                                               // :1576, :1702, :398
+            case K_BOW_KF_F: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;          // :224-226
+            default: ok = bd < ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;                   // :791-793
+          }
+          if (ok) { accept_t = bt; accept_d = bd; }
+        }
+      } else {
+        // SearchForTriangulation :896-958: candidates with dist <= TH_LOW sorted by (dist, idx2); walk while
+        // dist <= 2 * best; the first one passing the epipolar test wins.  Entries already are (dist << 22) | idx2.
+        uint32_t last = 0;
+        bool first = true;
+        int dist_th = 0;
+        const float x1 = a.src.x[P.qsrc + src], y1 = a.src.y[P.qsrc + src];
+        while (true) {
+          uint32_t m = kNone;
+          for (int j = lane; j < cnt; j += 32) {
+            const uint32_t e = cand[off + j];
+            const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+            if (d <= ORBM_TH_LOW && ts[t].x == -1 && (first || e > last)) m = min(m, e);
+          }
+          m = __reduce_min_sync(0xffffffffu, m);
+          if (m == kNone) break;
+          const int d = (int)(m >> kCandShift), t = (int)(m & kCandMask);
+          if (first) { dist_th = 2 * d; first = false; }
+          if (d > dist_th) break;
+          const int gt = P.tbase + t;
+          int lvl = a.s2.octave[gt];
+          lvl = min(max(lvl, 0), a.nlevels - 1);
+          if (epipolar_ok(x1, y1, a.s2.x[gt], a.s2.y[gt], F, a.sigma2[lvl])) { accept_t = t; accept_d = d; break; }
+          last = m;
+        }
       }
-      if (lane == 0) {
+      if (accept_t >= 0 && lane == 0) {
         if (kind == K_INIT) {  // steal :656-663
           const int prev = ts[accept_t].x;
           if (prev >= 0) qr[prev].match = -1;
         }
         ts[accept_t] = make_int2(src, accept_d);
         qr[q].match = accept_t;
+        qr[q].bin = use_hist ? accept_t : -1;   // the accepted target; turned into its rotation bin after the loop
+      }
+      __syncwarp();
+    }
+  }
+
+  // rotation histogram over the accept events (rotHist[bin].push_back at :665-676 and its siblings), in parallel
+  int hist = 0;                             // lane b (< 30) = rotHist[b].size()
+  if (use_hist) {
+    s_hist[warp][lane] = 0;
+    __syncwarp();
+    for (int q = lane; q < P.nq; q += 32) {
+      const int t = qr[q].bin;
+      if (t >= 0) {
+        const int bin = rot_bin(a.src.angle[P.qsrc + qr[q].src], a.s2.angle[P.tbase + t]);
         qr[q].bin = bin;
+        atomicAdd(&s_hist[warp][bin], 1);
       }
     }
     __syncwarp();
+    hist = s_hist[warp][lane];
   }
-
   // rotation consistency (ComputeThreeMaxima, src/ORBmatcher.cc:1748-1789) + removal of the other bins
   if (a.check_ori && use_hist) {
     int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
@@ -445,6 +493,9 @@ __global__ void __launch_bounds__(64) commit_kernel(SearchArgs a) {
       }
     }
     __syncwarp();
+  }
+  if (ts_in_smem) {
+    for (int i = lane; i < P.nt; i += 32) gts[i] = ts[i];
   }
   int n = 0;
   for (int q = lane; q < P.nq; q += 32) n += qr[q].match >= 0;
