@@ -144,7 +144,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-matching", action="store_true", help="skip the Hamming-matching legs")
     ap.add_argument("--query-keyframes", type=int, default=8, help="config 5: query keyframes (x1000 descriptors) per step")
-    ap.add_argument("--match-pairs", type=int, default=256, help="config 4: frame pairs per GPU per step")
+    ap.add_argument("--match-pairs", type=int, default=2048, help="config 4: frame pairs per GPU per step")
     ap.add_argument("--all-configs", action="store_true", help="also time BASELINE configs 1 and 3 (rank 0, N=1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -169,7 +169,8 @@ int run_job(orbm_handle* h, const HostJob& J) {
       if (bow) bow_fill_kernel<<<blocks, 256, 0, st>>>(a, (int)qtot);
       else grid_fill_kernel<<<blocks, 256, 0, st>>>(a, (int)qtot);
     }
-    commit_kernel<<<(np + kCommitWarps - 1) / kCommitWarps, 32 * kCommitWarps, 0, st>>>(a);
+    cudaFuncSetAttribute(commit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCommitSmemBytes);
+    commit_kernel<<<(np + kCommitWarps - 1) / kCommitWarps, 32 * kCommitWarps, kCommitSmemBytes, st>>>(a);
     emit_kernel<<<np, 128, 0, st>>>(a);
     ORBM_CK(cudaEventRecord(h->ev1, st));
     h->launches += 3 + (ttot ? 1 : 0) + (qtot ? 2 : 0);

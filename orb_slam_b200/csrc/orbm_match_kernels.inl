@@ -329,9 +329,10 @@ __device__ __forceinline__ bool epipolar_ok(float x1, float y1, float x2, float 
 // histogram counts accept EVENTS, a later steal does not remove the entry: :656-663 leaves rotHist alone).
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kCommitWarps = 2, kCommitSmemTargets = 2048;
+constexpr int kCommitSmemBytes = kCommitWarps * (kCommitSmemTargets * 8 + 2 * 32 * 32 * 4);
 
 __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a) {
-  __shared__ int2 s_ts[kCommitWarps][kCommitSmemTargets];
+  extern __shared__ __align__(16) uint8_t commit_smem[];
   __shared__ int s_hist[kCommitWarps][32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int p = blockIdx.x * kCommitWarps + warp;
@@ -341,11 +342,10 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
   QRec* qr = a.q + P.qstart;
   int2* gts = a.tstate + P.tstart;
   const bool ts_in_smem = P.nt <= kCommitSmemTargets;
-  int2* ts = ts_in_smem ? s_ts[warp] : gts;
-  if (ts_in_smem) {
-    for (int i = lane; i < P.nt; i += 32) ts[i] = gts[i];
-    __syncwarp();
-  }
+  int2* ts = ts_in_smem ? reinterpret_cast<int2*>(commit_smem) + warp * kCommitSmemTargets : gts;
+  // first 32 candidates of each query of a 32-query batch, double-buffered: [2][query in batch][lane]
+  uint32_t* s_cb = reinterpret_cast<uint32_t*>(commit_smem + kCommitWarps * kCommitSmemTargets * 8) + warp * (2 * 32 * 32);
+  const uint32_t s_cb_addr = (uint32_t)__cvta_generic_to_shared(s_cb);
   const uint32_t* cand = a.cand + P.cand_base;
   const int kind = a.kind;
   const float ratio = a.ratio;
@@ -355,17 +355,43 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
   if (kind == K_TRIANG)
     for (int k = 0; k < 9; k++) F[k] = a.F12[(int64_t)p * 9 + k];
 
-  for (int q0 = 0; q0 < P.nq; q0 += 32) {
-    // lane i holds the record of query q0 + i
-    int my_cnt = 0, my_off = 0, my_src = 0;
-    if (q0 + lane < P.nq) { my_cnt = qr[q0 + lane].cnt; my_off = qr[q0 + lane].off; my_src = qr[q0 + lane].src; }
-    unsigned todo = __ballot_sync(0xffffffffu, my_cnt != 0);  // inactive query / empty window / empty node list: skip
-    uint32_t e_next = 0;
-    if (todo && kind != K_TRIANG) {
-      const int i = __ffs(todo) - 1;
-      const int c = __shfl_sync(0xffffffffu, my_cnt, i), o = __shfl_sync(0xffffffffu, my_off, i);
-      if (lane < c) e_next = cand[o + lane];
+  // asynchronous copy of the first 32 candidates of every non-empty query of one batch (lane i holds query i's record)
+  auto stage_batch = [&](int cnt_i, int off_i, int buf) {
+    unsigned m = kind == K_TRIANG ? 0u : __ballot_sync(0xffffffffu, cnt_i != 0);
+    while (m) {
+      const int i = __ffs(m) - 1;
+      m &= m - 1;
+      const int c = __shfl_sync(0xffffffffu, cnt_i, i), o = __shfl_sync(0xffffffffu, off_i, i);
+      if (lane < c)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s_cb_addr + 4u * (uint32_t)((buf * 32 + i) * 32 + lane)),
+                     "l"(__cvta_generic_to_global(cand + o + lane)) : "memory");
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  // records: batch k in my_*, batch k+1 in nx_* (loaded one batch ahead), candidates of batch k+1 staged during batch k
+  int my_cnt = 0, my_off = 0, my_src = 0, nx_cnt = 0, nx_off = 0, nx_src = 0;
+  if (lane < P.nq) { my_cnt = qr[lane].cnt; my_off = qr[lane].off; my_src = qr[lane].src; }
+  if (32 + lane < P.nq) { nx_cnt = qr[32 + lane].cnt; nx_off = qr[32 + lane].off; nx_src = qr[32 + lane].src; }
+  stage_batch(my_cnt, my_off, 0);
+  if (ts_in_smem) {                                            // four loads in flight per lane
+    for (int i = lane; i < P.nt; i += 128) {
+      int2 v[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) if (i + 32 * k < P.nt) v[k] = gts[i + 32 * k];
+#pragma unroll
+      for (int k = 0; k < 4; k++) if (i + 32 * k < P.nt) ts[i + 32 * k] = v[k];
+    }
+  }
+  int buf = 0;
+  for (int q0 = 0; q0 < P.nq; q0 += 32, buf ^= 1) {
+    stage_batch(nx_cnt, nx_off, buf ^ 1);                      // reads of buf ^ 1 (batch k - 1) ended with a __syncwarp
+    int nn_cnt = 0, nn_off = 0, nn_src = 0;
+    if (q0 + 64 + lane < P.nq) { nn_cnt = qr[q0 + 64 + lane].cnt; nn_off = qr[q0 + 64 + lane].off; nn_src = qr[q0 + 64 + lane].src; }
+    asm volatile("cp.async.wait_group 1;" ::: "memory");       // this batch's candidates have landed
+    __syncwarp();
+    const uint32_t* cb = s_cb + buf * (32 * 32);
+    unsigned todo = __ballot_sync(0xffffffffu, my_cnt != 0);  // inactive query / empty window / empty node list: skip
     while (todo) {
       const int i = __ffs(todo) - 1;
       todo &= todo - 1;
@@ -374,16 +400,10 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
       const int src = __shfl_sync(0xffffffffu, my_src, i);
       int accept_t = -1, accept_d = 0;
       if (kind != K_TRIANG) {
-        const uint32_t e0 = e_next;
-        if (todo) {                                            // prefetch the next query's first 32 candidates
-          const int i2 = __ffs(todo) - 1;
-          const int c2 = __shfl_sync(0xffffffffu, my_cnt, i2), o2 = __shfl_sync(0xffffffffu, my_off, i2);
-          if (lane < c2) e_next = cand[o2 + lane];
-        }
         uint32_t b = kNone, s = kNone;
         int tb = 0, tsec = 0;                                  // targets of this lane's best / second keys
         for (int j = lane; j < cnt; j += 32) {
-          const uint32_t e = j < 32 ? e0 : cand[off + j];
+          const uint32_t e = j < 32 ? cb[i * 32 + lane] : cand[off + j];
           const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
           const int2 st = ts[t];
           const bool skip = kind == K_INIT ? st.y <= d : st.x != -1;  // :637 / `if (taken) continue`
@@ -393,8 +413,9 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
             else if (key < s) { s = key; tsec = t; }
           }
         }
-        uint32_t gb = b, gs = s;
-        warp_top2(gb, gs);
+        // warp-wide (best, second) with two REDUX: the second is the smallest key that is not the best
+        const uint32_t gb = __reduce_min_sync(0xffffffffu, b);
+        const uint32_t gs = __reduce_min_sync(0xffffffffu, b == gb ? s : b);
         if (gb != kNone) {
           const int bd = (int)(gb >> kCandShift);
           const int bt = __shfl_sync(0xffffffffu, tb, (int)(gb & 31u));   // list position j lives on lane j % 32
@@ -456,7 +477,10 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
       }
       __syncwarp();
     }
+    my_cnt = nx_cnt; my_off = nx_off; my_src = nx_src;
+    nx_cnt = nn_cnt; nx_off = nn_off; nx_src = nn_src;
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 
   // rotation histogram over the accept events (rotHist[bin].push_back at :665-676 and its siblings), in parallel
   int hist = 0;                             // lane b (< 30) = rotHist[b].size()

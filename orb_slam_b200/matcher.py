@@ -296,9 +296,11 @@ class ORBmatcher:
         assert i1.shape == i2.shape
         return i1, i2
 
-    def SearchForInitialization(self, set1: FrameSet, set2: FrameSet, idx1, idx2, vbPrevMatched, windowSize=10):
+    def SearchForInitialization(self, set1: FrameSet, set2: FrameSet, idx1, idx2, vbPrevMatched, windowSize=10,
+                                out=None, nm=None):
         """src/ORBmatcher.cc:598-713.  vbPrevMatched: list (per pair) of [n1,2] float arrays, or one packed float32
-        array [pairs, set1.max_n, 2]; updated in place either way.
+        array [pairs, set1.max_n, 2]; updated in place either way.  `out` [pairs, set1.max_n] int32 / `nm` [pairs]
+        int32 may be supplied (e.g. views of pinned memory) to avoid a fresh pageable allocation per call.
         Returns (nmatches[np], vnMatches12 rows [np, stride])."""
         i1, i2 = self._pairs(idx1, idx2)
         stride = max(set1.max_n, 1)
@@ -310,7 +312,12 @@ class ORBmatcher:
             xy = np.zeros((len(i1), stride, 2), np.float32)
             for p, a in enumerate(vbPrevMatched):
                 xy[p, : len(a)] = a
-        out = np.empty((len(i1), stride), np.int32); nm = np.empty(len(i1), np.int32)
+        if out is None:
+            out = np.empty((len(i1), stride), np.int32)
+        if nm is None:
+            nm = np.empty(len(i1), np.int32)
+        assert out.shape == (len(i1), stride) and out.dtype == np.int32 and out.flags.c_contiguous
+        assert nm.shape == (len(i1),) and nm.dtype == np.int32
         self.m._check(self._L.orbm_search_for_initialization(self.m._h, set1._s, set2._s, i1.ctypes.data, i2.ctypes.data,
                                                              len(i1), xy.ctypes.data, stride, int(windowSize),
                                                              self.mfNNratio, int(self.mbCheckOrientation),
