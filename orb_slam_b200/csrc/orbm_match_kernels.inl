@@ -177,10 +177,15 @@ __global__ void __launch_bounds__(128) offsets_kernel(SearchArgs a) {
   }
 }
 
-// grid family: one warp per query walks the cell window column by column (each column is ONE contiguous CSR range),
-// keeps what Frame::GetFeaturesInArea keeps, in its order, and attaches the Hamming distance
+// grid family: one warp per query.  Every column of the cell window is ONE contiguous CSR range; the ranges are
+// concatenated (prefix sums in shared memory) and walked 32 items at a time with all lanes busy - a 21 x 21 cell
+// window holds ~6 items per column, so a column-at-a-time walk would leave 80 % of the lanes idle.  Order = column by
+// column, CSR order inside a column = Frame::GetFeaturesInArea's order; survivors keep it (ballot prefix) and get
+// their Hamming distance attached.
 __global__ void __launch_bounds__(256) grid_fill_kernel(SearchArgs a, int qtotal) {
-  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  __shared__ int s_pre[8][kGridCols + 1];   // exclusive prefix of the column lengths, [ncol] = total
+  __shared__ int s_s0[8][kGridCols];        // CSR start of each column's range
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (i >= qtotal) return;
   QRec& r = a.q[i];
   if (r.cnt == 0) return;  // inactive query or empty window: the bound is already 0
@@ -194,26 +199,50 @@ __global__ void __launch_bounds__(256) grid_fill_kernel(SearchArgs a, int qtotal
   const int32_t* cs = a.s2.cell_start + (int64_t)P.tframe * (kGridCells + 1);
   const int32_t* items = a.s2.items + P.tbase;
   uint32_t* out = a.cand + P.cand_base + r.off;
-  int n = 0;
-  for (int ix = cx0; ix <= cx1; ix++) {
-    const int s0 = cs[ix * kGridRows + cy0], s1 = cs[ix * kGridRows + cy1 + 1];
-    for (int sb = s0; sb < s1; sb += 32) {
-      const int s = sb + lane;
-      bool on = false;
-      int t = 0;
-      if (s < s1) {
-        t = items[s];
-        const int gt = P.tbase + t;
-        on = area_accept(a.s2.x[gt], a.s2.y[gt], a.s2.octave[gt], x, y, rad, minl, maxl);
-      }
-      const unsigned bal = __ballot_sync(0xffffffffu, on);
-      if (on) {
-        const int gt = P.tbase + t;
-        const int dist = hamming256(d0, d1, a.s2.desc[2 * (int64_t)gt], a.s2.desc[2 * (int64_t)gt + 1]);
-        out[n + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)dist << kCandShift) | (uint32_t)t;
-      }
-      n += __popc(bal);
+  const int ncol = cx1 - cx0 + 1;           // <= kGridCols
+  int* pre = s_pre[warp];
+  int* st0 = s_s0[warp];
+  int total = 0;
+  for (int c0 = 0; c0 < ncol; c0 += 32) {
+    const int c = c0 + lane;
+    int s0 = 0, len = 0;
+    if (c < ncol) {
+      s0 = cs[(cx0 + c) * kGridRows + cy0];
+      len = cs[(cx0 + c) * kGridRows + cy1 + 1] - s0;
     }
+    int incl = len;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (c < ncol) { st0[c] = s0; pre[c] = total + incl - len; }
+    total += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) pre[ncol] = total;
+  __syncwarp();
+  int n = 0;
+  for (int k0 = 0; k0 < total; k0 += 32) {
+    const int k = k0 + lane;
+    bool on = false;
+    int t = 0;
+    if (k < total) {
+      // the column holding item k: the largest c with pre[c] <= k (empty columns repeat a prefix; the last one wins)
+      int c = 0;
+#pragma unroll
+      for (int step = 32; step >= 1; step >>= 1)
+        if (c + step < ncol && pre[c + step] <= k) c += step;
+      t = items[st0[c] + (k - pre[c])];
+      const int gt = P.tbase + t;
+      on = area_accept(a.s2.x[gt], a.s2.y[gt], a.s2.octave[gt], x, y, rad, minl, maxl);
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, on);
+    if (on) {
+      const int gt = P.tbase + t;
+      const int dist = hamming256(d0, d1, a.s2.desc[2 * (int64_t)gt], a.s2.desc[2 * (int64_t)gt + 1]);
+      out[n + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)dist << kCandShift) | (uint32_t)t;
+    }
+    n += __popc(bal);
   }
   __syncwarp();
   if (lane == 0) r.cnt = n;
