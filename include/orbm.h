@@ -93,6 +93,30 @@ int orbm_descriptor_distance(orbm_handle* h, const uint8_t* a, const uint8_t* b,
 int orbm_frameset_create(orbm_handle* h, const orbm_frame* frames, const orbm_featvec* fvs, int nframes,
                          orbm_frameset** out);
 void orbm_frameset_destroy(orbm_frameset* s);
+
+/* ---- N1: Frame glue on the device ---------------------------------------------------------------
+ * What the Frame constructor does between the extractor call and the first search (src/Frame.cc:59-127):
+ * UndistortKeyPoints (:288-318, cv::undistortPoints with K, D = (k1,k2,p1,p2,k3), P = K), ComputeImageBounds
+ * (:320-349), grid element sizes (:75-76) and the 64x48 grid binning (:108-122, :266-276).  Values are the CV_32F
+ * entries the reference stores (src/Tracking.cc:52-71). */
+typedef struct orbm_camera {
+  float fx, fy, cx, cy;
+  float k1, k2, p1, p2, k3;
+  int32_t width, height;   /* im.cols, im.rows */
+} orbm_camera;
+/* bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}, inv = {mfGridElementWidthInv, mfGridElementHeightInv}.  Host only. */
+int orbm_image_bounds(const orbm_camera* cam, int32_t bounds[4], float inv[2]);
+/* Builds a frame set straight from the extractor's DEVICE outputs (orbx_extract_batch_device): d_kps
+ * [nframes][kp_stride] 28-byte cv::KeyPoint records, d_desc [nframes][kp_stride][32], d_n [nframes] counts, all
+ * written on `stream`.  Only the counts (4 bytes per frame) cross to the host.  valid flags start at 0, no feature
+ * vectors. */
+int orbm_frameset_from_extractor(orbm_handle* h, const void* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                                 int nframes, int kp_stride, const orbm_camera* cam, void* stream,
+                                 orbm_frameset** out);
+/* Introspection: per-frame keypoint counts; the (undistorted) SoA columns of one frame (outputs may be NULL). */
+int orbm_frameset_counts(orbm_frameset* s, int32_t* n_out);
+int orbm_frameset_keypoints(orbm_frameset* s, int frame, float* x, float* y, float* angle, int32_t* octave,
+                            uint8_t* desc);
 /* Replaces the valid flags of one frame (MapPoint associations change between searches). */
 int orbm_frameset_set_valid(orbm_frameset* s, int frame, const uint8_t* valid);
 /* The device-built grid as CSR in the reference's visiting order: cell = ix * 48 + iy (src/Frame.cc:232-258),

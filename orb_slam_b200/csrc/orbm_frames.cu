@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "orbm_match.cuh"
+#include "orbm_undistort.cuh"
 
 using namespace orbm;
 
@@ -212,6 +213,144 @@ extern "C" int orbm_frameset_create(orbm_handle* h, const orbm_frame* frames, co
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
   if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return fail(e);  // host vectors die here
   *out = s;
+  return ORBM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// N1  Frame glue on the device (reference src/Frame.cc:59-127): extractor output -> frame set, no host round trip of
+// the features.  One CTA per frame: AoS cv::KeyPoint records -> SoA, UndistortKeyPoints (:288-318) in double with
+// individually rounded operations (orbm_undistort.cuh), descriptors gathered to the packed layout.
+// ------------------------------------------------------------------------------------------------------------------
+struct KeyPoint28 { float x, y, size, angle, response; int32_t octave, class_id; };  // == cv::KeyPoint == orbx_keypoint
+
+__global__ void __launch_bounds__(256) frame_glue_kernel(const KeyPoint28* kps, const uint8_t* desc, int kp_stride,
+                                                         const int32_t* frame_off, Camera cam, int undistort,
+                                                         float* ox, float* oy, float* oangle, int32_t* ooct,
+                                                         uint4* odesc, uint8_t* ovalid) {
+  const int f = blockIdx.x;
+  const int base = frame_off[f], n = frame_off[f + 1] - base;
+  const KeyPoint28* kp = kps + (int64_t)f * kp_stride;
+  const uint4* d = reinterpret_cast<const uint4*>(desc + (int64_t)f * kp_stride * 32);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const KeyPoint28 k = kp[i];
+    float x = k.x, y = k.y;
+    if (undistort) undistort_point(cam, k.x, k.y, &x, &y);
+    ox[base + i] = x; oy[base + i] = y; oangle[base + i] = k.angle; ooct[base + i] = k.octave;
+    ovalid[base + i] = 0;
+    odesc[2 * (int64_t)(base + i)] = d[2 * i];
+    odesc[2 * (int64_t)(base + i) + 1] = d[2 * i + 1];
+  }
+}
+
+static Camera camera_of(const orbm_camera& c) {
+  Camera k;
+  k.fx = c.fx; k.fy = c.fy; k.cx = c.cx; k.cy = c.cy; k.k1 = c.k1; k.k2 = c.k2; k.p1 = c.p1; k.p2 = c.p2; k.k3 = c.k3;
+  return k;
+}
+
+// Frame::ComputeImageBounds (:320-349) + grid element sizes (:75-76); four points, on the host
+extern "C" int orbm_image_bounds(const orbm_camera* cam, int32_t bounds[4], float inv[2]) {
+  if (!cam || !bounds || !inv || cam->width <= 0 || cam->height <= 0) return ORBM_ERR_ARG;
+  if (cam->k1 != 0.0f) {
+    const Camera k = camera_of(*cam);
+    const float cx[4] = {0.f, (float)cam->width, 0.f, (float)cam->width};
+    const float cy[4] = {0.f, 0.f, (float)cam->height, (float)cam->height};
+    float ux[4], uy[4];
+    for (int i = 0; i < 4; i++) undistort_point(k, cx[i], cy[i], &ux[i], &uy[i]);
+    bounds[0] = (int32_t)fminf(floorf(ux[0]), floorf(ux[2]));
+    bounds[1] = (int32_t)fmaxf(ceilf(ux[1]), ceilf(ux[3]));
+    bounds[2] = (int32_t)fminf(floorf(uy[0]), floorf(uy[1]));
+    bounds[3] = (int32_t)fmaxf(ceilf(uy[2]), ceilf(uy[3]));
+  } else {
+    bounds[0] = 0; bounds[1] = cam->width; bounds[2] = 0; bounds[3] = cam->height;
+  }
+  if (bounds[1] <= bounds[0] || bounds[3] <= bounds[2]) return ORBM_ERR_ARG;
+  inv[0] = (float)kGridCols / (float)(bounds[1] - bounds[0]);
+  inv[1] = (float)kGridRows / (float)(bounds[3] - bounds[2]);
+  return ORBM_OK;
+}
+
+extern "C" int orbm_frameset_from_extractor(orbm_handle* h, const void* d_kps, const uint8_t* d_desc,
+                                            const int32_t* d_n, int nframes, int kp_stride, const orbm_camera* cam,
+                                            void* stream, orbm_frameset** out) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!d_kps || !d_desc || !d_n || !cam || !out || nframes < 1 || kp_stride < 1 || kp_stride > 65535) {
+    h->err = "null device arrays / bad sizes";
+    return ORBM_ERR_ARG;
+  }
+  *out = nullptr;
+  int32_t bounds[4];
+  float inv[2];
+  if (orbm_image_bounds(cam, bounds, inv) != ORBM_OK) { h->err = "bad camera (image size / degenerate bounds)"; return ORBM_ERR_ARG; }
+  ORBM_CK(cudaSetDevice(h->device));
+  cudaStream_t st = h->stream;
+  // the extractor wrote its outputs on the caller's stream: order this handle's stream after it
+  cudaEvent_t ev;
+  ORBM_CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  ORBM_CK(cudaEventRecord(ev, (cudaStream_t)stream));
+  ORBM_CK(cudaStreamWaitEvent(st, ev, 0));
+  cudaEventDestroy(ev);
+  std::vector<int32_t> cnt(nframes);
+  ORBM_CK(cudaMemcpyAsync(cnt.data(), d_n, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));  // 4 bytes per frame
+  ORBM_CK(cudaStreamSynchronize(st));
+  orbm_frameset* s = new orbm_frameset();
+  s->h = h; s->nframes = nframes; s->has_fv = false;
+  s->frame_off.assign(nframes + 1, 0);
+  for (int f = 0; f < nframes; f++) {
+    if (cnt[f] < 0 || cnt[f] > kp_stride) { h->err = "keypoint count outside [0, kp_stride]"; delete s; return ORBM_ERR_ARG; }
+    s->frame_off[f + 1] = s->frame_off[f] + cnt[f];
+    s->max_n = std::max(s->max_n, cnt[f]);
+  }
+  const int64_t N = s->total_kp = s->frame_off[nframes];
+  auto fail = [&](cudaError_t e) {
+    h->err = std::string("frameset from extractor: ") + cudaGetErrorString(e);
+    orbm_frameset_destroy(s);
+    return ORBM_ERR_CUDA;
+  };
+  cudaError_t e;
+  const size_t n1 = std::max<size_t>(N, 1);
+  std::vector<float4> gp(nframes, make_float4((float)bounds[0], (float)bounds[2], inv[0], inv[1]));
+  if ((e = upload(&s->d_frame_off, s->frame_off, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(&s->d_gridp, gp, st)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_x, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_y, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_angle, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_octave, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_desc, n1 * 32 + 16)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_valid, n1 + 16)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_cell_start, (size_t)nframes * (kGridCells + 1) * 4)) != cudaSuccess) return fail(e);
+  if ((e = cudaMalloc(&s->d_items, n1 * 4)) != cudaSuccess) return fail(e);
+  frame_glue_kernel<<<nframes, 256, 0, st>>>(static_cast<const KeyPoint28*>(d_kps), d_desc, kp_stride, s->d_frame_off,
+                                             camera_of(*cam), cam->k1 != 0.0f ? 1 : 0, s->d_x, s->d_y, s->d_angle,
+                                             s->d_octave, reinterpret_cast<uint4*>(s->d_desc), s->d_valid);
+  grid_build_kernel<<<nframes, 32, 0, st>>>(view_of(s));
+  h->launches += 2;
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
+  if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return fail(e);  // host vectors die here
+  *out = s;
+  return ORBM_OK;
+}
+
+// introspection: per-frame keypoint counts and the SoA columns of one frame (any of the outputs may be NULL)
+extern "C" int orbm_frameset_counts(orbm_frameset* s, int32_t* n_out) {
+  if (!s || !n_out) return ORBM_ERR_ARG;
+  for (int f = 0; f < s->nframes; f++) n_out[f] = s->frame_off[f + 1] - s->frame_off[f];
+  return ORBM_OK;
+}
+
+extern "C" int orbm_frameset_keypoints(orbm_frameset* s, int frame, float* x, float* y, float* angle, int32_t* octave,
+                                       uint8_t* desc) {
+  if (!s) return ORBM_ERR_ARG;
+  orbm_handle* h = s->h;
+  if (frame < 0 || frame >= s->nframes) { h->err = "frame index out of range"; return ORBM_ERR_ARG; }
+  ORBM_CK(cudaSetDevice(h->device));
+  const size_t o = s->frame_off[frame], n = s->frame_off[frame + 1] - o;
+  if (!n) return ORBM_OK;
+  if (x) ORBM_CK(cudaMemcpy(x, s->d_x + o, n * 4, cudaMemcpyDeviceToHost));
+  if (y) ORBM_CK(cudaMemcpy(y, s->d_y + o, n * 4, cudaMemcpyDeviceToHost));
+  if (angle) ORBM_CK(cudaMemcpy(angle, s->d_angle + o, n * 4, cudaMemcpyDeviceToHost));
+  if (octave) ORBM_CK(cudaMemcpy(octave, s->d_octave + o, n * 4, cudaMemcpyDeviceToHost));
+  if (desc) ORBM_CK(cudaMemcpy(desc, s->d_desc + o * 32, n * 32, cudaMemcpyDeviceToHost));
   return ORBM_OK;
 }
 

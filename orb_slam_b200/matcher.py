@@ -33,6 +33,12 @@ class _FeatVec(C.Structure):
     _fields_ = [("nnodes", C.c_int32), ("node_id", C.c_void_p), ("start", C.c_void_p), ("items", C.c_void_p)]
 
 
+class Camera(C.Structure):
+    """orbm_camera: the CV_32F intrinsics / distortion the reference stores (src/Tracking.cc:52-71) + image size."""
+    _fields_ = [(n, C.c_float) for n in ("fx", "fy", "cx", "cy", "k1", "k2", "p1", "p2", "k3")] + \
+               [("width", C.c_int32), ("height", C.c_int32)]
+
+
 class _Points(C.Structure):
     _fields_ = [("n", C.c_int32), ("u", C.c_void_p), ("v", C.c_void_p), ("radius", C.c_void_p),
                 ("min_level", C.c_void_p), ("max_level", C.c_void_p), ("desc", C.c_void_p), ("angle", C.c_void_p),
@@ -53,6 +59,10 @@ def _bind(L):
     L.orbm_frameset_destroy.argtypes = [vp]; L.orbm_frameset_destroy.restype = None
     L.orbm_frameset_set_valid.argtypes = [vp, C.c_int, vp]
     L.orbm_frameset_grid.argtypes = [vp, C.c_int, vp, vp]
+    L.orbm_image_bounds.argtypes = [C.POINTER(Camera), vp, vp]
+    L.orbm_frameset_from_extractor.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(Camera), vp, C.POINTER(vp)]
+    L.orbm_frameset_counts.argtypes = [vp, vp]
+    L.orbm_frameset_keypoints.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
     L.orbm_features_in_area.argtypes = [vp, C.c_int, f32, f32, f32, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
     L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, C.c_int, vp, vp]
     L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
@@ -175,6 +185,16 @@ class Matcher:
                                                    match_ptr, stream))
 
 
+def image_bounds(camera: Camera):
+    """Frame::ComputeImageBounds + grid element sizes (src/Frame.cc:320-349, :75-76), computed by the library (host
+    side, no device needed): ((mnMinX, mnMaxX, mnMinY, mnMaxY), (mfGridElementWidthInv, mfGridElementHeightInv))."""
+    L = _bind(lib())
+    b = np.zeros(4, np.int32); inv = np.zeros(2, np.float32)
+    if L.orbm_image_bounds(C.byref(camera), b.ctypes.data, inv.ctypes.data) != 0:
+        raise ValueError("bad camera")
+    return tuple(int(v) for v in b), (float(inv[0]), float(inv[1]))
+
+
 class FrameSet:
     """Frames resident on the device with their 64x48 grids (reference src/Frame.cc:108-122)."""
 
@@ -190,6 +210,33 @@ class FrameSet:
         matcher._check(self._L.orbm_frameset_create(matcher._h, arr, fvs, len(self.frames), C.byref(self._s)))
         self.max_n = max(f.n for f in self.frames)
 
+    @classmethod
+    def from_extractor(cls, matcher: Matcher, kps_ptr, desc_ptr, n_ptr, nframes, kp_stride, camera: Camera,
+                       stream=None):
+        """N1: the Frame constructor's glue on the device (src/Frame.cc:59-127) — builds the frame set
+        from orbx_extract_batch_device's DEVICE outputs (undistort + grid), no host round trip of the features."""
+        self = cls.__new__(cls)
+        self.m, self._L, self.frames = matcher, matcher._L, None
+        self._s = C.c_void_p()
+        matcher._check(self._L.orbm_frameset_from_extractor(matcher._h, kps_ptr, desc_ptr, n_ptr, nframes, kp_stride,
+                                                            C.byref(camera), stream, C.byref(self._s)))
+        self.counts = np.zeros(nframes, np.int32)
+        matcher._check(self._L.orbm_frameset_counts(self._s, self.counts.ctypes.data))
+        self.max_n = int(self.counts.max()) if nframes else 0
+        return self
+
+    def frame_n(self, frame):
+        return self.frames[frame].n if self.frames is not None else int(self.counts[frame])
+
+    def keypoints(self, frame):
+        """(x, y, angle, octave, desc) of one resident frame (undistorted coordinates)."""
+        n = self.frame_n(frame)
+        x = np.zeros(n, np.float32); y = np.zeros(n, np.float32); a = np.zeros(n, np.float32)
+        o = np.zeros(n, np.int32); d = np.zeros((n, 32), np.uint8)
+        self.m._check(self._L.orbm_frameset_keypoints(self._s, frame, x.ctypes.data, y.ctypes.data, a.ctypes.data,
+                                                      o.ctypes.data, d.ctypes.data))
+        return x, y, a, o, d
+
     def close(self):
         if getattr(self, "_s", None) and getattr(self.m, "_h", None):
             self._L.orbm_frameset_destroy(self._s)
@@ -203,12 +250,12 @@ class FrameSet:
 
     def grid(self, frame):
         cs = np.zeros(FRAME_GRID_COLS * FRAME_GRID_ROWS + 1, np.int32)
-        items = np.zeros(max(self.frames[frame].n, 1), np.int32)
+        items = np.zeros(max(self.frame_n(frame), 1), np.int32)
         self.m._check(self._L.orbm_frameset_grid(self._s, frame, cs.ctypes.data, items.ctypes.data))
         return cs, items[: cs[-1]]
 
     def features_in_area(self, frame, x, y, r, min_level=-1, max_level=-1):
-        cap = max(self.frames[frame].n, 1)
+        cap = max(self.frame_n(frame), 1)
         out = np.zeros(cap, np.int32)
         n = C.c_int(0)
         self.m._check(self._L.orbm_features_in_area(self._s, frame, x, y, r, min_level, max_level, out.ctypes.data, cap,
