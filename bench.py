@@ -284,6 +284,8 @@ def main():
         if rank == 0 and not args.no_cpu:
             knn["cpu_baseline"] = BM.bench_knn2_cpu(args)
         matching = {"knn2_all_pairs": knn, "search_for_initialization": init}
+        if rank == 0:
+            matching["frame_glue"] = BM.bench_frame_glue(args, dev, local, mt)
     other = None
     if args.all_configs and world == 1:
         import bench_configs

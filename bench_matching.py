@@ -201,3 +201,59 @@ def bench_knn2_cpu(args):
     return {"value": len(q) * len(db) / dt, "unit": "pairs/s", "cores": threads, "kind": "port",
             "single_thread_value": 4 * len(db) / dt1,
             "sample": f"{len(q)} queries x 200,000 database descriptors, oracle SWAR popcount (-O3 -march=native)"}
+
+
+def bench_frame_glue(args, dev, local, matcher):
+    """N1: extractor DEVICE output -> searchable frame set (undistort + 64x48 grid), the Frame constructor's
+    glue (reference src/Frame.cc:59-127) with the shipped camera model scaled to 640x480.  CPU column: oracle
+    undistortion + grid binning of the same keypoints, one host thread (what the reference's Tracking thread does)."""
+    import torch
+    from orb_slam_b200 import Camera, FrameSet, KP_DTYPE, ORBextractor, synth_frames_device
+    W, H, NF, F = 640, 480, 1000, 256
+    cam = (268.9633 * 2, 269.9858 * 2, 157.6087 * 2, 114.6369 * 2, -0.4157, 0.2624, 0.0, 0.0, -0.1178, W, H)
+    d_frames = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
+    synth_frames_device(d_frames.data_ptr(), F, W, H, W, H * W, seed0=90_000)
+    ex = ORBextractor(NF, 1.2, 8, 1, 20, max_width=W, max_height=H, max_batch=F, device=local)
+    d_k = torch.zeros((F, NF, 28), dtype=torch.uint8, device=dev)
+    d_d = torch.zeros((F, NF, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(F, dtype=torch.int32, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    ex.extract_batch_device(d_frames.data_ptr(), F, W, H, W, H * W, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(),
+                            stream.cuda_stream)
+    torch.cuda.synchronize()
+    camera = Camera(*cam)
+
+    def step():
+        fs = FrameSet.from_extractor(matcher, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), F, NF, camera,
+                                     stream.cuda_stream)
+        fs.close()
+    for _ in range(3):
+        step()
+    t = time.perf_counter()
+    for _ in range(max(args.steps, 5)):
+        step()
+    ms = (time.perf_counter() - t) * 1e3 / max(args.steps, 5)
+    out = {"metric": "Frame glue frames/s (1000 kp: undistort + 64x48 grid, extractor device output -> frame set)",
+           "value": F / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms, "frames_per_step": F,
+           "note": "wall clock of orbm_frameset_from_extractor incl. its allocations, the 4 B/frame count read-back and "
+                   "the final sync; features never leave the device"}
+    if not args.no_cpu:
+        from oracle import frame_oracle as FO
+        from oracle import match_oracle as MO
+        from orb_slam_b200 import MatchFrame
+        kps = d_k.cpu().numpy().view(KP_DTYPE).reshape(F, NF)
+        desc = d_d.cpu().numpy(); n = d_n.cpu().numpy()
+        ocam = FO.Camera(*cam[:9])
+        (mnx, mxx, mny, mxy), _ = FO.image_bounds(ocam, W, H)
+        nc = 32
+        t = time.perf_counter()
+        for f in range(nc):
+            k = kps[f, :n[f]]
+            un = FO.undistort_points(ocam, np.stack([k["x"], k["y"]], 1))
+            MO.grid_csr(MatchFrame(un[:, 0], un[:, 1], k["angle"], k["octave"], desc[f, :n[f]], min_x=float(mnx),
+                                   min_y=float(mny), max_x=float(mxx), max_y=float(mxy)))
+        dt = time.perf_counter() - t
+        out["cpu_baseline"] = {"value": nc / dt, "unit": "frames/s", "cores": 1, "kind": "port",
+                               "sample": f"{nc} of the same frames, oracle undistort + grid through ctypes"}
+    ex.close()
+    return out
