@@ -46,7 +46,7 @@ def build(fast: bool = False, force: bool = False) -> str:
         sig = hashlib.sha1(flags.encode()).hexdigest()
         if os.path.exists(path) and (not os.path.exists(stamp) or open(stamp).read() != sig):
             force = True
-    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith(".cc")]
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith(".cc") and not f.startswith("ref_")]
     srcs.append(os.path.join(_HERE, "..", "orb_slam_b200", "csrc", "orb_pattern_31.inc"))
     stale = (not os.path.exists(path)) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs)
     if force or stale:
@@ -56,6 +56,15 @@ def build(fast: bool = False, force: bool = False) -> str:
         if fast:
             open(stamp, "w").write(sig)
     return path
+
+
+def build_ref(reference: str = "/root/reference") -> str | None:
+    """oracle/_ref/libref_dbow2.so: the reference's own DBoW2 compiled where it lies (Makefile target `ref`).  Only
+    possible where the reference tree exists (the authoring container); elsewhere the prebuilt file is used as is."""
+    out = os.path.join(_HERE, "_ref", "libref_dbow2.so")
+    if os.path.isdir(os.path.join(reference, "Thirdparty", "DBoW2")):
+        subprocess.run(["make", "-C", _HERE, "ref", f"REFERENCE={reference}"], check=True, capture_output=True)
+    return out if os.path.exists(out) else None
 
 
 _libs = {}
