@@ -286,6 +286,7 @@ def main():
         matching = {"knn2_all_pairs": knn, "search_for_initialization": init}
         if rank == 0:
             matching["frame_glue"] = BM.bench_frame_glue(args, dev, local, mt)
+            matching["bow"] = BM.bench_bow(args, dev, local, mt)
     other = None
     if args.all_configs and world == 1:
         import bench_configs

@@ -257,3 +257,70 @@ def bench_frame_glue(args, dev, local, matcher):
                                "sample": f"{nc} of the same frames, oracle undistort + grid through ctypes"}
     ex.close()
     return out
+
+
+def bench_bow(args, dev, local, matcher):
+    """N2 (SURVEY 8f): Frame::ComputeBoW (src/Frame.cc:279-286) for a set of resident frames with an ORBvoc-sized tree
+    (k = 10, L = 6: 1,111,111 nodes, 10^6 words; synthetic, the vocabulary file is not in the reference tree).
+    CPU column: the reference's own DBoW2 transform (oracle/_ref, compiled from the reference sources) when that
+    library travelled with the snapshot, else the pinned oracle port; one host thread, as in the reference."""
+    import torch
+    from oracle import bow_oracle as B
+    from orb_slam_b200 import MatchFrame, ORBVocabulary
+    F, NF = 512, 1000
+    V = B.synth_vocabulary_fast(k=10, L=6, seed=1)
+    keys = ("k", "L", "scoring", "weighting", "parent", "desc", "weight", "is_leaf")
+    G = ORBVocabulary.from_arrays(matcher, **{k: V[k] for k in keys})
+    rng = np.random.default_rng(5)
+    leaves = V["desc"][V["is_leaf"] == 1]
+    frames = []
+    for f in range(F):
+        d = leaves[rng.integers(0, len(leaves), NF)].copy()
+        noise = rng.integers(0, 256, (NF, 3))
+        for c in range(3):
+            d[np.arange(NF), noise[:, c] >> 3] ^= (1 << (noise[:, c] & 7)).astype(np.uint8)
+        z = np.zeros(NF, np.float32)
+        frames.append(MatchFrame(z, z, z, np.zeros(NF, np.int32), d))
+    fs = matcher.upload(frames)
+    for _ in range(3):
+        fs.compute_bow(G, 4)
+    kms = []
+    t = time.perf_counter()
+    steps = max(args.steps, 5)
+    for _ in range(steps):
+        fs.compute_bow(G, 4)
+        kms.append(matcher.last_kernel_ms())
+    ms = (time.perf_counter() - t) * 1e3 / steps
+    kms = float(np.mean(kms))
+    out = {"metric": "ComputeBoW frames/s (1000 descriptors/frame, k=10 L=6 vocabulary, levelsup 4)",
+           "value": F / (kms * 1e-3), "unit": "frames/s", "kernel_ms_per_step": kms, "frames_per_step": F,
+           "e2e": {"value": F / (ms * 1e-3), "unit": "frames/s",
+                   "note": "wall clock of orbm_frameset_compute_bow incl. its allocations and the offsets read-back"},
+           "descriptor_distances_per_s": F * NF * 60 / (kms * 1e-3)}
+    if not args.no_cpu:
+        nc = 16
+        if B.have_ref():
+            import tempfile
+            V2 = B.synth_vocabulary_fast(k=10, L=4, seed=1)     # text round trip of a 10^6-word file takes minutes
+            with tempfile.TemporaryDirectory() as td:
+                p = td + "/voc.txt"
+                B.save_text(p, **V2)
+                R = B.RefVocabulary.load_text(p)
+            t = time.perf_counter()
+            for f in range(nc):
+                R.transform(frames[f].desc, 2)
+            dt = time.perf_counter() - t
+            out["cpu_baseline"] = {"value": nc / dt, "unit": "frames/s", "cores": 1, "kind": "reference",
+                                   "sample": f"{nc} frames through the reference's DBoW2 transform (oracle/_ref) with a "
+                                             "k=10 L=4 tree (40 distances/descriptor instead of 60: an upper bound "
+                                             "on its L=6 rate)"}
+        else:
+            O = B.Vocabulary.from_arrays(**{k: V[k] for k in keys}, fast=True)
+            t = time.perf_counter()
+            for f in range(nc):
+                O.transform(frames[f].desc, 4)
+            dt = time.perf_counter() - t
+            out["cpu_baseline"] = {"value": nc / dt, "unit": "frames/s", "cores": 1, "kind": "port",
+                                   "sample": f"{nc} of the same frames, oracle transform, same tree"}
+    fs.close(); G.close()
+    return out

@@ -127,6 +127,47 @@ int orbm_frameset_grid(orbm_frameset* s, int frame, int32_t* cell_start, int32_t
 int orbm_features_in_area(orbm_frameset* s, int frame, float x, float y, float r, int min_level, int max_level,
                           int32_t* out, int cap, int* n_out);
 
+/* ---- N2: BoW transform on the device ------------------------------------------------------------
+ * Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:279-286, src/KeyFrame.cc) call
+ * ORBVocabulary::transform(descriptors, BowVector, FeatureVector, levelsup = 4)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1126-1194): every descriptor descends the k-ary vocabulary tree
+ * (:1217-1259; FORB::distance = the 256-bit Hamming distance of M1, first strict minimum in child order), the words'
+ * weights accumulate into the BowVector (BowVector.cpp:34-85, normalised as the scoring type asks) and the feature
+ * index is filed under its ancestor `levelsup` levels above the leaves (FeatureVector.cpp:31-47).  Doubles are added
+ * in the reference's order with individually rounded operations, so weights are BIT-exact.
+ *
+ * The vocabulary is handed over as flat arrays in the node numbering of loadFromTextFile (:1337-1424): node 0 is the
+ * root, parent[i] < i, children of a node in ascending id = the reference's child order, word ids count the leaves in
+ * id order.  scoring / weighting are the DBoW2 enums (BowVector.h:36-53).  Two defined behaviours where the
+ * reference's is undefined: a blank line ends a text file (the reference turns the trailing newline into a node with
+ * an uninitialised parent); a leaf above level L - levelsup is filed under itself (the reference leaves the NodeId
+ * unset). */
+typedef struct orbm_vocabulary orbm_vocabulary;
+int orbm_vocabulary_create(orbm_handle* h, int k, int L, int scoring, int weighting, int nnodes,
+                           const int32_t* parent, const uint8_t* desc /* nnodes x 32 */, const double* weight,
+                           const uint8_t* is_leaf, orbm_vocabulary** out);
+/* ORBVocabulary::loadFromTextFile (the ORBvoc.txt format). */
+int orbm_vocabulary_load_text(orbm_handle* h, const char* path, orbm_vocabulary** out);
+void orbm_vocabulary_destroy(orbm_vocabulary* v);
+/* info = {k, L, scoring, weighting, number of words, number of nodes} */
+int orbm_vocabulary_info(const orbm_vocabulary* v, int32_t info[6]);
+/* transform() of ONE descriptor set given as a HOST buffer (n x 32).  Outputs in std::map order (ascending id):
+ * bow_word / bow_weight [<= n], fv_node [<= n], fv_start [<= n + 1], fv_items [<= n]. */
+int orbm_vocabulary_transform(orbm_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* bow_word,
+                              double* bow_weight, int32_t* n_bow, int32_t* fv_node, int32_t* fv_start,
+                              int32_t* fv_items, int32_t* n_nodes);
+/* ComputeBoW for every frame of a device-resident set (descriptors never leave the GPU): replaces the set's feature
+ * vectors (so orbm_search_by_bow can run on it) and stores the BowVectors. */
+int orbm_frameset_compute_bow(orbm_frameset* s, const orbm_vocabulary* v, int levelsup);
+/* Per-frame sizes after compute_bow / create-with-feature-vectors: words in the BowVector (0 when none was computed),
+ * nodes and items of the FeatureVector.  Any output may be NULL. */
+int orbm_frameset_bow_sizes(orbm_frameset* s, int32_t* n_words, int32_t* n_nodes, int32_t* n_items);
+int orbm_frameset_bowvec(orbm_frameset* s, int frame, int32_t* word, double* weight);
+int orbm_frameset_featvec(orbm_frameset* s, int frame, int32_t* node_id, int32_t* start, int32_t* items);
+/* L1Scoring::score (ScoringObject.cpp:23-67) between BowVectors of frame pairs, summed in word order: bit-exact. */
+int orbm_bow_score_l1(orbm_frameset* set1, orbm_frameset* set2, const int32_t* idx1, const int32_t* idx2, int npairs,
+                      double* score);
+
 /* ---- pair searches: pair p = (frame idx1[p] of set1, frame idx2[p] of set2) ----------------------------------
  * Per-pair outputs are rows of `stride` int32 (stride >= the largest frame of the written side); unused tail
  * entries are set to -1.  nmatches[p] = the routine's return value. */

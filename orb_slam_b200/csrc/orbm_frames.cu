@@ -360,7 +360,7 @@ extern "C" void orbm_frameset_destroy(orbm_frameset* s) {
   cudaStreamSynchronize(s->h->stream);
   void* ptrs[] = {s->d_frame_off, s->d_x, s->d_y, s->d_angle, s->d_octave, s->d_desc, s->d_valid, s->d_gridp,
                   s->d_cell_start, s->d_items, s->d_node_off, s->d_fvitem_off, s->d_node_id, s->d_node_start,
-                  s->d_fv_items};
+                  s->d_fv_items, s->d_bow_word, s->d_bow_val};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete s;
 }

@@ -54,6 +54,7 @@ struct orbm_handle {
   orbm::DevBuf knn_part;     // per-chunk partial top-2 keys
   orbm::DevBuf stage_a, stage_b, stage_c;  // staging for host-pointer entry points
   orbm::DevBuf ws_problem, ws_query, ws_target, ws_cand, ws_misc, ws_io;
+  orbm::DevBuf ws_bow;       // per-keypoint descent results + uncompacted per-frame vectors (orbm_bow.cu)
   void* pinned = nullptr;    // pinned host staging for small result read-backs
   size_t pinned_cap = 0;
 };
@@ -77,6 +78,11 @@ struct orbm_frameset {
   int32_t *d_node_off = nullptr, *d_fvitem_off = nullptr, *d_node_id = nullptr, *d_node_start = nullptr,
           *d_fv_items = nullptr;    // node_start has nnodes + 1 entries per frame, stored at node_off[f] + f
   bool has_fv = false;
+  // BowVectors (orbm_frameset_compute_bow): words of frame f at frame_off[f] .. + bow_cnt[f], ascending word id
+  int32_t* d_bow_word = nullptr;
+  double* d_bow_val = nullptr;
+  std::vector<int32_t> bow_cnt;     // host copy [nframes] (empty until computed)
+  bool bow_sized = false;           // the feature / bow vector arrays have their upper-bound sizes (reusable)
 };
 
 #define ORBM_CK(call)                                                          \

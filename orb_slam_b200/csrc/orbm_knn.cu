@@ -45,7 +45,7 @@ extern "C" void orbm_destroy(orbm_handle* h) {
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->knn_part, &h->stage_a, &h->stage_b, &h->stage_c, &h->ws_problem, &h->ws_query,
-                    &h->ws_target, &h->ws_cand, &h->ws_misc, &h->ws_io};
+                    &h->ws_target, &h->ws_cand, &h->ws_misc, &h->ws_io, &h->ws_bow};
   for (DevBuf* b : bufs) b->release();
   if (h->pinned) cudaFreeHost(h->pinned);
   if (h->ev0) cudaEventDestroy(h->ev0);

@@ -6,6 +6,7 @@ numpy only owns memory: every distance and every match decision comes from the C
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -64,6 +65,16 @@ def _bind(L):
     L.orbm_frameset_counts.argtypes = [vp, vp]
     L.orbm_frameset_keypoints.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
     L.orbm_features_in_area.argtypes = [vp, C.c_int, f32, f32, f32, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
+    L.orbm_vocabulary_create.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.POINTER(vp)]
+    L.orbm_vocabulary_load_text.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    L.orbm_vocabulary_destroy.argtypes = [vp]; L.orbm_vocabulary_destroy.restype = None
+    L.orbm_vocabulary_info.argtypes = [vp, vp]
+    L.orbm_vocabulary_transform.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp]
+    L.orbm_frameset_compute_bow.argtypes = [vp, vp, C.c_int]
+    L.orbm_frameset_bow_sizes.argtypes = [vp, vp, vp, vp]
+    L.orbm_frameset_bowvec.argtypes = [vp, C.c_int, vp, vp]
+    L.orbm_frameset_featvec.argtypes = [vp, C.c_int, vp, vp, vp]
+    L.orbm_bow_score_l1.argtypes = [vp, vp, vp, vp, C.c_int, vp]
     L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, C.c_int, vp, vp]
     L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_search_by_projection_frames.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, vp, vp]
@@ -185,6 +196,77 @@ class Matcher:
                                                    match_ptr, stream))
 
 
+class ORBVocabulary:
+    """ORB_SLAM::ORBVocabulary = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (reference
+    include/ORBVocabulary.h:31-32) resident on the device.  Node and word ids are the reference's
+    (loadFromTextFile numbering, Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1337-1424)."""
+
+    def __init__(self, matcher: Matcher, handle):
+        self.m, self._L, self._v = matcher, matcher._L, handle
+        info = np.zeros(6, np.int32)
+        matcher._check(self._L.orbm_vocabulary_info(self._v, info.ctypes.data))
+        self.k, self.L, self.scoring, self.weighting, self.nwords, self.nnodes = (int(x) for x in info)
+
+    @classmethod
+    def loadFromTextFile(cls, matcher: Matcher, filename):
+        v = C.c_void_p()
+        matcher._check(matcher._L.orbm_vocabulary_load_text(matcher._h, os.fsencode(filename), C.byref(v)))
+        return cls(matcher, v)
+
+    @classmethod
+    def from_arrays(cls, matcher: Matcher, k, L, scoring, weighting, parent, desc, weight, is_leaf):
+        parent = _i32(parent); desc = np.ascontiguousarray(desc, np.uint8)
+        weight = np.ascontiguousarray(weight, np.float64); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        if not (len(parent) == len(weight) == len(is_leaf) and desc.size == 32 * len(parent)):
+            raise ValueError("vocabulary arrays disagree in length")
+        v = C.c_void_p()
+        matcher._check(matcher._L.orbm_vocabulary_create(matcher._h, k, L, scoring, weighting, len(parent),
+                                                         parent.ctypes.data, desc.ctypes.data, weight.ctypes.data,
+                                                         is_leaf.ctypes.data, C.byref(v)))
+        return cls(matcher, v)
+
+    def size(self):
+        return self.nwords
+
+    def getBranchingFactor(self):
+        return self.k
+
+    def getDepthLevels(self):
+        return self.L
+
+    def transform(self, features, levelsup=4):
+        """transform(features, BowVector, FeatureVector, levelsup) (TemplatedVocabulary.h:1126-1194) of one
+        descriptor set [n, 32] -> ((word_id, weight), (node_id, start, items)), ids ascending as in the std::maps."""
+        d = np.ascontiguousarray(features, np.uint8).reshape(-1, 32)
+        n = len(d)
+        bw = np.zeros(max(n, 1), np.int32); bv = np.zeros(max(n, 1), np.float64)
+        fn = np.zeros(max(n, 1), np.int32); fs = np.zeros(n + 1, np.int32); fi = np.zeros(max(n, 1), np.int32)
+        nb = np.zeros(1, np.int32); nn = np.zeros(1, np.int32)
+        self.m._check(self._L.orbm_vocabulary_transform(self._v, d.ctypes.data, n, levelsup, bw.ctypes.data,
+                                                        bv.ctypes.data, nb.ctypes.data, fn.ctypes.data,
+                                                        fs.ctypes.data, fi.ctypes.data, nn.ctypes.data))
+        nb, nn = int(nb[0]), int(nn[0])
+        return (bw[:nb].copy(), bv[:nb].copy()), (fn[:nn].copy(), fs[:nn + 1].copy(), fi[:fs[nn]].copy())
+
+    def score(self, set1, set2, idx1, idx2):
+        """TemplatedVocabulary::score for L1_NORM vocabularies (ScoringObject.cpp:23-67) between the BowVectors of
+        frame pairs of two sets on which compute_bow has run."""
+        if self.scoring != 0:
+            raise ValueError("only L1_NORM scoring (the ORB_SLAM vocabulary's) is implemented")
+        i1, i2 = _i32(idx1), _i32(idx2)
+        out = np.zeros(len(i1), np.float64)
+        self.m._check(self._L.orbm_bow_score_l1(set1._s, set2._s, i1.ctypes.data, i2.ctypes.data, len(i1),
+                                                out.ctypes.data))
+        return out
+
+    def close(self):
+        if getattr(self, "_v", None) and getattr(self.m, "_h", None):
+            self._L.orbm_vocabulary_destroy(self._v)
+        self._v = None
+
+    __del__ = close
+
+
 def image_bounds(camera: Camera):
     """Frame::ComputeImageBounds + grid element sizes (src/Frame.cc:320-349, :75-76), computed by the library (host
     side, no device needed): ((mnMinX, mnMaxX, mnMinY, mnMaxY), (mfGridElementWidthInv, mfGridElementHeightInv))."""
@@ -236,6 +318,33 @@ class FrameSet:
         self.m._check(self._L.orbm_frameset_keypoints(self._s, frame, x.ctypes.data, y.ctypes.data, a.ctypes.data,
                                                       o.ctypes.data, d.ctypes.data))
         return x, y, a, o, d
+
+    def compute_bow(self, vocabulary: "ORBVocabulary", levelsup=4):
+        """N2 (SURVEY 8f): Frame::ComputeBoW (src/Frame.cc:279-286) for every resident frame, on the device; the set
+        can then take part in SearchByBoW."""
+        self.m._check(self._L.orbm_frameset_compute_bow(self._s, vocabulary._v, levelsup))
+        self._has_fv = True
+
+    def _sizes(self):
+        nf = len(self.frames) if self.frames is not None else len(self.counts)
+        w = np.zeros(nf, np.int32); n = np.zeros(nf, np.int32); i = np.zeros(nf, np.int32)
+        self.m._check(self._L.orbm_frameset_bow_sizes(self._s, w.ctypes.data, n.ctypes.data, i.ctypes.data))
+        return w, n, i
+
+    def bow_vector(self, frame):
+        """mBowVec of one frame: (word_id[], weight[]) in ascending word id."""
+        nw = int(self._sizes()[0][frame])
+        w = np.zeros(max(nw, 1), np.int32); v = np.zeros(max(nw, 1), np.float64)
+        self.m._check(self._L.orbm_frameset_bowvec(self._s, frame, w.ctypes.data, v.ctypes.data))
+        return w[:nw], v[:nw]
+
+    def feature_vector(self, frame):
+        """mFeatVec of one frame: (node_id[], start[], items[])."""
+        _, nn, ni = self._sizes()
+        nn, ni = int(nn[frame]), int(ni[frame])
+        a = np.zeros(max(nn, 1), np.int32); s = np.zeros(nn + 1, np.int32); it = np.zeros(max(ni, 1), np.int32)
+        self.m._check(self._L.orbm_frameset_featvec(self._s, frame, a.ctypes.data, s.ctypes.data, it.ctypes.data))
+        return a[:nn], s, it[:ni]
 
     def close(self):
         if getattr(self, "_s", None) and getattr(self.m, "_h", None):
