@@ -324,3 +324,39 @@ def bench_bow(args, dev, local, matcher):
                                    "sample": f"{nc} of the same frames, oracle transform, same tree"}
     fs.close(); G.close()
     return out
+
+
+def bench_distinctive(args, dev, local, matcher):
+    """N4 (SURVEY 8f): MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a batch of map points with
+    2..30 observations each (what LocalMapping re-runs for every point a new keyframe touches)."""
+    from oracle import match_oracle as MO
+    rng = np.random.default_rng(17)
+    P = 200_000
+    sizes = rng.integers(2, 31, P)
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    desc = rng.integers(0, 256, (int(start[-1]), 32), dtype=np.uint8)
+    for _ in range(2):
+        matcher.distinctive_descriptors(desc, start)
+    kms = []
+    t = time.perf_counter()
+    steps = max(args.steps, 5)
+    for _ in range(steps):
+        best, _ = matcher.distinctive_descriptors(desc, start)
+        kms.append(matcher.last_kernel_ms())
+    ms = (time.perf_counter() - t) * 1e3 / steps
+    kms = float(np.mean(kms))
+    pairs = float((sizes.astype(np.int64) ** 2).sum())
+    out = {"metric": "ComputeDistinctiveDescriptors map points/s (2..30 observations per point)",
+           "value": P / (kms * 1e-3), "unit": "points/s", "kernel_ms_per_step": kms, "points_per_step": P,
+           "descriptor_distances_per_s": pairs / (kms * 1e-3),
+           "e2e": {"value": P / (ms * 1e-3), "unit": "points/s",
+                   "h2d_bytes_per_step": int(desc.nbytes + start.nbytes), "d2h_bytes_per_step": P * 36}}
+    if not args.no_cpu:
+        nc = 20_000
+        t = time.perf_counter()
+        ref = MO.distinctive_descriptors(desc[: start[nc]], start[: nc + 1])
+        dt = time.perf_counter() - t
+        out["cpu_baseline"] = {"value": nc / dt, "unit": "points/s", "cores": 1, "kind": "port",
+                               "sample": f"first {nc} of the same points, oracle (-O2), one thread"}
+        out["gpu_equals_cpu"] = bool(np.array_equal(best[:nc], ref))
+    return out

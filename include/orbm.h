@@ -168,6 +168,15 @@ int orbm_frameset_featvec(orbm_frameset* s, int frame, int32_t* node_id, int32_t
 int orbm_bow_score_l1(orbm_frameset* set1, orbm_frameset* set2, const int32_t* idx1, const int32_t* idx2, int npairs,
                       double* score);
 
+/* ---- N4: MapPoint::ComputeDistinctiveDescriptors batched (src/MapPoint.cc:185-250) ---------------------------
+ * Point p observes the descriptors desc[start[p] .. start[p+1]) (HOST buffers; the caller has already dropped bad
+ * keyframes, :205-209).  best[p] = index inside the point's list of the descriptor with the least median Hamming
+ * distance to the others (median = sorted row [(int)(0.5*(N-1))] with the self-distance 0 included, first strictly
+ * smaller median wins, :231-243); -1 for a point without observations.  out_desc (npoints x 32, may be NULL) receives
+ * that descriptor = the new mDescriptor (zeros where best = -1). */
+int orbm_distinctive_descriptors(orbm_handle* h, const uint8_t* desc, const int32_t* start, int npoints,
+                                 int32_t* best, uint8_t* out_desc);
+
 /* ---- pair searches: pair p = (frame idx1[p] of set1, frame idx2[p] of set2) ----------------------------------
  * Per-pair outputs are rows of `stride` int32 (stride >= the largest frame of the written side); unused tail
  * entries are set to -1.  nmatches[p] = the routine's return value. */

@@ -152,6 +152,37 @@ extern "C" {
 
 int mo_descriptor_distance(const uint8_t* a, const uint8_t* b) { return descriptor_distance(a, b); }
 
+// N4: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a batch of map points.
+// Point p observes descriptors desc[start[p] .. start[p+1]); best[p] = index (within the point's list) of the
+// descriptor with the least median distance to the rest: row i sorted ascending (the 0 self-distance included),
+// median = row[(int)(0.5 * (N - 1))], first strictly smaller median wins.  best[p] = -1 for a point without
+// observations (the reference returns before touching mDescriptor).
+void mo_distinctive_descriptors(const uint8_t* desc, const int32_t* start, int npoints, int32_t* best) {
+  for (int p = 0; p < npoints; p++) {
+    const int n = start[p + 1] - start[p];
+    const uint8_t* d = desc + (size_t)start[p] * 32;
+    best[p] = -1;
+    if (n <= 0) continue;
+    std::vector<float> dist((size_t)n * n);   // `float Distances[N][N]` in the reference; values are exact integers
+    for (int i = 0; i < n; i++) {
+      dist[(size_t)i * n + i] = 0;
+      for (int j = i + 1; j < n; j++) {
+        const int dij = descriptor_distance(d + (size_t)i * 32, d + (size_t)j * 32);
+        dist[(size_t)i * n + j] = (float)dij;
+        dist[(size_t)j * n + i] = (float)dij;
+      }
+    }
+    int best_median = INT_MAX, best_idx = 0;
+    for (int i = 0; i < n; i++) {
+      std::vector<int> v(dist.begin() + (size_t)i * n, dist.begin() + (size_t)(i + 1) * n);
+      std::sort(v.begin(), v.end());
+      const int median = v[(size_t)(0.5 * (n - 1))];
+      if (median < best_median) { best_median = median; best_idx = i; }
+    }
+    best[p] = best_idx;
+  }
+}
+
 // Grid introspection for tests: CSR in the reference's visiting order (ix outer, iy inner, insertion order).
 void mo_grid_csr(const mo_frame* f, int32_t* cell_start /*3073*/, int32_t* items /*n*/) {
   Grid g;

@@ -84,6 +84,16 @@ def descriptor_distance(a, b) -> int:
     return int(lib().mo_descriptor_distance(a.ctypes.data, b.ctypes.data))
 
 
+def distinctive_descriptors(desc, start):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a batch: best index per point."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); start = np.ascontiguousarray(start, np.int32)
+    best = np.zeros(len(start) - 1, np.int32)
+    L = lib()
+    L.mo_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.mo_distinctive_descriptors(desc.ctypes.data, start.ctypes.data, len(best), best.ctypes.data)
+    return best
+
+
 def grid_csr(f):
     h = frame_struct(f)
     cs = np.zeros(GRID_COLS * GRID_ROWS + 1, np.int32); items = np.zeros(max(h.s.n, 1), np.int32)

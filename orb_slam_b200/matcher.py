@@ -75,6 +75,7 @@ def _bind(L):
     L.orbm_frameset_bowvec.argtypes = [vp, C.c_int, vp, vp]
     L.orbm_frameset_featvec.argtypes = [vp, C.c_int, vp, vp, vp]
     L.orbm_bow_score_l1.argtypes = [vp, vp, vp, vp, C.c_int, vp]
+    L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, C.c_int, vp, vp]
     L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, C.c_int, vp, vp]
     L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_search_by_projection_frames.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, vp, vp]
@@ -182,6 +183,18 @@ class Matcher:
         return out
 
     # M8
+    def distinctive_descriptors(self, desc, start):
+        """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a batch of map points: point p
+        observes desc[start[p]:start[p+1]].  -> (best index per point, chosen descriptor per point [npoints, 32])."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); st = np.ascontiguousarray(start, np.int32)
+        npts = len(st) - 1
+        if npts < 0 or (npts and int(st[-1]) != len(d)):
+            raise ValueError("start must have npoints + 1 entries ending at len(desc)")
+        best = np.zeros(max(npts, 0), np.int32); out = np.zeros((max(npts, 0), 32), np.uint8)
+        self._check(self._L.orbm_distinctive_descriptors(self._h, d.ctypes.data if len(d) else None, st.ctypes.data,
+                                                         npts, best.ctypes.data, out.ctypes.data))
+        return best, out
+
     def knn2(self, q, db, idx_base=0):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32); db = np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
         out = np.empty((len(q), 2), np.uint32)

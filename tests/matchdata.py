@@ -33,7 +33,7 @@ _cache = {}
 
 def make_pair(oracle, seed, w=640, h=480, nfeat=1000, shift=None, with_fv=True):
     """Two views of one synthetic scene: view 2 is translated by `shift` px with fresh +-2 noise."""
-    key = (seed, w, h, nfeat, shift)
+    key = (seed, w, h, nfeat, shift, with_fv)
     if key in _cache:
         return _cache[key]
     rng = np.random.default_rng(1000 + seed)

@@ -218,3 +218,25 @@ def test_knn2_sharded_merge_single_gpu(M, matcher):
     ok = (bd <= 50) & (bd.astype(np.float32) < np.float32(0.75) * sd.astype(np.float32))
     exp = np.where(ok, (ref[:, 0] & 0x7FFFFF).astype(np.int64), -1)
     assert np.array_equal(match.cpu().numpy(), exp) and ok.sum() > 500
+
+
+def test_distinctive_descriptors(M, matcher):
+    """N4: batched MapPoint::ComputeDistinctiveDescriptors equals the oracle (index and chosen descriptor)."""
+    rng = np.random.default_rng(21)
+    sizes = np.concatenate([[1, 2, 3, 0, 32, 33, 64, 65, 300, 0], rng.integers(1, 40, 3000)])
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = rng.integers(0, 256, (len(sizes), 32), dtype=np.uint8)
+    desc = np.repeat(base, sizes, axis=0)
+    flips = rng.random((len(desc), 256)) < rng.uniform(0.0, 0.2, (len(desc), 1))
+    desc = np.packbits(np.unpackbits(desc, axis=1) ^ flips, axis=1)
+    best, out = matcher.distinctive_descriptors(desc, start)
+    ref = M.distinctive_descriptors(desc, start)
+    assert np.array_equal(best, ref)
+    has = ref >= 0
+    assert np.array_equal(out[has], desc[start[:-1][has] + ref[has]]) and not out[~has].any()
+    # ties everywhere: identical observations -> index 0
+    same = np.repeat(base[:5], 9, axis=0)
+    b2, _ = matcher.distinctive_descriptors(same, np.arange(0, 46, 9))
+    assert list(b2) == [0] * 5
+    b3, o3 = matcher.distinctive_descriptors(np.zeros((0, 32), np.uint8), [0, 0, 0])
+    assert list(b3) == [-1, -1]

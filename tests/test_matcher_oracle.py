@@ -148,3 +148,48 @@ def test_knn2_oracle(M):
     assert got[0, 0] == 5 and got[0, 1] == 17
     assert np.array_equal(M.knn2(q, db, threads=3), got)
     assert np.array_equal(M.knn2(q, db[:1])[:, 1], np.full(40, 0xFFFFFFFF, np.uint32))
+
+
+# ---- N4: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) ------------------------------------------
+def _np_distinctive(desc, start):
+    """Independent numpy restatement: full distance matrix, np.sort per row, first minimum of the medians."""
+    out = []
+    for p in range(len(start) - 1):
+        d = desc[start[p]:start[p + 1]]
+        n = len(d)
+        if n == 0:
+            out.append(-1)
+            continue
+        D = np.unpackbits(d[:, None, :] ^ d[None, :, :], axis=2).sum(2)
+        med = np.sort(D, axis=1)[:, int(0.5 * (n - 1))]
+        out.append(int(np.argmin(med)))
+    return np.asarray(out, np.int32)
+
+
+def test_distinctive_descriptors_hand_cases():
+    from oracle import match_oracle as M
+    z = np.zeros((1, 32), np.uint8)
+    a = z.copy(); a[0, 0] = 0x0F           # 4 bits from z
+    b = z.copy(); b[0, :2] = 0xFF          # 16 bits from z
+    # one observation: itself
+    assert list(M.distinctive_descriptors(z, [0, 1])) == [0]
+    # two observations: medians are row[(int)(0.5*1)] = row[0] = 0 for both -> first wins
+    assert list(M.distinctive_descriptors(np.vstack([a, b]), [0, 2])) == [0]
+    # three: rows sorted {0,4,16}, {0,4,12}, {0,12,16}; medians 4, 4, 12 -> index 0 (first of the tie)
+    assert list(M.distinctive_descriptors(np.vstack([z, a, b]), [0, 3])) == [0]
+    # three with the central one last: {0,12,16}, {0,4,16}... order (b, z, a): medians 12, 4, 4 -> index 1
+    assert list(M.distinctive_descriptors(np.vstack([b, z, a]), [0, 3])) == [1]
+    # empty point in a batch
+    assert list(M.distinctive_descriptors(np.vstack([z, a, b]), [0, 0, 3, 3])) == [-1, 0, -1]
+
+
+def test_distinctive_descriptors_random_vs_numpy():
+    from oracle import match_oracle as M
+    rng = np.random.default_rng(11)
+    sizes = [1, 2, 3, 4, 5, 8, 31, 32, 33, 64, 100, 0, 7]
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = rng.integers(0, 256, (len(sizes), 32), dtype=np.uint8)
+    desc = np.repeat(base, sizes, axis=0)
+    flips = rng.random((len(desc), 256)) < rng.uniform(0.02, 0.2, (len(desc), 1))
+    desc = np.packbits(np.unpackbits(desc, axis=1) ^ flips, axis=1)
+    assert np.array_equal(M.distinctive_descriptors(desc, start), _np_distinctive(desc, start))
