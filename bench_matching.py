@@ -360,3 +360,42 @@ def bench_distinctive(args, dev, local, matcher):
                                "sample": f"first {nc} of the same points, oracle (-O2), one thread"}
         out["gpu_equals_cpu"] = bool(np.array_equal(best[:nc], ref))
     return out
+
+
+def bench_frustum(args, dev, local, matcher):
+    """N3 (SURVEY 8f): Frame::isInFrustum (src/Frame.cc:136-197) of a 20,000-point local map against 64 views."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests"))
+    import matchdata as MD
+    from oracle import frame_oracle as FO
+    from orb_slam_b200 import FrustumView
+    NV, NP = 64, 20_000
+    scenes = [MD.frustum_scene(s, n=NP) for s in range(NV)]
+    pos, nrm, mn, mx = scenes[0][5:]
+    oviews = [FO.make_view(Rcw, tcw, *K, b, sf) for Rcw, tcw, K, b, sf, *_ in scenes]
+    views = [FrustumView.make(sc[0], sc[1], np.array(ov.Ow, np.float32), *sc[2], sc[3], sc[4])
+             for sc, ov in zip(scenes, oviews)]
+    for _ in range(2):
+        matcher.is_in_frustum(views, pos, nrm, mn, mx)
+    kms = []
+    steps = max(args.steps, 5)
+    t = time.perf_counter()
+    for _ in range(steps):
+        res = matcher.is_in_frustum(views, pos, nrm, mn, mx)
+        kms.append(matcher.last_kernel_ms())
+    ms = (time.perf_counter() - t) * 1e3 / steps
+    kms = float(np.mean(kms))
+    out = {"metric": "isInFrustum (view, map point) tests/s", "value": NV * NP / (kms * 1e-3), "unit": "tests/s",
+           "kernel_ms_per_step": kms, "tests_per_step": NV * NP,
+           "e2e": {"value": NV * NP / (ms * 1e-3), "unit": "tests/s", "h2d_bytes_per_step": NP * 32 + NV * 148,
+                   "d2h_bytes_per_step": NV * NP * 17}}
+    if not args.no_cpu:
+        t = time.perf_counter()
+        ref = [FO.is_in_frustum(ov, pos, nrm, mn, mx) for ov in oviews[:8]]
+        dt = time.perf_counter() - t
+        out["cpu_baseline"] = {"value": 8 * NP / dt, "unit": "tests/s", "cores": 1, "kind": "port",
+                               "sample": "8 of the views, oracle (-O2), one thread"}
+        out["gpu_equals_cpu"] = bool(all(np.array_equal(res[0][w], ref[w][0]) and
+                                         np.array_equal(res[1][w].view(np.uint32), ref[w][1].view(np.uint32))
+                                         for w in range(8)))
+    return out

@@ -168,6 +168,26 @@ int orbm_frameset_featvec(orbm_frameset* s, int frame, int32_t* node_id, int32_t
 int orbm_bow_score_l1(orbm_frameset* set1, orbm_frameset* set2, const int32_t* idx1, const int32_t* idx2, int npairs,
                       double* score);
 
+/* ---- N3: Frame::isInFrustum batched (src/Frame.cc:136-197; Tracking::SearchReferencePointsInFrustum,
+ * src/Tracking.cc:701-752) ------------------------------------------------------------------------------------
+ * A view is what a Frame holds after UpdatePoseMatrices (src/Frame.cc:129-134): mRcw (row major), mtcw, mOw, the
+ * intrinsics, the static image bounds (ints) and the scale pyramid.  Every (view, map point) pair is tested: positive
+ * depth, projection inside the bounds, distance inside [min_dist, max_dist] (MapPoint::GetMin/MaxDistanceInvariance),
+ * viewing cosine >= cos_limit (0.5 at the call site), predicted level = lower_bound(mvScaleFactors, dist/min_dist)
+ * clamped to nlevels - 1.  Outputs are [nviews][n]: in_view = mbTrackInView, u/v = mTrackProjX/Y, level =
+ * mnTrackScaleLevel, view_cos = mTrackViewCos (0 / -1 where in_view is 0).  Float results are BIT-exact: the cv::Mat
+ * expressions are evaluated as OpenCV does (gemm small-matrix branch, double accumulation in norm / dot). */
+typedef struct orbm_frustum_view {
+  float Rcw[9], tcw[3], Ow[3];
+  float fx, fy, cx, cy;
+  int32_t min_x, max_x, min_y, max_y;
+  int32_t nlevels;             /* 1..16 */
+  float scale_factors[16];
+} orbm_frustum_view;
+int orbm_is_in_frustum(orbm_handle* h, const orbm_frustum_view* views, int nviews, const float* pos /* n x 3 */,
+                       const float* normal /* n x 3 */, const float* min_dist, const float* max_dist, int n,
+                       float cos_limit, uint8_t* in_view, float* u, float* v, int32_t* level, float* view_cos);
+
 /* ---- N4: MapPoint::ComputeDistinctiveDescriptors batched (src/MapPoint.cc:185-250) ---------------------------
  * Point p observes the descriptors desc[start[p] .. start[p+1]) (HOST buffers; the caller has already dropped bad
  * keyframes, :205-209).  best[p] = index inside the point's list of the descriptor with the least median Hamming

@@ -40,6 +40,21 @@ class Camera(C.Structure):
                [("width", C.c_int32), ("height", C.c_int32)]
 
 
+class FrustumView(C.Structure):
+    """orbm_frustum_view: a Frame's pose (mRcw row major, mtcw, mOw), intrinsics, image bounds and scale pyramid."""
+    _fields_ = [("Rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("Ow", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("min_x", C.c_int32), ("max_x", C.c_int32), ("min_y", C.c_int32), ("max_y", C.c_int32),
+                ("nlevels", C.c_int32), ("scale_factors", C.c_float * 16)]
+
+    @classmethod
+    def make(cls, Rcw, tcw, Ow, fx, fy, cx, cy, bounds, scale_factors):
+        sf = np.zeros(16, np.float32); sf[:len(scale_factors)] = scale_factors
+        return cls((C.c_float * 9)(*np.asarray(Rcw, np.float32).ravel()), (C.c_float * 3)(*np.asarray(tcw, np.float32)),
+                   (C.c_float * 3)(*np.asarray(Ow, np.float32)), fx, fy, cx, cy, *[int(b) for b in bounds],
+                   len(scale_factors), (C.c_float * 16)(*sf))
+
+
 class _Points(C.Structure):
     _fields_ = [("n", C.c_int32), ("u", C.c_void_p), ("v", C.c_void_p), ("radius", C.c_void_p),
                 ("min_level", C.c_void_p), ("max_level", C.c_void_p), ("desc", C.c_void_p), ("angle", C.c_void_p),
@@ -75,6 +90,7 @@ def _bind(L):
     L.orbm_frameset_bowvec.argtypes = [vp, C.c_int, vp, vp]
     L.orbm_frameset_featvec.argtypes = [vp, C.c_int, vp, vp, vp]
     L.orbm_bow_score_l1.argtypes = [vp, vp, vp, vp, C.c_int, vp]
+    L.orbm_is_in_frustum.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, f32, vp, vp, vp, vp, vp]
     L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, C.c_int, vp, vp]
     L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, C.c_int, vp, vp]
     L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
@@ -183,6 +199,23 @@ class Matcher:
         return out
 
     # M8
+    def is_in_frustum(self, views, pos, normal, min_dist, max_dist, cos_limit=0.5):
+        """Frame::isInFrustum (src/Frame.cc:136-197) for every (view, map point) pair ->
+        (in_view u8, u, v, level, view_cos), each [nviews, n]."""
+        views = list(views)
+        arr = (FrustumView * len(views))(*views)
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3); nrm = np.ascontiguousarray(normal, np.float32)
+        mn = np.ascontiguousarray(min_dist, np.float32); mx = np.ascontiguousarray(max_dist, np.float32)
+        n, nv = len(pos), len(views)
+        if nrm.size != 3 * n or len(mn) != n or len(mx) != n:
+            raise ValueError("per-point arrays disagree in length")
+        iv = np.zeros((nv, n), np.uint8); u = np.zeros((nv, n), np.float32); v = np.zeros((nv, n), np.float32)
+        lv = np.zeros((nv, n), np.int32); vc = np.zeros((nv, n), np.float32)
+        self._check(self._L.orbm_is_in_frustum(self._h, arr, nv, pos.ctypes.data, nrm.ctypes.data, mn.ctypes.data,
+                                               mx.ctypes.data, n, cos_limit, iv.ctypes.data, u.ctypes.data,
+                                               v.ctypes.data, lv.ctypes.data, vc.ctypes.data))
+        return iv, u, v, lv, vc
+
     def distinctive_descriptors(self, desc, start):
         """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a batch of map points: point p
         observes desc[start[p]:start[p+1]].  -> (best index per point, chosen descriptor per point [npoints, 32])."""

@@ -67,3 +67,31 @@ def random_valid(n, frac, seed):
 def to_matchframe(f):
     from orb_slam_b200 import MatchFrame
     return MatchFrame(f.x, f.y, f.angle, f.octave, f.desc, f.valid, f.min_x, f.min_y, f.max_x, f.max_y, f.featvec)
+
+
+def frustum_scene(seed, n=5000, w=640, h=480, nlevels=8):
+    """A random camera pose and map points spread so that every exit of Frame::isInFrustum is taken: behind the
+    camera, outside the image, too near / too far, grazing view, and accepted points over all predicted levels.
+    Returns (Rcw, tcw, intrinsics, bounds, scale_factors, pos, normal, min_dist, max_dist), all float32."""
+    rng = np.random.default_rng(seed)
+    q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+    if np.linalg.det(q) < 0:
+        q[:, 0] = -q[:, 0]
+    Rcw = q.astype(np.float32)
+    tcw = rng.normal(size=3).astype(np.float32) * 2
+    fx, fy, cx, cy = np.float32(525.0), np.float32(523.5), np.float32(w / 2 - 3.5), np.float32(h / 2 + 1.25)
+    sf = np.cumprod(np.concatenate([[1.0], np.full(nlevels - 1, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    # points in camera coordinates, then moved to the world
+    z = rng.uniform(-2, 30, n)
+    x = rng.uniform(-0.9, 0.9, n) * np.abs(z) * (w / 2) / 525.0
+    y = rng.uniform(-0.9, 0.9, n) * np.abs(z) * (h / 2) / 523.5
+    pc = np.stack([x, y, z], 1)
+    pos = ((pc - tcw.astype(np.float64)) @ Rcw.astype(np.float64)).astype(np.float32)   # R^T (pc - t)
+    Ow = -(Rcw.astype(np.float64).T @ tcw.astype(np.float64))
+    po = pos.astype(np.float64) - Ow
+    dist = np.linalg.norm(po, axis=1)
+    nrm = po / np.maximum(dist[:, None], 1e-9) + rng.normal(size=(n, 3)) * 0.8
+    nrm = (nrm / np.linalg.norm(nrm, axis=1, keepdims=True)).astype(np.float32)
+    mn = (dist / rng.uniform(0.7, 6.0, n)).astype(np.float32)
+    mx = (mn * rng.uniform(1.0, 5.0, n)).astype(np.float32)
+    return Rcw, tcw, (fx, fy, cx, cy), (0, w, 0, h), sf, pos, nrm, mn, mx

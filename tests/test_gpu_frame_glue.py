@@ -67,3 +67,38 @@ def test_frameset_from_extractor(oracle, cam):
         assert np.array_equal(rows_a[p, :n[i1[p]]], rows_b[p, :n[i1[p]]])
         assert np.array_equal(prev_a[p], prev_b[p])
     fs.close(); hs.close(); ex.close()
+
+
+def test_is_in_frustum_equals_oracle():
+    """N3: batched Frame::isInFrustum (several views x the same map points) — flags, levels and raw float bits."""
+    import matchdata as MD
+    from oracle import frame_oracle as FO
+    from orb_slam_b200 import FrustumView, Matcher
+    m = Matcher(0)
+    scenes = [MD.frustum_scene(s, n=20000) for s in (0, 1, 2)]
+    pos, nrm, mn, mx = scenes[0][5:]
+    views, oviews = [], []
+    for Rcw, tcw, K, bounds, sf, *_ in scenes:
+        ov = FO.make_view(Rcw, tcw, *K, bounds, sf)
+        oviews.append(ov)
+        views.append(FrustumView.make(Rcw, tcw, np.array(ov.Ow, np.float32), *K, bounds, sf))
+    # a 5-level pyramid as well (clamp to nlevels - 1)
+    ov = FO.make_view(scenes[0][0], scenes[0][1], *scenes[0][2], scenes[0][3], scenes[0][4][:5])
+    oviews.append(ov)
+    views.append(FrustumView.make(scenes[0][0], scenes[0][1], np.array(ov.Ow, np.float32), *scenes[0][2], scenes[0][3],
+                                  scenes[0][4][:5]))
+    iv, u, v, lv, vc = m.is_in_frustum(views, pos, nrm, mn, mx, 0.5)
+    for w, ov in enumerate(oviews):
+        oiv, ou, ovv, olv, ovc = FO.is_in_frustum(ov, pos, nrm, mn, mx, 0.5)
+        assert np.array_equal(iv[w], oiv) and np.array_equal(lv[w], olv), w
+        for a, b in ((u[w], ou), (v[w], ovv), (vc[w], ovc)):
+            assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), w
+    assert iv[0].mean() > 0.1 and lv[3].max() == 4
+    # the accepted points feed SearchByProjection's point records
+    from orb_slam_b200 import ProjectedPoints
+    ok = iv[0] == 1
+    pts = ProjectedPoints.for_local_map(u[0][ok], v[0][ok], vc[0][ok], lv[0][ok],
+                                        np.zeros((int(ok.sum()), 32), np.uint8), scenes[0][4])
+    assert pts.n == int(ok.sum())
+    e = m.is_in_frustum(views[:1], np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32), [], [])
+    assert e[0].shape == (1, 0)
