@@ -289,6 +289,7 @@ def main():
             matching["bow"] = BM.bench_bow(args, dev, local, mt)
             matching["distinctive_descriptors"] = BM.bench_distinctive(args, dev, local, mt)
             matching["is_in_frustum"] = BM.bench_frustum(args, dev, local, mt)
+            matching["frontend_chain"] = BM.bench_chain(args, dev, local, mt)
     other = None
     if args.all_configs and world == 1:
         import bench_configs

@@ -399,3 +399,91 @@ def bench_frustum(args, dev, local, matcher):
                                          np.array_equal(res[1][w].view(np.uint32), ref[w][1].view(np.uint32))
                                          for w in range(8)))
     return out
+
+
+def bench_chain(args, dev, local, matcher):
+    """The relocalisation / loop-detection front-end as ONE device-resident chain, per step 128 frame pairs (two shifted
+    640x480 views of one scene each): ORB extraction (E0-E10) -> Frame glue (N1: undistort + grid) -> ComputeBoW (N2,
+    k=10 L=6 vocabulary) -> SearchByBoW between the two views of every pair (M5, kf_kf, ratio 0.75, orientation
+    check).  Images start in HBM; only the match rows and counts come back.  CPU column: the same chain through the
+    oracle on one host thread (what one reference thread does), results compared."""
+    import torch
+    from oracle import bow_oracle as B
+    from orb_slam_b200 import Camera, FrameSet, KP_DTYPE, ORBextractor, ORBmatcher, ORBVocabulary, synth_frames_device
+    W, H, BW, BH, NF, NP = 640, 480, 704, 544, 1000, 128
+    big = torch.empty((NP, BH, BW), dtype=torch.uint8, device=dev)
+    synth_frames_device(big.data_ptr(), NP, BW, BH, BW, BH * BW, seed0=70_000)
+    rng = np.random.default_rng(9)
+    sh = rng.integers(-30, 31, (NP, 2))
+    frames = torch.empty((2 * NP, H, W), dtype=torch.uint8, device=dev)
+    for p in range(NP):
+        frames[2 * p] = big[p, 32:32 + H, 32:32 + W]
+        frames[2 * p + 1] = big[p, 32 + sh[p, 1]:32 + sh[p, 1] + H, 32 + sh[p, 0]:32 + sh[p, 0] + W]
+    del big
+    cam = (268.9633 * 2, 269.9858 * 2, 157.6087 * 2, 114.6369 * 2, -0.4157, 0.2624, 0.0, 0.0, -0.1178, W, H)
+    camera = Camera(*cam)
+    V = B.synth_vocabulary_fast(k=10, L=6, seed=1)
+    keys = ("k", "L", "scoring", "weighting", "parent", "desc", "weight", "is_leaf")
+    voc = ORBVocabulary.from_arrays(matcher, **{k: V[k] for k in keys})
+    F = 2 * NP
+    ex = ORBextractor(NF, 1.2, 8, 1, 20, max_width=W, max_height=H, max_batch=F, device=local)
+    d_k = torch.zeros((F, NF, 28), dtype=torch.uint8, device=dev)
+    d_d = torch.zeros((F, NF, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(F, dtype=torch.int32, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    om = ORBmatcher(0.75, True, matcher=matcher)
+    i1 = np.arange(0, F, 2, dtype=np.int32); i2 = i1 + 1
+
+    def step(keep=False):
+        ex.extract_batch_device(frames.data_ptr(), F, W, H, W, H * W, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(),
+                                stream.cuda_stream)
+        fs = FrameSet.from_extractor(matcher, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), F, NF, camera,
+                                     stream.cuda_stream)
+        fs.fill_valid(True)
+        fs.compute_bow(voc, 4)
+        nm, rows = om.SearchByBoW(fs, fs, i1, i2, "kf_kf")
+        if keep:
+            return fs, nm, rows
+        fs.close()
+        return None, nm, rows
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    steps = max(args.steps, 5)
+    t = time.perf_counter()
+    for _ in range(steps):
+        _, nm, rows = step()
+    ms = (time.perf_counter() - t) * 1e3 / steps
+    out = {"metric": "front-end chain frames/s (extract -> frame glue -> ComputeBoW -> SearchByBoW, device resident)",
+           "value": F / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms, "frames_per_step": F,
+           "pairs_per_step": NP, "mean_matches_per_pair": float(nm.mean()), "d2h_bytes_per_step": int(rows.nbytes + nm.nbytes + 3 * 4 * F),
+           "note": "wall clock incl. all allocations and syncs of the four calls; images resident in HBM"}
+    if not args.no_cpu:
+        from oracle import frame_oracle as FO
+        from oracle import match_oracle as MO
+        from oracle import oracle as O
+        from orb_slam_b200 import MatchFrame
+        nc = 4
+        himg = frames[: 2 * nc].cpu().numpy()
+        ovoc = B.Vocabulary.from_arrays(**{k: V[k] for k in keys}, fast=True)
+        E = O.OracleExtractor(NF, 1.2, 8, 1, 20, fast_build=True)
+        ocam = FO.Camera(*cam[:9])
+        (mnx, mxx, mny, mxy), _ = FO.image_bounds(ocam, W, H)
+        t = time.perf_counter()
+        ok = True
+        for p in range(nc):
+            fr = []
+            for f in (2 * p, 2 * p + 1):
+                k, d = E(himg[f])
+                un = FO.undistort_points(ocam, np.stack([k["x"], k["y"]], 1))
+                _, fv = ovoc.transform(d, 4)
+                fr.append(MatchFrame(un[:, 0], un[:, 1], k["angle"], k["octave"], d, np.ones(len(k), np.uint8),
+                                     float(mnx), float(mny), float(mxx), float(mxy), fv))
+            on, orow = MO.search_by_bow(fr[0], fr[1], "kf_kf", 0.75, True)
+            ok = ok and on == nm[p] and np.array_equal(rows[p][: len(orow)], orow)
+        dt = time.perf_counter() - t
+        out["cpu_baseline"] = {"value": 2 * nc / dt, "unit": "frames/s", "cores": 1, "kind": "port",
+                               "sample": f"{nc} of the same pairs through the oracle chain (-O3 -march=native)"}
+        out["gpu_equals_cpu"] = bool(ok)
+    ex.close(); voc.close()
+    return out

@@ -119,6 +119,8 @@ int orbm_frameset_keypoints(orbm_frameset* s, int frame, float* x, float* y, flo
                             uint8_t* desc);
 /* Replaces the valid flags of one frame (MapPoint associations change between searches). */
 int orbm_frameset_set_valid(orbm_frameset* s, int frame, const uint8_t* valid);
+/* Sets the valid flag of EVERY keypoint of EVERY frame to value != 0 (asynchronous on the handle's stream). */
+int orbm_frameset_fill_valid(orbm_frameset* s, int value);
 /* The device-built grid as CSR in the reference's visiting order: cell = ix * 48 + iy (src/Frame.cc:232-258),
  * insertion order inside a cell.  cell_start: 3073 entries, items: n entries (count = cell_start[3072]). */
 int orbm_frameset_grid(orbm_frameset* s, int frame, int32_t* cell_start, int32_t* items);

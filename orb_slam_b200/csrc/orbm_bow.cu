@@ -570,14 +570,14 @@ extern "C" int orbm_frameset_compute_bow(orbm_frameset* s, const orbm_vocabulary
   if (!s->bow_sized) {   // first ComputeBoW on this set (or feature vectors uploaded at their exact size): reallocate
     void** old[] = {(void**)&s->d_node_off, (void**)&s->d_fvitem_off, (void**)&s->d_node_id, (void**)&s->d_node_start,
                     (void**)&s->d_fv_items, (void**)&s->d_bow_word, (void**)&s->d_bow_val};
-    for (void** p : old) { if (*p) cudaFree(*p); *p = nullptr; }
-    ORBM_CK(cudaMalloc(&s->d_node_off, (nf + 1) * 4));
-    ORBM_CK(cudaMalloc(&s->d_fvitem_off, (nf + 1) * 4));
-    ORBM_CK(cudaMalloc(&s->d_node_id, n1 * 4));
-    ORBM_CK(cudaMalloc(&s->d_node_start, (n1 + nf) * 4));
-    ORBM_CK(cudaMalloc(&s->d_fv_items, n1 * 4));
-    ORBM_CK(cudaMalloc(&s->d_bow_word, n1 * 4));
-    ORBM_CK(cudaMalloc(&s->d_bow_val, n1 * 8));
+    for (void** p : old) { orbm_free(h, *p); *p = nullptr; }
+    ORBM_CK(orbm_alloc(h, &s->d_node_off, (nf + 1) * 4));
+    ORBM_CK(orbm_alloc(h, &s->d_fvitem_off, (nf + 1) * 4));
+    ORBM_CK(orbm_alloc(h, &s->d_node_id, n1 * 4));
+    ORBM_CK(orbm_alloc(h, &s->d_node_start, (n1 + nf) * 4));
+    ORBM_CK(orbm_alloc(h, &s->d_fv_items, n1 * 4));
+    ORBM_CK(orbm_alloc(h, &s->d_bow_word, n1 * 4));
+    ORBM_CK(orbm_alloc(h, &s->d_bow_val, n1 * 8));
     s->bow_sized = true;
   }
   BowTargets o{s->d_node_off, s->d_fvitem_off, s->d_node_id, s->d_node_start, s->d_fv_items, s->d_bow_word,

@@ -110,9 +110,9 @@ FrameSetView orbm::view_of(const orbm_frameset* s) {
 }
 
 template <class T>
-static cudaError_t upload(T** dptr, const std::vector<T>& v, cudaStream_t s) {
+static cudaError_t upload(orbm_handle* h, T** dptr, const std::vector<T>& v, cudaStream_t s) {
   const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
-  cudaError_t e = cudaMalloc((void**)dptr, bytes + 16);
+  cudaError_t e = orbm_alloc(h, dptr, bytes + 16);
   if (e != cudaSuccess) return e;
   if (!v.empty()) e = cudaMemcpyAsync(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s);
   return e;
@@ -191,22 +191,22 @@ extern "C" int orbm_frameset_create(orbm_handle* h, const orbm_frame* frames, co
   };
   cudaError_t e;
   cudaStream_t st = h->stream;
-  if ((e = upload(&s->d_frame_off, s->frame_off, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_x, x, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_y, y, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_angle, ang, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_octave, oct, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_desc, desc, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_valid, valid, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_gridp, gp, st)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_cell_start, (size_t)nframes * (kGridCells + 1) * 4)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_items, std::max<size_t>(N, 1) * 4)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_frame_off, s->frame_off, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_x, x, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_y, y, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_angle, ang, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_octave, oct, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_desc, desc, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_valid, valid, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_gridp, gp, st)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_cell_start, (size_t)nframes * (kGridCells + 1) * 4)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_items, std::max<size_t>(N, 1) * 4)) != cudaSuccess) return fail(e);
   if (fvs) {
-    if ((e = upload(&s->d_node_off, s->node_off, st)) != cudaSuccess) return fail(e);
-    if ((e = upload(&s->d_fvitem_off, s->fvitem_off, st)) != cudaSuccess) return fail(e);
-    if ((e = upload(&s->d_node_id, node_id, st)) != cudaSuccess) return fail(e);
-    if ((e = upload(&s->d_node_start, node_start, st)) != cudaSuccess) return fail(e);
-    if ((e = upload(&s->d_fv_items, fv_items, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(h, &s->d_node_off, s->node_off, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(h, &s->d_fvitem_off, s->fvitem_off, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(h, &s->d_node_id, node_id, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(h, &s->d_node_start, node_start, st)) != cudaSuccess) return fail(e);
+    if ((e = upload(h, &s->d_fv_items, fv_items, st)) != cudaSuccess) return fail(e);
   }
   grid_build_kernel<<<nframes, 32, 0, st>>>(view_of(s));
   h->launches++;
@@ -310,16 +310,16 @@ extern "C" int orbm_frameset_from_extractor(orbm_handle* h, const void* d_kps, c
   cudaError_t e;
   const size_t n1 = std::max<size_t>(N, 1);
   std::vector<float4> gp(nframes, make_float4((float)bounds[0], (float)bounds[2], inv[0], inv[1]));
-  if ((e = upload(&s->d_frame_off, s->frame_off, st)) != cudaSuccess) return fail(e);
-  if ((e = upload(&s->d_gridp, gp, st)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_x, n1 * 4 + 16)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_y, n1 * 4 + 16)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_angle, n1 * 4 + 16)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_octave, n1 * 4 + 16)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_desc, n1 * 32 + 16)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_valid, n1 + 16)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_cell_start, (size_t)nframes * (kGridCells + 1) * 4)) != cudaSuccess) return fail(e);
-  if ((e = cudaMalloc(&s->d_items, n1 * 4)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_frame_off, s->frame_off, st)) != cudaSuccess) return fail(e);
+  if ((e = upload(h, &s->d_gridp, gp, st)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_x, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_y, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_angle, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_octave, n1 * 4 + 16)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_desc, n1 * 32 + 16)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_valid, n1 + 16)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_cell_start, (size_t)nframes * (kGridCells + 1) * 4)) != cudaSuccess) return fail(e);
+  if ((e = orbm_alloc(h, &s->d_items, n1 * 4)) != cudaSuccess) return fail(e);
   frame_glue_kernel<<<nframes, 256, 0, st>>>(static_cast<const KeyPoint28*>(d_kps), d_desc, kp_stride, s->d_frame_off,
                                              camera_of(*cam), cam->k1 != 0.0f ? 1 : 0, s->d_x, s->d_y, s->d_angle,
                                              s->d_octave, reinterpret_cast<uint4*>(s->d_desc), s->d_valid);
@@ -361,7 +361,7 @@ extern "C" void orbm_frameset_destroy(orbm_frameset* s) {
   void* ptrs[] = {s->d_frame_off, s->d_x, s->d_y, s->d_angle, s->d_octave, s->d_desc, s->d_valid, s->d_gridp,
                   s->d_cell_start, s->d_items, s->d_node_off, s->d_fvitem_off, s->d_node_id, s->d_node_start,
                   s->d_fv_items, s->d_bow_word, s->d_bow_val};
-  for (void* p : ptrs) if (p) cudaFree(p);
+  for (void* p : ptrs) orbm_free(s->h, p);
   delete s;
 }
 
@@ -375,6 +375,14 @@ extern "C" int orbm_frameset_set_valid(orbm_frameset* s, int frame, const uint8_
   if (valid) ORBM_CK(cudaMemcpyAsync(s->d_valid + o, valid, n, cudaMemcpyHostToDevice, h->stream));
   else ORBM_CK(cudaMemsetAsync(s->d_valid + o, 0, n, h->stream));
   ORBM_CK(cudaStreamSynchronize(h->stream));
+  return ORBM_OK;
+}
+
+extern "C" int orbm_frameset_fill_valid(orbm_frameset* s, int value) {
+  if (!s) return ORBM_ERR_ARG;
+  orbm_handle* h = s->h;
+  ORBM_CK(cudaSetDevice(h->device));
+  if (s->total_kp) ORBM_CK(cudaMemsetAsync(s->d_valid, value ? 1 : 0, (size_t)s->total_kp, h->stream));
   return ORBM_OK;
 }
 

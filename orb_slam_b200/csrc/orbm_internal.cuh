@@ -85,6 +85,15 @@ struct orbm_frameset {
   bool bow_sized = false;           // the feature / bow vector arrays have their upper-bound sizes (reusable)
 };
 
+// Frame-set arrays come from the device's stream-ordered pool (cudaMallocAsync on the handle's stream; the pool's
+// release threshold is lifted at orbm_create so freed blocks are reused instead of returned to the driver): creating
+// and destroying a frame set per tracked batch then costs microseconds, not a dozen cudaMalloc/cudaFree round trips.
+inline cudaError_t orbm_alloc(orbm_handle* h, void** p, size_t bytes) { return cudaMallocAsync(p, bytes, h->stream); }
+template <class T> inline cudaError_t orbm_alloc(orbm_handle* h, T** p, size_t bytes) {
+  return cudaMallocAsync(reinterpret_cast<void**>(p), bytes, h->stream);
+}
+inline void orbm_free(orbm_handle* h, void* p) { if (p) cudaFreeAsync(p, h->stream); }
+
 #define ORBM_CK(call)                                                          \
   do {                                                                         \
     cudaError_t e_ = (call);                                                   \

@@ -32,6 +32,11 @@ extern "C" int orbm_create(int device, orbm_handle** out) {
     cudaDeviceProp prop;
     ORBM_CK(cudaGetDeviceProperties(&prop, device));
     h->num_sms = prop.multiProcessorCount;
+    // frame-set arrays are pool allocations (orbm_alloc): keep freed blocks cached in the pool
+    cudaMemPool_t pool;
+    ORBM_CK(cudaDeviceGetDefaultMemPool(&pool, device));
+    unsigned long long keep = ~0ull;
+    ORBM_CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
     return ORBM_OK;
   };
   int rc = body();

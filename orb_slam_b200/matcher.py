@@ -75,6 +75,7 @@ def _bind(L):
     L.orbm_frameset_destroy.argtypes = [vp]; L.orbm_frameset_destroy.restype = None
     L.orbm_frameset_set_valid.argtypes = [vp, C.c_int, vp]
     L.orbm_frameset_grid.argtypes = [vp, C.c_int, vp, vp]
+    L.orbm_frameset_fill_valid.argtypes = [vp, C.c_int]
     L.orbm_image_bounds.argtypes = [C.POINTER(Camera), vp, vp]
     L.orbm_frameset_from_extractor.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(Camera), vp, C.POINTER(vp)]
     L.orbm_frameset_counts.argtypes = [vp, vp]
@@ -402,6 +403,9 @@ class FrameSet:
     def set_valid(self, frame, valid):
         v = None if valid is None else np.ascontiguousarray(valid, np.uint8)
         self.m._check(self._L.orbm_frameset_set_valid(self._s, frame, None if v is None else v.ctypes.data))
+
+    def fill_valid(self, value=True):
+        self.m._check(self._L.orbm_frameset_fill_valid(self._s, int(bool(value))))
 
     def grid(self, frame):
         cs = np.zeros(FRAME_GRID_COLS * FRAME_GRID_ROWS + 1, np.int32)
