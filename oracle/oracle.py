@@ -59,12 +59,13 @@ def build(fast: bool = False, force: bool = False) -> str:
 
 
 def build_ref(reference: str = "/root/reference") -> str | None:
-    """oracle/_ref/libref_dbow2.so: the reference's own DBoW2 compiled where it lies (Makefile target `ref`).  Only
+    """oracle/_ref/libref_dbow2.so + libref_orbextractor.so: the reference's own DBoW2 and src/ORBextractor.cc compiled
+    where they lie (Makefile target `ref`).  Only
     possible where the reference tree exists (the authoring container); elsewhere the prebuilt file is used as is."""
     out = os.path.join(_HERE, "_ref", "libref_dbow2.so")
     if os.path.isdir(os.path.join(reference, "Thirdparty", "DBoW2")):
         subprocess.run(["make", "-C", _HERE, "ref", f"REFERENCE={reference}"], check=True, capture_output=True)
-    return out if os.path.exists(out) else None
+    return out if os.path.exists(out) and os.path.exists(os.path.join(_HERE, "_ref", "libref_orbextractor.so")) else None
 
 
 _libs = {}

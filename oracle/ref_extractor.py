@@ -1,0 +1,127 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.
+
+The reference's OWN extractor: /root/reference/src/ORBextractor.cc compiled in place (oracle/Makefile target `ref`,
+oracle/ref_orbextractor.cc, type-only OpenCV stand-in oracle/ref_shim_cv/) with its five OpenCV library calls bridged
+to the real OpenCV installed here (cv2): cv::resize, cv::copyMakeBorder, cv::GaussianBlur, cv::FAST, cv::fastAtan2.
+`RefExtractor` mirrors ORB_SLAM::ORBextractor (include/ORBextractor.h:32-77).  Needs oracle/_ref/libref_orbextractor.so
+(built where /root/reference exists) and an importable cv2; tests that use it skip otherwise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_LIB = os.path.join(_HERE, "_ref", "libref_orbextractor.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+
+_u8p = C.POINTER(C.c_uint8)
+_RESIZE = C.CFUNCTYPE(None, _u8p, C.c_int, C.c_int, C.c_long, _u8p, C.c_int, C.c_int, C.c_long, C.c_int)
+_BORDER = C.CFUNCTYPE(None, _u8p, C.c_int, C.c_int, C.c_long, _u8p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
+_BLUR = C.CFUNCTYPE(None, _u8p, C.c_int, C.c_int, C.c_long, C.c_int, C.c_double, C.c_int)
+_FAST = C.CFUNCTYPE(C.c_int, _u8p, C.c_int, C.c_int, C.c_long, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_int)
+_ATAN = C.CFUNCTYPE(C.c_float, C.c_float, C.c_float)
+
+
+def available() -> bool:
+    if not os.path.exists(REF_LIB):
+        return False
+    try:
+        import cv2  # noqa: F401
+    except Exception:
+        return False
+    return True
+
+
+def _view(ptr, w, h, step):
+    """numpy view of an 8-bit image the C++ side owns (rows `step` bytes apart)."""
+    n = (h - 1) * step + w
+    flat = np.ctypeslib.as_array(ptr, shape=(n,))
+    return np.lib.stride_tricks.as_strided(flat, shape=(h, w), strides=(step, 1))
+
+
+_state = {}
+
+
+def _lib():
+    if "L" in _state:
+        return _state["L"]
+    import cv2
+    cv2.setNumThreads(1)
+    detectors = {}
+
+    def resize(src, sw, sh, sstep, dst, dw, dh, dstep, interp):
+        out = cv2.resize(np.ascontiguousarray(_view(src, sw, sh, sstep)), (dw, dh), interpolation=interp)
+        _view(dst, dw, dh, dstep)[:] = out
+
+    def border(src, w, h, sstep, dst, dstep, top, bottom, left, right, btype):
+        # the source may be a view INTO the destination (ComputePyramid :806): copy it out first.  BORDER_ISOLATED is
+        # implied: the array handed to cv2 has no parent
+        s = np.ascontiguousarray(_view(src, w, h, sstep))
+        out = cv2.copyMakeBorder(s, top, bottom, left, right, btype & ~16)
+        _view(dst, w + left + right, h + top + bottom, dstep)[:] = out
+
+    def blur(img, w, h, step, ksize, sigma, btype):
+        # in place on a view whose parent holds the reflect-101 border the reference built (:806-816); the filter
+        # would read those parent pixels, which equal what BORDER_REFLECT_101 synthesises for the isolated view
+        v = _view(img, w, h, step)
+        v[:] = cv2.GaussianBlur(np.ascontiguousarray(v), (ksize, ksize), sigma, sigmaY=sigma, borderType=btype)
+
+    def fast(img, w, h, step, th, nonmax, xyr, cap):
+        key = (th, nonmax)
+        if key not in detectors:
+            detectors[key] = cv2.FastFeatureDetector_create(th, bool(nonmax), cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+        kps = detectors[key].detect(np.ascontiguousarray(_view(img, w, h, step)))
+        n = min(len(kps), cap)
+        out = np.ctypeslib.as_array(xyr, shape=(cap * 3,))
+        for i in range(n):
+            k = kps[i]
+            out[3 * i] = k.pt[0]; out[3 * i + 1] = k.pt[1]; out[3 * i + 2] = k.response
+        return n
+
+    def atan2(y, x):
+        return cv2.fastAtan2(y, x)
+
+    L = C.CDLL(REF_LIB)
+    cbs = (_RESIZE(resize), _BORDER(border), _BLUR(blur), _FAST(fast), _ATAN(atan2))
+    L.ref_orb_set_bridge.argtypes = [_RESIZE, _BORDER, _BLUR, _FAST, _ATAN, C.c_int]
+    L.ref_orb_create.restype = C.c_void_p
+    L.ref_orb_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+    L.ref_orb_destroy.argtypes = [C.c_void_p]
+    L.ref_orb_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_long, C.c_void_p, C.c_void_p, C.c_int]
+    _state.update(L=L, cbs=cbs, cv2_version=cv2.__version__)
+    set_retain_mode(1)
+    return L
+
+
+def set_retain_mode(mode: int):
+    """KeyPointsFilter::retainBest variant: 0 = OpenCV 2.4 (nth_element at begin + n), 1 = OpenCV >= 3.4 (begin + n - 1,
+    what the installed cv2 4.13 itself does)."""
+    L = _state["L"]
+    L.ref_orb_set_bridge(*_state["cbs"], mode)
+
+
+class RefExtractor:
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, scoreType=1, fastTh=20):
+        self._L = _lib()
+        self._h = self._L.ref_orb_create(nfeatures, scaleFactor, nlevels, scoreType, fastTh)
+
+    def __call__(self, image):
+        img = np.ascontiguousarray(image, np.uint8)
+        h, w = img.shape
+        cap = 1 << 16
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+        n = self._L.ref_orb_extract(self._h, img.ctypes.data, w, h, w, kps.ctypes.data, desc.ctypes.data, cap)
+        if n < 0:
+            raise RuntimeError("keypoint capacity too small")
+        return kps[:n].copy(), desc[:n].copy()
+
+    def __del__(self):
+        try:
+            self._L.ref_orb_destroy(self._h)
+        except Exception:
+            pass

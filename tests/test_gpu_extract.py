@@ -205,3 +205,28 @@ def test_low_contrast_retry_path(oracle, div, seed):
         assert np.array_equal(nt, ont), f"nTotal level {l}"
         assert np.array_equal(nr, onr), f"nToRetain level {l}"
     _cmp_final(k, d, ok, od)
+
+
+def test_cuda_equals_reference_generated_golden():
+    """The CUDA extractor against vectors produced by the reference's OWN src/ORBextractor.cc (compiled in place, OpenCV
+    routines served by cv2 4.13; tests/golden/make_ref_extract_golden.py): every field and descriptor byte, for both
+    retainBest variants, with the OpenCV >= 3.4 Gaussian taps (blur_mode = 1)."""
+    import os
+    from orb_slam_b200 import ORBextractor
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_extract.npz"))
+    for c in range(int(g["ncases"])):
+        nf, nl, st, th, sf = (int(v) for v in g[f"params{c}"])
+        img = g[f"img{c}"]
+        for mode in (1, 0):
+            ex = ORBextractor(nf, sf / 1000.0, nl, st, th, max_width=img.shape[1], max_height=img.shape[0], max_batch=2,
+                              blur_mode=1, retain_mode=mode)
+            k, d = ex(img)
+            rk, rd = g[f"kps{c}_{mode}"], g[f"desc{c}_{mode}"]
+            assert len(k) == len(rk), (c, mode)
+            for f in ("x", "y", "size", "angle", "response", "octave", "class_id"):
+                a, b = k[f], rk[f]
+                if a.dtype.kind == "f":
+                    a, b = a.view(np.uint32), b.view(np.uint32)
+                assert np.array_equal(a, b), (c, mode, f)
+            assert np.array_equal(d, rd), (c, mode)
+            ex.close()
