@@ -25,6 +25,7 @@ _BORDER = C.CFUNCTYPE(None, _u8p, C.c_int, C.c_int, C.c_long, _u8p, C.c_long, C.
 _BLUR = C.CFUNCTYPE(None, _u8p, C.c_int, C.c_int, C.c_long, C.c_int, C.c_double, C.c_int)
 _FAST = C.CFUNCTYPE(C.c_int, _u8p, C.c_int, C.c_int, C.c_long, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_int)
 _ATAN = C.CFUNCTYPE(C.c_float, C.c_float, C.c_float)
+_UNDIST = C.CFUNCTYPE(None, C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int)
 
 
 def available() -> bool:
@@ -47,9 +48,11 @@ def _view(ptr, w, h, step):
 _state = {}
 
 
-def _lib():
-    if "L" in _state:
-        return _state["L"]
+def _lib(path=None):
+    """Loads a library that contains ref_orbextractor.cc and points its OpenCV bridge at cv2."""
+    key = path or REF_LIB
+    if key in _state:
+        return _state[key]["L"]
     import cv2
     cv2.setNumThreads(1)
     detectors = {}
@@ -86,28 +89,38 @@ def _lib():
     def atan2(y, x):
         return cv2.fastAtan2(y, x)
 
-    L = C.CDLL(REF_LIB)
+    def undistort(xy, n, K9, D, nd):
+        pts = np.ctypeslib.as_array(xy, shape=(n, 2))
+        K = np.ctypeslib.as_array(K9, shape=(9,)).reshape(3, 3).copy()
+        Dv = np.ctypeslib.as_array(D, shape=(nd,)).reshape(nd, 1).copy()
+        pts[:] = cv2.undistortPoints(pts.reshape(-1, 1, 2).copy(), K, Dv, None, K).reshape(-1, 2)
+
+    L = C.CDLL(key)
     cbs = (_RESIZE(resize), _BORDER(border), _BLUR(blur), _FAST(fast), _ATAN(atan2))
+    und = _UNDIST(undistort)
+    L.ref_orb_set_undistort.argtypes = [_UNDIST]
+    L.ref_orb_set_undistort(und)
     L.ref_orb_set_bridge.argtypes = [_RESIZE, _BORDER, _BLUR, _FAST, _ATAN, C.c_int]
     L.ref_orb_create.restype = C.c_void_p
     L.ref_orb_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
     L.ref_orb_destroy.argtypes = [C.c_void_p]
     L.ref_orb_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_long, C.c_void_p, C.c_void_p, C.c_int]
-    _state.update(L=L, cbs=cbs, cv2_version=cv2.__version__)
-    set_retain_mode(1)
+    _state[key] = dict(L=L, cbs=cbs, und=und, cv2_version=cv2.__version__)
+    set_retain_mode(1, key)
     return L
 
 
-def set_retain_mode(mode: int):
+def set_retain_mode(mode: int, path=None):
     """KeyPointsFilter::retainBest variant: 0 = OpenCV 2.4 (nth_element at begin + n), 1 = OpenCV >= 3.4 (begin + n - 1,
     what the installed cv2 4.13 itself does)."""
-    L = _state["L"]
-    L.ref_orb_set_bridge(*_state["cbs"], mode)
+    for key, st in _state.items():
+        if path is None or key == path:
+            st["L"].ref_orb_set_bridge(*st["cbs"], mode)
 
 
 class RefExtractor:
-    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, scoreType=1, fastTh=20):
-        self._L = _lib()
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, scoreType=1, fastTh=20, lib_path=None):
+        self._L = _lib(lib_path)
         self._h = self._L.ref_orb_create(nfeatures, scaleFactor, nlevels, scoreType, fastTh)
 
     def __call__(self, image):

@@ -1,0 +1,149 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.
+
+The reference's OWN front-end objects: Frame / KeyFrame / MapPoint / ORBmatcher / ORBVocabulary compiled from
+/root/reference (oracle/ref_orbmatcher.cc, oracle/_ref/libref_orbslam.so), OpenCV routines served by cv2
+(oracle/ref_extractor.py).  Frames are built by Frame's own constructor from an IMAGE: extraction, undistortion, image
+bounds and grid binning are all the reference's code.  Authoring container only; tests skip without it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import ref_extractor as RE
+
+LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_orbslam.so")
+_P, _I, _F = C.c_void_p, C.c_int, C.c_float
+
+
+def available() -> bool:
+    if not os.path.exists(LIB):
+        return False
+    try:
+        import cv2  # noqa: F401
+    except Exception:
+        return False
+    return True
+
+
+def _lib():
+    L = RE._lib(LIB)
+    if not getattr(L, "_m_ready", False):
+        L.ref_m_world_create.restype = _P; L.ref_m_world_create.argtypes = [C.c_char_p]
+        L.ref_m_frame_create.restype = _P; L.ref_m_frame_create.argtypes = [_P, _P, _P, _I, _I, _P, _P, _I]
+        L.ref_m_frame_n.argtypes = [_P]
+        L.ref_m_frame_bounds.argtypes = [_P, _P, _P]
+        L.ref_m_frame_read.argtypes = [_P, _P, _P, _P, _P]
+        L.ref_m_frame_grid.argtypes = [_P, _P, _P]
+        L.ref_m_features_in_area.argtypes = [_P, _F, _F, _F, _I, _I, _P]
+        L.ref_m_search_for_initialization.argtypes = [_P, _P, _P, _P, _I, _F, _I]
+        L.ref_m_frame_set_valid.argtypes = [_P, _P]
+        L.ref_m_window_search.argtypes = [_P, _P, _I, _I, _I, _F, _I, _P]
+        L.ref_m_frame_compute_bow.argtypes = [_P]
+        L.ref_m_frame_bow.argtypes = [_P] + [_P] * 7
+        L.ref_m_keyframe_create.restype = _P; L.ref_m_keyframe_create.argtypes = [_P]
+        L.ref_m_search_by_bow_kf_f.argtypes = [_P, _P, _P, _F, _I, _P]
+        L.ref_m_search_by_bow_kf_kf.argtypes = [_P, _P, _P, _I, _F, _I, _P]
+        L.ref_m_distinctive_desc.argtypes = [_P, _P, _P, _I, _P, _P]
+        L._m_ready = True
+    return L
+
+
+class World:
+    """One object graph: vocabulary (optional text file), Map, KeyFrameDatabase, and the extractor frames are made with."""
+
+    def __init__(self, voc_path=None, nfeatures=1000, scaleFactor=1.2, nlevels=8, scoreType=1, fastTh=20):
+        self._L = _lib()
+        self._w = self._L.ref_m_world_create(os.fsencode(voc_path) if voc_path else b"")
+        if not self._w:
+            raise ValueError("vocabulary load failed")
+        self.extractor = RE.RefExtractor(nfeatures, scaleFactor, nlevels, scoreType, fastTh, lib_path=LIB)
+
+    def frame(self, image, K, D, reset_static=False):
+        return RefFrame(self, image, K, D, reset_static)
+
+    def distinctive(self, keyframes, idx):
+        """MapPoint::ComputeDistinctiveDescriptors for a point observed at keypoint idx[k] of keyframes[k] ->
+        (mDescriptor, order): `order` = the sequence in which the reference's std::map<KeyFrame*,..> visits them."""
+        n = len(keyframes)
+        arr = (C.c_void_p * n)(*[k for k in keyframes])
+        ix = np.ascontiguousarray(idx, np.int32); out = np.zeros(32, np.uint8); order = np.zeros(n, np.int32)
+        self._L.ref_m_distinctive_desc(self._w, arr, ix.ctypes.data, n, out.ctypes.data, order.ctypes.data)
+        return out, order
+
+
+class RefFrame:
+    def __init__(self, world: World, image, K, D, reset_static):
+        self.world, self._L = world, world._L
+        img = np.ascontiguousarray(image, np.uint8)
+        K = np.ascontiguousarray(K, np.float32).reshape(9); D = np.ascontiguousarray(D, np.float32).reshape(5)
+        self._f = self._L.ref_m_frame_create(world._w, world.extractor._h, img.ctypes.data, img.shape[1], img.shape[0],
+                                             K.ctypes.data, D.ctypes.data, int(reset_static))
+        self.n = self._L.ref_m_frame_n(self._f)
+        b = np.zeros(4, np.int32); inv = np.zeros(2, np.float32)
+        self._L.ref_m_frame_bounds(self._f, b.ctypes.data, inv.ctypes.data)
+        self.bounds, self.inv = tuple(int(v) for v in b), (float(inv[0]), float(inv[1]))
+        n1 = max(self.n, 1)
+        self.kps = np.zeros(n1, RE.KP_DTYPE); self.xu = np.zeros(n1, np.float32); self.yu = np.zeros(n1, np.float32)
+        self.desc = np.zeros((n1, 32), np.uint8)
+        self._L.ref_m_frame_read(self._f, self.kps.ctypes.data, self.xu.ctypes.data, self.yu.ctypes.data,
+                                 self.desc.ctypes.data)
+        self.kps, self.xu, self.yu, self.desc = self.kps[:self.n], self.xu[:self.n], self.yu[:self.n], self.desc[:self.n]
+        self._kf = None
+
+    def grid(self):
+        cs = np.zeros(64 * 48 + 1, np.int32); items = np.zeros(max(self.n, 1), np.int32)
+        self._L.ref_m_frame_grid(self._f, cs.ctypes.data, items.ctypes.data)
+        return cs, items[:cs[-1]]
+
+    def features_in_area(self, x, y, r, minl=-1, maxl=-1):
+        out = np.zeros(max(self.n, 1), np.int32)
+        n = self._L.ref_m_features_in_area(self._f, x, y, r, minl, maxl, out.ctypes.data)
+        return out[:n].copy()
+
+    def set_valid(self, valid):
+        v = np.ascontiguousarray(valid, np.uint8)
+        self._L.ref_m_frame_set_valid(self._f, v.ctypes.data)
+        self._kf = None
+
+    def compute_bow(self):
+        self._L.ref_m_frame_compute_bow(self._f)
+        n1 = max(self.n, 1)
+        w = np.zeros(n1, np.int32); v = np.zeros(n1, np.float64); nw = np.zeros(1, np.int32)
+        nd = np.zeros(n1, np.int32); st = np.zeros(n1 + 1, np.int32); it = np.zeros(n1, np.int32); nn = np.zeros(1, np.int32)
+        self._L.ref_m_frame_bow(self._f, w.ctypes.data, v.ctypes.data, nw.ctypes.data, nd.ctypes.data, st.ctypes.data,
+                                it.ctypes.data, nn.ctypes.data)
+        nw, nn = int(nw[0]), int(nn[0])
+        return (w[:nw].copy(), v[:nw].copy()), (nd[:nn].copy(), st[:nn + 1].copy(), it[:st[nn]].copy())
+
+    def keyframe(self):
+        """KeyFrame(F, map, db): call after set_valid / compute_bow."""
+        if self._kf is None:
+            self._kf = self._L.ref_m_keyframe_create(self._f)
+        return self._kf
+
+
+def search_for_initialization(f1: RefFrame, f2: RefFrame, prev_xy, window, ratio, check_ori):
+    prev = np.ascontiguousarray(prev_xy, np.float32).copy()
+    m = np.zeros(max(f1.n, 1), np.int32)
+    n = _lib().ref_m_search_for_initialization(f1._f, f2._f, prev.ctypes.data, m.ctypes.data, window, ratio, int(check_ori))
+    return n, m[:f1.n], prev
+
+
+def window_search(f1: RefFrame, f2: RefFrame, window, minl, maxl, ratio, check_ori):
+    m = np.zeros(max(f2.n, 1), np.int32)
+    n = _lib().ref_m_window_search(f1._f, f2._f, window, minl, maxl, ratio, int(check_ori), m.ctypes.data)
+    return n, m[:f2.n]
+
+
+def search_by_bow(f1: RefFrame, f2: RefFrame, variant, ratio, check_ori):
+    L = _lib()
+    if variant == "kf_f":
+        m = np.zeros(max(f2.n, 1), np.int32)
+        n = L.ref_m_search_by_bow_kf_f(f1.keyframe(), f1._f, f2._f, ratio, int(check_ori), m.ctypes.data)
+        return n, m[:f2.n]
+    m = np.zeros(max(f1.n, 1), np.int32)
+    n = L.ref_m_search_by_bow_kf_kf(f1.keyframe(), f2.keyframe(), f2._f, f1.n, ratio, int(check_ori), m.ctypes.data)
+    return n, m[:f1.n]

@@ -17,6 +17,7 @@ border_fn border = nullptr;
 blur_fn blur = nullptr;
 fast_fn fast = nullptr;
 atan2_fn atan2f32 = nullptr;
+undistort_fn undistort = nullptr;
 int retain_mode = 0;
 }  // namespace ref_cv
 
@@ -27,6 +28,8 @@ void ref_orb_set_bridge(ref_cv::resize_fn r, ref_cv::border_fn b, ref_cv::blur_f
   ref_cv::resize = r; ref_cv::border = b; ref_cv::blur = g; ref_cv::fast = f; ref_cv::atan2f32 = a;
   ref_cv::retain_mode = retain_mode;
 }
+
+void ref_orb_set_undistort(ref_cv::undistort_fn u) { ref_cv::undistort = u; }
 
 void* ref_orb_create(int nfeatures, float scaleFactor, int nlevels, int scoreType, int fastTh) {
   return new ORB_SLAM::ORBextractor(nfeatures, scaleFactor, nlevels, scoreType, fastTh);

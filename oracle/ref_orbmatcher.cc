@@ -1,0 +1,260 @@
+// ORACLE / test infrastructure: C wrapper around the UNMODIFIED reference front-end — src/ORBmatcher.cc, src/Frame.cc,
+// src/KeyFrame.cc, src/MapPoint.cc, src/Map.cc, src/KeyFrameDatabase.cc, src/ORBextractor.cc and the vendored DBoW2 are
+// compiled from /root/reference where they lie (oracle/Makefile target `ref` -> oracle/_ref/libref_orbslam.so) against
+// the type-only stand-ins in oracle/ref_shim_cv/ (OpenCV types, boost::mutex, ros macros, a Converter.h that drops
+// Eigen/g2o).  The OpenCV ROUTINES on the path (resize, copyMakeBorder, GaussianBlur, FAST, fastAtan2,
+// undistortPoints) are served by the installed cv2 through oracle/ref_extractor.py.
+//
+// Objects are built by the reference's own constructors: Frame(im, t, extractor, voc, K, distCoef) extracts,
+// undistorts, computes the image bounds and bins the grid (src/Frame.cc:59-127); KeyFrame(F, map, db) copies it
+// (src/KeyFrame.cc:30-52); MapPoint(pos, refKF, map).  "valid" flags of the flat-array world become real MapPoint
+// objects hung on mvpMapPoints.  Results come back as indices.
+//
+// Pins oracle/match_oracle.cc (M2-M5), oracle/frame_oracle.cc (N1) and oracle/bow_oracle.cc (N2 inside Frame::ComputeBoW)
+// — tests/test_ref_matcher.py — and generates tests/golden/ref_match.npz.
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <new>
+#include <set>
+#include <string>
+#include <vector>
+
+#include <opencv/cv.h>
+
+#include "Frame.h"
+#include "KeyFrame.h"
+#include "KeyFrameDatabase.h"
+#include "Map.h"
+#include "MapPoint.h"
+#include "ORBVocabulary.h"
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+#include "Converter.h"
+
+using namespace ORB_SLAM;
+
+// the one Converter function the compiled sources call (src/Converter.cc:27-36: one row per descriptor)
+std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors) {
+  std::vector<cv::Mat> vDesc;
+  vDesc.reserve(Descriptors.rows);
+  for (int j = 0; j < Descriptors.rows; j++) vDesc.push_back(Descriptors.row(j));
+  return vDesc;
+}
+
+namespace {
+
+struct World {                       // what owns the object graph of one test scene
+  ORBVocabulary* voc = nullptr;
+  Map map;
+  KeyFrameDatabase* db = nullptr;
+  std::vector<MapPoint*> points;
+  std::vector<KeyFrame*> keyframes;
+  KeyFrame* anchor = nullptr;        // MapPoint's constructor wants a reference keyframe
+  float inv_w = 0.f, inv_h = 0.f;    // grid element sizes of the first frame (see ref_m_frame_create)
+};
+
+struct FrameBox {
+  World* w;
+  Frame* f;
+  std::map<MapPoint*, int> index;    // MapPoint -> keypoint index in this frame
+};
+
+cv::Mat mat_from(const float* v, int r, int c) {
+  cv::Mat m(r, c, CV_32F);
+  for (int i = 0; i < r; i++) for (int j = 0; j < c; j++) m.at<float>(i, j) = v[i * c + j];
+  return m;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* ref_m_world_create(const char* voc_path) {
+  World* w = new World();
+  w->voc = new ORBVocabulary();
+  if (voc_path && *voc_path && !w->voc->loadFromTextFile(voc_path)) { delete w->voc; delete w; return nullptr; }
+  w->db = new KeyFrameDatabase(*w->voc);
+  return w;
+}
+
+// Frame::Frame(im, timeStamp, extractor, voc, K, distCoef).  reset_static: the image bounds / grid element sizes are
+// statics computed for the first frame only (mbInitialComputations, src/Frame.cc:74-87)
+void* ref_m_frame_create(void* world, void* extractor, const uint8_t* img, int width, int height, const float* K9,
+                         const float* D5, int reset_static) {
+  World* w = static_cast<World*>(world);
+  cv::Mat im(height, width, CV_8UC1);
+  for (int y = 0; y < height; y++) memcpy(im.ptr(y), img + (size_t)y * width, width);
+  cv::Mat K = mat_from(K9, 3, 3), D = mat_from(D5, 5, 1);
+  if (reset_static) Frame::mbInitialComputations = true;
+  FrameBox* b = new FrameBox();
+  b->w = w;
+  // The reference's constructor sets mfGridElementWidthInv / HeightInv (plain float members) only while
+  // mbInitialComputations is true, i.e. for the FIRST frame (src/Frame.cc:72-87); later frames leave them
+  // uninitialised and read whatever the storage held.  In the running system every Frame is a temporary built in the
+  // same stack slot and then copied (src/Tracking.cc: mCurrentFrame = Frame(...)), so the first frame's values
+  // survive.  Same here: later frames are constructed in storage pre-loaded with those two values.
+  void* mem = ::operator new(sizeof(Frame));
+  memset(mem, 0, sizeof(Frame));
+  if (!Frame::mbInitialComputations) {
+    Frame* shell = static_cast<Frame*>(mem);
+    memcpy(reinterpret_cast<char*>(&shell->mfGridElementWidthInv), &w->inv_w, 4);
+    memcpy(reinterpret_cast<char*>(&shell->mfGridElementHeightInv), &w->inv_h, 4);
+  }
+  b->f = new (mem) Frame(im, 0.0, static_cast<ORBextractor*>(extractor), w->voc, K, D);
+  if (reset_static) { w->inv_w = b->f->mfGridElementWidthInv; w->inv_h = b->f->mfGridElementHeightInv; }
+  b->f->mTcw = cv::Mat::eye(4, 4, CV_32F);
+  return b;
+}
+
+int ref_m_frame_n(void* fb) { return static_cast<FrameBox*>(fb)->f->N; }
+
+void ref_m_frame_bounds(void* fb, int32_t bounds[4], float inv[2]) {
+  Frame* f = static_cast<FrameBox*>(fb)->f;
+  bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMaxX; bounds[2] = Frame::mnMinY; bounds[3] = Frame::mnMaxY;
+  inv[0] = f->mfGridElementWidthInv; inv[1] = f->mfGridElementHeightInv;
+}
+
+// mvKeys (28-byte records), undistorted positions, descriptors
+void ref_m_frame_read(void* fb, void* kps, float* xu, float* yu, uint8_t* desc) {
+  Frame* f = static_cast<FrameBox*>(fb)->f;
+  static_assert(sizeof(cv::KeyPoint) == 28, "cv::KeyPoint layout");
+  if (f->N) memcpy(kps, f->mvKeys.data(), (size_t)f->N * 28);
+  for (int i = 0; i < f->N; i++) {
+    xu[i] = f->mvKeysUn[i].pt.x; yu[i] = f->mvKeysUn[i].pt.y;
+    memcpy(desc + (size_t)i * 32, f->mDescriptors.ptr(i), 32);
+  }
+}
+
+// the grid as CSR in visiting order (ix outer, iy inner), as orbm_frameset_grid returns it
+void ref_m_frame_grid(void* fb, int32_t* cell_start, int32_t* items) {
+  Frame* f = static_cast<FrameBox*>(fb)->f;
+  int k = 0;
+  for (int ix = 0; ix < FRAME_GRID_COLS; ix++)
+    for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) {
+      cell_start[ix * FRAME_GRID_ROWS + iy] = k;
+      for (size_t v : f->mGrid[ix][iy]) items[k++] = (int32_t)v;
+    }
+  cell_start[FRAME_GRID_COLS * FRAME_GRID_ROWS] = k;
+}
+
+int ref_m_features_in_area(void* fb, float x, float y, float r, int minl, int maxl, int32_t* out) {
+  std::vector<size_t> v = static_cast<FrameBox*>(fb)->f->GetFeaturesInArea(x, y, r, minl, maxl);
+  for (size_t i = 0; i < v.size(); i++) out[i] = (int32_t)v[i];
+  return (int)v.size();
+}
+
+// ORBmatcher(nnratio, checkOri).SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+int ref_m_search_for_initialization(void* fb1, void* fb2, float* prev_xy, int32_t* matches12, int window, float ratio,
+                                    int check_ori) {
+  Frame* f1 = static_cast<FrameBox*>(fb1)->f;
+  Frame* f2 = static_cast<FrameBox*>(fb2)->f;
+  std::vector<cv::Point2f> prev(f1->N);
+  for (int i = 0; i < f1->N; i++) prev[i] = cv::Point2f(prev_xy[2 * i], prev_xy[2 * i + 1]);
+  std::vector<int> m12;
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchForInitialization(*f1, *f2, prev, m12, window);
+  for (int i = 0; i < f1->N; i++) { matches12[i] = m12[i]; prev_xy[2 * i] = prev[i].x; prev_xy[2 * i + 1] = prev[i].y; }
+  return n;
+}
+
+// valid[i] != 0 -> keypoint i carries a (good) MapPoint; valid[i] == 2 -> a MapPoint whose isBad() is true
+void ref_m_frame_set_valid(void* fb, const uint8_t* valid) {
+  FrameBox* b = static_cast<FrameBox*>(fb);
+  World* w = b->w;
+  if (!w->anchor) {
+    w->anchor = new KeyFrame(*b->f, &w->map, w->db);
+    w->keyframes.push_back(w->anchor);
+  }
+  b->index.clear();
+  for (int i = 0; i < b->f->N; i++) {
+    b->f->mvpMapPoints[i] = nullptr;
+    if (!valid[i]) continue;
+    MapPoint* p = new MapPoint(cv::Mat::zeros(3, 1, CV_32F), w->anchor, &w->map);
+    if (valid[i] == 2) p->SetBadFlag();
+    w->points.push_back(p);
+    b->f->mvpMapPoints[i] = p;
+    b->index[p] = i;
+  }
+}
+
+// WindowSearch(F1, F2, windowSize, vpMapPointMatches2, minScaleLevel, maxScaleLevel): matches21[i2] = i1 or -1
+int ref_m_window_search(void* fb1, void* fb2, int window, int minl, int maxl, float ratio, int check_ori,
+                        int32_t* matches21) {
+  FrameBox* b1 = static_cast<FrameBox*>(fb1);
+  FrameBox* b2 = static_cast<FrameBox*>(fb2);
+  std::vector<MapPoint*> out;
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.WindowSearch(*b1->f, *b2->f, window, out, minl, maxl);
+  for (int i = 0; i < b2->f->N; i++) matches21[i] = out[i] ? b1->index.at(out[i]) : -1;
+  return n;
+}
+
+// Frame::ComputeBoW (src/Frame.cc:279-286) and its results in std::map order
+void ref_m_frame_compute_bow(void* fb) { static_cast<FrameBox*>(fb)->f->ComputeBoW(); }
+
+void ref_m_frame_bow(void* fb, int32_t* word, double* weight, int32_t* n_words, int32_t* node, int32_t* start,
+                     int32_t* items, int32_t* n_nodes) {
+  Frame* f = static_cast<FrameBox*>(fb)->f;
+  int i = 0;
+  for (DBoW2::BowVector::const_iterator it = f->mBowVec.begin(); it != f->mBowVec.end(); ++it, ++i) {
+    word[i] = (int32_t)it->first; weight[i] = it->second;
+  }
+  *n_words = i;
+  int k = 0, pos = 0;
+  for (DBoW2::FeatureVector::const_iterator it = f->mFeatVec.begin(); it != f->mFeatVec.end(); ++it, ++k) {
+    node[k] = (int32_t)it->first; start[k] = pos;
+    for (size_t j = 0; j < it->second.size(); j++) items[pos++] = (int32_t)it->second[j];
+  }
+  start[k] = pos;
+  *n_nodes = k;
+}
+
+// KeyFrame(F, map, db): takes the frame's keypoints, descriptors, MapPoints, BoW vectors and grid
+void* ref_m_keyframe_create(void* fb) {
+  FrameBox* b = static_cast<FrameBox*>(fb);
+  KeyFrame* kf = new KeyFrame(*b->f, &b->w->map, b->w->db);
+  b->w->keyframes.push_back(kf);
+  return kf;
+}
+
+// SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches): matchesF[iF] = keypoint index in the keyframe, or -1.
+// kf_box = the frame the keyframe was made from (for the MapPoint -> index map)
+int ref_m_search_by_bow_kf_f(void* kf, void* kf_box, void* fb, float ratio, int check_ori, int32_t* matchesF) {
+  FrameBox* bk = static_cast<FrameBox*>(kf_box);
+  FrameBox* bf = static_cast<FrameBox*>(fb);
+  std::vector<MapPoint*> out;
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchByBoW(static_cast<KeyFrame*>(kf), *bf->f, out);
+  for (int i = 0; i < bf->f->N; i++) matchesF[i] = out[i] ? bk->index.at(out[i]) : -1;
+  return n;
+}
+
+// SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12): matches12[i1] = keypoint index in keyframe 2, or -1
+int ref_m_search_by_bow_kf_kf(void* kf1, void* kf2, void* kf2_box, int n1, float ratio, int check_ori,
+                              int32_t* matches12) {
+  FrameBox* b2 = static_cast<FrameBox*>(kf2_box);
+  std::vector<MapPoint*> out;
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchByBoW(static_cast<KeyFrame*>(kf1), static_cast<KeyFrame*>(kf2), out);
+  for (int i = 0; i < n1; i++) matches12[i] = out[i] ? b2->index.at(out[i]) : -1;
+  return n;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a MapPoint observed at keypoint idx[k] of
+// keyframe kfs[k].  The reference walks its std::map<KeyFrame*, size_t> in POINTER order; `order` reports that order
+// (positions into kfs/idx) so the caller can hand the oracle the descriptors in the same sequence.  out32 = mDescriptor.
+void ref_m_distinctive_desc(void* world, void** kfs, const int32_t* idx, int nobs, uint8_t* out32, int32_t* order) {
+  World* w = static_cast<World*>(world);
+  MapPoint* p = new MapPoint(cv::Mat::zeros(3, 1, CV_32F), static_cast<KeyFrame*>(kfs[0]), &w->map);
+  w->points.push_back(p);
+  std::map<KeyFrame*, size_t> obs;
+  for (int k = 0; k < nobs; k++) { p->AddObservation(static_cast<KeyFrame*>(kfs[k]), idx[k]); obs[static_cast<KeyFrame*>(kfs[k])] = k; }
+  int pos = 0;
+  for (std::map<KeyFrame*, size_t>::iterator it = obs.begin(); it != obs.end(); ++it) order[pos++] = (int32_t)it->second;
+  p->ComputeDistinctiveDescriptors();
+  cv::Mat d = p->GetDescriptor();
+  memcpy(out32, d.ptr(0), 32);
+}
+
+}  // extern "C"

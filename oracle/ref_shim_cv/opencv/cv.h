@@ -21,10 +21,18 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <limits.h>
+
 #include <algorithm>
 #include <cmath>
+#include <fstream>
 #include <iostream>
+#include <list>
+#include <map>
 #include <memory>
+#include <set>
+#include <sstream>
+#include <string>
 #include <vector>
 
 typedef unsigned char uchar;
@@ -44,7 +52,9 @@ typedef void (*border_fn)(const uchar* src, int w, int h, long sstep, uchar* dst
                           int left, int right, int border_type);
 typedef void (*blur_fn)(uchar* img, int w, int h, long step, int ksize, double sigma, int border_type);
 typedef int (*fast_fn)(const uchar* img, int w, int h, long step, int threshold, int nonmax, float* xyr, int cap);
+typedef void (*undistort_fn)(float* xy, int n, const float* K9, const float* D, int nd);
 typedef float (*atan2_fn)(float y, float x);
+extern undistort_fn undistort;
 extern resize_fn resize;
 extern border_fn border;
 extern blur_fn blur;
@@ -135,6 +145,28 @@ class Mat {
   template <class T> const T* ptr(int r = 0) const { return reinterpret_cast<const T*>(data + (size_t)r * step); }
   template <class T> T& at(int r, int c) { return reinterpret_cast<T*>(data + (size_t)r * step)[c]; }
   template <class T> const T& at(int r, int c) const { return reinterpret_cast<const T*>(data + (size_t)r * step)[c]; }
+  // single-index access of a row or column vector (cv::Mat::at(int i0))
+  template <class T> T& at(int i) {
+    if (rows == 1) return reinterpret_cast<T*>(data)[i];
+    if (cols == 1) return *reinterpret_cast<T*>(data + (size_t)i * step);
+    return at<T>(i / cols, i % cols);
+  }
+  template <class T> const T& at(int i) const { return const_cast<Mat*>(this)->at<T>(i); }
+  Mat row(int r) const { return Mat(*this, Rect(0, r, cols, 1)); }
+  Mat col(int c) const { return Mat(*this, Rect(c, 0, 1, rows)); }
+  Mat reshape(int) const { return *this; }   // channels are not modelled: an N x 2 float matrix stays N x 2
+  void copyTo(Mat&& dst) const { Mat d = dst; copyTo(d); }   // into a temporary VIEW: create() keeps its buffer
+  void copyTo(Mat& dst) const {
+    if (empty()) { dst.release(); return; }
+    dst.create(rows, cols, type_);
+    for (int r = 0; r < rows; r++) memcpy(dst.data + (size_t)r * dst.step, data + (size_t)r * step, (size_t)cols * elemSize1());
+  }
+  Mat(const ZerosExpr& e) : Mat() { *this = e; }
+  // ---- small float matrix algebra (poses, normals).  Plain loops: NOT a model of cv::gemm; nothing that is pinned
+  // against this build goes through it (the searches read keypoints, descriptors, grids and flags only) ----------
+  static Mat eye(int r, int c, int t) { Mat m = ZerosExpr{r, c, t}; for (int i = 0; i < std::min(r, c); i++) m.at<float>(i, i) = 1.f; return m; }
+  Mat t() const { Mat m(cols, rows, type_); for (int r = 0; r < rows; r++) for (int c = 0; c < cols; c++) m.at<float>(c, r) = at<float>(r, c); return m; }
+  double dot(const Mat& o) const { double s = 0; for (int r = 0; r < rows; r++) for (int c = 0; c < cols; c++) s += (double)at<float>(r, c) * o.at<float>(r, c); return s; }
   static ZerosExpr zeros(int r, int c, int t) { return ZerosExpr{r, c, t}; }
   // MatExpr assignment (MatOp_Initializer::assign): create() on the destination, then fill -> writes through a view
   Mat& operator=(const ZerosExpr& e) {
@@ -151,6 +183,46 @@ class Mat {
   int type_;
   std::shared_ptr<std::vector<uchar>> buf_;
 };
+
+inline Mat operator*(const Mat& a, const Mat& b) {
+  Mat m(a.rows, b.cols, CV_32F);
+  for (int r = 0; r < a.rows; r++) for (int c = 0; c < b.cols; c++) { float s = 0; for (int k = 0; k < a.cols; k++) s += a.at<float>(r, k) * b.at<float>(k, c); m.at<float>(r, c) = s; }
+  return m;
+}
+template <class F> inline Mat mat_zip(const Mat& a, const Mat& b, F f) {
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int r = 0; r < a.rows; r++) for (int c = 0; c < a.cols; c++) m.at<float>(r, c) = f(a.at<float>(r, c), b.at<float>(r, c));
+  return m;
+}
+inline Mat operator+(const Mat& a, const Mat& b) { return mat_zip(a, b, [](float x, float y) { return x + y; }); }
+inline Mat operator-(const Mat& a, const Mat& b) { return mat_zip(a, b, [](float x, float y) { return x - y; }); }
+inline Mat operator-(const Mat& a) { return mat_zip(a, a, [](float x, float) { return -x; }); }
+inline Mat operator*(double s, const Mat& a) { return mat_zip(a, a, [s](float x, float) { return (float)(x * s); }); }
+inline Mat operator*(const Mat& a, double s) { return s * a; }
+inline Mat operator/(const Mat& a, double s) { return mat_zip(a, a, [s](float x, float) { return (float)(x / s); }); }
+inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
+
+// inert: the YAML members of DBoW2::TemplatedVocabulary are virtual and get instantiated, never called
+class FileNode {
+ public:
+  size_t size() const { return 0; }
+  FileNode operator[](int) const { return FileNode(); }
+  FileNode operator[](const char*) const { return FileNode(); }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+  operator int() const { return 0; }
+  operator float() const { return 0.f; }
+  operator double() const { return 0.0; }
+  operator std::string() const { return std::string(); }
+};
+class FileStorage {
+ public:
+  enum { READ = 0, WRITE = 1 };
+  FileStorage(const std::string&, int) {}
+  bool isOpened() const { return false; }
+  FileNode operator[](const char*) const { return FileNode(); }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+};
+template <class T> inline FileStorage& operator<<(FileStorage& fs, const T&) { return fs; }
 
 typedef const Mat& InputArray;
 typedef Mat& OutputArray;
@@ -185,6 +257,18 @@ inline void FAST(const Mat& image, std::vector<KeyPoint>& keypoints, int thresho
                              xyr.data(), cap);
   keypoints.clear();
   for (int i = 0; i < n; i++) keypoints.push_back(KeyPoint(xyr[3 * i], xyr[3 * i + 1], 7.f, -1, xyr[3 * i + 2]));
+}
+
+// cv::undistortPoints(src, dst, K, D, R = Mat(), P): N x 2 float points, forwarded to the real OpenCV.  P must be K and
+// R empty (the only call the reference makes, src/Frame.cc:306 and :333).
+inline void undistortPoints(const Mat& src, Mat& dst, const Mat& K, const Mat& D, const Mat& R, const Mat& P) {
+  assert(src.data == dst.data && R.empty() && P.data == K.data && src.cols == 2);
+  std::vector<float> xy((size_t)src.rows * 2), k(9), d;
+  for (int i = 0; i < src.rows; i++) { xy[2 * i] = src.at<float>(i, 0); xy[2 * i + 1] = src.at<float>(i, 1); }
+  for (int i = 0; i < 9; i++) k[i] = K.at<float>(i / 3, i % 3);
+  for (int i = 0; i < D.rows * D.cols; i++) d.push_back(D.at<float>(i));
+  ref_cv::undistort(xy.data(), src.rows, k.data(), d.data(), (int)d.size());
+  for (int i = 0; i < src.rows; i++) { dst.at<float>(i, 0) = xy[2 * i]; dst.at<float>(i, 1) = xy[2 * i + 1]; }
 }
 
 struct KeypointResponseGreaterThanThreshold {

@@ -240,3 +240,39 @@ def test_distinctive_descriptors(M, matcher):
     assert list(b2) == [0] * 5
     b3, o3 = matcher.distinctive_descriptors(np.zeros((0, 32), np.uint8), [0, 0, 0])
     assert list(b3) == [-1, -1]
+
+
+def test_cuda_equals_reference_generated_golden(matcher):
+    """The CUDA matcher against vectors produced by the reference's OWN Frame / KeyFrame / MapPoint / ORBmatcher code
+    (tests/golden/make_ref_match_golden.py): grid, GetFeaturesInArea, SearchForInitialization incl. the updated
+    vbPrevMatched, WindowSearch, SearchByBoW (both overloads)."""
+    import refgolden as RG
+    from orb_slam_b200 import ORBmatcher
+    g = RG.load()
+    for s in range(int(g["nscenes"])):
+        fr = [RG.frame(g, s, 0), RG.frame(g, s, 1)]
+        fs = matcher.upload(fr)
+        for f in (0, 1):
+            p = f"s{s}_f{f}_"
+            cs, it = fs.grid(f)
+            assert np.array_equal(cs, g[p + "cell_start"]) and np.array_equal(it, g[p + "grid_items"])
+            st = g[p + "area_start"]
+            for k, ((x, y, r), (l0, l1)) in enumerate(zip(g[p + "area_q"], g[p + "area_lv"])):
+                got = fs.features_in_area(f, float(x), float(y), float(r), int(l0), int(l1))
+                assert np.array_equal(got, g[p + "area_items"][st[k]:st[k + 1]]), (s, f, k)
+        prev0 = np.stack([fr[0].x, fr[0].y], 1)
+        for k, (win, ratio, ori) in enumerate(RG.SFI):
+            om = ORBmatcher(ratio, bool(ori), matcher=matcher)
+            prev = [prev0.copy()]
+            nm, rows = om.SearchForInitialization(fs, fs, [0], [1], prev, win)
+            ref = g[f"s{s}_sfi{k}_m"]
+            assert nm[0] == int(g[f"s{s}_sfi{k}_n"]) and _rows_equal(rows[0], ref)
+            assert np.array_equal(prev[0], g[f"s{s}_sfi{k}_prev"])
+        for k, (win, l0, l1, ratio, ori) in enumerate(RG.WIN):
+            om = ORBmatcher(ratio, bool(ori), matcher=matcher)
+            nm, rows = om.WindowSearch(fs, fs, [0], [1], win, l0, l1)
+            assert nm[0] == int(g[f"s{s}_win{k}_n"]) and _rows_equal(rows[0], g[f"s{s}_win{k}_m"])
+        for k, (variant, ratio, ori) in enumerate(RG.BOW):
+            om = ORBmatcher(ratio, bool(ori), matcher=matcher)
+            nm, rows = om.SearchByBoW(fs, fs, [0], [1], variant)
+            assert nm[0] == int(g[f"s{s}_bow{k}_n"]) and _rows_equal(rows[0], g[f"s{s}_bow{k}_m"])

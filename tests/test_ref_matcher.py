@@ -1,0 +1,126 @@
+"""Matcher + Frame glue pins against the REFERENCE'S OWN CODE (Frame / KeyFrame / MapPoint / ORBmatcher /
+ORBVocabulary compiled in place, oracle/ref_orbmatcher.cc; OpenCV routines from cv2).
+ * golden (runs anywhere): oracle/match_oracle.cc reproduces tests/golden/ref_match.npz — grid CSR, GetFeaturesInArea,
+   SearchForInitialization (matches and the updated vbPrevMatched), WindowSearch, SearchByBoW (KeyFrame-Frame and
+   KeyFrame-KeyFrame).
+ * live (authoring container): the whole chain image -> Frame (extract, undistort, bounds, grid) -> ComputeBoW ->
+   searches, oracle against the compiled reference, plus MapPoint::ComputeDistinctiveDescriptors."""
+import numpy as np
+import pytest
+
+import refgolden as RG
+import refscene as RS
+
+
+@pytest.fixture(scope="module")
+def M(oracle):
+    from oracle import match_oracle
+    match_oracle.lib()
+    return match_oracle
+
+
+def test_oracle_reproduces_reference_golden(M):
+    g = RG.load()
+    for s in range(int(g["nscenes"])):
+        fr = [RG.frame(g, s, 0), RG.frame(g, s, 1)]
+        for f in (0, 1):
+            p = f"s{s}_f{f}_"
+            cs, it = M.grid_csr(fr[f])
+            assert np.array_equal(cs, g[p + "cell_start"]) and np.array_equal(it, g[p + "grid_items"])
+            st = g[p + "area_start"]
+            for k, ((x, y, r), (l0, l1)) in enumerate(zip(g[p + "area_q"], g[p + "area_lv"])):
+                got = M.features_in_area(fr[f], float(x), float(y), float(r), int(l0), int(l1))
+                assert np.array_equal(got, g[p + "area_items"][st[k]:st[k + 1]]), (s, f, k)
+        prev0 = np.stack([fr[0].x, fr[0].y], 1)
+        for k, (win, ratio, ori) in enumerate(RG.SFI):
+            prev = prev0.copy()
+            n, m = M.search_for_initialization(fr[0], fr[1], prev, win, ratio, bool(ori))
+            assert n == int(g[f"s{s}_sfi{k}_n"]) and np.array_equal(m, g[f"s{s}_sfi{k}_m"])
+            assert np.array_equal(prev, g[f"s{s}_sfi{k}_prev"])
+        for k, (win, l0, l1, ratio, ori) in enumerate(RG.WIN):
+            n, m = M.window_search(fr[0], fr[1], win, ratio, bool(ori), l0, l1)
+            assert n == int(g[f"s{s}_win{k}_n"]) and np.array_equal(m, g[f"s{s}_win{k}_m"])
+        for k, (variant, ratio, ori) in enumerate(RG.BOW):
+            n, m = M.search_by_bow(fr[0], fr[1], variant, ratio, bool(ori))
+            assert n == int(g[f"s{s}_bow{k}_n"]) and np.array_equal(m, g[f"s{s}_bow{k}_m"])
+            assert n > 50
+
+
+def _rf():
+    from oracle import ref_frontend as RF
+    if not RF.available():
+        pytest.skip("compiled reference front-end / cv2 not available here")
+    return RF
+
+
+@pytest.mark.parametrize("seed,cam,nfeat", [(21, RS.CAM_SHIPPED, 500), (22, RS.CAM_PINHOLE, 300)])
+def test_chain_equals_compiled_reference(oracle, M, tmp_path, seed, cam, nfeat):
+    RF = _rf()
+    from oracle import bow_oracle as B
+    from oracle import frame_oracle as FO
+    V = B.synth_vocabulary(k=3, L=5, seed=seed, stop_frac=0.02)
+    vpath = str(tmp_path / "voc.txt")
+    B.save_text(vpath, **V)
+    ovoc = B.Vocabulary.load_text(vpath)
+    w = RF.World(vpath, nfeat, 1.2, 6, 1, 20)
+    ims = RS.images(oracle, seed)
+    E = oracle.OracleExtractor(nfeat, 1.2, 6, 1, 20, blur_mode=1, retain_mode=1)
+    ocam = FO.Camera(*cam)
+    ob, oinv = FO.image_bounds(ocam, 320, 240)
+    rfs = [w.frame(ims[0], RS.K_of(cam), cam[4:9], reset_static=True), w.frame(ims[1], RS.K_of(cam), cam[4:9])]
+    assert rfs[0].bounds == ob and rfs[0].inv == oinv                      # ComputeImageBounds, grid element sizes
+    ofr = []
+    for f, rf in enumerate(rfs):
+        k, d = E(ims[f])                                                    # extraction
+        assert np.array_equal(k, rf.kps) and np.array_equal(d, rf.desc)
+        un = FO.undistort_points(ocam, np.stack([k["x"], k["y"]], 1)) if cam[4] != 0 else np.stack([k["x"], k["y"]], 1)
+        assert np.array_equal(un[:, 0], rf.xu) and np.array_equal(un[:, 1], rf.yu)   # UndistortKeyPoints
+        valid = RS.valid_flags(rf.n, seed + f)
+        rf.set_valid(valid)
+        (rw, rv), rfv = rf.compute_bow()                                    # Frame::ComputeBoW
+        (ow, ov), ofv = ovoc.transform(d, 4)
+        assert np.array_equal(rw, ow) and np.array_equal(rv.view(np.int64), ov.view(np.int64))
+        assert all(np.array_equal(a, b) for a, b in zip(rfv, ofv)) and len(ofv[0]) > 1
+        mf = RS.match_frame(rf, valid, ofv)
+        ofr.append(mf)
+        cs, it = rf.grid()
+        ocs, oit = M.grid_csr(mf)
+        assert np.array_equal(cs, ocs) and np.array_equal(it, oit)          # grid binning
+    prev0 = np.stack([ofr[0].x, ofr[0].y], 1)
+    for win, ratio, ori in ((100, 0.9, True), (30, 0.8, False)):
+        rn, rm, rp = RF.search_for_initialization(rfs[0], rfs[1], prev0, win, ratio, ori)
+        op = prev0.copy()
+        on, om = M.search_for_initialization(ofr[0], ofr[1], op, win, ratio, ori)
+        assert rn == on and np.array_equal(rm, om) and np.array_equal(rp, op) and on > 30
+    for win, l0, l1, ratio, ori in ((200, 0, 2**31 - 1, 0.8, True), (100, 1, 3, 0.8, False), (50, -1, 2**31 - 1, 0.9, True)):
+        rn, rm = RF.window_search(rfs[0], rfs[1], win, l0, l1, ratio, ori)
+        on, om = M.window_search(ofr[0], ofr[1], win, ratio, ori, l0, l1)
+        assert rn == on and np.array_equal(rm, om)
+    for variant in ("kf_f", "kf_kf"):
+        for ratio, ori in ((0.75, True), (0.6, False)):
+            rn, rm = RF.search_by_bow(rfs[0], rfs[1], variant, ratio, ori)
+            on, om = M.search_by_bow(ofr[0], ofr[1], variant, ratio, ori)
+            assert rn == on and np.array_equal(rm, om) and on > 30
+
+
+def test_distinctive_descriptors_equal_compiled_reference(oracle, M):
+    RF = _rf()
+    w = RF.World(None, 300, 1.2, 4, 1, 20)
+    cam = RS.CAM_PINHOLE
+    frames = []
+    for s in range(6):
+        im, _ = RS.images(oracle, 40 + s)
+        f = w.frame(im, RS.K_of(cam), cam[4:9], reset_static=(s == 0))
+        f.set_valid(np.zeros(f.n, np.uint8))
+        frames.append(f)
+    kfs = [f.keyframe() for f in frames]
+    rng = np.random.default_rng(2)
+    for nobs in (1, 2, 3, 5, 6):
+        for _ in range(6):
+            sel = rng.choice(6, nobs, replace=False)
+            idx = [int(rng.integers(0, frames[k].n)) for k in sel]
+            got, order = w.distinctive([kfs[k] for k in sel], idx)
+            # descriptors in the order the reference's std::map<KeyFrame*, size_t> visits the observations
+            desc = np.stack([frames[sel[o]].desc[idx[o]] for o in order])
+            best = M.distinctive_descriptors(desc, [0, nobs])[0]
+            assert np.array_equal(got, desc[best])
