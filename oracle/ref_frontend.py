@@ -47,6 +47,8 @@ def _lib():
         L.ref_m_search_by_bow_kf_f.argtypes = [_P, _P, _P, _F, _I, _P]
         L.ref_m_search_by_bow_kf_kf.argtypes = [_P, _P, _P, _I, _F, _I, _P]
         L.ref_m_distinctive_desc.argtypes = [_P, _P, _P, _I, _P, _P]
+        L.ref_m_search_by_projection_local.argtypes = [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P]
+        L.ref_m_search_by_projection_last.argtypes = [_P, _P, _P, _F, _F, _I, _P]
         L._m_ready = True
     return L
 
@@ -147,3 +149,25 @@ def search_by_bow(f1: RefFrame, f2: RefFrame, variant, ratio, check_ori):
     m = np.zeros(max(f1.n, 1), np.int32)
     n = L.ref_m_search_by_bow_kf_kf(f1.keyframe(), f2.keyframe(), f2._f, f1.n, ratio, int(check_ori), m.ctypes.data)
     return n, m[:f1.n]
+
+
+def search_by_projection_local(f: RefFrame, desc_frame: RefFrame, u, v, level, view_cos, in_view, bad, desc_idx, th,
+                               ratio):
+    """SearchByProjection(F, vpMapPoints, th): point k carries descriptor desc_idx[k] of desc_frame."""
+    g = lambda a, t: np.ascontiguousarray(a, t)
+    u, v, vc = g(u, np.float32), g(v, np.float32), g(view_cos, np.float32)
+    lv, di = g(level, np.int32), g(desc_idx, np.int32)
+    iv, bd = g(in_view, np.uint8), g(bad, np.uint8)
+    m = np.zeros(max(f.n, 1), np.int32)
+    n = _lib().ref_m_search_by_projection_local(f._f, desc_frame._f, len(u), u.ctypes.data, v.ctypes.data, lv.ctypes.data,
+                                                vc.ctypes.data, iv.ctypes.data, bd.ctypes.data, di.ctypes.data, th, ratio,
+                                                m.ctypes.data)
+    return n, m[:f.n]
+
+
+def search_by_projection_last(cur: RefFrame, last: RefFrame, pos, th, ratio, check_ori):
+    """SearchByProjection(CurrentFrame, LastFrame, th) with the current pose at identity; pos [last.n, 3]."""
+    pos = np.ascontiguousarray(pos, np.float32)
+    m = np.zeros(max(cur.n, 1), np.int32)
+    n = _lib().ref_m_search_by_projection_last(cur._f, last._f, pos.ctypes.data, th, ratio, int(check_ori), m.ctypes.data)
+    return n, m[:cur.n]

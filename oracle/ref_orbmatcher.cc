@@ -241,6 +241,69 @@ int ref_m_search_by_bow_kf_kf(void* kf1, void* kf2, void* kf2_box, int n1, float
   return n;
 }
 
+// SearchByProjection(Frame& F, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:49-125), the local-map tracking search.
+// Point k: a MapPoint whose descriptor is keypoint desc_idx[k] of the keyframe made from `desc_fb` (one observation ->
+// ComputeDistinctiveDescriptors picks it), with the tracking fields isInFrustum would have written.
+// matchesF[i] = index of the point newly hung on keypoint i of F, else -1.
+int ref_m_search_by_projection_local(void* fb, void* desc_fb, int npts, const float* u, const float* v,
+                                     const int32_t* level, const float* view_cos, const uint8_t* in_view,
+                                     const uint8_t* bad, const int32_t* desc_idx, float th, float ratio,
+                                     int32_t* matchesF) {
+  FrameBox* b = static_cast<FrameBox*>(fb);
+  FrameBox* bd = static_cast<FrameBox*>(desc_fb);
+  World* w = b->w;
+  KeyFrame* kf = new KeyFrame(*bd->f, &w->map, w->db);
+  w->keyframes.push_back(kf);
+  std::vector<MapPoint*> pts(npts);
+  std::map<MapPoint*, int> which;
+  for (int k = 0; k < npts; k++) {
+    MapPoint* p = new MapPoint(cv::Mat::zeros(3, 1, CV_32F), kf, &w->map);
+    w->points.push_back(p);
+    p->AddObservation(kf, desc_idx[k]);
+    p->ComputeDistinctiveDescriptors();
+    p->mbTrackInView = in_view[k] != 0;
+    p->mTrackProjX = u[k]; p->mTrackProjY = v[k];
+    p->mnTrackScaleLevel = level[k];
+    p->mTrackViewCos = view_cos[k];
+    if (bad[k]) p->SetBadFlag();
+    pts[k] = p;
+    which[p] = k;
+  }
+  ORBmatcher matcher(ratio, true);
+  const int n = matcher.SearchByProjection(*b->f, pts, th);
+  for (int i = 0; i < b->f->N; i++) {
+    MapPoint* p = b->f->mvpMapPoints[i];
+    std::map<MapPoint*, int>::iterator it = p ? which.find(p) : which.end();
+    matchesF[i] = it == which.end() ? -1 : it->second;
+  }
+  return n;
+}
+
+// SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th) (src/ORBmatcher.cc:1507-1622) with the current
+// pose left at identity, so that Rcw*x3Dw+tcw returns the world point unchanged (adding zeros is exact) and
+// u = fx*x/z + cx is the float expression of :1535-1538 only.  pos: last.N x 3 world positions for last's MapPoints.
+// matchesCur[i2] = index in the last frame, else -1 (only matches made by this call).
+int ref_m_search_by_projection_last(void* cur_fb, void* last_fb, const float* pos, float th, float ratio, int check_ori,
+                                    int32_t* matchesCur) {
+  FrameBox* bc = static_cast<FrameBox*>(cur_fb);
+  FrameBox* bl = static_cast<FrameBox*>(last_fb);
+  for (int i = 0; i < bl->f->N; i++) {
+    MapPoint* p = bl->f->mvpMapPoints[i];
+    if (!p) continue;
+    cv::Mat x(3, 1, CV_32F);
+    for (int k = 0; k < 3; k++) x.at<float>(k) = pos[3 * i + k];
+    p->SetWorldPos(x);
+  }
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchByProjection(*bc->f, *bl->f, th);
+  for (int i = 0; i < bc->f->N; i++) {
+    MapPoint* p = bc->f->mvpMapPoints[i];
+    std::map<MapPoint*, int>::iterator it = p ? bl->index.find(p) : bl->index.end();
+    matchesCur[i] = it == bl->index.end() ? -1 : it->second;
+  }
+  return n;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a MapPoint observed at keypoint idx[k] of
 // keyframe kfs[k].  The reference walks its std::map<KeyFrame*, size_t> in POINTER order; `order` reports that order
 // (positions into kfs/idx) so the caller can hand the oracle the descriptors in the same sequence.  out32 = mDescriptor.
