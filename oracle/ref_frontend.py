@@ -49,6 +49,7 @@ def _lib():
         L.ref_m_distinctive_desc.argtypes = [_P, _P, _P, _I, _P, _P]
         L.ref_m_search_by_projection_local.argtypes = [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P]
         L.ref_m_search_by_projection_last.argtypes = [_P, _P, _P, _F, _F, _I, _P]
+        L.ref_m_search_for_triangulation.argtypes = [_P, _P, _P, _I, _F, _I, _P]
         L._m_ready = True
     return L
 
@@ -171,3 +172,12 @@ def search_by_projection_last(cur: RefFrame, last: RefFrame, pos, th, ratio, che
     m = np.zeros(max(cur.n, 1), np.int32)
     n = _lib().ref_m_search_by_projection_last(cur._f, last._f, pos.ctypes.data, th, ratio, int(check_ori), m.ctypes.data)
     return n, m[:cur.n]
+
+
+def search_for_triangulation(f1: RefFrame, f2: RefFrame, F12, ratio, check_ori):
+    """SearchForTriangulation between the keyframes made from f1 and f2 (after set_valid / compute_bow)."""
+    F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    m = np.zeros(max(f1.n, 1), np.int32)
+    n = _lib().ref_m_search_for_triangulation(f1.keyframe(), f2.keyframe(), F.ctypes.data, f1.n, ratio, int(check_ori),
+                                              m.ctypes.data)
+    return n, m[:f1.n]

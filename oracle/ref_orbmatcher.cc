@@ -304,6 +304,20 @@ int ref_m_search_by_projection_last(void* cur_fb, void* last_fb, const float* po
   return n;
 }
 
+// SearchForTriangulation(pKF1, pKF2, F12, vMatchedKeys1, vMatchedKeys2, vMatchedPairs) (src/ORBmatcher.cc:852-1014):
+// match12[i1] = i2 from vMatchedPairs, else -1
+int ref_m_search_for_triangulation(void* kf1, void* kf2, const float* F12, int n1, float ratio, int check_ori,
+                                   int32_t* match12) {
+  cv::Mat F = mat_from(F12, 3, 3);
+  std::vector<cv::KeyPoint> k1, k2;
+  std::vector<std::pair<size_t, size_t> > pairs;
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchForTriangulation(static_cast<KeyFrame*>(kf1), static_cast<KeyFrame*>(kf2), F, k1, k2, pairs);
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  for (size_t k = 0; k < pairs.size(); k++) match12[pairs[k].first] = (int32_t)pairs[k].second;
+  return n;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a MapPoint observed at keypoint idx[k] of
 // keyframe kfs[k].  The reference walks its std::map<KeyFrame*, size_t> in POINTER order; `order` reports that order
 // (positions into kfs/idx) so the caller can hand the oracle the descriptors in the same sequence.  out32 = mDescriptor.

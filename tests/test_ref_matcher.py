@@ -178,3 +178,32 @@ def test_search_by_projection_equals_compiled_reference(oracle, M, seed, cam):
         tgt.valid = (v2 != 0).astype(np.uint8)
         on, om = M.search_by_projection(tgt, pts, "best", 100, ratio, ori)
         assert rn == on and np.array_equal(rm, om) and on > 40, (th, ratio, ori)
+
+
+@pytest.mark.parametrize("ori", [True, False])
+def test_search_for_triangulation_equals_compiled_reference(oracle, M, tmp_path, ori):
+    """M9: SearchForTriangulation (src/ORBmatcher.cc:852-1014, CheckDistEpipolarLine :136-153) between two real
+    KeyFrames (feature vectors from the reference's ComputeBoW, MapPoints on some keypoints)."""
+    RF = _rf()
+    from oracle import bow_oracle as B
+    V = B.synth_vocabulary(k=3, L=5, seed=5, stop_frac=0.0)
+    vpath = str(tmp_path / "voc.txt")
+    B.save_text(vpath, **V)
+    cam = RS.CAM_SHIPPED
+    w = RF.World(vpath, 500, 1.2, 6, 1, 20)
+    ims = RS.images(oracle, 51, shift=(9, -7))
+    rfs = [w.frame(ims[0], RS.K_of(cam), cam[4:9], reset_static=True), w.frame(ims[1], RS.K_of(cam), cam[4:9])]
+    ofr = []
+    for f, rf in enumerate(rfs):
+        valid = (np.random.default_rng(60 + f).random(rf.n) < 0.3).astype(np.uint8)   # keypoints that already have a MapPoint
+        rf.set_valid(valid)
+        _, fv = rf.compute_bow()
+        ofr.append(RS.match_frame(rf, valid, fv))
+    sf = np.cumprod(np.concatenate([[1.0], np.full(5, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    sigma2 = (sf * sf).astype(np.float32)                                     # mvLevelSigma2 (src/Frame.cc:99-103)
+    t = np.array([9.0, -7.0, 0.0]) + 1e-3
+    F12 = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]], np.float32) * np.float32(0.05)
+    for ratio in (0.6, 0.8):
+        rn, rm = RF.search_for_triangulation(rfs[0], rfs[1], F12, ratio, ori)
+        on, om = M.search_for_triangulation(ofr[0], ofr[1], F12, sigma2, ori)
+        assert rn == on and np.array_equal(rm, om) and on > 20, (ratio, ori)
