@@ -50,6 +50,10 @@ def _lib():
         L.ref_m_search_by_projection_local.argtypes = [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P]
         L.ref_m_search_by_projection_last.argtypes = [_P, _P, _P, _F, _F, _I, _P]
         L.ref_m_search_for_triangulation.argtypes = [_P, _P, _P, _I, _F, _I, _P]
+        L.ref_m_frame_set_point_geometry.argtypes = [_P, _P, _P, _P, _P]
+        L.ref_m_frame_points_take_descriptors.argtypes = [_P, _P]
+        L.ref_m_search_by_projection_reloc.argtypes = [_P, _P, _P, _P, _F, _I, _F, _I, _P]
+        L.ref_m_search_by_projection_sim3.argtypes = [_P, _P, _P, _P, _P, _I, _I, _F, _P]
         L._m_ready = True
     return L
 
@@ -127,6 +131,18 @@ class RefFrame:
             self._kf = self._L.ref_m_keyframe_create(self._f)
         return self._kf
 
+    def set_point_geometry(self, pos, min_dist, max_dist, normal=None):
+        """World position, scale-invariance distances and normal of the MapPoints set_valid created (per keypoint)."""
+        g = lambda a: np.ascontiguousarray(a, np.float32)
+        pos, mn, mx = g(pos), g(min_dist), g(max_dist)
+        nr = g(normal) if normal is not None else None
+        self._L.ref_m_frame_set_point_geometry(self._f, pos.ctypes.data, mn.ctypes.data, mx.ctypes.data,
+                                               nr.ctypes.data if nr is not None else None)
+
+    def points_take_descriptors(self):
+        """Each MapPoint of this frame observes its own keypoint in the frame's keyframe -> GetDescriptor() = that row."""
+        self._L.ref_m_frame_points_take_descriptors(self._f, self.keyframe())
+
 
 def search_for_initialization(f1: RefFrame, f2: RefFrame, prev_xy, window, ratio, check_ori):
     prev = np.ascontiguousarray(prev_xy, np.float32).copy()
@@ -181,3 +197,23 @@ def search_for_triangulation(f1: RefFrame, f2: RefFrame, F12, ratio, check_ori):
     n = _lib().ref_m_search_for_triangulation(f1.keyframe(), f2.keyframe(), F.ctypes.data, f1.n, ratio, int(check_ori),
                                               m.ctypes.data)
     return n, m[:f1.n]
+
+
+def search_by_projection_reloc(cur: RefFrame, kf_frame: RefFrame, already, th, orb_dist, ratio, check_ori):
+    """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), current pose = identity; pKF = the keyframe of
+    kf_frame (set_valid, set_point_geometry, points_take_descriptors done)."""
+    a = np.ascontiguousarray(already, np.uint8)
+    m = np.zeros(max(cur.n, 1), np.int32)
+    n = _lib().ref_m_search_by_projection_reloc(cur._f, kf_frame.keyframe(), kf_frame._f, a.ctypes.data, th, int(orb_dist),
+                                                ratio, int(check_ori), m.ctypes.data)
+    return n, m[:cur.n]
+
+
+def search_by_projection_sim3(kf_frame: RefFrame, src: RefFrame, sel, pre, th, ratio):
+    """SearchByProjection(pKF, Scw = identity, vpPoints, vpMatched, th): vpPoints = src's MapPoints sel[k];
+    pre[k] >= 0 pre-assigns point k to keyframe keypoint pre[k].  Returns (n, matched[idx] = k or -1)."""
+    sel = np.ascontiguousarray(sel, np.int32); pre = np.ascontiguousarray(pre, np.int32)
+    m = np.zeros(max(kf_frame.n, 1), np.int32)
+    n = _lib().ref_m_search_by_projection_sim3(kf_frame.keyframe(), kf_frame._f, src._f, sel.ctypes.data, pre.ctypes.data,
+                                               len(sel), int(th), ratio, m.ctypes.data)
+    return n, m[:kf_frame.n]

@@ -304,6 +304,84 @@ int ref_m_search_by_projection_last(void* cur_fb, void* last_fb, const float* po
   return n;
 }
 
+// Geometry state of the MapPoint on keypoint i of `fb` (protected members; this file is compiled with
+// -fno-access-control): world position, scale-invariance distances (what UpdateNormalAndDepth writes,
+// src/MapPoint.cc:265-312) and viewing normal.  pos / normal: n x 3; min_dist / max_dist: n.  Call BEFORE the frame is
+// turned into a KeyFrame or used as a point source.
+void ref_m_frame_set_point_geometry(void* fb, const float* pos, const float* min_dist, const float* max_dist,
+                                    const float* normal) {
+  FrameBox* b = static_cast<FrameBox*>(fb);
+  for (int i = 0; i < b->f->N; i++) {
+    MapPoint* p = b->f->mvpMapPoints[i];
+    if (!p) continue;
+    cv::Mat x(3, 1, CV_32F), nrm(3, 1, CV_32F);
+    for (int k = 0; k < 3; k++) { x.at<float>(k) = pos[3 * i + k]; nrm.at<float>(k) = normal ? normal[3 * i + k] : 0.f; }
+    p->SetWorldPos(x);
+    p->mNormalVector = nrm;
+    p->mfMinDistance = min_dist[i];
+    p->mfMaxDistance = max_dist[i];
+  }
+}
+
+// Gives the MapPoint on keypoint i of `fb` the descriptor of that keypoint (one observation in `kf`, the keyframe made
+// from fb -> ComputeDistinctiveDescriptors picks it, src/MapPoint.cc:185-250).
+void ref_m_frame_points_take_descriptors(void* fb, void* kf) {
+  FrameBox* b = static_cast<FrameBox*>(fb);
+  for (int i = 0; i < b->f->N; i++) {
+    MapPoint* p = b->f->mvpMapPoints[i];
+    if (!p) continue;
+    p->AddObservation(static_cast<KeyFrame*>(kf), i);
+    p->ComputeDistinctiveDescriptors();
+  }
+}
+
+// SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th, ORBdist)
+// (src/ORBmatcher.cc:1622-1746, relocalisation) with the current pose at identity: Rcw*x3Dw+tcw and x3Dw-Ow return the
+// world point unchanged, so the float projection (:1652-1653), the bounds tests, dist3D/minDistance -> lower_bound level
+// prediction (:1660-1667), the radius, the area query, the best-only scan and the rotation check are the reference's.
+// already[i] != 0 -> keyframe MapPoint i is in sAlreadyFound.  matchesCur[i2] = keyframe keypoint index, else -1.
+int ref_m_search_by_projection_reloc(void* cur_fb, void* kf, void* kf_box, const uint8_t* already, float th,
+                                     int orb_dist, float ratio, int check_ori, int32_t* matchesCur) {
+  FrameBox* bc = static_cast<FrameBox*>(cur_fb);
+  FrameBox* bk = static_cast<FrameBox*>(kf_box);
+  std::set<MapPoint*> found;
+  for (int i = 0; i < bk->f->N; i++)
+    if (already[i] && bk->f->mvpMapPoints[i]) found.insert(bk->f->mvpMapPoints[i]);
+  bc->f->mTcw = cv::Mat::eye(4, 4, CV_32F);
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchByProjection(*bc->f, static_cast<KeyFrame*>(kf), found, th, orb_dist);
+  for (int i = 0; i < bc->f->N; i++) {
+    MapPoint* p = bc->f->mvpMapPoints[i];
+    std::map<MapPoint*, int>::iterator it = p ? bk->index.find(p) : bk->index.end();
+    matchesCur[i] = it == bk->index.end() ? -1 : it->second;
+  }
+  return n;
+}
+
+// SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:286-407, loop closing)
+// with Scw = identity (scw = 1).  vpPoints = the MapPoints of src_fb's keypoints sel[0..npts) (in that order);
+// vpMatched starts as the MapPoints already on the keyframe's own frame kf_box (set_valid) plus, for pre[k] >= 0, point
+// sel[k] pre-assigned to keyframe keypoint pre[k] ("already found").  matched[idx] = position k in sel of the point
+// NEWLY matched to keyframe keypoint idx, else -1.
+int ref_m_search_by_projection_sim3(void* kf, void* kf_box, void* src_fb, const int32_t* sel, const int32_t* pre,
+                                    int npts, int th, float ratio, int32_t* matched) {
+  FrameBox* bk = static_cast<FrameBox*>(kf_box);
+  FrameBox* bs = static_cast<FrameBox*>(src_fb);
+  std::vector<MapPoint*> pts(npts), vm(bk->f->N);
+  std::map<MapPoint*, int> which;
+  for (int i = 0; i < bk->f->N; i++) vm[i] = bk->f->mvpMapPoints[i];
+  for (int k = 0; k < npts; k++) {
+    pts[k] = bs->f->mvpMapPoints[sel[k]];
+    which[pts[k]] = k;
+    if (pre[k] >= 0) vm[pre[k]] = pts[k];
+  }
+  std::vector<MapPoint*> before = vm;
+  ORBmatcher matcher(ratio, true);
+  const int n = matcher.SearchByProjection(static_cast<KeyFrame*>(kf), cv::Mat::eye(4, 4, CV_32F), pts, vm, th);
+  for (int i = 0; i < bk->f->N; i++) matched[i] = (vm[i] && vm[i] != before[i]) ? which.at(vm[i]) : -1;
+  return n;
+}
+
 // SearchForTriangulation(pKF1, pKF2, F12, vMatchedKeys1, vMatchedKeys2, vMatchedPairs) (src/ORBmatcher.cc:852-1014):
 // match12[i1] = i2 from vMatchedPairs, else -1
 int ref_m_search_for_triangulation(void* kf1, void* kf2, const float* F12, int n1, float ratio, int check_ori,

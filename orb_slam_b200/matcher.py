@@ -477,6 +477,32 @@ class ProjectedPoints:
         return cls(u, v, radius, octave - 1, octave + 1, desc, angle, valid)
 
 
+    @classmethod
+    def for_relocalisation(cls, u, v, level, desc, angle, scale_factors, th, valid=None):
+        """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1669-1672: radius =
+        th * mvScaleFactors[predicted level], levels [pred-1, pred+1]; use variant 'best' with th_dist = ORBdist."""
+        level = _i32(level)
+        radius = (np.float32(th) * np.asarray(scale_factors, np.float32)[level]).astype(np.float32)
+        return cls(u, v, radius, level - 1, level + 1, desc, angle, valid)
+
+    @classmethod
+    def for_sim3(cls, u, v, level, desc, scale_factors, th, valid=None):
+        """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th), src/ORBmatcher.cc:362-383: radius = th *
+        GetScaleFactor(pred) (th is an int there), candidates on levels [pred-1, pred], no orientation check; use
+        variant 'best' with th_dist = TH_LOW and checkOri off."""
+        level = _i32(level)
+        radius = (np.float32(int(th)) * np.asarray(scale_factors, np.float32)[level]).astype(np.float32)
+        return cls(u, v, radius, level - 1, level, desc, None, valid)
+
+
+def predict_scale_level(dist, min_distance, scale_factors):
+    """`ratio = dist / minDistance; lower_bound(mvScaleFactors, ratio)` clamped to nLevels-1, all in float
+    (src/ORBmatcher.cc:1660-1667, :355-360; src/Frame.cc:178-186)."""
+    sf = np.asarray(scale_factors, np.float32)
+    ratio = (np.asarray(dist, np.float32) / np.asarray(min_distance, np.float32)).astype(np.float32)
+    return np.minimum(np.searchsorted(sf, ratio, side="left"), len(sf) - 1).astype(np.int32)
+
+
 class ORBmatcher:
     """ORB_SLAM::ORBmatcher(nnratio = 0.6, checkOri = true), include/ORBmatcher.h:41.  Every Search* method takes
     frame sets and lists of frame pairs (batched); a single pair is a list of length one."""

@@ -276,3 +276,22 @@ def test_cuda_equals_reference_generated_golden(matcher):
             om = ORBmatcher(ratio, bool(ori), matcher=matcher)
             nm, rows = om.SearchByBoW(fs, fs, [0], [1], variant)
             assert nm[0] == int(g[f"s{s}_bow{k}_n"]) and _rows_equal(rows[0], g[f"s{s}_bow{k}_m"])
+
+
+def test_cuda_equals_reference_generated_projection_golden(matcher):
+    """The CUDA orbm_search_by_projection against vectors produced by the reference's OWN SearchByProjection overloads
+    (local map :49-125, last frame :1507-1620, relocalisation :1622-1746, Sim3 :286-407) run on its own Frame / KeyFrame /
+    MapPoint objects (tests/golden/make_ref_proj_golden.py), all cases of a scene in ONE batched call per variant."""
+    import refgolden as RG
+    from orb_slam_b200 import ORBmatcher
+    cases = list(RG.proj_cases())
+    assert len(cases) == 20
+    fs = matcher.upload([c["target"] for c in cases])
+    groups = {}
+    for i, c in enumerate(cases):
+        groups.setdefault((c["variant"], c["th_dist"], c["ratio"], c["ori"]), []).append(i)
+    for (variant, th_dist, ratio, ori), idx in groups.items():
+        om = ORBmatcher(ratio, ori, matcher=matcher)
+        nm, rows = om.SearchByProjection(fs, idx, [cases[i]["points"] for i in idx], variant, th_dist)
+        for k, i in enumerate(idx):
+            assert nm[k] == cases[i]["ref_n"] and _rows_equal(rows[k], cases[i]["ref_m"]), cases[i]["name"]

@@ -103,6 +103,17 @@ def test_chain_equals_compiled_reference(oracle, M, tmp_path, seed, cam, nfeat):
             assert rn == on and np.array_equal(rm, om) and on > 30
 
 
+def test_oracle_reproduces_reference_projection_golden(M):
+    """Runs anywhere: the oracle against tests/golden/ref_proj.npz — the reference's own SearchByProjection overloads
+    (local map, last frame, relocalisation, Sim3; tests/golden/make_ref_proj_golden.py)."""
+    names = set()
+    for c in RG.proj_cases():
+        on, om = M.search_by_projection(c["target"], c["points"], c["variant"], c["th_dist"], c["ratio"], c["ori"])
+        assert on == c["ref_n"] and np.array_equal(om, c["ref_m"]), c["name"]
+        names.add(c["name"].split(":")[1])
+    assert names == {"local_map", "last_frame", "reloc", "sim3"}
+
+
 def test_distinctive_descriptors_equal_compiled_reference(oracle, M):
     RF = _rf()
     w = RF.World(None, 300, 1.2, 4, 1, 20)
@@ -126,58 +137,22 @@ def test_distinctive_descriptors_equal_compiled_reference(oracle, M):
             assert np.array_equal(got, desc[best])
 
 
-@pytest.mark.parametrize("seed,cam", [(31, RS.CAM_SHIPPED), (32, RS.CAM_PINHOLE)])
+@pytest.mark.parametrize("seed,cam", [(31, RS.CAM_SHIPPED), (32, RS.CAM_PINHOLE), (71, RS.CAM_SHIPPED)])
 def test_search_by_projection_equals_compiled_reference(oracle, M, seed, cam):
-    """M6: SearchByProjection(Frame, vector<MapPoint*>, th) (local-map tracking, src/ORBmatcher.cc:49-125) and
-    SearchByProjection(CurrentFrame, LastFrame, th) (:1507-1622) run by the reference on its own Frame / MapPoint
-    objects against the oracle's flat-array forms."""
+    """M6, all four overloads run by the reference on its own Frame / KeyFrame / MapPoint objects (scenes and the
+    caller-side float expressions: tests/refscene.py::projection_cases) against the oracle's flat-array form:
+    local map SearchByProjection(Frame, vector<MapPoint*>, th) (src/ORBmatcher.cc:49-125), last frame
+    SearchByProjection(CurrentFrame, LastFrame, th) (:1507-1620), relocalisation SearchByProjection(CurrentFrame, pKF,
+    sAlreadyFound, th, ORBdist) (:1622-1746), loop closing SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)
+    (:286-407); poses at identity, so the pose algebra returns the world point unchanged and everything else is the
+    reference's own code."""
     RF = _rf()
-    from orb_slam_b200.matcher import ProjectedPoints
-    w = RF.World(None, 400, 1.2, 6, 1, 20)
-    ims = RS.images(oracle, seed)
-    f1 = w.frame(ims[0], RS.K_of(cam), cam[4:9], reset_static=True)
-    f2 = w.frame(ims[1], RS.K_of(cam), cam[4:9])
-    sf = np.cumprod(np.concatenate([[1.0], np.full(5, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
-    rng = np.random.default_rng(seed)
-    # ---- local map: one point per keypoint of f1, projected near where the scene moved to in f2 ----------------
-    v2 = RS.valid_flags(f2.n, seed + 1)
-    for th, ratio in ((1.0, 0.8), (5.0, 0.8), (3.0, 0.6)):
-        f2.set_valid(v2)
-        n = f1.n
-        u = (f1.xu - 11 + rng.normal(0, 1.5, n)).astype(np.float32)
-        v = (f1.yu - 6 + rng.normal(0, 1.5, n)).astype(np.float32)
-        level = np.clip(f1.kps["octave"] + rng.integers(-1, 2, n), 0, 5).astype(np.int32)
-        vcos = rng.choice(np.array([0.6, 0.9, 0.998, 0.9985, 1.0], np.float32), n)
-        in_view = (rng.random(n) < 0.9).astype(np.uint8)
-        bad = (rng.random(n) < 0.05).astype(np.uint8)
-        idx = np.arange(n, dtype=np.int32)
-        rn, rm = RF.search_by_projection_local(f2, f1, u, v, level, vcos, in_view, bad, idx, th, ratio)
-        pts = ProjectedPoints.for_local_map(u, v, vcos, level, f1.desc, sf, th, valid=(in_view == 1) & (bad == 0))
-        tgt = RS.match_frame(f2, v2, None)
-        tgt.valid = (v2 != 0).astype(np.uint8)       # :91 skips a keypoint that holds ANY MapPoint pointer
-        on, om = M.search_by_projection(tgt, pts, "local_map", 100, ratio, True)
-        assert rn == on and np.array_equal(rm, om) and on > 40, (th, ratio)
-    # ---- last frame -> current frame, current pose = identity ---------------------------------------------------
-    v1 = RS.valid_flags(f1.n, seed + 2)
-    fx, fy, cx, cy = (np.float32(cam[0]), np.float32(cam[1]), np.float32(cam[2]), np.float32(cam[3]))
-    for th, ratio, ori in ((15.0, 0.9, True), (7.0, 0.9, False)):
-        f1.set_valid(v1); f2.set_valid(v2)
-        z = rng.uniform(1.0, 8.0, f1.n).astype(np.float32)
-        tu = f1.xu - 11 + rng.normal(0, 2, f1.n); tv = f1.yu - 6 + rng.normal(0, 2, f1.n)
-        tu[:5] = -400.0                                # projected outside the image: skipped (:1540-1543)
-        pos = np.stack([(tu - cx) / fx * z, (tv - cy) / fy * z, z], 1).astype(np.float32)
-        rn, rm = RF.search_by_projection_last(f2, f1, pos, th, ratio, ori)
-        invz = (1.0 / pos[:, 2].astype(np.float64)).astype(np.float32)
-        uu = (fx * pos[:, 0]) * invz + cx                # float32 throughout, left to right (:1535-1538)
-        vv = (fy * pos[:, 1]) * invz + cy
-        b = f1.bounds
-        inside = ~((uu < np.float32(b[0])) | (uu > np.float32(b[1])) | (vv < np.float32(b[2])) | (vv > np.float32(b[3])))
-        pts = ProjectedPoints.for_last_frame(uu, vv, f1.kps["octave"], f1.desc, f1.kps["angle"], sf, th,
-                                             valid=(v1 != 0) & inside)
-        tgt = RS.match_frame(f2, v2, None)
-        tgt.valid = (v2 != 0).astype(np.uint8)
-        on, om = M.search_by_projection(tgt, pts, "best", 100, ratio, ori)
-        assert rn == on and np.array_equal(rm, om) and on > 40, (th, ratio, ori)
+    seen = set()
+    for c in RS.projection_cases(oracle, RF, seed, cam):
+        on, om = M.search_by_projection(c["target"], c["points"], c["variant"], c["th_dist"], c["ratio"], c["ori"])
+        assert c["ref_n"] == on and np.array_equal(c["ref_m"], om) and on > 15, (c["name"], c["ref_n"], on)
+        seen.add(c["name"].split(":")[0])
+    assert seen == {"local_map", "last_frame", "reloc", "sim3"}
 
 
 @pytest.mark.parametrize("ori", [True, False])
