@@ -54,6 +54,7 @@ def _lib():
         L.ref_m_frame_points_take_descriptors.argtypes = [_P, _P]
         L.ref_m_search_by_projection_reloc.argtypes = [_P, _P, _P, _P, _F, _I, _F, _I, _P]
         L.ref_m_search_by_projection_sim3.argtypes = [_P, _P, _P, _P, _P, _I, _I, _F, _P]
+        L.ref_m_is_in_frustum.argtypes = [_P, _P, _F] + [_P] * 6
         L._m_ready = True
     return L
 
@@ -217,3 +218,15 @@ def search_by_projection_sim3(kf_frame: RefFrame, src: RefFrame, sel, pre, th, r
     n = _lib().ref_m_search_by_projection_sim3(kf_frame.keyframe(), kf_frame._f, src._f, sel.ctypes.data, pre.ctypes.data,
                                                len(sel), int(th), ratio, m.ctypes.data)
     return n, m[:kf_frame.n]
+
+
+def is_in_frustum(view: RefFrame, src: RefFrame, cos_limit=0.5):
+    """Frame::isInFrustum of `view` (pose identity) for the MapPoint on every keypoint of `src` ->
+    (ret, in_view, u, v, level, view_cos), zeros where src has no MapPoint."""
+    n = max(src.n, 1)
+    ret = np.zeros(n, np.uint8); iv = np.zeros(n, np.uint8); u = np.zeros(n, np.float32); v = np.zeros(n, np.float32)
+    lv = np.zeros(n, np.int32); vc = np.zeros(n, np.float32)
+    _lib().ref_m_is_in_frustum(view._f, src._f, cos_limit, ret.ctypes.data, iv.ctypes.data, u.ctypes.data, v.ctypes.data,
+                               lv.ctypes.data, vc.ctypes.data)
+    k = src.n
+    return ret[:k], iv[:k], u[:k], v[:k], lv[:k], vc[:k]

@@ -382,6 +382,26 @@ int ref_m_search_by_projection_sim3(void* kf, void* kf_box, void* src_fb, const 
   return n;
 }
 
+// Frame::isInFrustum(pMP, viewingCosLimit) (src/Frame.cc:136-197) of frame `view_fb` (pose = identity through the
+// reference's own UpdatePoseMatrices, :129-134) for the MapPoint on every keypoint of `src_fb` (geometry from
+// ref_m_frame_set_point_geometry).  Outputs per source keypoint: the return value and the tracking fields it writes
+// (left at the values below for keypoints without a MapPoint).
+void ref_m_is_in_frustum(void* view_fb, void* src_fb, float cos_limit, uint8_t* ret, uint8_t* in_view, float* u, float* v,
+                         int32_t* level, float* view_cos) {
+  Frame* f = static_cast<FrameBox*>(view_fb)->f;
+  FrameBox* bs = static_cast<FrameBox*>(src_fb);
+  f->mTcw = cv::Mat::eye(4, 4, CV_32F);
+  f->UpdatePoseMatrices();
+  for (int i = 0; i < bs->f->N; i++) {
+    MapPoint* p = bs->f->mvpMapPoints[i];
+    ret[i] = 0; in_view[i] = 0; u[i] = v[i] = view_cos[i] = 0.f; level[i] = 0;
+    if (!p) continue;
+    ret[i] = f->isInFrustum(p, cos_limit) ? 1 : 0;
+    in_view[i] = p->mbTrackInView ? 1 : 0;
+    if (p->mbTrackInView) { u[i] = p->mTrackProjX; v[i] = p->mTrackProjY; level[i] = p->mnTrackScaleLevel; view_cos[i] = p->mTrackViewCos; }
+  }
+}
+
 // SearchForTriangulation(pKF1, pKF2, F12, vMatchedKeys1, vMatchedKeys2, vMatchedPairs) (src/ORBmatcher.cc:852-1014):
 // match12[i1] = i2 from vMatchedPairs, else -1
 int ref_m_search_for_triangulation(void* kf1, void* kf2, const float* F12, int n1, float ratio, int check_ori,

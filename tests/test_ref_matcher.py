@@ -155,6 +155,45 @@ def test_search_by_projection_equals_compiled_reference(oracle, M, seed, cam):
     assert seen == {"local_map", "last_frame", "reloc", "sim3"}
 
 
+@pytest.mark.parametrize("seed,cam", [(81, RS.CAM_SHIPPED), (82, RS.CAM_PINHOLE)])
+def test_is_in_frustum_equals_compiled_reference(oracle, seed, cam):
+    """N3: Frame::isInFrustum (src/Frame.cc:136-197) run by the reference's own Frame on its own MapPoints (pose at
+    identity through UpdatePoseMatrices, so mRcw*P+mtcw and P-mOw return P) against the oracle: return value,
+    mbTrackInView, mTrackProjX/Y, mnTrackScaleLevel, mTrackViewCos compared as raw bits.  The matrix expressions under a
+    general pose are pinned against OpenCV itself in tests/test_frame_oracle.py."""
+    RF = _rf()
+    from oracle import frame_oracle as FO
+    w = RF.World(None, 400, 1.2, 6, 1, 20)
+    ims = RS.images(oracle, seed)
+    f1 = w.frame(ims[0], RS.K_of(cam), cam[4:9], reset_static=True)
+    f2 = w.frame(ims[1], RS.K_of(cam), cam[4:9])
+    sf = np.cumprod(np.concatenate([[1.0], np.full(5, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    rng = np.random.default_rng(seed)
+    n = f1.n
+    fx, fy, cx, cy = (np.float32(c) for c in cam[:4])
+    z = rng.uniform(0.5, 9.0, n).astype(np.float32)
+    z[rng.random(n) < 0.08] *= -1                                         # behind the camera
+    tu = rng.uniform(-60, 380, n); tv = rng.uniform(-60, 300, n)          # a band outside the image on every side
+    pos = np.stack([(tu - cx) / fx * z, (tv - cy) / fy * z, z], 1).astype(np.float32)
+    dist = RS._norm3(pos)
+    min_dist = (dist / rng.uniform(0.7, 1.2 ** 7, n).astype(np.float32)).astype(np.float32)    # some closer than min
+    max_dist = (min_dist * rng.choice(np.array([1.5, 3.0, 1.2 ** 6], np.float32), n)).astype(np.float32)
+    d = rng.normal(0, 1, (n, 3)); d /= np.linalg.norm(d, axis=1)[:, None]
+    normal = (0.6 * pos / np.abs(dist[:, None]) + 0.8 * d).astype(np.float32)   # cosines spread around the 0.5 limit
+    f1.set_valid(np.ones(n, np.uint8))
+    f1.set_point_geometry(pos, min_dist, max_dist, normal)
+    view = FO.make_view(np.eye(3), [0, 0, 0], fx, fy, cx, cy, (f2.bounds[0], f2.bounds[1], f2.bounds[2], f2.bounds[3]), sf)
+    for lim in (0.5, 0.8):
+        ret, iv, u, v, lv, vc = RF.is_in_frustum(f2, f1, lim)
+        o_iv, o_u, o_v, o_lv, o_vc = FO.is_in_frustum(view, pos, normal, min_dist, max_dist, lim)
+        assert np.array_equal(ret, iv) and np.array_equal(iv, o_iv)
+        k = iv == 1
+        assert 0.03 < k.mean() < 0.7 and len(set(lv[k].tolist())) >= 5
+        assert np.array_equal(lv[k], o_lv[k])
+        for a, b in ((u, o_u), (v, o_v), (vc, o_vc)):
+            assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32))
+
+
 @pytest.mark.parametrize("ori", [True, False])
 def test_search_for_triangulation_equals_compiled_reference(oracle, M, tmp_path, ori):
     """M9: SearchForTriangulation (src/ORBmatcher.cc:852-1014, CheckDistEpipolarLine :136-153) between two real
