@@ -38,7 +38,9 @@ def is_stale() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB
-    cmd = [NVCC, *FLAGS, "-o", LIB, *sources()]
+    # experiments: ORBX_NVCC_EXTRA="-DORBX_FAST_THREADS=128" ORBX_LIB_OUT=/path/variant.so python -m orb_slam_b200.build --force
+    out = os.environ.get("ORBX_LIB_OUT", LIB)
+    cmd = [NVCC, *FLAGS, *os.environ.get("ORBX_NVCC_EXTRA", "").split(), "-o", out, *sources()]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))
@@ -47,7 +49,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

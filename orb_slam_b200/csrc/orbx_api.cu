@@ -1,6 +1,8 @@
 // C-ABI layer of the extractor (include/orbx.h): handle, device memory, chunked / pipelined execution.
 // Host glue only — all arithmetic is in orbx_kernels.cu.  No CPU fallback: without a CUDA device orbx_create fails.
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
@@ -8,6 +10,11 @@
 #include "orbx_kernels.cuh"
 
 using namespace orbx;
+
+// Independent chunk lanes (scratch set + streams) and host staging slots.  Consecutive chunks have no data dependence;
+// more lanes let the issue-bound stages of one chunk fill the barrier / tail bubbles of another.
+constexpr int kLanes = 4;          // upper bound; a handle uses h->nlanes of them (ORBX_LANES in the environment, default below)
+constexpr int kDefaultLanes = 2;
 
 struct orbx_handle {
   orbx_params p;
@@ -24,24 +31,25 @@ struct orbx_handle {
     int32_t *d_n_total = nullptr, *d_n_retain = nullptr, *d_kp_count = nullptr;
     cudaStream_t s_main = nullptr, s_aux = nullptr;                       // blur runs beside select on s_aux
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
-  } lane[2];
-  uint8_t* d_in[2] = {nullptr, nullptr};
-  uint8_t* d_raw[2] = {nullptr, nullptr};   // tightly packed host rows land here first (one contiguous H2D), then D2D repitch
+  } lane[kLanes];
+  int nlanes = kDefaultLanes;
+  uint8_t* d_in[kLanes] = {};
+  uint8_t* d_raw[kLanes] = {};   // tightly packed host rows land here first (one contiguous H2D), then D2D repitch
   int32_t* d_err = nullptr;
   DevicePlan* d_plan = nullptr;
   CellPlan* d_cells = nullptr;
   ResizeX* d_rx = nullptr;
   ResizeY* d_ry = nullptr;
-  orbx_keypoint* d_out_kps[2] = {nullptr, nullptr};
-  uint8_t* d_out_desc[2] = {nullptr, nullptr};
-  int32_t* d_out_n[2] = {nullptr, nullptr};
+  orbx_keypoint* d_out_kps[kLanes] = {};
+  uint8_t* d_out_desc[kLanes] = {};
+  int32_t* d_out_n[kLanes] = {};
   size_t cap_cells = 0, cap_rx = 0, cap_ry = 0;
   int64_t cap_pyr = 0, cap_cand = 0, cap_list = 0, cap_cells_frame = 0;
   int in_pitch = 0;
   int64_t in_frame_bytes = 0;
   cudaStream_t s_in = nullptr, s_out = nullptr;
   cudaEvent_t ev_user = nullptr;                      // fork point on a caller's stream (device-resident API)
-  cudaEvent_t ev_in[2], ev_compute[2], ev_out[2], ev_stage[ORBX_STAGE_COUNT + 1];
+  cudaEvent_t ev_in[kLanes], ev_compute[kLanes], ev_out[kLanes], ev_stage[ORBX_STAGE_COUNT + 1];
   bool profiling = false;
   float prof_ms[ORBX_STAGE_COUNT] = {0};
   int64_t prof_launch[ORBX_STAGE_COUNT] = {0};
@@ -118,7 +126,7 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     h->err = "cell too large for the shared-memory FAST tile (cell area > ~100k px)";
     return ORBX_ERR_UNSUPPORTED;
   }
-  for (auto& ln : h->lane) CK(cudaStreamSynchronize(ln.s_main));
+  for (int li = 0; li < h->nlanes; li++) CK(cudaStreamSynchronize(h->lane[li].s_main));
   CK(cudaMemcpy(h->d_plan, &dp, sizeof(dp), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(h->d_cells, h->hp.cells.data(), h->hp.cells.size() * sizeof(CellPlan), cudaMemcpyHostToDevice));
   if (!h->hp.rx.empty()) {
@@ -171,7 +179,9 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     h->cap_cells_frame = dp.total_cells * 2 + 64;
     h->in_pitch = (pp->max_width + 15) / 16 * 16;
     h->in_frame_bytes = (int64_t)h->in_pitch * pp->max_height;
-    for (auto& ln : h->lane) {
+    if (const char* e = getenv("ORBX_LANES")) h->nlanes = std::min(kLanes, std::max(1, atoi(e)));
+    for (int li = 0; li < h->nlanes; li++) {
+      orbx_handle::Lane& ln = h->lane[li];
       CK(cudaMalloc(&ln.d_pyr, B * h->cap_pyr));
       CK(cudaMalloc(&ln.d_blur, B * h->cap_pyr));
       CK(cudaMalloc(&ln.d_cand, B * h->cap_cand * sizeof(Cand)));
@@ -192,7 +202,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     CK(cudaMalloc(&h->d_cells, h->cap_cells * sizeof(CellPlan)));
     CK(cudaMalloc(&h->d_rx, h->cap_rx * sizeof(ResizeX)));
     CK(cudaMalloc(&h->d_ry, h->cap_ry * sizeof(ResizeY)));
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < h->nlanes; i++) {
       CK(cudaMalloc(&h->d_in[i], B * h->in_frame_bytes));
       CK(cudaMalloc(&h->d_raw[i], B * h->in_frame_bytes));
       CK(cudaMalloc(&h->d_out_kps[i], B * pp->nfeatures * sizeof(orbx_keypoint)));
@@ -218,9 +228,12 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   if (!h) return;
   cudaSetDevice(h->p.device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_in[0], h->d_in[1], h->d_raw[0], h->d_raw[1], h->d_out_kps[0],
-                  h->d_out_kps[1], h->d_out_desc[0], h->d_out_desc[1], h->d_out_n[0], h->d_out_n[1]};
+  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry};
   for (void* p : ptrs) if (p) cudaFree(p);
+  for (int i = 0; i < kLanes; i++) {
+    void* sp[] = {h->d_in[i], h->d_raw[i], h->d_out_kps[i], h->d_out_desc[i], h->d_out_n[i]};
+    for (void* p : sp) if (p) cudaFree(p);
+  }
   for (auto& ln : h->lane) {
     void* lp[] = {ln.d_pyr, ln.d_blur, ln.d_cand, ln.d_list, ln.d_kp, ln.d_n_total, ln.d_n_retain, ln.d_kp_count};
     for (void* p : lp) if (p) cudaFree(p);
@@ -233,7 +246,7 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   if (h->s_in) {
     cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
     if (h->ev_user) cudaEventDestroy(h->ev_user);
-    for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_compute[i]); cudaEventDestroy(h->ev_out[i]); }
+    for (int i = 0; i < h->nlanes; i++) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_compute[i]); cudaEventDestroy(h->ev_out[i]); }
     for (int i = 0; i <= ORBX_STAGE_COUNT; i++) cudaEventDestroy(h->ev_stage[i]);
   }
   delete h;
@@ -308,7 +321,7 @@ extern "C" int orbx_synchronize(orbx_handle* h) {
   if (!h) return ORBX_ERR_ARG;
   CK(cudaSetDevice(h->p.device));
   CK(cudaStreamSynchronize(h->s_in));
-  for (auto& ln : h->lane) CK(cudaStreamSynchronize(ln.s_main));
+  for (int li = 0; li < h->nlanes; li++) CK(cudaStreamSynchronize(h->lane[li].s_main));
   CK(cudaStreamSynchronize(h->s_out));
   int32_t flag = 0;
   CK(cudaMemcpy(&flag, h->d_err, sizeof(flag), cudaMemcpyDeviceToHost));
@@ -343,24 +356,25 @@ extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, 
     }
     return ORBX_OK;
   }
-  // several chunks: fork the caller's stream into the two lanes, alternate chunks between them, join at the end
+  // several chunks: fork the caller's stream into the lanes, deal chunks round-robin, join at the end
   CK(cudaEventRecord(h->ev_user, s));
-  for (auto& ln : h->lane) CK(cudaStreamWaitEvent(ln.s_main, h->ev_user, 0));
+  for (int li = 0; li < h->nlanes; li++) CK(cudaStreamWaitEvent(h->lane[li].s_main, h->ev_user, 0));
   int k = 0;
   for (int f0 = 0; f0 < nframes; f0 += B, k++) {
     const int n = std::min(B, nframes - f0);
-    rc = run_chunk(h, k & 1, d_imgs + (size_t)f0 * frame_stride, n, stride, frame_stride, d_kps + (size_t)f0 * nf,
-                   d_desc + (size_t)f0 * nf * 32, d_n_out + f0, h->lane[k & 1].s_main);
+    rc = run_chunk(h, k % h->nlanes, d_imgs + (size_t)f0 * frame_stride, n, stride, frame_stride, d_kps + (size_t)f0 * nf,
+                   d_desc + (size_t)f0 * nf * 32, d_n_out + f0, h->lane[k % h->nlanes].s_main);
     if (rc != ORBX_OK) return rc;
   }
-  for (auto& ln : h->lane) {
+  for (int li = 0; li < h->nlanes; li++) {
+    orbx_handle::Lane& ln = h->lane[li];
     CK(cudaEventRecord(ln.ev_done, ln.s_main));
     CK(cudaStreamWaitEvent(s, ln.ev_done, 0));
   }
   return ORBX_OK;
 }
 
-// HOST buffers: chunk k's H2D (s_in), kernels (lane k & 1) and D2H (s_out) overlap with chunks k-1 / k+1 through two
+// HOST buffers: chunk k's H2D (s_in), kernels (lane k % h->nlanes) and D2H (s_out) overlap with chunks k-1 / k+1 through kLanes
 // staging slots.  Pinned caller memory makes the copies truly asynchronous; pageable memory still works.
 extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nframes, int w, int hgt, size_t stride,
                                   size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int* n_out) {
@@ -378,8 +392,8 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nfram
   const size_t fbytes = (size_t)pitch * hgt;
   int k = 0;
   for (int f0 = 0; f0 < nframes; f0 += B, k++) {
-    const int n = std::min(B, nframes - f0), slot = k & 1;
-    if (k >= 2) CK(cudaStreamWaitEvent(h->s_in, h->ev_compute[slot], 0));  // slot's previous input consumed
+    const int n = std::min(B, nframes - f0), slot = k % h->nlanes;
+    if (k >= h->nlanes) CK(cudaStreamWaitEvent(h->s_in, h->ev_compute[slot], 0));  // slot's previous input consumed
     const uint8_t* src = imgs + (size_t)f0 * frame_stride;
     if (frame_stride == stride * (size_t)hgt && stride == (size_t)pitch) {
       // rows already have the device pitch: one contiguous copy (a strided 2-D H2D costs a DMA descriptor per row)
@@ -399,7 +413,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nfram
     CK(cudaEventRecord(h->ev_in[slot], h->s_in));
     cudaStream_t sc = h->lane[h->profiling ? 0 : slot].s_main;
     CK(cudaStreamWaitEvent(sc, h->ev_in[slot], 0));
-    if (k >= 2) CK(cudaStreamWaitEvent(sc, h->ev_out[slot], 0));  // slot's previous output drained
+    if (k >= h->nlanes) CK(cudaStreamWaitEvent(sc, h->ev_out[slot], 0));  // slot's previous output drained
     rc = run_chunk(h, h->profiling ? 0 : slot, h->d_in[slot], n, pitch, fbytes, h->d_out_kps[slot], h->d_out_desc[slot],
                    h->d_out_n[slot], sc);
     if (rc != ORBX_OK) return rc;

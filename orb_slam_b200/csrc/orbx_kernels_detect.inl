@@ -53,7 +53,10 @@ __device__ float harris_response(const uint8_t* p, int step) {
 // Pixels failing the reject keep score 0 instead of their true S < tmin: harmless, a neighbour below tmin can never
 // suppress a survivor (S_c >= t >= tmin > S_n), which is also why one threshold-free map serves both thresholds.
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kFastThreads = 256, kFastWarps = kFastThreads / 32, kFastQueue = 160, kFastSub = 4;
+#ifndef ORBX_FAST_THREADS
+#define ORBX_FAST_THREADS 256
+#endif
+constexpr int kFastThreads = ORBX_FAST_THREADS, kFastWarps = kFastThreads / 32, kFastQueue = 160, kFastSub = 4;
 
 __device__ __forceinline__ uint32_t hw_mid(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }
 
@@ -174,7 +177,7 @@ struct FastLevels {
   int64_t off[kMaxLevels];
 };
 
-__global__ void __launch_bounds__(kFastThreads, 4) fast_cells_kernel(ChunkBuffers b, FastLevels fl) {
+__global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads) fast_cells_kernel(ChunkBuffers b, FastLevels fl) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ uint32_t s_queue[kFastWarps][kFastQueue];
   __shared__ int s_cnt[2];
