@@ -84,26 +84,51 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_baseline(nframes, threads, d_frames_cpu):
-    """Oracle restatement (-O3 -march=native, the reference's flags) on the box's host cores, bounded sample."""
+def _cpu_arms(frames, threads, reps=1, warm=True):
+    """The reference's CPU path on `threads` host threads over `frames` [F,H,W], two ways: (i) "reference" — the
+    reference's own src/ORBextractor.cc compiled in place (oracle/_ref/libref_orbextractor_native.so, its -O3) with its
+    five OpenCV routines served by the oracle's cv2-pinned scalar restatements; (ii) "port" — the oracle restatement
+    built with the reference's flags (-O3 -march=native).  Returns {kind: (frames/s, mean keypoints)}.  Real OpenCV is
+    SIMD-optimised, the bridge's primitives are not, so the compiled reference here is SLOWER than it would be with
+    OpenCV; the faster arm is the conservative baseline and is the one reported as `value`."""
     from oracle import oracle as O
-    E = O.OracleExtractor(NFEAT, 1.2, 8, 1, 20, fast_build=True)
-    E.extract_many(d_frames_cpu[:min(threads, nframes)], threads)  # warm
-    t = time.perf_counter()
-    _, _, n = E.extract_many(d_frames_cpu[:nframes], threads)
-    dt = time.perf_counter() - t
-    t1 = time.perf_counter()
-    E.extract_many(d_frames_cpu[:max(nframes // (2 * threads), 8)], 1)
-    dt1 = time.perf_counter() - t1
-    return {"value": nframes / dt, "unit": "frames/s", "cores": threads, "kind": "port",
-            "sample": f"{nframes} of the workload's 640x480 frames, {threads} host threads, oracle/liborb_oracle_fast.so "
-                      f"(-O3 -march=native)", "single_thread_value": max(nframes // (2 * threads), 8) / dt1,
-            "keypoints_per_frame": float(n.mean())}
+    from oracle import ref_extractor as RE
+    out = {}
+    arms = [("port", O.OracleExtractor(NFEAT, 1.2, 8, 1, 20, fast_build=True))]
+    if RE.native_available():
+        arms.append(("reference", RE.NativeRefExtractor(NFEAT, 1.2, 8, 1, 20)))
+    for kind, E in arms:
+        if warm:
+            E.extract_many(frames[:min(threads, len(frames))], threads)
+        t = time.perf_counter()
+        for _ in range(reps):
+            _, _, n = E.extract_many(frames, threads)
+        out[kind] = (len(frames) * reps / (time.perf_counter() - t), float(n.mean()))
+    return out
+
+
+def _cpu_pick(arms):
+    kind = max(arms, key=lambda k: arms[k][0])
+    extra = {f"{k}_value": v[0] for k, v in arms.items()}
+    return kind, arms[kind][0], extra
+
+
+def cpu_baseline(nframes, threads, d_frames_cpu):
+    """CPU baseline on the box's host cores, bounded sample (see _cpu_arms)."""
+    arms = _cpu_arms(d_frames_cpu[:nframes], threads)
+    kind, v, extra = _cpu_pick(arms)
+    n1 = max(nframes // (2 * threads), 8)
+    one = _cpu_arms(d_frames_cpu[:n1], 1, warm=False)
+    return {"value": v, "unit": "frames/s", "cores": threads, "kind": kind,
+            "sample": f"{nframes} of the workload's 640x480 frames, {threads} host threads; both CPU arms timed, the "
+                      f"faster one reported (reference = src/ORBextractor.cc compiled in place, OpenCV routines from "
+                      f"the oracle's scalar restatements; port = oracle/liborb_oracle_fast.so, -O3 -march=native)",
+            **extra, "single_thread_value": one[kind][0], "keypoints_per_frame": arms[kind][1]}
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation of the path.  The reference cannot be compiled here
-    (OpenCV C++ headers / ROS absent), so this is the oracle port, all host threads, bounded sample."""
+    """--impl reference: the reference's own CPU implementation of the path on all host threads, bounded sample per
+    step.  Both CPU arms of _cpu_arms are timed; the faster is the line's value (cpu_baseline.kind says which)."""
     if rank != 0:
         return
     import numpy as np
@@ -111,22 +136,21 @@ def run_reference(args, rank, world):
     threads = os.cpu_count() or 1
     nframes = args.ref_frames
     frames = np.stack([O.synth(H, W, s) for s in range(nframes)])
-    E = O.OracleExtractor(NFEAT, 1.2, 8, 1, 20, fast_build=True)
     for _ in range(args.warmup):
-        E.extract_many(frames[:threads], threads)
-    t = time.perf_counter()
-    for _ in range(args.steps):
-        E.extract_many(frames, threads)
-    dt = (time.perf_counter() - t) / args.steps
-    v = nframes / dt
-    sample = f"{nframes} frames per step of the 640x480 synthetic sequence, {threads} host threads"
+        _cpu_arms(frames[:threads], threads, warm=False)
+    arms = _cpu_arms(frames, threads, reps=args.steps, warm=False)
+    kind, v, extra = _cpu_pick(arms)
+    dt = nframes / v
+    sample = (f"{nframes} frames per step of the 640x480 synthetic sequence, {threads} host threads; both CPU arms timed "
+              f"(reference = src/ORBextractor.cc compiled in place with scalar OpenCV stand-in routines, port = oracle "
+              f"restatement with the reference's flags), the faster one reported")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": "configs[1]: batched ORB extraction, synthetic 640x480 sequence, 1000 features, 8 levels, "
                                "scale 1.2, fastTh 20 (bounded CPU sample)", "frames_per_step": nframes},
-        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind, "sample": sample, **extra},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 

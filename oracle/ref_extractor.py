@@ -138,3 +138,53 @@ class RefExtractor:
             self._L.ref_orb_destroy(self._h)
         except Exception:
             pass
+
+
+# ---- the same compiled reference with its OpenCV routines served natively (oracle/ref_native_bridge.cc) -------------
+NATIVE_LIB = os.path.join(_HERE, "_ref", "libref_orbextractor_native.so")
+_native = {}
+
+
+def native_available() -> bool:
+    return os.path.exists(NATIVE_LIB)
+
+
+def _native_lib():
+    if "L" not in _native:
+        L = C.CDLL(NATIVE_LIB)
+        L.ref_orb_use_native_bridge.argtypes = [C.c_int, C.c_int]
+        L.ref_orb_extract_many.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                           C.c_int, C.c_long, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                           C.c_int]
+        _native["L"] = L
+    return _native["L"]
+
+
+class NativeRefExtractor:
+    """ORB_SLAM::ORBextractor (the reference's own src/ORBextractor.cc, -O3) with cv::resize / copyMakeBorder /
+    GaussianBlur / FAST / fastAtan2 served by the oracle's cv2-pinned native restatements: no Python in the loop, no
+    cv2 needed.  The timed CPU baseline of bench.py (`kind: "reference"`).  retain_mode / blur_mode: 0 = OpenCV 2.4
+    behaviour, 1 = OpenCV >= 3.4 (what the cv2-bridged build sees)."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, scoreType=1, fastTh=20, retain_mode=0, blur_mode=0):
+        self._L = _native_lib()
+        self.args = (nfeatures, scaleFactor, nlevels, scoreType, fastTh)
+        self.modes = (retain_mode, blur_mode)
+        self.nfeatures = nfeatures
+
+    def extract_many(self, images: np.ndarray, nthreads: int = 1, cap: int | None = None):
+        """images [F,H,W] uint8 -> (kps [F,cap], desc [F,cap,32], n [F])."""
+        assert images.dtype == np.uint8 and images.ndim == 3 and images.strides[2] == 1
+        self._L.ref_orb_use_native_bridge(*self.modes)      # process-wide bridge state: set per call
+        F, H, W = images.shape
+        cap = cap or self.nfeatures + 64
+        kps = np.zeros((F, cap), KP_DTYPE); desc = np.zeros((F, cap, 32), np.uint8); n = np.zeros(F, np.int32)
+        rc = self._L.ref_orb_extract_many(*self.args, images.ctypes.data, F, W, H, images.strides[1], images.strides[0],
+                                          kps.ctypes.data, desc.ctypes.data, n.ctypes.data, cap, nthreads)
+        if rc != 0:
+            raise RuntimeError("keypoint capacity too small")
+        return kps, desc, n
+
+    def __call__(self, image):
+        k, d, n = self.extract_many(np.ascontiguousarray(image, np.uint8)[None], 1)
+        return k[0, :n[0]].copy(), d[0, :n[0]].copy()

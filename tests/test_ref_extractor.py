@@ -69,3 +69,30 @@ def test_compiled_reference_edge_images(oracle):
     rk, rd = R(low)
     ok, od = E(low)
     assert same_keypoints(ok, rk) and np.array_equal(od, rd)
+
+
+@pytest.mark.parametrize("cfg", [(480, 640, 1000, 8, 1, 20, (0, 1, 2)), (376, 1241, 2000, 8, 1, 20, (0,)),
+                                 (480, 640, 1000, 8, 0, 20, (3,)), (243, 317, 700, 5, 1, 35, (4,))])
+def test_native_bridged_reference_equals_oracle_and_cv2_bridged(oracle, cfg):
+    """The timed CPU baseline (bench.py cpu_baseline.kind = "reference"): the SAME compiled src/ORBextractor.cc with its
+    OpenCV routines served natively (oracle/ref_native_bridge.cc) returns exactly what the oracle returns in every
+    OpenCV-era mode, and, where cv2 is importable, exactly what the cv2-bridged build returns."""
+    from oracle import ref_extractor as RE
+    if not RE.native_available():
+        pytest.skip("oracle/_ref/libref_orbextractor_native.so not built here")
+    h, w, nf, nl, st, th, seeds = cfg
+    imgs = np.stack([oracle.synth(h, w, s) for s in seeds])
+    for retain, blur in ((1, 1), (0, 0), (0, 1)):
+        N = RE.NativeRefExtractor(nf, 1.2, nl, st, th, retain_mode=retain, blur_mode=blur)
+        E = oracle.OracleExtractor(nf, 1.2, nl, st, th, blur_mode=blur, retain_mode=retain)
+        k, d, n = N.extract_many(imgs, nthreads=min(len(seeds), 3))
+        for i in range(len(seeds)):
+            ok, od = E(imgs[i])
+            assert same_keypoints(ok, k[i, :n[i]]) and np.array_equal(od, d[i, :n[i]]), (cfg, retain, blur, i)
+    if RE.available():
+        R = RE.RefExtractor(nf, 1.2, nl, st, th)
+        RE.set_retain_mode(1)
+        N = RE.NativeRefExtractor(nf, 1.2, nl, st, th, retain_mode=1, blur_mode=1)
+        rk, rd = R(imgs[0])
+        nk, nd = N(imgs[0])
+        assert same_keypoints(nk, rk) and np.array_equal(nd, rd)
