@@ -15,6 +15,7 @@ using namespace orbx;
 // more lanes let the issue-bound stages of one chunk fill the barrier / tail bubbles of another.
 constexpr int kLanes = 4;          // upper bound; a handle uses h->nlanes of them (ORBX_LANES in the environment, default below)
 constexpr int kDefaultLanes = 2;
+constexpr int kPdlMaxFrames = 16;
 
 struct orbx_handle {
   orbx_params p;
@@ -33,6 +34,7 @@ struct orbx_handle {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
   } lane[kLanes];
   int nlanes = kDefaultLanes;
+  int pdl_mode = 1;                 // 0 never, 1 chunks of <= kPdlMaxFrames frames, 2 always (ORBX_PDL)
   uint8_t* d_in[kLanes] = {};
   uint8_t* d_raw[kLanes] = {};   // tightly packed host rows land here first (one contiguous H2D), then D2D repitch
   int32_t* d_err = nullptr;
@@ -179,6 +181,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     h->cap_cells_frame = dp.total_cells * 2 + 64;
     h->in_pitch = (pp->max_width + 15) / 16 * 16;
     h->in_frame_bytes = (int64_t)h->in_pitch * pp->max_height;
+    if (const char* e = getenv("ORBX_PDL")) h->pdl_mode = std::min(2, std::max(0, atoi(e)));
     if (const char* e = getenv("ORBX_LANES")) h->nlanes = std::min(kLanes, std::max(1, atoi(e)));
     for (int li = 0; li < h->nlanes; li++) {
       orbx_handle::Lane& ln = h->lane[li];
@@ -269,6 +272,9 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   b.list = ln.d_list; b.kp = ln.d_kp; b.kp_count = ln.d_kp_count; b.err_flag = h->d_err;
   b.plan = h->d_plan; b.cells = h->d_cells; b.rx = h->d_rx; b.ry = h->d_ry;
   const bool prof = h->profiling;
+  // launch-latency-bound chains (a few frames per chunk) use programmatic dependent launch; full chunks keep the
+  // plain stream order, where the other lane's kernels already fill the tails (ORBX_PDL=0 never / 2 always)
+  set_launch_pdl(h->pdl_mode == 2 || (h->pdl_mode == 1 && n <= kPdlMaxFrames));
   int st = 0;
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   for (int l = 1; l < dp.nlevels; l++) launch_resize_level(b, dp, l, n, s);

@@ -6,7 +6,34 @@
 
 #include "orbx_kernels.cuh"
 
+#include <algorithm>
+#include <cstdlib>
+#include <utility>
+
 namespace orbx {
+
+static thread_local bool g_launch_pdl = false;
+void set_launch_pdl(bool on) { g_launch_pdl = on; }
+
+// Launch with (optionally) the programmatic-stream-serialization attribute; see set_launch_pdl.
+template <class... KArgs, class... Args>
+static void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = g_launch_pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
+// First statement of every chained kernel: let the successor start launching, then wait until the predecessor grid
+// has completed and its writes are visible.  Both are no-ops for a launch without the attribute.
+#define ORBX_PDL_ENTRY()                                         \
+  do {                                                           \
+    asm volatile("griddepcontrol.launch_dependents;");           \
+    asm volatile("griddepcontrol.wait;" ::: "memory");           \
+  } while (0)
 
 // ------------------------------------------------------------------------------------------------------------------
 // helpers
@@ -49,6 +76,7 @@ __device__ __forceinline__ const uint8_t* level_ptr(const ChunkBuffers& b, const
 constexpr int kResizeRows = 6, kResizeSrcMax = 10;
 
 __global__ void __launch_bounds__(256) resize_level_kernel(ChunkBuffers b, int level) {
+  ORBX_PDL_ENTRY();
   const DevicePlan* P = b.plan;
   const LevelPlan& L = P->lv[level];
   const int frame = blockIdx.z, lane = threadIdx.x;
@@ -152,7 +180,7 @@ __global__ void __launch_bounds__(256) resize_level_kernel(ChunkBuffers b, int l
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s) {
   const LevelPlan& L = hp.lv[level];
   dim3 block(32, 8), grid((L.w + 127) / 128, (L.h + 8 * kResizeRows - 1) / (8 * kResizeRows), nframes);
-  resize_level_kernel<<<grid, block, 0, s>>>(b, level);
+  launch_k(resize_level_kernel, grid, block, 0, s, b, level);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -173,6 +201,7 @@ void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level,
 constexpr int kBlurTW = 64, kBlurTH = 58, kBlurRows = 64, kBlurInW = 20;  // staged row = image columns x0-8 .. x0+71
 
 __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles tiles) {
+  ORBX_PDL_ENTRY();
   int level = 0;
   while (level + 1 < tiles.nlevels && (int)blockIdx.x >= tiles.base[level + 1]) level++;
   const int t = blockIdx.x - tiles.base[level];
@@ -300,7 +329,7 @@ __global__ void __launch_bounds__(256) blur7_kernel(ChunkBuffers b, BlurTiles ti
 
 void launch_blur(const ChunkBuffers& b, const DevicePlan& hp, const BlurTiles& t, int nframes, cudaStream_t s) {
   dim3 grid(t.base[hp.nlevels], nframes);
-  blur7_kernel<<<grid, 256, 0, s>>>(b, t);
+  launch_k(blur7_kernel, grid, dim3(256), 0, s, b, t);
 }
 
 // ------------------------------------------------------------------------------------------------------------------

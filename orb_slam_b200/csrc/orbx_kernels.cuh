@@ -34,6 +34,12 @@ struct BlurTiles {            // everything blur7_kernel needs per level, passed
   int64_t frame_bytes;        // DevicePlan::pyr_frame_bytes == blur_frame_bytes
 };
 
+// Programmatic dependent launch (griddepcontrol): when on, every extractor kernel is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, signals `launch_dependents` on entry and waits for its
+// predecessor with `griddepcontrol.wait` before touching memory, so the NEXT kernel of the chain is already resident
+// when this one drains.  Pays off when the chain is launch-latency bound (a chunk of a few frames); per host thread.
+void set_launch_pdl(bool on);
+
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s);
 void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s);

@@ -108,10 +108,12 @@ __global__ void __launch_bounds__(32 * kDescWarps, 4) describe_kernel(ChunkBuffe
   __shared__ float2 s_pat[16 * 32];            // [j][lane] = pattern point 16 * lane + j
   const DevicePlan* P = b.plan;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int t = threadIdx.x; t < 512; t += 32 * kDescWarps) {
+  asm volatile("griddepcontrol.launch_dependents;");
+  for (int t = threadIdx.x; t < 512; t += 32 * kDescWarps) {   // constant table: legal before the dependency wait
     const int pl = t & 31, pj = t >> 5, pt = 16 * pl + pj;
     s_pat[t] = make_float2((float)d_pattern[2 * pt], (float)d_pattern[2 * pt + 1]);
   }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
   const int nfeatures = P->nfeatures, nlevels = P->nlevels;
   const int my_base = lane < nlevels ? P->lv[lane].kp_base : 0x7fffffff;
@@ -332,7 +334,7 @@ void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, o
     max_ctas = sms * (per_sm > 0 ? per_sm : 1);
   }
   const int ctas = (nslots + kDescWarps - 1) / kDescWarps;
-  describe_kernel<<<ctas < max_ctas ? ctas : max_ctas, 32 * kDescWarps, 0, s>>>(b, d_kps, d_desc, d_n_out, nslots);
+  launch_k(describe_kernel, dim3(ctas < max_ctas ? ctas : max_ctas), dim3(32 * kDescWarps), 0, s, b, d_kps, d_desc, d_n_out, nslots);
 }
 
 }  // namespace orbx

@@ -178,6 +178,7 @@ struct FastLevels {
 };
 
 __global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads) fast_cells_kernel(ChunkBuffers b, FastLevels fl) {
+  ORBX_PDL_ENTRY();
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ uint32_t s_queue[kFastWarps][kFastQueue];
   __shared__ int s_cnt[2];
@@ -423,7 +424,7 @@ void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_byt
   fl.cand_per_frame = hp.cand_per_frame; fl.frame_bytes = hp.pyr_frame_bytes;
   for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
   dim3 grid(hp.total_cells, nframes);
-  fast_cells_kernel<<<grid, kFastThreads, smem_bytes, s>>>(b, fl);
+  launch_k(fast_cells_kernel, grid, dim3(kFastThreads), (size_t)smem_bytes, s, b, fl);
 }
 
 }  // namespace orbx

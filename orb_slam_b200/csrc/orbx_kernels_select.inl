@@ -124,6 +124,7 @@ __device__ __forceinline__ void retain_best_port(Cand* v, int size, int n, int r
 // Serial sections are a few hundred steps; thousands of (level, frame) warps run concurrently.
 // ------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_total) {
+  ORBX_PDL_ENTRY();
   const DevicePlan* P = b.plan;
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (gw >= nwarps_total) return;
@@ -211,7 +212,10 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
 // A cell with more than kSelCap candidates is partitioned in place in global memory as before (never seen at the
 // headline configurations: ~35 candidates per cell).
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kSelCap = 128, kSelStride = kSelCap + 1;
+#ifndef ORBX_SEL_CAP
+#define ORBX_SEL_CAP 128
+#endif
+constexpr int kSelCap = ORBX_SEL_CAP, kSelStride = kSelCap + 1;
 
 __host__ __device__ inline int select_smem_bytes(int list_cap, int ncells) {
   return (list_cap + 32 * kSelStride) * (int)sizeof(Cand) + 3 * ((ncells + 3) & ~3) * (int)sizeof(int32_t);
@@ -219,6 +223,7 @@ __host__ __device__ inline int select_smem_bytes(int list_cap, int ncells) {
 
 __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwarps_total, int max_list_cap,
                                                         int max_cells) {
+  ORBX_PDL_ENTRY();
   extern __shared__ __align__(16) uint8_t sel_smem[];
   const DevicePlan* P = b.plan;
   const int gw = blockIdx.x, lane = threadIdx.x;
@@ -327,19 +332,26 @@ __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwa
   if (lane == 0) b.kp_count[frame * kMaxLevels + level] = count;
 }
 
+// Which one: a chunk of a few frames is a handful of warps whose serial chains ARE the stage's latency -> shared memory
+// (43 instead of 90 us for one frame).  A full chunk runs thousands of such warps beside blur7_kernel, hidden behind it;
+// there the global version wins because it leaves the SMs' shared memory to the blur CTAs (A/B on one box, 10k frames:
+// 56.00 ms with the global kernel, 57.39 with this one at kSelCap 128, 56.27 at kSelCap 64).
+constexpr int kSelectSmemMaxFrames = 32;
+
 void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s) {
   const int nwarps = hp.nlevels * nframes;
   int max_list = 0, max_cells = 0;
   for (int l = 0; l < hp.nlevels; l++) { max_list = std::max(max_list, hp.lv[l].list_cap); max_cells = std::max(max_cells, hp.lv[l].nCells); }
   max_list = (max_list + 1) & ~1;
   const int smem = select_smem_bytes(max_list, max_cells);
-  if (smem <= 160 * 1024) {
+  static const char* force = getenv("ORBX_SELECT");             // experiments: "global" / "smem"
+  const bool want_smem = force ? force[0] == 's' : nframes <= kSelectSmemMaxFrames;
+  if (want_smem && smem <= 160 * 1024) {
     cudaFuncSetAttribute(select_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    select_smem_kernel<<<nwarps, 32, smem, s>>>(b, nwarps, max_list, max_cells);
+    launch_k(select_smem_kernel, dim3(nwarps), dim3(32), (size_t)smem, s, b, nwarps, max_list, max_cells);
     return;
   }
-  // absurdly large level lists: the global-memory version
-  select_kernel<<<(nwarps * 32 + 127) / 128, 128, 0, s>>>(b, nwarps);
+  launch_k(select_kernel, dim3((nwarps * 32 + 127) / 128), dim3(128), 0, s, b, nwarps);
 }
 
 }  // namespace orbx
