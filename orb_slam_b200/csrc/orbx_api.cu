@@ -38,6 +38,7 @@ struct orbx_handle {
   uint8_t* d_in[kLanes] = {};
   uint8_t* d_raw[kLanes] = {};   // tightly packed host rows land here first (one contiguous H2D), then D2D repitch
   int32_t* d_err = nullptr;
+  int32_t* h_err = nullptr;                 // pinned mirror of d_err, filled by an async copy behind the outputs
   DevicePlan* d_plan = nullptr;
   CellPlan* d_cells = nullptr;
   ResizeX* d_rx = nullptr;
@@ -201,6 +202,8 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     }
     CK(cudaMalloc(&h->d_err, sizeof(int32_t)));
     CK(cudaMemset(h->d_err, 0, sizeof(int32_t)));
+    CK(cudaHostAlloc((void**)&h->h_err, sizeof(int32_t), cudaHostAllocDefault));
+    *h->h_err = 0;
     CK(cudaMalloc(&h->d_plan, sizeof(DevicePlan)));
     CK(cudaMalloc(&h->d_cells, h->cap_cells * sizeof(CellPlan)));
     CK(cudaMalloc(&h->d_rx, h->cap_rx * sizeof(ResizeX)));
@@ -233,6 +236,7 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   cudaDeviceSynchronize();
   void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry};
   for (void* p : ptrs) if (p) cudaFree(p);
+  if (h->h_err) cudaFreeHost(h->h_err);
   for (int i = 0; i < kLanes; i++) {
     void* sp[] = {h->d_in[i], h->d_raw[i], h->d_out_kps[i], h->d_out_desc[i], h->d_out_n[i]};
     for (void* p : sp) if (p) cudaFree(p);
@@ -323,14 +327,22 @@ static int check_args(orbx_handle* h, const void* img, int n, int w, int hgt, si
   return ORBX_OK;
 }
 
+static int check_err_flag(orbx_handle* h);
+
 extern "C" int orbx_synchronize(orbx_handle* h) {
   if (!h) return ORBX_ERR_ARG;
   CK(cudaSetDevice(h->p.device));
   CK(cudaStreamSynchronize(h->s_in));
   for (int li = 0; li < h->nlanes; li++) CK(cudaStreamSynchronize(h->lane[li].s_main));
   CK(cudaStreamSynchronize(h->s_out));
-  int32_t flag = 0;
-  CK(cudaMemcpy(&flag, h->d_err, sizeof(flag), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, h->s_out));
+  CK(cudaStreamSynchronize(h->s_out));
+  return check_err_flag(h);
+}
+
+// the sticky device-side overflow flag, after its pinned mirror has been refreshed
+static int check_err_flag(orbx_handle* h) {
+  const int32_t flag = *h->h_err;
   if (flag) {
     cudaMemset(h->d_err, 0, sizeof(flag));
     h->err = flag == 1 ? "cell candidate list overflow" : "level list overflow";
@@ -432,7 +444,11 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int nfram
     CK(cudaMemcpyAsync(n_out + f0, h->d_out_n[slot], sizeof(int) * n, cudaMemcpyDeviceToHost, h->s_out));
     CK(cudaEventRecord(h->ev_out[slot], h->s_out));
   }
-  return orbx_synchronize(h);
+  // s_out is ordered behind every chunk's kernels (which are ordered behind their H2D): one copy of the error flag
+  // behind the last outputs and ONE synchronisation end the call
+  CK(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, h->s_out));
+  CK(cudaStreamSynchronize(h->s_out));
+  return check_err_flag(h);
 }
 
 extern "C" int orbx_extract(orbx_handle* h, const uint8_t* img, int w, int hgt, size_t stride, orbx_keypoint* kps,

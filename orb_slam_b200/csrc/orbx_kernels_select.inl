@@ -58,6 +58,10 @@ __device__ void nth_heap_select(Cand* first, int middle, int last) {  // [0,midd
     }
 }
 
+// kBatch: the two scan loops of the partition read four consecutive keys per trip (independent loads, one latency) and
+// then test them in order — same result, a quarter of the dependent round trips.  The scans may read up to 3 records
+// beyond either end of [first, last): only legal where the caller pads the array (the shared-memory kernel does).
+template <bool kBatch>
 __device__ void nth_element_port(Cand* v, int nth, int n) {
   if (n == 0 || nth == n) return;
   int first = 0, last = n;
@@ -84,9 +88,29 @@ __device__ void nth_element_port(Cand* v, int nth, int n) {
     int lo = first + 1, hi = last;
     const float pivot = v[first].resp;  // the pivot element itself never moves during the partition
     while (true) {
-      while (v[lo].resp > pivot) ++lo;
-      --hi;
-      while (pivot > v[hi].resp) --hi;
+      if (kBatch) {
+        for (;;) {
+          const float a0 = v[lo].resp, a1 = v[lo + 1].resp, a2 = v[lo + 2].resp, a3 = v[lo + 3].resp;
+          if (!(a0 > pivot)) break;
+          if (!(a1 > pivot)) { lo += 1; break; }
+          if (!(a2 > pivot)) { lo += 2; break; }
+          if (!(a3 > pivot)) { lo += 3; break; }
+          lo += 4;
+        }
+        --hi;
+        for (;;) {
+          const float a0 = v[hi].resp, a1 = v[hi - 1].resp, a2 = v[hi - 2].resp, a3 = v[hi - 3].resp;
+          if (!(pivot > a0)) break;
+          if (!(pivot > a1)) { hi -= 1; break; }
+          if (!(pivot > a2)) { hi -= 2; break; }
+          if (!(pivot > a3)) { hi -= 3; break; }
+          hi -= 4;
+        }
+      } else {
+        while (v[lo].resp > pivot) ++lo;
+        --hi;
+        while (pivot > v[hi].resp) --hi;
+      }
       if (!(lo < hi)) break;
       cswap(v, lo, hi);
       ++lo;
@@ -110,8 +134,9 @@ __device__ void nth_element_port(Cand* v, int nth, int n) {
 }
 
 // retainBest(keys, n) followed by resize(n): the first min(n, size) entries survive            (:683-685)
+template <bool kBatch = false>
 __device__ __forceinline__ void retain_best_port(Cand* v, int size, int n, int retain_mode) {
-  if (n > 0 && size > n) nth_element_port(v, retain_mode == ORBX_RETAIN_CV24 ? n : n - 1, size);
+  if (n > 0 && size > n) nth_element_port<kBatch>(v, retain_mode == ORBX_RETAIN_CV24 ? n : n - 1, size);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -215,10 +240,12 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
 #ifndef ORBX_SEL_CAP
 #define ORBX_SEL_CAP 128
 #endif
-constexpr int kSelCap = ORBX_SEL_CAP, kSelStride = kSelCap + 1;
+constexpr int kSelCap = ORBX_SEL_CAP, kSelStride = kSelCap + 5;   // row padding: the batched scans over-read <= 3 records
+constexpr int kSelPad = 4;
 
 __host__ __device__ inline int select_smem_bytes(int list_cap, int ncells) {
-  return (list_cap + 32 * kSelStride) * (int)sizeof(Cand) + 3 * ((ncells + 3) & ~3) * (int)sizeof(int32_t);
+  return (kSelPad + list_cap + kSelPad + 32 * kSelStride + kSelPad) * (int)sizeof(Cand) +
+         3 * ((ncells + 3) & ~3) * (int)sizeof(int32_t);
 }
 
 __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwarps_total, int max_list_cap,
@@ -231,9 +258,9 @@ __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwa
   const int level = gw % P->nlevels, frame = gw / P->nlevels;
   const LevelPlan& L = P->lv[level];
   const int nCells = L.nCells, q = L.quota, retain_mode = P->retain_mode;
-  Cand* s_list = reinterpret_cast<Cand*>(sel_smem);
-  Cand* s_slab = s_list + max_list_cap;
-  int32_t* s_tot = reinterpret_cast<int32_t*>(s_slab + 32 * kSelStride);
+  Cand* s_list = reinterpret_cast<Cand*>(sel_smem) + kSelPad;
+  Cand* s_slab = s_list + max_list_cap + kSelPad;
+  int32_t* s_tot = reinterpret_cast<int32_t*>(s_slab + 32 * kSelStride + kSelPad);
   int32_t* s_ret = s_tot + ((max_cells + 3) & ~3);
   int32_t* s_off = s_ret + ((max_cells + 3) & ~3);
   const int32_t* nTotal = b.n_total + (int64_t)frame * P->total_cells + L.cell_base;
@@ -304,10 +331,10 @@ __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwa
         for (int u = 0; u < 8; u++) row[k + u] = t[u];
       }
       for (; k < tot; k++) row[k] = src[k];
-      nth_element_port(row, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
+      nth_element_port<true>(row, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
       src = row;
     } else if (reorder) {
-      nth_element_port(src, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
+      nth_element_port<false>(src, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
     }
     Cand* dst = s_list + s_off[c];
     int k = 0;
@@ -323,7 +350,7 @@ __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwa
   __syncwarp();
   int count = run;
   if (run > L.nDesired) {                              // level cap retainBest + resize (:697-701)
-    if (lane == 0) retain_best_port(s_list, run, L.nDesired, retain_mode);
+    if (lane == 0) retain_best_port<true>(s_list, run, L.nDesired, retain_mode);
     count = L.nDesired;
   }
   __syncwarp();
