@@ -113,13 +113,22 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
   ORBM_CK(cudaMemsetAsync(d_err, 0, sizeof(int), s));
   if (nq == 0) return ORBM_OK;
   if (ndb == 0) { ORBM_CK(cudaMemsetAsync(d_top2, 0xFF, (size_t)nq * 8, s)); return ORBM_OK; }
-  const int qpt = nq > 2 * kKnnThreads ? 4 : (nq > kKnnThreads ? 2 : 1);
-  const int qtiles = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
-  // chunks: about 2 CTAs per SM over the whole grid; each chunk a whole number of tiles and >= 8 tiles
-  int64_t want = std::max<int64_t>(1, (2 * (int64_t)h->num_sms + qtiles - 1) / qtiles);
-  int64_t chunk_len = (ndb + want - 1) / want;
-  chunk_len = std::max<int64_t>((chunk_len + kKnnTile - 1) / kKnnTile * kKnnTile, 8 * kKnnTile);
-  const int nchunks = (int)((ndb + chunk_len - 1) / chunk_len);
+  // chunks: about 2 CTAs per SM over the whole grid; each chunk a whole number of tiles and >= 8 tiles (the TMA ring
+  // needs a few tiles to reach its steady state).  A database too small to give every SM a CTA that way (frame-to-frame
+  // matching: 1000 x 1000) is latency bound instead: one query per thread and single-tile chunks, which spreads the
+  // same pairs over up to 8 x more CTAs (1000 x 1000: 1 CTA -> 32, 246 -> ~40 us).
+  int qpt = nq > 2 * kKnnThreads ? 4 : (nq > kKnnThreads ? 2 : 1);
+  int qtiles = 0, nchunks = 0;
+  int64_t chunk_len = 0;
+  auto plan = [&](int min_tiles) {
+    qtiles = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
+    const int64_t want = std::max<int64_t>(1, (2 * (int64_t)h->num_sms + qtiles - 1) / qtiles);
+    chunk_len = (ndb + want - 1) / want;
+    chunk_len = std::max<int64_t>((chunk_len + kKnnTile - 1) / kKnnTile * kKnnTile, (int64_t)min_tiles * kKnnTile);
+    nchunks = (int)((ndb + chunk_len - 1) / chunk_len);
+  };
+  plan(8);
+  if ((int64_t)nchunks * qtiles < h->num_sms) { qpt = 1; plan(1); }
   ORBM_CK(h->knn_part.reserve((size_t)nchunks * nq * 8 + 16));
   dim3 grid(nchunks, qtiles);
   const uint4* q4 = reinterpret_cast<const uint4*>(d_q);

@@ -1,5 +1,7 @@
 // Search routines of the matcher (M2, M4, M5, M6, M7, M9): C-ABI entry points + the batched pipeline driver.
 // Kernels: orbm_match_kernels.inl.  Public surface: include/orbm.h.
+#include <cstdlib>
+#include <utility>
 #include <algorithm>
 #include <cstring>
 
@@ -37,6 +39,19 @@ T* carve(uint8_t*& p, size_t n) {
   p += (n * sizeof(T) + 255) / 256 * 256;
   return r;
 }
+// Kernel launch with (optionally) the programmatic-stream-serialization attribute: the chain of six small kernels of a
+// search over a few problems is launch-latency bound, and every kernel starts with ORBM_PDL_ENTRY().
+template <class... KArgs, class... Args>
+void launch_k(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 size_t padded(size_t bytes) { return (bytes + 255) / 256 * 256; }
 
 int run_job(orbm_handle* h, const HostJob& J) {
@@ -56,6 +71,7 @@ int run_job(orbm_handle* h, const HostJob& J) {
   // ---- problem table ------------------------------------------------------------------------------------------
   std::vector<Problem> prob(np);
   int64_t qtot = 0, ttot = 0, ptot = 0;
+  int max_nq = 0, max_nt = 0;   // nq is an upper bound for the BoW kinds (bow_prep writes the exact count)
   const bool per_source = J.kind == K_INIT || J.kind == K_BOW_KF_KF || J.kind == K_TRIANG;
   for (int p = 0; p < np; p++) {
     Problem& P = prob[p];
@@ -82,6 +98,7 @@ int run_job(orbm_handle* h, const HostJob& J) {
     if ((J.kind == K_INIT || J.kind == K_PROJ_FF) && P.nsrc > J.stride) { h->err = "stride smaller than a frame"; return ORBM_ERR_ARG; }
     P.qstart = (int)qtot; P.tstart = (int)ttot; P.cand_base = -1;
     qtot += P.nq; ttot += P.nt;
+    max_nq = std::max(max_nq, P.nq); max_nt = std::max(max_nt, P.nt);
     if (qtot > INT_MAX / 2 || ttot > INT_MAX / 2) { h->err = "batch too large"; return ORBM_ERR_UNSUPPORTED; }
   }
 
@@ -158,23 +175,71 @@ int run_job(orbm_handle* h, const HostJob& J) {
     if (J.kind == K_INIT)  // emit updates prev_xy in place, so a rerun needs the caller's values again
       ORBM_CK(cudaMemcpyAsync(d_xy, J.xy_inout, xy_bytes, cudaMemcpyHostToDevice, st));
     ORBM_CK(cudaEventRecord(h->ev0, st));
-    if (ttot) target_init_kernel<<<(int)((ttot + 255) / 256), 256, 0, st>>>(a, (int)ttot);
+    const bool pdl = np <= 512;   // the latency regime (see the commit choice below)
+    if (ttot) launch_k(pdl, target_init_kernel, dim3((unsigned)((ttot + 255) / 256)), dim3(256), 0, st, a, (int)ttot);
     if (qtot) {
-      if (bow) bow_prep_kernel<<<(np * 32 + 127) / 128, 128, 0, st>>>(a);
-      else grid_prep_kernel<<<(int)((qtot + 255) / 256), 256, 0, st>>>(a, (int)qtot);
+      if (bow) launch_k(pdl, bow_prep_kernel, dim3((np * 32 + 127) / 128), dim3(128), 0, st, a);
+      else launch_k(pdl, grid_prep_kernel, dim3((unsigned)((qtot + 255) / 256)), dim3(256), 0, st, a, (int)qtot);
     }
-    offsets_kernel<<<(np * 32 + 127) / 128, 128, 0, st>>>(a);
+    launch_k(pdl, offsets_kernel, dim3((np * 32 + 127) / 128), dim3(128), 0, st, a);
     if (qtot) {
-      const int blocks = (int)((qtot * 32 + 255) / 256);
-      if (bow) bow_fill_kernel<<<blocks, 256, 0, st>>>(a, (int)qtot);
-      else grid_fill_kernel<<<blocks, 256, 0, st>>>(a, (int)qtot);
+      const unsigned blocks = (unsigned)((qtot * 32 + 255) / 256);
+      if (bow) launch_k(pdl, bow_fill_kernel, dim3(blocks), dim3(256), 0, st, a, (int)qtot);
+      else launch_k(pdl, grid_fill_kernel, dim3(blocks), dim3(256), 0, st, a, (int)qtot);
     }
-    cudaFuncSetAttribute(commit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCommitSmemBytes);
-    commit_kernel<<<(np + kCommitWarps - 1) / kCommitWarps, 32 * kCommitWarps, kCommitSmemBytes, st>>>(a);
-    emit_kernel<<<np, 128, 0, st>>>(a);
+    // commit: the parallel fixed-point kernel (CTA per problem) wherever it applies and its state fits in shared
+    // memory; the in-order replay (warp per problem) for SearchForTriangulation and oversized problems.
+    // ORBM_COMMIT=serial|parallel overrides (experiments / tests).
+    static const char* force_commit = getenv("ORBM_COMMIT");
+    const size_t par_smem = commit_par_smem(max_nq, max_nt);
+    const bool par_ok = J.kind != K_TRIANG && par_smem <= 96 * 1024;
+    // crossover measured with SearchForInitialization on 1000-keypoint pairs: 0.27 vs 0.33 ms at 256 pairs, 0.43 vs
+    // 0.46 at 512, 0.86 vs 0.73 at 1024 (parallel vs replay): the replay's chain is latency, the fixed point is work
+    const bool want_par = force_commit ? force_commit[0] == 'p' : np <= 512;
+    if (par_ok && want_par) {
+      const int threads = np >= 148 * 4 ? 256 : (np >= 148 ? 512 : 1024);
+      cudaFuncSetAttribute(commit_par_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par_smem);
+      launch_k(pdl, commit_par_kernel, dim3(np), dim3(threads), par_smem, st, a, max_nq, max_nt);
+    } else {
+      cudaFuncSetAttribute(commit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCommitSmemBytes);
+      launch_k(pdl, commit_kernel, dim3((np + kCommitWarps - 1) / kCommitWarps), dim3(32 * kCommitWarps), (size_t)kCommitSmemBytes, st, a);
+    }
+    launch_k(pdl, emit_kernel, dim3(np), dim3(128), 0, st, a);
     ORBM_CK(cudaEventRecord(h->ev1, st));
     h->launches += 3 + (ttot ? 1 : 0) + (qtot ? 2 : 0);
     ORBM_CK(cudaGetLastError());
+    // Small jobs (the per-frame calls of a tracker) are latency bound: results and the overflow cursor travel
+    // together into pinned staging and ONE synchronisation ends the call; on overflow the results are simply not
+    // used.  Large jobs keep the two-step form (no extra host copy of megabytes of rows).
+    const size_t small_bytes = 64 + padded(out_bytes) + padded((size_t)np * 4) + padded(xy_bytes);
+    const bool small = small_bytes <= (256u << 10);
+    if (small) {
+      if (h->pinned_cap < small_bytes) {
+        if (h->pinned) cudaFreeHost(h->pinned);
+        h->pinned = nullptr; h->pinned_cap = 0;
+        ORBM_CK(cudaHostAlloc(&h->pinned, 256u << 10, cudaHostAllocDefault));
+        h->pinned_cap = 256u << 10;
+      }
+      uint8_t* hp = static_cast<uint8_t*>(h->pinned);
+      uint8_t* h_out = hp + 64; uint8_t* h_nm = h_out + padded(out_bytes); uint8_t* h_xy = h_nm + padded((size_t)np * 4);
+      ORBM_CK(cudaMemcpyAsync(hp, a.cursor, 16, cudaMemcpyDeviceToHost, st));
+      ORBM_CK(cudaMemcpyAsync(h_out, d_out, out_bytes, cudaMemcpyDeviceToHost, st));
+      ORBM_CK(cudaMemcpyAsync(h_nm, d_nm, (size_t)np * 4, cudaMemcpyDeviceToHost, st));
+      if (J.kind == K_INIT) ORBM_CK(cudaMemcpyAsync(h_xy, d_xy, xy_bytes, cudaMemcpyDeviceToHost, st));
+      ORBM_CK(cudaStreamSynchronize(st));
+      unsigned long long cursor[2];
+      memcpy(cursor, hp, 16);
+      if (!cursor[1]) {
+        memcpy(J.out, h_out, out_bytes);
+        memcpy(J.nmatches, h_nm, (size_t)np * 4);
+        if (J.kind == K_INIT) memcpy(J.xy_inout, h_xy, xy_bytes);
+        cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+        return ORBM_OK;
+      }
+      if (attempt == 2) { h->err = "candidate arena overflow"; return ORBM_ERR_OVERFLOW; }
+      ORBM_CK(h->ws_cand.reserve((size_t)cursor[0] * 4 + 1024));
+      continue;
+    }
     unsigned long long cursor[2] = {0, 0};
     ORBM_CK(cudaMemcpyAsync(cursor, a.cursor, 16, cudaMemcpyDeviceToHost, st));
     ORBM_CK(cudaStreamSynchronize(st));

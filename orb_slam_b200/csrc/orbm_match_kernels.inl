@@ -10,6 +10,13 @@
 //   emit    output rows in the layout of include/orbm.h
 namespace {
 
+// Programmatic dependent launch (see orbx_kernels.cu): first statement of every kernel of the search chain.
+#define ORBM_PDL_ENTRY()                                         \
+  do {                                                           \
+    asm volatile("griddepcontrol.launch_dependents;");           \
+    asm volatile("griddepcontrol.wait;" ::: "memory");           \
+  } while (0)
+
 enum Kind { K_INIT = 0, K_WINDOW, K_PROJ_FF, K_PROJ_LOCAL, K_PROJ_BEST, K_BOW_KF_F, K_BOW_KF_KF, K_TRIANG };
 
 struct Problem {
@@ -84,6 +91,7 @@ __device__ __forceinline__ int find_problem(const Problem* prob, int np, int idx
 
 // per-target state on entry
 __global__ void __launch_bounds__(256) target_init_kernel(SearchArgs a, int ttotal) {
+  ORBM_PDL_ENTRY();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= ttotal) return;
   const Problem& P = a.prob[find_problem(a.prob, a.nproblems, i, true)];
@@ -100,6 +108,7 @@ __global__ void __launch_bounds__(256) target_init_kernel(SearchArgs a, int ttot
 
 // grid family: query record + candidate upper bound (sum of the CSR column ranges of the cell window)
 __global__ void __launch_bounds__(256) grid_prep_kernel(SearchArgs a, int qtotal) {
+  ORBM_PDL_ENTRY();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= qtotal) return;
   const int p = find_problem(a.prob, a.nproblems, i, false);
@@ -152,21 +161,33 @@ __global__ void __launch_bounds__(256) grid_prep_kernel(SearchArgs a, int qtotal
 
 // one warp per problem: exclusive scan of the per-query bounds, block allocation in the shared candidate arena
 __global__ void __launch_bounds__(128) offsets_kernel(SearchArgs a) {
+  ORBM_PDL_ENTRY();
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= a.nproblems) return;
   Problem& P = a.prob[p];
   QRec* q = a.q + P.qstart;
   int run = 0;
-  for (int i0 = 0; i0 < P.nq; i0 += 32) {
-    const int i = i0 + lane;
-    const int n = i < P.nq ? q[i].cnt : 0;
-    int incl = n;
+  for (int i0 = 0; i0 < P.nq; i0 += 128) {      // four consecutive queries per lane: independent loads, one round trip
+    int n[4], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int i = i0 + 4 * lane + k;
+      n[k] = i < P.nq ? q[i].cnt : 0;
+      sum += n[k];
+    }
+    int incl = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const int o = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += o;
     }
-    if (i < P.nq) q[i].off = run + incl - n;
+    int o = run + incl - sum;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int i = i0 + 4 * lane + k;
+      if (i < P.nq) q[i].off = o;
+      o += n[k];
+    }
     run += __shfl_sync(0xffffffffu, incl, 31);
   }
   if (lane == 0) {
@@ -183,6 +204,7 @@ __global__ void __launch_bounds__(128) offsets_kernel(SearchArgs a) {
 // column, CSR order inside a column = Frame::GetFeaturesInArea's order; survivors keep it (ballot prefix) and get
 // their Hamming distance attached.
 __global__ void __launch_bounds__(256) grid_fill_kernel(SearchArgs a, int qtotal) {
+  ORBM_PDL_ENTRY();
   __shared__ int s_pre[8][kGridCols + 1];   // exclusive prefix of the column lengths, [ncol] = total
   __shared__ int s_s0[8][kGridCols];        // CSR start of each column's range
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -251,6 +273,7 @@ __global__ void __launch_bounds__(256) grid_fill_kernel(SearchArgs a, int qtotal
 // BoW family: one warp per problem.  Shared vocabulary nodes in ascending id order (the merge-join of
 // src/ORBmatcher.cc:176-259 visits exactly these); queries = the source features of every shared node, in order.
 __global__ void __launch_bounds__(128) bow_prep_kernel(SearchArgs a) {
+  ORBM_PDL_ENTRY();
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= a.nproblems) return;
   Problem& P = a.prob[p];
@@ -297,6 +320,7 @@ __global__ void __launch_bounds__(128) bow_prep_kernel(SearchArgs a) {
 }
 
 __global__ void __launch_bounds__(256) bow_fill_kernel(SearchArgs a, int qtotal) {
+  ORBM_PDL_ENTRY();
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (i >= qtotal) return;
   const Problem& P = a.prob[find_problem(a.prob, a.nproblems, i, false)];
@@ -346,6 +370,215 @@ __device__ __forceinline__ bool epipolar_ok(float x1, float y1, float x2, float 
 }
 
 
+// What follows the query loop, by ONE warp: rotation histogram over the accept events, ComputeThreeMaxima + removal of
+// the other bins, copy-out of a shared-memory target state (copy_to != nullptr) and the match count.
+__device__ void commit_tail(const SearchArgs& a, Problem& P, int p, QRec* qr, int2* ts, int2* copy_to, int* s_hist_row,
+                            bool use_hist, int lane) {
+  // rotation histogram over the accept events (rotHist[bin].push_back at :665-676 and its siblings), in parallel
+  int hist = 0;                             // lane b (< 30) = rotHist[b].size()
+  if (use_hist) {
+    s_hist_row[lane] = 0;
+    __syncwarp();
+    for (int q = lane; q < P.nq; q += 32) {
+      const int t = qr[q].bin;
+      if (t >= 0) {
+        const int bin = rot_bin(a.src.angle[P.qsrc + qr[q].src], a.s2.angle[P.tbase + t]);
+        qr[q].bin = bin;
+        atomicAdd(&s_hist_row[bin], 1);
+      }
+    }
+    __syncwarp();
+    hist = s_hist_row[lane];
+  }
+  // rotation consistency (ComputeThreeMaxima, src/ORBmatcher.cc:1748-1789) + removal of the other bins
+  if (a.check_ori && use_hist) {
+    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+    for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+      const int sz = __shfl_sync(0xffffffffu, hist, i);
+      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+      else if (sz > max3) { max3 = sz; ind3 = i; }
+    }
+    if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+    for (int q = lane; q < P.nq; q += 32) {
+      const int bin = qr[q].bin;
+      if (bin >= 0 && bin != ind1 && bin != ind2 && bin != ind3 && qr[q].match >= 0) {
+        ts[qr[q].match].x = -1;
+        qr[q].match = -1;
+      }
+    }
+    __syncwarp();
+  }
+  if (copy_to) {
+    for (int i = lane; i < P.nt; i += 32) copy_to[i] = ts[i];
+  }
+  int n = 0;
+  for (int q = lane; q < P.nq; q += 32) n += qr[q].match >= 0;
+  n = __reduce_add_sync(0xffffffffu, n);
+  if (lane == 0) { P.nmatches = n; a.nmatches[p] = n; }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// commit, PARALLEL form (every kind but SearchForTriangulation): one CTA per problem finds the fixed point of the
+// reference's sequential query loop instead of replaying it.
+// The loop-carried state is tiny: a query's decision depends on the earlier queries only through which of ITS candidate
+// targets they accepted (and, for SearchForInitialization, at which distance: `vMatchedDistance[i2] <= dist` skips).
+// Let A(q) be the target query q accepts.  Round 0 evaluates every query against the state on entry; round r + 1
+// evaluates every query q against "state on entry + the accepts A_r(q') of the queries q' < q".  A(q) depends only on
+// A(q' < q), so after round r the first r queries are final and the iteration reaches the sequential result; in
+// practice conflicts are sparse and it stops after a handful of rounds (queries below the first one that changed are
+// final and are not evaluated again).  Each round is fully parallel: warp = query, lanes share its candidate list.
+//   taken kinds   taker[t] = min{q : A(q) = t} (-1: taken on entry); q skips t  <=>  taker[t] < q
+//   K_INIT        the accepts on t form a list (head[t], next[q]); q skips (t, d)  <=>  min{D(q') : q' < q on t} <= d;
+//                 a later accept steals the target: the owner is the LAST accepter, earlier ones lose their match
+//                 (:656-663) but keep their rotation-histogram entry.
+// Shared memory: A, D double-buffered [nq], taker / head [nt], next [nq], base [nt] -> 20 nq + 5 nt bytes.
+// ------------------------------------------------------------------------------------------------------------------
+__host__ __device__ inline size_t commit_par_smem(int max_nq, int max_nt) {
+  return (size_t)((max_nq + 3) & ~3) * 20 + (size_t)((max_nt + 3) & ~3) * 5 + 64;
+}
+
+__global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_nq, int max_nt) {
+  ORBM_PDL_ENTRY();
+  extern __shared__ __align__(16) uint8_t par_smem[];
+  __shared__ int s_hist[32];
+  __shared__ int s_first_changed;
+  const int p = blockIdx.x;
+  Problem& P = a.prob[p];
+  if (P.cand_base < 0) return;  // arena overflow: the host grows the arena and reruns
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nq = P.nq, nt = P.nt;
+  const int qpad = (max_nq + 3) & ~3, tpad = (max_nt + 3) & ~3;
+  int* s_A0 = reinterpret_cast<int*>(par_smem);
+  int* s_A1 = s_A0 + qpad;
+  int* s_D0 = s_A1 + qpad;
+  int* s_D1 = s_D0 + qpad;
+  int* s_next = s_D1 + qpad;
+  int* s_link = s_next + qpad;                 // taker[t] (taken kinds) or head[t] (K_INIT)
+  uint8_t* s_base = reinterpret_cast<uint8_t*>(s_link + tpad);   // 1 = taken on entry
+  QRec* qr = a.q + P.qstart;
+  int2* gts = a.tstate + P.tstart;
+  const uint32_t* cand = a.cand + P.cand_base;
+  const int kind = a.kind;
+  const float ratio = a.ratio;
+  const float kIntMaxF = 2147483648.0f;  // (float)INT_MAX
+  const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL);
+  const int kFree = 0x7fffffff;
+
+  for (int t = tid; t < nt; t += blockDim.x) {
+    const bool taken = gts[t].x != -1;
+    s_base[t] = taken;
+    s_link[t] = kind == K_INIT ? -1 : (taken ? -1 : kFree);
+  }
+  for (int q = tid; q < nq; q += blockDim.x) { s_A0[q] = -1; s_D0[q] = 0; }
+  if (tid == 0) s_first_changed = kFree;
+  __syncthreads();
+
+  int* Aprev = s_A0; int* Dprev = s_D0; int* Acur = s_A1; int* Dcur = s_D1;
+  int first = 0;                                // queries below `first` are final
+  for (;;) {
+    // ---- evaluate queries first .. nq-1 against the accepts of the previous round ---------------------------------
+    // thread = query: a problem has ~10^3 queries with 10^1..10^2 candidates each, so one thread per query keeps every
+    // list walk of the round in flight at once; four candidates are loaded per trip and examined in list order
+    for (int q = first + tid; q < nq; q += blockDim.x) {
+      const int cnt = qr[q].cnt, off = qr[q].off;
+      uint32_t b = kNone, sk = kNone;          // best / second packed (dist, list position) keys
+      int tb = 0, tsec = 0;                    // their targets
+      auto visit = [&](uint32_t e, int j) {
+        const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+        bool skip;
+        if (kind == K_INIT) {                                   // :637  vMatchedDistance[i2] <= dist
+          int dmin = INT_MAX;
+          for (int ev = s_link[t]; ev >= 0; ev = s_next[ev])
+            if (ev < q) dmin = min(dmin, Dprev[ev]);
+          skip = dmin <= d;
+        } else {
+          skip = s_link[t] < q;                                 // `if (taken) continue`
+        }
+        if (!skip) {
+          const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
+          if (key < b) { sk = b; tsec = tb; b = key; tb = t; }
+          else if (key < sk) { sk = key; tsec = t; }
+        }
+      };
+      const uint32_t* cl = cand + off;
+      int j = 0;
+      for (; j + 4 <= cnt; j += 4) {
+        const uint32_t e0 = cl[j], e1 = cl[j + 1], e2 = cl[j + 2], e3 = cl[j + 3];
+        visit(e0, j); visit(e1, j + 1); visit(e2, j + 2); visit(e3, j + 3);
+      }
+      for (; j < cnt; j++) visit(cl[j], j);
+      int accept_t = -1, accept_d = 0;
+      if (b != kNone) {
+        const int bd = (int)(b >> kCandShift), bt = tb;
+        const float sdf = sk == kNone ? kIntMaxF : (float)(int)(sk >> kCandShift);
+        bool ok = false;
+        switch (kind) {
+          case K_INIT: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(sdf, ratio); break;            // :652-654
+          case K_WINDOW: case K_PROJ_FF: ok = (float)bd <= __fmul_rn(sdf, ratio) && bd <= ORBM_TH_HIGH; break;  // :476, :585
+          case K_PROJ_LOCAL:                                                                            // :112-117
+            if (bd <= ORBM_TH_HIGH) {
+              const int l1 = a.s2.octave[P.tbase + bt];
+              const int l2 = sk == kNone ? -1 : a.s2.octave[P.tbase + tsec];
+              ok = !(l1 == l2 && (float)bd > __fmul_rn(ratio, sdf));
+            }
+            break;
+          case K_PROJ_BEST: ok = bd <= a.th_dist; break;                                               // :1576, :1702, :398
+          case K_BOW_KF_F: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;          // :224-226
+          default: ok = bd < ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;                   // :791-793
+        }
+        if (ok) { accept_t = bt; accept_d = bd; }
+      }
+      Acur[q] = accept_t; Dcur[q] = accept_d;
+      if (accept_t != Aprev[q] || accept_d != Dprev[q]) atomicMin(&s_first_changed, q);
+    }
+    __syncthreads();
+    const int changed = s_first_changed;
+    // queries below `first` were not evaluated: carry them over
+    for (int q = tid; q < first; q += blockDim.x) { Acur[q] = Aprev[q]; Dcur[q] = Dprev[q]; }
+    __syncthreads();
+    if (changed == kFree) break;                 // fixed point: Acur == Aprev everywhere
+    // ---- rebuild the per-target view of the accepts ---------------------------------------------------------------
+    for (int t = tid; t < nt; t += blockDim.x) s_link[t] = kind == K_INIT ? -1 : (s_base[t] ? -1 : kFree);
+    __syncthreads();
+    for (int q = tid; q < nq; q += blockDim.x) {
+      const int t = Acur[q];
+      if (t >= 0) {
+        if (kind == K_INIT) s_next[q] = atomicExch(&s_link[t], q);
+        else atomicMin(&s_link[t], q);
+      }
+    }
+    __syncthreads();
+    first = changed;                             // A(q) for q < changed did not change and cannot change any more
+    if (tid == 0) s_first_changed = kFree;       // every thread read it two barriers ago; next use is after the barrier below
+    int* tA = Aprev; Aprev = Acur; Acur = tA;
+    int* tD = Dprev; Dprev = Dcur; Dcur = tD;
+    __syncthreads();
+  }
+  // ---- the final state, written the way the sequential loop leaves it --------------------------------------------------
+  // (s_link / s_next describe Aprev == Acur)
+  for (int q = tid; q < nq; q += blockDim.x) {
+    const int t = Acur[q];
+    int match = t;
+    if (t >= 0) {
+      if (kind == K_INIT) {                      // the last accepter owns the target; earlier ones were robbed
+        int owner = q;
+        for (int ev = s_link[t]; ev >= 0; ev = s_next[ev]) owner = max(owner, ev);
+        if (owner == q) gts[t] = make_int2(qr[q].src, Dcur[q]);
+        else match = -1;
+      } else {
+        gts[t] = make_int2(qr[q].src, Dcur[q]);
+      }
+    }
+    qr[q].match = match;
+    qr[q].bin = (use_hist && t >= 0) ? t : -1;
+  }
+  __threadfence_block();
+  __syncthreads();
+  if (warp == 0) commit_tail(a, P, p, qr, gts, nullptr, s_hist, use_hist, lane);
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // commit: one warp per problem replays the reference's query loop IN ORDER.  For one query the 32 lanes share the
 // candidate list: each evaluates the skip rule against the current state, keeps its own (best, second) packed
@@ -361,6 +594,7 @@ constexpr int kCommitWarps = 2, kCommitSmemTargets = 2048;
 constexpr int kCommitSmemBytes = kCommitWarps * (kCommitSmemTargets * 8 + 2 * 32 * 32 * 4);
 
 __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a) {
+  ORBM_PDL_ENTRY();
   extern __shared__ __align__(16) uint8_t commit_smem[];
   __shared__ int s_hist[kCommitWarps][32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -511,53 +745,12 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 
-  // rotation histogram over the accept events (rotHist[bin].push_back at :665-676 and its siblings), in parallel
-  int hist = 0;                             // lane b (< 30) = rotHist[b].size()
-  if (use_hist) {
-    s_hist[warp][lane] = 0;
-    __syncwarp();
-    for (int q = lane; q < P.nq; q += 32) {
-      const int t = qr[q].bin;
-      if (t >= 0) {
-        const int bin = rot_bin(a.src.angle[P.qsrc + qr[q].src], a.s2.angle[P.tbase + t]);
-        qr[q].bin = bin;
-        atomicAdd(&s_hist[warp][bin], 1);
-      }
-    }
-    __syncwarp();
-    hist = s_hist[warp][lane];
-  }
-  // rotation consistency (ComputeThreeMaxima, src/ORBmatcher.cc:1748-1789) + removal of the other bins
-  if (a.check_ori && use_hist) {
-    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-    for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
-      const int sz = __shfl_sync(0xffffffffu, hist, i);
-      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
-      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
-      else if (sz > max3) { max3 = sz; ind3 = i; }
-    }
-    if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-    else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
-    for (int q = lane; q < P.nq; q += 32) {
-      const int bin = qr[q].bin;
-      if (bin >= 0 && bin != ind1 && bin != ind2 && bin != ind3 && qr[q].match >= 0) {
-        ts[qr[q].match].x = -1;
-        qr[q].match = -1;
-      }
-    }
-    __syncwarp();
-  }
-  if (ts_in_smem) {
-    for (int i = lane; i < P.nt; i += 32) gts[i] = ts[i];
-  }
-  int n = 0;
-  for (int q = lane; q < P.nq; q += 32) n += qr[q].match >= 0;
-  n = __reduce_add_sync(0xffffffffu, n);
-  if (lane == 0) { P.nmatches = n; a.nmatches[p] = n; }
+  commit_tail(a, P, p, qr, ts, ts_in_smem ? gts : nullptr, s_hist[warp], use_hist, lane);
 }
 
 // output rows (include/orbm.h): per-source for K_INIT / K_BOW_KF_KF / K_TRIANG, per-target otherwise
 __global__ void __launch_bounds__(128) emit_kernel(SearchArgs a) {
+  ORBM_PDL_ENTRY();
   const int p = blockIdx.x;
   const Problem& P = a.prob[p];
   int32_t* out = a.out + (int64_t)p * a.stride;
