@@ -295,3 +295,61 @@ def test_cuda_equals_reference_generated_projection_golden(matcher):
         nm, rows = om.SearchByProjection(fs, idx, [cases[i]["points"] for i in idx], variant, th_dist)
         for k, i in enumerate(idx):
             assert nm[k] == cases[i]["ref_n"] and _rows_equal(rows[k], cases[i]["ref_m"]), cases[i]["name"]
+
+
+def _clustered_frame(rng, n, base_desc, nflip, w=640, h=480):
+    """n keypoints packed into a 30 x 30 px patch on one octave with near-identical descriptors: every query wants the
+    same few targets, so the accept / taken / steal logic forms dependency chains as long as the frame."""
+    from types import SimpleNamespace
+    x = rng.uniform(300, 330, n).astype(np.float32); y = rng.uniform(200, 230, n).astype(np.float32)
+    desc = np.repeat(base_desc[None], n, 0).copy()
+    for i in range(n):
+        for b in rng.choice(256, rng.integers(0, nflip + 1), replace=False):
+            desc[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    ang = rng.uniform(0, 360, n).astype(np.float32)
+    return SimpleNamespace(x=x, y=y, angle=ang, octave=np.zeros(n, np.int32), desc=desc, valid=np.zeros(n, np.uint8),
+                           min_x=0.0, min_y=0.0, max_x=float(w), max_y=float(h), featvec=None, n=n)
+
+
+@pytest.mark.parametrize("seed,n", [(0, 300), (1, 700), (2, 64)])
+def test_commit_fixed_point_under_long_dependency_chains(M, matcher, seed, n):
+    """The parallel (fixed-point) commit against the oracle's sequential loop where it has to work hardest: greedy
+    best-only assignment (SearchByProjection 'best', th = 256: every query takes the best FREE target, so query q's
+    result depends on all earlier ones), SearchForInitialization with ratio 1 (steals), WindowSearch."""
+    from orb_slam_b200 import ORBmatcher
+    from orb_slam_b200.matcher import ProjectedPoints
+    rng = np.random.default_rng(100 + seed)
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    f1, f2 = _clustered_frame(rng, n, base, 24), _clustered_frame(rng, n, base, 24)
+    fs = matcher.upload([MD.to_matchframe(f1), MD.to_matchframe(f2)])
+    sf = np.ones(8, np.float32)
+    # greedy best-only assignment: chains of length ~n
+    for ori in (False, True):
+        pts = ProjectedPoints(f1.x, f1.y, np.full(n, 60.0, np.float32), np.zeros(n, np.int32), np.zeros(n, np.int32),
+                              f1.desc, f1.angle, None)
+        om = ORBmatcher(0.9, ori, matcher=matcher)
+        nm, rows = om.SearchByProjection(fs, [1], [pts], "best", 256)
+        on, orow = M.search_by_projection(f2, pts, "best", 256, 0.9, ori)
+        assert nm[0] == on and _rows_equal(rows[0], orow)
+        if not ori:
+            assert on == n                       # everybody ends up with somebody
+    # local-map variant (ratio only when best and second share a level: they always do here)
+    pts = ProjectedPoints(f1.x, f1.y, np.full(n, 60.0, np.float32), np.full(n, -1, np.int32), np.zeros(n, np.int32),
+                          f1.desc, None, None)
+    om = ORBmatcher(0.95, True, matcher=matcher)
+    nm, rows = om.SearchByProjection(fs, [1], [pts], "local_map", 100)
+    on, orow = M.search_by_projection(f2, pts, "local_map", 100, 0.95, True)
+    assert nm[0] == on and _rows_equal(rows[0], orow)
+    # SearchForInitialization with steals, WindowSearch with taken targets
+    for ratio, ori in ((1.0, False), (0.97, True)):
+        om = ORBmatcher(ratio, ori, matcher=matcher)
+        prev = [np.stack([f1.x, f1.y], 1).astype(np.float32)]
+        oprev = prev[0].copy()
+        nm, rows = om.SearchForInitialization(fs, fs, [0], [1], prev, 100)
+        on, orow = M.search_for_initialization(f1, f2, oprev, 100, ratio, ori)
+        assert nm[0] == on and _rows_equal(rows[0], orow) and np.array_equal(prev[0], oprev)
+        g1 = MD.with_valid(f1, np.ones(n, np.uint8))
+        fsv = matcher.upload([MD.to_matchframe(g1), MD.to_matchframe(f2)])
+        nm, rows = om.WindowSearch(fsv, fsv, [0], [1], 100, 0, 7)
+        on, orow = M.window_search(g1, f2, 100, ratio, ori, 0, 7)
+        assert nm[0] == on and _rows_equal(rows[0], orow)
