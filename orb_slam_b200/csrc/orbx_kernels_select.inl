@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// The same selection with every serial chain in SHARED memory: one single-warp CTA per (level, frame).
+// The same selection with every serial chain in SHARED memory: one CTA per (level, frame), one warp per cell.
 // std::nth_element's element order is part of the output, so the partitions stay sequential (one lane per cell, lane 0
 // for the level cap) — what can change is the cost of one dependent step: ~25 cycles in shared memory instead of an
 // L1/L2 round trip.  Single-frame latency of the stage: 90 -> ~20 us; per 10k frames 5.5 -> ~1.5 ms.
@@ -248,12 +248,12 @@ __host__ __device__ inline int select_smem_bytes(int list_cap, int ncells) {
          3 * ((ncells + 3) & ~3) * (int)sizeof(int32_t);
 }
 
-__global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwarps_total, int max_list_cap,
-                                                        int max_cells) {
+__global__ void __launch_bounds__(1024) select_smem_kernel(ChunkBuffers b, int nwarps_total, int max_list_cap,
+                                                          int max_cells) {
   ORBX_PDL_ENTRY();
   extern __shared__ __align__(16) uint8_t sel_smem[];
   const DevicePlan* P = b.plan;
-  const int gw = blockIdx.x, lane = threadIdx.x;
+  const int gw = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
   if (gw >= nwarps_total) return;
   const int level = gw % P->nlevels, frame = gw / P->nlevels;
   const LevelPlan& L = P->lv[level];
@@ -263,17 +263,18 @@ __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwa
   int32_t* s_tot = reinterpret_cast<int32_t*>(s_slab + 32 * kSelStride + kSelPad);
   int32_t* s_ret = s_tot + ((max_cells + 3) & ~3);
   int32_t* s_off = s_ret + ((max_cells + 3) & ~3);
+  __shared__ int s_run;
   const int32_t* nTotal = b.n_total + (int64_t)frame * P->total_cells + L.cell_base;
   int32_t* nToRetain = b.n_retain + (int64_t)frame * P->total_cells + L.cell_base;
   Cand* cand = b.cand + (int64_t)frame * P->cand_per_frame;
   const CellPlan* cells = b.cells + L.cell_base;
 
-  for (int c = lane; c < nCells; c += 32) {
+  for (int c = tid; c < nCells; c += blockDim.x) {
     s_tot[c] = nTotal[c];
     s_off[c] = cells[c].skipped;                       // borrowed until the prefix below
   }
-  __syncwarp();
-  if (lane == 0) {                                     // quota + redistribution, :622-636 / :644-670 (see select_kernel)
+  __syncthreads();
+  if (tid == 0) {                                      // quota + redistribution, :622-636 / :644-670 (see select_kernel)
     int nNoMore = 0, nToDistribute = 0;
     for (int c = 0; c < nCells; c++) {
       const int nKeys = s_tot[c];
@@ -294,69 +295,63 @@ __global__ void __launch_bounds__(32) select_smem_kernel(ChunkBuffers b, int nwa
     for (int c = 0; c < nCells; c++)
       if (s_ret[c] < 0) s_ret[c] = -s_ret[c] - 1;
   }
-  __syncwarp();
-  // exclusive prefix of the survivors per cell -> offsets into the level list
-  int run = 0;
-  for (int c0 = 0; c0 < nCells; c0 += 32) {
-    const int c = c0 + lane;
-    const int n = c < nCells ? min(s_ret[c], s_tot[c]) : 0;
-    if (c < nCells) nToRetain[c] = s_ret[c];
-    int incl = n;
+  __syncthreads();
+  // exclusive prefix of the survivors per cell -> offsets into the level list (warp 0)
+  if (warp == 0) {
+    int run = 0;
+    for (int c0 = 0; c0 < nCells; c0 += 32) {
+      const int c = c0 + lane;
+      const int n = c < nCells ? min(s_ret[c], s_tot[c]) : 0;
+      if (c < nCells) nToRetain[c] = s_ret[c];
+      int incl = n;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int o = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += o;
+      for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      if (c < nCells) s_off[c] = run + incl - n;
+      run += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (c < nCells) s_off[c] = run + incl - n;
-    run += __shfl_sync(0xffffffffu, incl, 31);
+    if (lane == 0) s_run = run;
   }
+  __syncthreads();
+  const int run = s_run;
   if (run > L.list_cap) {
-    if (lane == 0) { atomicExch(b.err_flag, 2); b.kp_count[frame * kMaxLevels + level] = 0; }
+    if (tid == 0) { atomicExch(b.err_flag, 2); b.kp_count[frame * kMaxLevels + level] = 0; }
     return;
   }
-  __syncwarp();
-  // per-cell retainBest (:678-685), one lane per cell, then the survivors into the level list (:687-694)
-  Cand* row = s_slab + lane * kSelStride;
-  for (int c = lane; c < nCells; c += 32) {
+  // per-cell retainBest (:678-685): ONE WARP per cell - the lanes copy the list in and the survivors out, lane 0 runs
+  // the sequential partition.  (A lane per cell made the 30 partitions of a level diverge inside one warp and
+  // serialised them: 33k cycles for this phase; a warp per cell runs them side by side on the SM's schedulers.)
+  Cand* row = s_slab + warp * kSelStride;
+  for (int c = warp; c < nCells; c += nw) {
     const int tot = s_tot[c], ret = s_ret[c], n = min(ret, tot);
     Cand* src = cand + cells[c].cand_off;
     const bool reorder = ret > 0 && tot > ret;
     if (reorder && tot <= kSelCap) {
-      int k = 0;
-      for (; k + 8 <= tot; k += 8) {                   // eight independent loads in flight
-        Cand t[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) t[u] = src[k + u];
-#pragma unroll
-        for (int u = 0; u < 8; u++) row[k + u] = t[u];
-      }
-      for (; k < tot; k++) row[k] = src[k];
-      nth_element_port<true>(row, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
+      for (int k = lane; k < tot; k += 32) row[k] = src[k];
+      __syncwarp();
+      if (lane == 0) nth_element_port<true>(row, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
+      __syncwarp();
       src = row;
     } else if (reorder) {
-      nth_element_port<false>(src, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
+      if (lane == 0) nth_element_port<false>(src, retain_mode == ORBX_RETAIN_CV24 ? ret : ret - 1, tot);
+      __syncwarp();
     }
     Cand* dst = s_list + s_off[c];
-    int k = 0;
-    for (; k + 4 <= n; k += 4) {
-      Cand t[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) t[u] = src[k + u];
-#pragma unroll
-      for (int u = 0; u < 4; u++) dst[k + u] = t[u];
-    }
-    for (; k < n; k++) dst[k] = src[k];
+    for (int k = lane; k < n; k += 32) dst[k] = src[k];
+    __syncwarp();
   }
-  __syncwarp();
+  __syncthreads();
   int count = run;
   if (run > L.nDesired) {                              // level cap retainBest + resize (:697-701)
-    if (lane == 0) retain_best_port<true>(s_list, run, L.nDesired, retain_mode);
+    if (tid == 0) retain_best_port<true>(s_list, run, L.nDesired, retain_mode);
     count = L.nDesired;
+    __syncthreads();
   }
-  __syncwarp();
   Cand* kp = b.kp + (int64_t)frame * P->nfeatures + L.kp_base;
-  for (int k = lane; k < count; k += 32) kp[k] = s_list[k];
-  if (lane == 0) b.kp_count[frame * kMaxLevels + level] = count;
+  for (int k = tid; k < count; k += blockDim.x) kp[k] = s_list[k];
+  if (tid == 0) b.kp_count[frame * kMaxLevels + level] = count;
 }
 
 // Which one: a chunk of a few frames is a handful of warps whose serial chains ARE the stage's latency -> shared memory
@@ -375,7 +370,8 @@ void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cud
   const bool want_smem = force ? force[0] == 's' : nframes <= kSelectSmemMaxFrames;
   if (want_smem && smem <= 160 * 1024) {
     cudaFuncSetAttribute(select_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    launch_k(select_smem_kernel, dim3(nwarps), dim3(32), (size_t)smem, s, b, nwarps, max_list, max_cells);
+    const int warps = std::min(32, std::max(1, max_cells));
+    launch_k(select_smem_kernel, dim3(nwarps), dim3(32 * warps), (size_t)smem, s, b, nwarps, max_list, max_cells);
     return;
   }
   launch_k(select_kernel, dim3((nwarps * 32 + 127) / 128), dim3(128), 0, s, b, nwarps);
