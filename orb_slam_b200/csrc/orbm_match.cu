@@ -192,7 +192,7 @@ int run_job(orbm_handle* h, const HostJob& J) {
     // ORBM_COMMIT=serial|parallel overrides (experiments / tests).
     static const char* force_commit = getenv("ORBM_COMMIT");
     const size_t par_smem = commit_par_smem(max_nq, max_nt);
-    const bool par_ok = J.kind != K_TRIANG && par_smem <= 96 * 1024;
+    const bool par_ok = J.kind != K_TRIANG && par_smem <= 200 * 1024;
     // crossover measured with SearchForInitialization on 1000-keypoint pairs: 0.27 vs 0.33 ms at 256 pairs, 0.43 vs
     // 0.46 at 512, 0.86 vs 0.73 at 1024 (parallel vs replay): the replay's chain is latency, the fixed point is work
     const bool want_par = force_commit ? force_commit[0] == 'p' : np <= 512;

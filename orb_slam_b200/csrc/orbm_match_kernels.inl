@@ -419,6 +419,62 @@ __device__ void commit_tail(const SearchArgs& a, Problem& P, int p, QRec* qr, in
   if (lane == 0) { P.nmatches = n; a.nmatches[p] = n; }
 }
 
+// commit_tail for a whole CTA (commit_par_kernel): the same steps with the query loops spread over all threads; ts is the
+// global target state.  s_hist32: 32 ints, s_misc: 4 ints of shared memory.
+__device__ void commit_tail_cta(const SearchArgs& a, Problem& P, int p, QRec* qr, int2* ts, int* s_hist32, int* s_misc,
+                                bool use_hist) {
+  const int tid = threadIdx.x, lane = tid & 31, nq = P.nq;
+  if (tid < 32) s_hist32[tid] = 0;
+  if (tid < 4) s_misc[tid] = tid == 3 ? 0 : -1;          // ind1, ind2, ind3, match count
+  __syncthreads();
+  if (use_hist) {
+    for (int q = tid; q < nq; q += blockDim.x) {
+      const int t = qr[q].bin;
+      if (t >= 0) {
+        const int bin = rot_bin(a.src.angle[P.qsrc + qr[q].src], a.s2.angle[P.tbase + t]);
+        qr[q].bin = bin;
+        atomicAdd(&s_hist32[bin], 1);
+      }
+    }
+    __syncthreads();
+  }
+  const bool remove = a.check_ori && use_hist;
+  if (remove) {
+    if (tid < 32) {                                       // ComputeThreeMaxima, src/ORBmatcher.cc:1748-1789
+      const int hist = s_hist32[lane];
+      int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+      for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+        const int sz = __shfl_sync(0xffffffffu, hist, i);
+        if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+        else if (sz > max3) { max3 = sz; ind3 = i; }
+      }
+      if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+      else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+      if (lane == 0) { s_misc[0] = ind1; s_misc[1] = ind2; s_misc[2] = ind3; }
+    }
+    __syncthreads();
+  }
+  const int ind1 = s_misc[0], ind2 = s_misc[1], ind3 = s_misc[2];
+  int n = 0;
+  for (int q = tid; q < nq; q += blockDim.x) {
+    int m = qr[q].match;
+    if (remove && m >= 0) {
+      const int bin = qr[q].bin;
+      if (bin >= 0 && bin != ind1 && bin != ind2 && bin != ind3) {
+        ts[m].x = -1;
+        qr[q].match = -1;
+        m = -1;
+      }
+    }
+    n += m >= 0;
+  }
+  n = __reduce_add_sync(0xffffffffu, n);
+  if (lane == 0 && n) atomicAdd(&s_misc[3], n);
+  __syncthreads();
+  if (tid == 0) { P.nmatches = s_misc[3]; a.nmatches[p] = s_misc[3]; }
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // commit, PARALLEL form (every kind but SearchForTriangulation): one CTA per problem finds the fixed point of the
 // reference's sequential query loop instead of replaying it.
@@ -428,26 +484,34 @@ __device__ void commit_tail(const SearchArgs& a, Problem& P, int p, QRec* qr, in
 // evaluates every query q against "state on entry + the accepts A_r(q') of the queries q' < q".  A(q) depends only on
 // A(q' < q), so after round r the first r queries are final and the iteration reaches the sequential result; in
 // practice conflicts are sparse and it stops after a handful of rounds (queries below the first one that changed are
-// final and are not evaluated again).  Each round is fully parallel: warp = query, lanes share its candidate list.
+// final and are not evaluated again).  Each round is fully parallel: thread = query.
 //   taken kinds   taker[t] = min{q : A(q) = t} (-1: taken on entry); q skips t  <=>  taker[t] < q
 //   K_INIT        the accepts on t form a list (head[t], next[q]); q skips (t, d)  <=>  min{D(q') : q' < q on t} <= d;
 //                 a later accept steals the target: the owner is the LAST accepter, earlier ones lose their match
 //                 (:656-663) but keep their rotation-histogram entry.
-// Shared memory: A, D double-buffered [nq], taker / head [nt], next [nq], base [nt] -> 20 nq + 5 nt bytes.
+// A query's decision under ANY state is "the first two candidates, in (distance, list position) order, that the state
+// does not skip", so the candidate lists are walked ONCE: a first pass keeps every query's kParTop smallest keys (and
+// their targets) in shared memory and the rounds only look at those; a query whose cached keys are all skipped while
+// its list holds more (rare) walks the list again.  A round then costs a few shared-memory reads per query, so even a
+// greedy assignment with chains of hundreds of rounds stays cheap.
+// Shared memory: A, D double-buffered [nq], next [nq], top keys / targets [kParTop][nq], flag [nq]; taker / head [nt],
+// base [nt], the round's
+// rescan list [nq]  ->  (25 + 6 kParTop) nq + 5 nt bytes.
 // ------------------------------------------------------------------------------------------------------------------
+constexpr int kParTop = 4;
 __host__ __device__ inline size_t commit_par_smem(int max_nq, int max_nt) {
-  return (size_t)((max_nq + 3) & ~3) * 20 + (size_t)((max_nt + 3) & ~3) * 5 + 64;
+  return (size_t)((max_nq + 3) & ~3) * (25 + 6 * kParTop) + (size_t)((max_nt + 3) & ~3) * 5 + 64;
 }
 
 __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_nq, int max_nt) {
   ORBM_PDL_ENTRY();
   extern __shared__ __align__(16) uint8_t par_smem[];
-  __shared__ int s_hist[32];
-  __shared__ int s_first_changed;
+  __shared__ int s_hist[32], s_misc[4];
+  __shared__ int s_first_changed, s_nres;
   const int p = blockIdx.x;
   Problem& P = a.prob[p];
   if (P.cand_base < 0) return;  // arena overflow: the host grows the arena and reruns
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   const int nq = P.nq, nt = P.nt;
   const int qpad = (max_nq + 3) & ~3, tpad = (max_nt + 3) & ~3;
   int* s_A0 = reinterpret_cast<int*>(par_smem);
@@ -455,8 +519,12 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
   int* s_D0 = s_A1 + qpad;
   int* s_D1 = s_D0 + qpad;
   int* s_next = s_D1 + qpad;
-  int* s_link = s_next + qpad;                 // taker[t] (taken kinds) or head[t] (K_INIT)
-  uint8_t* s_base = reinterpret_cast<uint8_t*>(s_link + tpad);   // 1 = taken on entry
+  int* s_res = s_next + qpad;                  // queries of this round whose cached keys were all skipped
+  uint32_t* s_key = reinterpret_cast<uint32_t*>(s_res + qpad);  // [kParTop][qpad] smallest keys of each query, ascending
+  int* s_link = reinterpret_cast<int*>(s_key + kParTop * qpad);   // taker[t] (taken kinds) or head[t] (K_INIT)
+  uint16_t* s_tgt = reinterpret_cast<uint16_t*>(s_link + tpad);   // [kParTop][qpad] their targets
+  uint8_t* s_more = reinterpret_cast<uint8_t*>(s_tgt + kParTop * qpad);   // [qpad] the list holds more than kParTop eligible
+  uint8_t* s_base = s_more + qpad;                                 // [tpad] 1 = taken on entry
   QRec* qr = a.q + P.qstart;
   int2* gts = a.tstate + P.tstart;
   const uint32_t* cand = a.cand + P.cand_base;
@@ -472,43 +540,59 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
     s_link[t] = kind == K_INIT ? -1 : (taken ? -1 : kFree);
   }
   for (int q = tid; q < nq; q += blockDim.x) { s_A0[q] = -1; s_D0[q] = 0; }
-  if (tid == 0) s_first_changed = kFree;
+  if (tid == 0) { s_first_changed = kFree; s_nres = 0; }
+  __syncthreads();
+
+  // ---- first pass: every query's kParTop smallest keys among the candidates that are not taken on entry -------------
+  // (a target taken on entry never becomes free; for K_INIT nothing is excluded on entry)
+  for (int q = tid; q < nq; q += blockDim.x) {
+    const int cnt = qr[q].cnt;
+    const uint32_t* cl = cand + qr[q].off;
+    uint32_t k0 = kNone, k1 = kNone, k2 = kNone, k3 = kNone;
+    int t0 = 0, t1 = 0, t2 = 0, t3 = 0, eligible = 0;
+    auto put = [&](uint32_t e, int j) {
+      const int t = (int)(e & kCandMask);
+      if (kind != K_INIT && s_base[t]) return;
+      eligible++;
+      const uint32_t key = (e & ~(uint32_t)kCandMask) | (uint32_t)j;   // (dist << kCandShift) | list position
+      if (key < k3) {                                                   // insertion into the ascending quadruple
+        if (key < k2) {
+          k3 = k2; t3 = t2;
+          if (key < k1) {
+            k2 = k1; t2 = t1;
+            if (key < k0) { k1 = k0; t1 = t0; k0 = key; t0 = t; } else { k1 = key; t1 = t; }
+          } else { k2 = key; t2 = t; }
+        } else { k3 = key; t3 = t; }
+      }
+    };
+    int j = 0;
+    for (; j + 4 <= cnt; j += 4) {
+      const uint32_t e0 = cl[j], e1 = cl[j + 1], e2 = cl[j + 2], e3 = cl[j + 3];
+      put(e0, j); put(e1, j + 1); put(e2, j + 2); put(e3, j + 3);
+    }
+    for (; j < cnt; j++) put(cl[j], j);
+    s_key[q] = k0; s_key[qpad + q] = k1; s_key[2 * qpad + q] = k2; s_key[3 * qpad + q] = k3;
+    s_tgt[q] = (uint16_t)t0; s_tgt[qpad + q] = (uint16_t)t1; s_tgt[2 * qpad + q] = (uint16_t)t2; s_tgt[3 * qpad + q] = (uint16_t)t3;
+    s_more[q] = eligible > kParTop;
+  }
   __syncthreads();
 
   int* Aprev = s_A0; int* Dprev = s_D0; int* Acur = s_A1; int* Dcur = s_D1;
   int first = 0;                                // queries below `first` are final
   for (;;) {
     // ---- evaluate queries first .. nq-1 against the accepts of the previous round ---------------------------------
-    // thread = query: a problem has ~10^3 queries with 10^1..10^2 candidates each, so one thread per query keeps every
-    // list walk of the round in flight at once; four candidates are loaded per trip and examined in list order
-    for (int q = first + tid; q < nq; q += blockDim.x) {
-      const int cnt = qr[q].cnt, off = qr[q].off;
-      uint32_t b = kNone, sk = kNone;          // best / second packed (dist, list position) keys
-      int tb = 0, tsec = 0;                    // their targets
-      auto visit = [&](uint32_t e, int j) {
-        const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
-        bool skip;
-        if (kind == K_INIT) {                                   // :637  vMatchedDistance[i2] <= dist
-          int dmin = INT_MAX;
-          for (int ev = s_link[t]; ev >= 0; ev = s_next[ev])
-            if (ev < q) dmin = min(dmin, Dprev[ev]);
-          skip = dmin <= d;
-        } else {
-          skip = s_link[t] < q;                                 // `if (taken) continue`
-        }
-        if (!skip) {
-          const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
-          if (key < b) { sk = b; tsec = tb; b = key; tb = t; }
-          else if (key < sk) { sk = key; tsec = t; }
-        }
-      };
-      const uint32_t* cl = cand + off;
-      int j = 0;
-      for (; j + 4 <= cnt; j += 4) {
-        const uint32_t e0 = cl[j], e1 = cl[j + 1], e2 = cl[j + 2], e3 = cl[j + 3];
-        visit(e0, j); visit(e1, j + 1); visit(e2, j + 2); visit(e3, j + 3);
+    // thread = query; the cached keys are in (distance, list position) order, so the first two that the state does not
+    // skip are the loop's best and second best
+    auto skipped = [&](int q, int t, int d) -> bool {
+      if (kind == K_INIT) {                                     // :637  vMatchedDistance[i2] <= dist
+        int dmin = INT_MAX;
+        for (int ev = s_link[t]; ev >= 0; ev = s_next[ev])
+          if (ev < q) dmin = min(dmin, Dprev[ev]);
+        return dmin <= d;
       }
-      for (; j < cnt; j++) visit(cl[j], j);
+      return s_link[t] < q;                                     // `if (taken) continue`
+    };
+    auto decide = [&](int q, uint32_t b, uint32_t sk, int tb, int tsec) -> bool {
       int accept_t = -1, accept_d = 0;
       if (b != kNone) {
         const int bd = (int)(b >> kCandShift), bt = tb;
@@ -531,7 +615,63 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
         if (ok) { accept_t = bt; accept_d = bd; }
       }
       Acur[q] = accept_t; Dcur[q] = accept_d;
-      if (accept_t != Aprev[q] || accept_d != Dprev[q]) atomicMin(&s_first_changed, q);
+      return accept_t != Aprev[q] || accept_d != Dprev[q];
+    };
+    // (whole warps walk the query range together so that the two shared counters get ONE atomic per warp: a thousand
+    // threads hitting the same shared word cost more than the evaluation itself)
+    for (int qb = first + (tid - lane); qb < nq; qb += blockDim.x) {
+      const int q = qb + lane;
+      bool rescan = false, changed_q = false;
+      if (q < nq) {
+        uint32_t b = kNone, sk = kNone;        // best / second packed (dist, list position) keys
+        int tb = 0, tsec = 0;                  // their targets
+        bool exhausted = true;                 // ran through the cache without finding two
+#pragma unroll
+        for (int k = 0; k < kParTop; k++) {
+          const uint32_t key = s_key[k * qpad + q];
+          if (key == kNone) { exhausted = false; break; }        // the list itself ended
+          const int t = s_tgt[k * qpad + q];
+          if (!skipped(q, t, (int)(key >> kCandShift))) {
+            if (b == kNone) { b = key; tb = t; }
+            else { sk = key; tsec = t; exhausted = false; break; }
+          }
+        }
+        rescan = exhausted && s_more[q];       // walk the whole list below, a warp per query
+        if (!rescan) changed_q = decide(q, b, sk, tb, tsec);
+      }
+      const unsigned rm = __ballot_sync(0xffffffffu, rescan);
+      if (rm) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&s_nres, __popc(rm));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (rescan) s_res[base + __popc(rm & ((1u << lane) - 1))] = q;
+      }
+      const int fc = __reduce_min_sync(0xffffffffu, changed_q ? q : kFree);
+      if (lane == 0 && fc != kFree) atomicMin(&s_first_changed, fc);
+    }
+    __syncthreads();
+    // the (few) queries whose cached keys did not settle the matter: lanes share the list, packed-key reduce
+    const int nres = s_nres;
+    for (int r = warp; r < nres; r += nwarps) {
+      const int q = s_res[r];
+      const int cnt = qr[q].cnt;
+      const uint32_t* cl = cand + qr[q].off;
+      uint32_t b = kNone, sk = kNone;
+      int tb = 0, tsec = 0;
+      for (int j = lane; j < cnt; j += 32) {
+        const uint32_t e = cl[j];
+        const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+        if (!skipped(q, t, d)) {
+          const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
+          if (key < b) { sk = b; tsec = tb; b = key; tb = t; }
+          else if (key < sk) { sk = key; tsec = t; }
+        }
+      }
+      const uint32_t gb = __reduce_min_sync(0xffffffffu, b);
+      const uint32_t gs = __reduce_min_sync(0xffffffffu, b == gb ? sk : b);
+      const int bt = __shfl_sync(0xffffffffu, tb, (int)(gb & 31u));          // list position j lives on lane j % 32
+      const int t2 = __shfl_sync(0xffffffffu, b == gs ? tb : tsec, (int)(gs & 31u));
+      if (lane == 0 && decide(q, gb, gs, bt, t2)) atomicMin(&s_first_changed, q);
     }
     __syncthreads();
     const int changed = s_first_changed;
@@ -551,7 +691,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
     }
     __syncthreads();
     first = changed;                             // A(q) for q < changed did not change and cannot change any more
-    if (tid == 0) s_first_changed = kFree;       // every thread read it two barriers ago; next use is after the barrier below
+    if (tid == 0) { s_first_changed = kFree; s_nres = 0; }   // all threads read them barriers ago; next use is after the barrier below
     int* tA = Aprev; Aprev = Acur; Acur = tA;
     int* tD = Dprev; Dprev = Dcur; Dcur = tD;
     __syncthreads();
@@ -576,7 +716,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
   }
   __threadfence_block();
   __syncthreads();
-  if (warp == 0) commit_tail(a, P, p, qr, gts, nullptr, s_hist, use_hist, lane);
+  commit_tail_cta(a, P, p, qr, gts, s_hist, s_misc, use_hist);
 }
 
 // ------------------------------------------------------------------------------------------------------------------

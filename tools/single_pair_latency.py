@@ -8,7 +8,7 @@ import matchdata as MD
 from orb_slam_b200 import Matcher, ORBmatcher
 from orb_slam_b200.matcher import ProjectedPoints
 m = Matcher(0)
-f1, f2, _ = MD.make_pair(O, 3)
+f1, f2, (dx, dy) = MD.make_pair(O, 3)
 F1, F2 = MD.to_matchframe(f1), MD.to_matchframe(f2)
 def t(fn, reps=200):
     for _ in range(10): fn()
@@ -25,7 +25,7 @@ om = ORBmatcher(0.9, True, matcher=m)
 prev = [np.stack([f1.x, f1.y], 1).astype(np.float32)]
 print("SearchForInitialization, 1 pair: %.1f us (kernels %.1f us)" % (t(lambda: om.SearchForInitialization(fs, fs, [0], [1], [prev[0].copy()], 100)), m.last_kernel_ms() * 1e3))
 sf = np.cumprod(np.concatenate([[1.0], np.full(7, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
-pts = ProjectedPoints.for_last_frame(f1.x - 5, f1.y + 3, f1.octave, f1.desc, f1.angle, sf, 15.0)
+pts = ProjectedPoints.for_last_frame(f1.x - dx, f1.y - dy, f1.octave, f1.desc, f1.angle, sf, 15.0)   # true motion of the pair
 om2 = ORBmatcher(0.9, True, matcher=m)
 print("SearchByProjection (last frame), 1 problem: %.1f us (kernels %.1f us)" % (t(lambda: om2.SearchByProjection(fs, [1], [pts], "best", 100)), m.last_kernel_ms() * 1e3))
 om3 = ORBmatcher(0.75, True, matcher=m)
