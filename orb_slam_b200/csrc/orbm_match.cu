@@ -118,6 +118,26 @@ int run_job(orbm_handle* h, const HostJob& J) {
   float* d_xy = xy_bytes ? carve<float>(cur, (size_t)np * J.stride * 2) : nullptr;
   float* d_F12 = carve<float>(cur, (size_t)np * 9);
   float* d_sigma = carve<float>(cur, 64);
+  // Small jobs: every host input (problem table, prev_xy / uv rows, F12, sigma2, the point arrays) is gathered in pinned
+  // staging that mirrors the device layout and goes up in TWO copies instead of up to a dozen pageable ones; the
+  // first 256 KB of the staging area receive the results (see the read-back below).
+  constexpr size_t kStageOut = 256u << 10, kStageProb = 32u << 10, kStageTotal = 1u << 20;
+  uint8_t* const in_base = reinterpret_cast<uint8_t*>(d_xy ? d_xy : d_F12);
+  const size_t in_span = (h->ws_io.as<uint8_t>() + io) - in_base;
+  const bool staged = in_span <= kStageTotal - kStageOut - kStageProb && sizeof(Problem) * (size_t)np <= kStageProb;
+  if (h->pinned_cap < kStageTotal) {
+    if (h->pinned) cudaFreeHost(h->pinned);
+    h->pinned = nullptr; h->pinned_cap = 0;
+    ORBM_CK(cudaHostAlloc(&h->pinned, kStageTotal, cudaHostAllocDefault));
+    h->pinned_cap = kStageTotal;
+  }
+  uint8_t* const stg_prob = static_cast<uint8_t*>(h->pinned) + kStageOut;
+  uint8_t* const stg_in = stg_prob + kStageProb;
+  auto h2d = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+    if (!bytes) return cudaSuccess;
+    if (staged) { memcpy(stg_in + (static_cast<uint8_t*>(dst) - in_base), src, bytes); return cudaSuccess; }
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+  };
 
   SearchArgs a;
   memset(&a, 0, sizeof(a));
@@ -130,12 +150,18 @@ int run_job(orbm_handle* h, const HostJob& J) {
   a.check_ori = J.check_ori; a.th_dist = J.th_dist; a.ratio = J.ratio; a.nlevels = J.nlevels;
   a.out = d_out; a.nmatches = d_nm; a.qxy = d_xy; a.out_xy = d_xy; a.F12 = d_F12; a.sigma2 = d_sigma;
 
-  ORBM_CK(cudaMemcpyAsync(a.prob, prob.data(), sizeof(Problem) * np, cudaMemcpyHostToDevice, st));
-  if (J.kind == K_PROJ_FF) ORBM_CK(cudaMemcpyAsync(d_xy, J.xy_in, xy_bytes, cudaMemcpyHostToDevice, st));
+  if (staged) {
+    memcpy(stg_prob, prob.data(), sizeof(Problem) * np);
+    ORBM_CK(cudaMemcpyAsync(a.prob, stg_prob, sizeof(Problem) * np, cudaMemcpyHostToDevice, st));
+  } else {
+    ORBM_CK(cudaMemcpyAsync(a.prob, prob.data(), sizeof(Problem) * np, cudaMemcpyHostToDevice, st));
+  }
+  if (J.kind == K_PROJ_FF) ORBM_CK(h2d(d_xy, J.xy_in, xy_bytes));
+  if (J.kind == K_INIT) ORBM_CK(h2d(d_xy, J.xy_inout, xy_bytes));
   if (J.kind == K_TRIANG) {
     if (!J.F12 || !J.sigma2 || J.nlevels < 1 || J.nlevels > 64) { h->err = "bad F12 / sigma2"; return ORBM_ERR_ARG; }
-    ORBM_CK(cudaMemcpyAsync(d_F12, J.F12, (size_t)np * 36, cudaMemcpyHostToDevice, st));
-    ORBM_CK(cudaMemcpyAsync(d_sigma, J.sigma2, (size_t)J.nlevels * 4, cudaMemcpyHostToDevice, st));
+    ORBM_CK(h2d(d_F12, J.F12, (size_t)np * 36));
+    ORBM_CK(h2d(d_sigma, J.sigma2, (size_t)J.nlevels * 4));
   }
   std::vector<uint8_t> pvalid;  // must outlive the async copies below (synchronised before return)
   if (points) {
@@ -149,16 +175,16 @@ int run_job(orbm_handle* h, const HostJob& J) {
       const orbm_points& pt = J.points[p];
       const size_t o = prob[p].qsrc, n = pt.n;
       if (!n) continue;
-      ORBM_CK(cudaMemcpyAsync(d_desc + o * 32, pt.desc, n * 32, cudaMemcpyHostToDevice, st));
-      ORBM_CK(cudaMemcpyAsync(d_u + o, pt.u, n * 4, cudaMemcpyHostToDevice, st));
-      ORBM_CK(cudaMemcpyAsync(d_v + o, pt.v, n * 4, cudaMemcpyHostToDevice, st));
-      ORBM_CK(cudaMemcpyAsync(d_r + o, pt.radius, n * 4, cudaMemcpyHostToDevice, st));
-      ORBM_CK(cudaMemcpyAsync(d_minl + o, pt.min_level, n * 4, cudaMemcpyHostToDevice, st));
-      ORBM_CK(cudaMemcpyAsync(d_maxl + o, pt.max_level, n * 4, cudaMemcpyHostToDevice, st));
-      if (pt.angle) ORBM_CK(cudaMemcpyAsync(d_ang + o, pt.angle, n * 4, cudaMemcpyHostToDevice, st));
+      ORBM_CK(h2d(d_desc + o * 32, pt.desc, n * 32));
+      ORBM_CK(h2d(d_u + o, pt.u, n * 4));
+      ORBM_CK(h2d(d_v + o, pt.v, n * 4));
+      ORBM_CK(h2d(d_r + o, pt.radius, n * 4));
+      ORBM_CK(h2d(d_minl + o, pt.min_level, n * 4));
+      ORBM_CK(h2d(d_maxl + o, pt.max_level, n * 4));
+      if (pt.angle) ORBM_CK(h2d(d_ang + o, pt.angle, n * 4));
       if (pt.valid) memcpy(&pvalid[o], pt.valid, n);
     }
-    if (ptot) ORBM_CK(cudaMemcpyAsync(d_valid, pvalid.data(), ptot, cudaMemcpyHostToDevice, st));
+    if (ptot) ORBM_CK(h2d(d_valid, pvalid.data(), ptot));
     a.src.desc = reinterpret_cast<const uint4*>(d_desc); a.src.angle = d_ang; a.src.valid = d_valid;
     a.pu = d_u; a.pv = d_v; a.pr = d_r; a.pminl = d_minl; a.pmaxl = d_maxl;
   } else {
@@ -166,14 +192,17 @@ int run_job(orbm_handle* h, const HostJob& J) {
     a.src.octave = a.s1.octave; a.src.valid = a.s1.valid;
   }
 
+  if (staged) ORBM_CK(cudaMemcpyAsync(in_base, stg_in, in_span, cudaMemcpyHostToDevice, st));
+
   // ---- kernels (rerun with a larger arena if the candidate lists do not fit) ---------------------------------------
   if (h->ws_cand.cap == 0) ORBM_CK(h->ws_cand.reserve(std::max<size_t>((size_t)qtot * 64 * 4, 4u << 20)));
   for (int attempt = 0; attempt < 3; attempt++) {
     a.cand = h->ws_cand.as<uint32_t>();
     a.cand_cap = (int64_t)(h->ws_cand.cap / 4);
     ORBM_CK(cudaMemsetAsync(a.cursor, 0, 16, st));
-    if (J.kind == K_INIT)  // emit updates prev_xy in place, so a rerun needs the caller's values again
-      ORBM_CK(cudaMemcpyAsync(d_xy, J.xy_inout, xy_bytes, cudaMemcpyHostToDevice, st));
+    if (J.kind == K_INIT && (attempt > 0 || !staged))  // emit updates prev_xy in place: a rerun needs the caller's values again
+      ORBM_CK(cudaMemcpyAsync(d_xy, staged ? static_cast<const void*>(stg_in + (reinterpret_cast<uint8_t*>(d_xy) - in_base))
+                                           : static_cast<const void*>(J.xy_inout), xy_bytes, cudaMemcpyHostToDevice, st));
     ORBM_CK(cudaEventRecord(h->ev0, st));
     const bool pdl = np <= 512;   // the latency regime (see the commit choice below)
     if (ttot) launch_k(pdl, target_init_kernel, dim3((unsigned)((ttot + 255) / 256)), dim3(256), 0, st, a, (int)ttot);
@@ -214,12 +243,6 @@ int run_job(orbm_handle* h, const HostJob& J) {
     const size_t small_bytes = 64 + padded(out_bytes) + padded((size_t)np * 4) + padded(xy_bytes);
     const bool small = small_bytes <= (256u << 10);
     if (small) {
-      if (h->pinned_cap < small_bytes) {
-        if (h->pinned) cudaFreeHost(h->pinned);
-        h->pinned = nullptr; h->pinned_cap = 0;
-        ORBM_CK(cudaHostAlloc(&h->pinned, 256u << 10, cudaHostAllocDefault));
-        h->pinned_cap = 256u << 10;
-      }
       uint8_t* hp = static_cast<uint8_t*>(h->pinned);
       uint8_t* h_out = hp + 64; uint8_t* h_nm = h_out + padded(out_bytes); uint8_t* h_xy = h_nm + padded((size_t)np * 4);
       ORBM_CK(cudaMemcpyAsync(hp, a.cursor, 16, cudaMemcpyDeviceToHost, st));
