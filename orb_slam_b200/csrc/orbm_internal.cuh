@@ -55,8 +55,9 @@ struct orbm_handle {
   orbm::DevBuf stage_a, stage_b, stage_c;  // staging for host-pointer entry points
   orbm::DevBuf ws_problem, ws_query, ws_target, ws_cand, ws_misc, ws_io;
   orbm::DevBuf ws_bow;       // per-keypoint descent results + uncompacted per-frame vectors (orbm_bow.cu)
-  void* pinned = nullptr;    // pinned host staging for small result read-backs
+  void* pinned = nullptr;    // pinned host staging (1 MB): small inputs go up / small results come back through it
   size_t pinned_cap = 0;
+  cudaEvent_t ev_order = nullptr;   // orders the handle's stream behind a caller's stream (created on first use)
 };
 
 // Device-resident frames: concatenated SoA + per-frame offsets + grids (+ optional feature vectors).
@@ -93,6 +94,15 @@ template <class T> inline cudaError_t orbm_alloc(orbm_handle* h, T** p, size_t b
   return cudaMallocAsync(reinterpret_cast<void**>(p), bytes, h->stream);
 }
 inline void orbm_free(orbm_handle* h, void* p) { if (p) cudaFreeAsync(p, h->stream); }
+constexpr size_t kOrbmPinnedBytes = 1u << 20;
+inline cudaError_t orbm_ensure_pinned(orbm_handle* h) {
+  if (h->pinned_cap >= kOrbmPinnedBytes) return cudaSuccess;
+  if (h->pinned) cudaFreeHost(h->pinned);
+  h->pinned = nullptr; h->pinned_cap = 0;
+  const cudaError_t e = cudaHostAlloc(&h->pinned, kOrbmPinnedBytes, cudaHostAllocDefault);
+  if (e == cudaSuccess) h->pinned_cap = kOrbmPinnedBytes;
+  return e;
+}
 
 #define ORBM_CK(call)                                                          \
   do {                                                                         \

@@ -53,6 +53,7 @@ extern "C" void orbm_destroy(orbm_handle* h) {
                     &h->ws_target, &h->ws_cand, &h->ws_misc, &h->ws_io, &h->ws_bow};
   for (DevBuf* b : bufs) b->release();
   if (h->pinned) cudaFreeHost(h->pinned);
+  if (h->ev_order) cudaEventDestroy(h->ev_order);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);

@@ -125,12 +125,8 @@ int run_job(orbm_handle* h, const HostJob& J) {
   uint8_t* const in_base = reinterpret_cast<uint8_t*>(d_xy ? d_xy : d_F12);
   const size_t in_span = (h->ws_io.as<uint8_t>() + io) - in_base;
   const bool staged = in_span <= kStageTotal - kStageOut - kStageProb && sizeof(Problem) * (size_t)np <= kStageProb;
-  if (h->pinned_cap < kStageTotal) {
-    if (h->pinned) cudaFreeHost(h->pinned);
-    h->pinned = nullptr; h->pinned_cap = 0;
-    ORBM_CK(cudaHostAlloc(&h->pinned, kStageTotal, cudaHostAllocDefault));
-    h->pinned_cap = kStageTotal;
-  }
+  static_assert(kStageTotal == kOrbmPinnedBytes, "staging layout");
+  ORBM_CK(orbm_ensure_pinned(h));
   uint8_t* const stg_prob = static_cast<uint8_t*>(h->pinned) + kStageOut;
   uint8_t* const stg_in = stg_prob + kStageProb;
   auto h2d = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
