@@ -212,12 +212,12 @@ int run_job(orbm_handle* h, const HostJob& J) {
       if (bow) launch_k(pdl, bow_fill_kernel, dim3(blocks), dim3(256), 0, st, a, (int)qtot);
       else launch_k(pdl, grid_fill_kernel, dim3(blocks), dim3(256), 0, st, a, (int)qtot);
     }
-    // commit: the parallel fixed-point kernel (CTA per problem) wherever it applies and its state fits in shared
-    // memory; the in-order replay (warp per problem) for SearchForTriangulation and oversized problems.
+    // commit: the parallel fixed-point kernel (CTA per problem) for small jobs whose state fits in shared memory;
+    // the in-order replay (warp per problem) for large jobs and oversized problems.
     // ORBM_COMMIT=serial|parallel overrides (experiments / tests).
     static const char* force_commit = getenv("ORBM_COMMIT");
     const size_t par_smem = commit_par_smem(max_nq, max_nt);
-    const bool par_ok = J.kind != K_TRIANG && par_smem <= 200 * 1024;
+    const bool par_ok = par_smem <= 200 * 1024;
     // crossover measured with SearchForInitialization on 1000-keypoint pairs: 0.27 vs 0.33 ms at 256 pairs, 0.43 vs
     // 0.46 at 512, 0.86 vs 0.73 at 1024 (parallel vs replay): the replay's chain is latency, the fixed point is work
     const bool want_par = force_commit ? force_commit[0] == 'p' : np <= 512;

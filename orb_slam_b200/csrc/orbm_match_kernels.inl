@@ -476,7 +476,7 @@ __device__ void commit_tail_cta(const SearchArgs& a, Problem& P, int p, QRec* qr
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// commit, PARALLEL form (every kind but SearchForTriangulation): one CTA per problem finds the fixed point of the
+// commit, PARALLEL form: one CTA per problem finds the fixed point of the
 // reference's sequential query loop instead of replaying it.
 // The loop-carried state is tiny: a query's decision depends on the earlier queries only through which of ITS candidate
 // targets they accepted (and, for SearchForInitialization, at which distance: `vMatchedDistance[i2] <= dist` skips).
@@ -533,6 +533,9 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
   const float kIntMaxF = 2147483648.0f;  // (float)INT_MAX
   const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL);
   const int kFree = 0x7fffffff;
+  float F[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (kind == K_TRIANG)
+    for (int k = 0; k < 9; k++) F[k] = a.F12[(int64_t)p * 9 + k];
 
   for (int t = tid; t < nt; t += blockDim.x) {
     const bool taken = gts[t].x != -1;
@@ -553,8 +556,10 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
     auto put = [&](uint32_t e, int j) {
       const int t = (int)(e & kCandMask);
       if (kind != K_INIT && s_base[t]) return;
+      if (kind == K_TRIANG && (int)(e >> kCandShift) > ORBM_TH_LOW) return;        // :918-921
       eligible++;
-      const uint32_t key = (e & ~(uint32_t)kCandMask) | (uint32_t)j;   // (dist << kCandShift) | list position
+      // (dist << kCandShift) | list position; SearchForTriangulation sorts by (dist, idx2), which the entry itself is
+      const uint32_t key = kind == K_TRIANG ? e : ((e & ~(uint32_t)kCandMask) | (uint32_t)j);
       if (key < k3) {                                                   // insertion into the ascending quadruple
         if (key < k2) {
           k3 = k2; t3 = t2;
@@ -573,7 +578,20 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
     for (; j < cnt; j++) put(cl[j], j);
     s_key[q] = k0; s_key[qpad + q] = k1; s_key[2 * qpad + q] = k2; s_key[3 * qpad + q] = k3;
     s_tgt[q] = (uint16_t)t0; s_tgt[qpad + q] = (uint16_t)t1; s_tgt[2 * qpad + q] = (uint16_t)t2; s_tgt[3 * qpad + q] = (uint16_t)t3;
-    s_more[q] = eligible > kParTop;
+    uint32_t flags = eligible > kParTop ? 1u : 0u;
+    if (kind == K_TRIANG) {                    // the epipolar test does not depend on the state: once per cached key
+      const int src = qr[q].src;
+      const float x1 = a.src.x[P.qsrc + src], y1 = a.src.y[P.qsrc + src];
+      const uint32_t ks[kParTop] = {k0, k1, k2, k3};
+#pragma unroll
+      for (int k = 0; k < kParTop; k++) {
+        if (ks[k] == kNone) break;
+        const int gt = P.tbase + (int)(ks[k] & kCandMask);
+        const int lvl = min(max(a.s2.octave[gt], 0), a.nlevels - 1);
+        if (epipolar_ok(x1, y1, a.s2.x[gt], a.s2.y[gt], F, a.sigma2[lvl])) flags |= 2u << k;
+      }
+    }
+    s_more[q] = (uint8_t)flags;               // bit 0: the list holds more eligible entries; bits 1..: epipolar test passed
   }
   __syncthreads();
 
@@ -617,12 +635,34 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
       Acur[q] = accept_t; Dcur[q] = accept_d;
       return accept_t != Aprev[q] || accept_d != Dprev[q];
     };
+    auto store = [&](int q, int accept_t, int accept_d) -> bool {
+      Acur[q] = accept_t; Dcur[q] = accept_d;
+      return accept_t != Aprev[q] || accept_d != Dprev[q];
+    };
     // (whole warps walk the query range together so that the two shared counters get ONE atomic per warp: a thousand
     // threads hitting the same shared word cost more than the evaluation itself)
     for (int qb = first + (tid - lane); qb < nq; qb += blockDim.x) {
       const int q = qb + lane;
       bool rescan = false, changed_q = false;
-      if (q < nq) {
+      if (q < nq && kind == K_TRIANG) {
+        // SearchForTriangulation :896-958: the free candidates (dist <= TH_LOW) in (dist, idx2) order; the first free one
+        // fixes the bound 2 * dist; the first one within the bound that passes the epipolar test wins
+        const uint32_t flags = s_more[q];
+        int accept_t = -1, accept_d = 0, dist_th = -1;
+        bool open = true;                      // undecided after the cached keys
+#pragma unroll
+        for (int k = 0; k < kParTop; k++) {
+          const uint32_t key = s_key[k * qpad + q];
+          if (key == kNone) { open = false; break; }             // the list itself ended: no match
+          const int t = (int)(key & kCandMask), d = (int)(key >> kCandShift);
+          if (s_link[t] < q) continue;                            // vbMatched2 / already a MapPoint
+          if (dist_th < 0) dist_th = 2 * d;
+          if (d > dist_th) { open = false; break; }
+          if (flags & (2u << k)) { accept_t = t; accept_d = d; open = false; break; }
+        }
+        rescan = open && (flags & 1u);
+        if (!rescan) changed_q = store(q, accept_t, accept_d);
+      } else if (q < nq) {
         uint32_t b = kNone, sk = kNone;        // best / second packed (dist, list position) keys
         int tb = 0, tsec = 0;                  // their targets
         bool exhausted = true;                 // ran through the cache without finding two
@@ -636,7 +676,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
             else { sk = key; tsec = t; exhausted = false; break; }
           }
         }
-        rescan = exhausted && s_more[q];       // walk the whole list below, a warp per query
+        rescan = exhausted && (s_more[q] & 1);   // walk the whole list below, a warp per query
         if (!rescan) changed_q = decide(q, b, sk, tb, tsec);
       }
       const unsigned rm = __ballot_sync(0xffffffffu, rescan);
@@ -656,6 +696,32 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
       const int q = s_res[r];
       const int cnt = qr[q].cnt;
       const uint32_t* cl = cand + qr[q].off;
+      if (kind == K_TRIANG) {                  // the ordered walk of commit_kernel, against the round's taker view
+        int accept_t = -1, accept_d = 0, dist_th = 0;
+        uint32_t last = 0;
+        bool first_free = true;
+        const int src = qr[q].src;
+        const float x1 = a.src.x[P.qsrc + src], y1 = a.src.y[P.qsrc + src];
+        while (true) {
+          uint32_t mn = kNone;
+          for (int j = lane; j < cnt; j += 32) {
+            const uint32_t e = cl[j];
+            const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
+            if (d <= ORBM_TH_LOW && !(s_link[t] < q) && (first_free || e > last)) mn = min(mn, e);
+          }
+          mn = __reduce_min_sync(0xffffffffu, mn);
+          if (mn == kNone) break;
+          const int d = (int)(mn >> kCandShift), t = (int)(mn & kCandMask);
+          if (first_free) { dist_th = 2 * d; first_free = false; }
+          if (d > dist_th) break;
+          const int gt = P.tbase + t;
+          const int lvl = min(max(a.s2.octave[gt], 0), a.nlevels - 1);
+          if (epipolar_ok(x1, y1, a.s2.x[gt], a.s2.y[gt], F, a.sigma2[lvl])) { accept_t = t; accept_d = d; break; }
+          last = mn;
+        }
+        if (lane == 0 && store(q, accept_t, accept_d)) atomicMin(&s_first_changed, q);
+        continue;
+      }
       uint32_t b = kNone, sk = kNone;
       int tb = 0, tsec = 0;
       for (int j = lane; j < cnt; j += 32) {

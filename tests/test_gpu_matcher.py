@@ -353,3 +353,25 @@ def test_commit_fixed_point_under_long_dependency_chains(M, matcher, seed, n):
         nm, rows = om.WindowSearch(fsv, fsv, [0], [1], 100, 0, 7)
         on, orow = M.window_search(g1, f2, 100, ratio, ori, 0, 7)
         assert nm[0] == on and _rows_equal(rows[0], orow)
+
+
+@pytest.mark.parametrize("seed,n,ori", [(0, 300, False), (1, 500, True)])
+def test_triangulation_fixed_point_under_long_dependency_chains(M, matcher, seed, n, ori):
+    """SearchForTriangulation through the fixed-point commit where every query competes for the same targets: all
+    keypoints in three vocabulary nodes, near-identical descriptors (every candidate within TH_LOW), an epipolar test
+    that passes for roughly half of the pairs."""
+    from orb_slam_b200 import ORBmatcher
+    rng = np.random.default_rng(200 + seed)
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    f1, f2 = _clustered_frame(rng, n, base, 20), _clustered_frame(rng, n, base, 20)
+    f1.featvec = MD.synth_featvec(f1.desc, nnodes=3, seed=1)
+    f2.featvec = MD.synth_featvec(f2.desc, nnodes=3, seed=1)
+    f1.valid = MD.random_valid(n, 0.1, 5 + seed); f2.valid = MD.random_valid(n, 0.1, 6 + seed)
+    fs = matcher.upload([MD.to_matchframe(f1), MD.to_matchframe(f2)])
+    sigma2 = np.full(8, 4.0, np.float32)
+    t = np.array([7.0, -3.0, 0.0]) + 1e-3
+    F12 = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]], np.float32) * np.float32(0.05)
+    om = ORBmatcher(0.6, ori, matcher=matcher)
+    nm, rows = om.SearchForTriangulation(fs, fs, [0], [1], F12[None], sigma2)
+    on, orow = M.search_for_triangulation(f1, f2, F12, sigma2, ori)
+    assert nm[0] == on and _rows_equal(rows[0], orow) and on > 20

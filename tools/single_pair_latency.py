@@ -33,3 +33,10 @@ fs.set_valid(0, np.ones(F1.n, np.uint8))
 print("SearchByBoW kf_f, 1 pair: %.1f us (kernels %.1f us)" % (t(lambda: om3.SearchByBoW(fs, fs, [0], [1], "kf_f")), m.last_kernel_ms() * 1e3))
 q = f1.desc; db = f2.desc
 print("knn2 1000 x 1000: %.1f us (kernels %.1f us)" % (t(lambda: m.knn2(q, db)), m.last_kernel_ms() * 1e3))
+# SearchForTriangulation, one keyframe pair (LocalMapping::CreateNewMapPoints, one neighbour)
+fv1 = MD.with_valid(f1, MD.random_valid(f1.n, 0.3, 60)); fv2 = MD.with_valid(f2, MD.random_valid(f2.n, 0.3, 70))
+fst = m.upload([MD.to_matchframe(fv1), MD.to_matchframe(fv2)])
+tvec = np.array([dx, dy, 0.0]) + 1e-3
+F12 = np.array([[0, -tvec[2], tvec[1]], [tvec[2], 0, -tvec[0]], [-tvec[1], tvec[0], 0]], np.float32) * np.float32(0.05)
+om4 = ORBmatcher(0.6, False, matcher=m)
+print("SearchForTriangulation, 1 pair: %.1f us (kernels %.1f us)" % (t(lambda: om4.SearchForTriangulation(fst, fst, [0], [1], F12[None], (sf * sf).astype(np.float32))), m.last_kernel_ms() * 1e3))
