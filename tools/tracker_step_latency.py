@@ -33,4 +33,13 @@ sf = np.cumprod(np.concatenate([[1.0], np.full(7, np.float32(1.2))]).astype(np.f
 pts = ProjectedPoints.for_last_frame(x + 3, y - 2, octv, desc, ang, sf, 15.0)
 om = ORBmatcher(0.9, True, matcher=m)
 c = t(lambda: om.SearchByProjection(fs, [0], [pts], "best", 100))
+from oracle import bow_oracle as B
+from orb_slam_b200 import ORBVocabulary
+V = B.synth_vocabulary_fast(k=10, L=6, seed=3)
+voc = ORBVocabulary.from_arrays(m, **{k: V[k] for k in ("k", "L", "scoring", "weighting", "parent", "desc", "weight", "is_leaf")})
+d = t(lambda: fs.compute_bow(voc, 4))
+om5 = ORBmatcher(0.75, True, matcher=m)
+fs.set_valid(0, np.ones(fs.frame_n(0), np.uint8))
+e = t(lambda: om5.SearchByBoW(fs, fs, [0], [0], "kf_f"))
+print("ComputeBoW (k=10, L=6 vocabulary, 1 frame) %.1f us | SearchByBoW against itself %.1f us" % (d, e))
 print("extract (device in/out) %.1f us | frame set from extractor %.1f us | SearchByProjection 1000 points %.1f us | step %.1f us" % (a, b, c, a + b + c))
