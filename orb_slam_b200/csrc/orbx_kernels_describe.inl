@@ -98,6 +98,12 @@ __device__ __forceinline__ void cp_async4(uint32_t dst_smem, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(__cvta_generic_to_global(src)) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// u8 x s8 dot product (IDP.4A)
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -106,12 +112,25 @@ __global__ void __launch_bounds__(32 * kDescWarps, 4) describe_kernel(ChunkBuffe
                                                                      int nslots_total) {
   __shared__ __align__(16) uint8_t s_buf[kDescWarps][2][kDescBufBytes];
   __shared__ float2 s_pat[16 * 32];            // [j][lane] = pattern point 16 * lane + j
+  __shared__ uint32_t s_icm[8 * 32];           // [w][lane]: disc row v = lane - 15, byte k = 0xff iff column 4w+k-15 is inside
   const DevicePlan* P = b.plan;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   asm volatile("griddepcontrol.launch_dependents;");
   for (int t = threadIdx.x; t < 512; t += 32 * kDescWarps) {   // constant table: legal before the dependency wait
     const int pl = t & 31, pj = t >> 5, pt = 16 * pl + pj;
     s_pat[t] = make_float2((float)d_pattern[2 * pt], (float)d_pattern[2 * pt + 1]);
+  }
+  {
+    const int t = threadIdx.x, w = t >> 5, l = t & 31;         // 256 threads = 8 words x 32 lanes
+    uint32_t wm = 0;
+    if (l < 31) {
+      const int um = kUmax[l < kHalfPatch ? kHalfPatch - l : l - kHalfPatch];
+      for (int k = 0; k < 4; k++) {
+        const int u = 4 * w + k - kHalfPatch;
+        if ((u < 0 ? -u : u) <= um) wm |= 0xffu << (8 * k);
+      }
+    }
+    s_icm[t] = wm;
   }
   asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
@@ -206,30 +225,37 @@ __global__ void __launch_bounds__(32 * kDescWarps, 4) describe_kernel(ChunkBuffe
     const LevelPlan& L = P->lv[level];
     // ---- E7 IC_Angle (:124-151): m10 = sum u*I, m01 = sum v*I over the 749-px disc, UNBLURRED level
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
+    if (r.flags & 4) {
+      // lane = ROW v of the staged window: its 9 words are shifted to start at column -15 and masked to the disc, then
+      // every word is two dot products (ones -> row sum, column numbers -> sum of u * I), 4 pixels per IDP
+      const uint32_t* row = reinterpret_cast<const uint32_t*>(buf + kBlurBufBytes) + min(lane, kRawRows - 1) * kRawWords;
+      uint32_t d[kRawWords];
+#pragma unroll
+      for (int w = 0; w < kRawWords; w++) d[w] = row[w];
+      const int sh = ((r.mis >> 8) & 3) * 8;
+      uint32_t rowsum = 0;
+#pragma unroll
+      for (int w = 0; w < 8; w++) {
+        const uint32_t x = __funnelshift_r(d[w], d[w + 1], sh) & s_icm[w * 32 + lane];
+        const int u0 = 4 * w - kHalfPatch;                     // columns u0 .. u0 + 3 as signed bytes
+        const uint32_t cols = (uint32_t)(u0 & 0xff) | ((uint32_t)((u0 + 1) & 0xff) << 8) |
+                              ((uint32_t)((u0 + 2) & 0xff) << 16) | ((uint32_t)((u0 + 3) & 0xff) << 24);
+        rowsum = __dp4a(x, 0x01010101u, rowsum);
+        m10 = dp4a_us(x, cols, m10);
+      }
+      m01 = (lane - kHalfPatch) * (int)rowsum;
+    } else if (lane < 31) {
       const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
       int colsum = 0;
-      if (r.flags & 4) {
-        const uint8_t* c = buf + kBlurBufBytes + kHalfPatch * kRawPitch + ((r.mis >> 8) & 3) + lane;
+      int pitch;
+      const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
+      const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
 #pragma unroll
-        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-          if (au <= kUmax[v < 0 ? -v : v]) {
-            const int I = c[v * kRawPitch];
-            colsum += I;
-            m01 += v * I;
-          }
-        }
-      } else {
-        int pitch;
-        const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
-        const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
-#pragma unroll
-        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-          if (au <= kUmax[v < 0 ? -v : v]) {
-            const int I = c[v * pitch];
-            colsum += I;
-            m01 += v * I;
-          }
+      for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+        if (au <= kUmax[v < 0 ? -v : v]) {
+          const int I = c[v * pitch];
+          colsum += I;
+          m01 += v * I;
         }
       }
       m10 = u * colsum;
