@@ -197,7 +197,10 @@ __global__ void __launch_bounds__(32 * kDescWarps, 4) describe_kernel(ChunkBuffe
         }
         int pitch;
         const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
-        if ((pitch & 3) == 0) {     // the window's misalignment is then the same on every row
+        // (a cell grid whose ceil() overshoots the border puts corners closer than 15 px to the right / bottom edge:
+        // their disc reaches the reference's reflect-101 frame (:806-814) and takes the per-pixel path in stage C)
+        if ((pitch & 3) == 0 && cx >= kHalfPatch && cx + kHalfPatch < lw && cy >= kHalfPatch && cy + kHalfPatch < lh) {
+          // the window's misalignment is the same on every row
           const uint8_t* w0 = img + (int64_t)(cy - kHalfPatch) * pitch + (cx - kHalfPatch);
           const int mis = (int)((uintptr_t)w0 & 3);
           const uint8_t* src = w0 - mis;
@@ -249,13 +252,25 @@ __global__ void __launch_bounds__(32 * kDescWarps, 4) describe_kernel(ChunkBuffe
       int colsum = 0;
       int pitch;
       const uint8_t* img = level_ptr(b, P, level, frame, &pitch);
-      const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
+      if (cx >= kHalfPatch && cx + kHalfPatch < L.w && cy >= kHalfPatch && cy + kHalfPatch < L.h) {   // warp-uniform
+        const uint8_t* c = img + (int64_t)cy * pitch + cx + u;
 #pragma unroll
-      for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-        if (au <= kUmax[v < 0 ? -v : v]) {
-          const int I = c[v * pitch];
-          colsum += I;
-          m01 += v * I;
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+          if (au <= kUmax[v < 0 ? -v : v]) {
+            const int I = c[v * pitch];
+            colsum += I;
+            m01 += v * I;
+          }
+        }
+      } else {                                                  // the disc reaches the reflect-101 frame of the level
+        const uint8_t* c = img + reflect101(cx + u, L.w);
+#pragma unroll 1
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+          if (au <= kUmax[v < 0 ? -v : v]) {
+            const int I = c[(int64_t)reflect101(cy + v, L.h) * pitch];
+            colsum += I;
+            m01 += v * I;
+          }
         }
       }
       m10 = u * colsum;

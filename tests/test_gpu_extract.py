@@ -52,6 +52,33 @@ def test_stagewise_parity(oracle, cfg):
     _cmp_final(k, d, ok, od)
 
 
+@pytest.mark.parametrize("w,h,nf,sf,nl,st,th,seed", [
+    (459, 193, 2000, 1.2, 6, 0, 3, 21000),      # level 5 (184x78): 9 rows of ceil(46 / 9) = 6 px overshoot H = 46
+    (459, 193, 2000, 1.2, 6, 1, 20, 5),
+    (1331, 79, 500, 1.5, 2, 1, 20, 7),          # ratio 16.8: 33 one-pixel rows over H = 21
+])
+def test_cell_grid_overshooting_the_border(oracle, w, h, nf, sf, nl, st, th, seed):
+    """ceil() in the cell size (:539-540) lets the rows before the last one run past maxBorderY: corners closer than
+    15 px to the bottom edge, whose IC_Angle disc and BRIEF pattern read the reference's reflect-101 frame (:806-814).
+    Found by tools/fuzz_extract_parity.py."""
+    img = oracle.synth(h, w, seed)
+    O = oracle.OracleExtractor(nf, sf, nl, st, th)
+    ok, od = O(img)
+    scale = O.tables()[1]
+    near = 0
+    for l in range(nl):
+        lw, lh = O.level_size(l)
+        m = ok["octave"] == l
+        near += int(((np.rint(ok["x"][m] / scale[l]) > lw - 16) | (np.rint(ok["y"][m] / scale[l]) > lh - 16)).sum())
+    assert near > 0, "the scene no longer exercises the overshoot"
+    ex = _ex(nfeatures=nf, scaleFactor=sf, nlevels=nl, scoreType=st, fastTh=th, max_width=w, max_height=h, max_batch=2)
+    k, d = ex(img)
+    _cmp_final(k, d, ok, od)
+    kps, desc, n = ex.extract_batch(np.stack([img, img, img]))
+    for i in range(3):
+        _cmp_final(kps[i, :n[i]], desc[i, :n[i]], ok, od)
+
+
 def test_cell_candidates(oracle):
     """Per-cell FAST candidates (after NMS and the th=7 retry rule) equal cv::FAST's per-cell output as a set; their
     row-major ORDER is what std::nth_element later depends on and is covered by the end-to-end order parity."""
