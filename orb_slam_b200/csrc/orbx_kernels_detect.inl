@@ -33,6 +33,28 @@ __device__ float harris_response(const uint8_t* p, int step) {
   return __fmul_rn(r, s4);
 }
 
+// The same for a corner closer than 4 px to the level's edge (a cell grid whose ceil() overshoots the border, see
+// describe_kernel): the 9x9 support reaches the reference's reflect-101 frame (:806-814).
+__device__ __noinline__ float harris_response_edge(const uint8_t* img, int step, int x, int y, int w, int h) {
+  uint8_t v[9][9];
+  for (int i = 0; i < 9; i++)
+    for (int j = 0; j < 9; j++) v[i][j] = img[(int64_t)reflect101(y + i - 4, h) * step + reflect101(x + j - 4, w)];
+  int a = 0, b = 0, c = 0;
+  for (int i = 1; i <= 7; i++)
+    for (int j = 1; j <= 7; j++) {
+      const int Ix = (v[i][j + 1] - v[i][j - 1]) * 2 + (v[i - 1][j + 1] - v[i - 1][j - 1]) + (v[i + 1][j + 1] - v[i + 1][j - 1]);
+      const int Iy = (v[i + 1][j] - v[i - 1][j]) * 2 + (v[i + 1][j - 1] - v[i - 1][j - 1]) + (v[i + 1][j + 1] - v[i - 1][j + 1]);
+      a += Ix * Ix; b += Iy * Iy; c += Ix * Iy;
+    }
+  float scale = __fmul_rn((float)(1 << 2) * 7, 255.0f);
+  scale = __fdiv_rn(1.0f, scale);
+  const float s4 = __fmul_rn(__fmul_rn(__fmul_rn(scale, scale), scale), scale);
+  const float fa = (float)a, fb = (float)b, fc = (float)c;
+  const float apb = __fadd_rn(fa, fb);
+  const float r = __fsub_rn(__fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc)), __fmul_rn(__fmul_rn(0.04f, apb), apb));
+  return __fmul_rn(r, s4);
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // One CTA per (cell, frame): FAST score of the cell's scored region, 3x3 strict NMS that never looks outside the
 // region (the reference runs cv::FAST per cell sub-image, :599-607), the "<= 3 corners -> redo with threshold 7"
@@ -177,6 +199,9 @@ struct FastLevels {
   int64_t off[kMaxLevels];
 };
 
+// kHarris: the Harris-score build carries the response code (and its rare reflect-101 variant, a real call); the
+// FAST-score build, the default and the benchmarked one, is free of it
+template <bool kHarris>
 __global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads) fast_cells_kernel(ChunkBuffers b, FastLevels fl) {
   ORBX_PDL_ENTRY();
   extern __shared__ __align__(16) uint8_t smem[];
@@ -404,8 +429,14 @@ __global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads) fast_cells_
         bits &= bits - 1;
         const int lx = c.x0 + x;
         Cand r;
-        r.resp = fl.score_type == ORBX_HARRIS_SCORE ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
-                                                    : (float)s_sc[(y + 1) * scp + 4 + x];
+        if constexpr (kHarris) {
+          const LevelPlan& LP = b.plan->lv[c.level];
+          r.resp = (lx >= 4 && ly >= 4 && lx + 4 < LP.w && ly + 4 < LP.h)
+                       ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
+                       : harris_response_edge(img, pitch, lx, ly, LP.w, LP.h);
+        } else {
+          r.resp = (float)s_sc[(y + 1) * scp + 4 + x];
+        }
         r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
         out[off++] = r;
       }
@@ -417,14 +448,15 @@ __global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads) fast_cells_
 
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s) {
   // per-device attributes; a few microseconds per chunk of up to max_batch frames
-  cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  auto* kern = hp.score_type == ORBX_HARRIS_SCORE ? fast_cells_kernel<true> : fast_cells_kernel<false>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   FastLevels fl;
   fl.fast_th = hp.fast_th; fl.score_type = hp.score_type; fl.total_cells = hp.total_cells;
   fl.cand_per_frame = hp.cand_per_frame; fl.frame_bytes = hp.pyr_frame_bytes;
   for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
   dim3 grid(hp.total_cells, nframes);
-  launch_k(fast_cells_kernel, grid, dim3(kFastThreads), (size_t)smem_bytes, s, b, fl);
+  launch_k(kern, grid, dim3(kFastThreads), (size_t)smem_bytes, s, b, fl);
 }
 
 }  // namespace orbx
