@@ -261,6 +261,19 @@ int orbm_knn2(orbm_handle* h, const uint8_t* q, int nq, const uint8_t* db, int64
               uint32_t* top2); /* HOST buffers */
 int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int64_t idx_base,
                      uint32_t* d_top2, void* stream); /* DEVICE buffers, asynchronous */
+/* orbm_knn2_device for callers that may not allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same result as orbm_knn2_device; the per-chunk partial keys and the error flag live in
+ * a file-scope device array of ORBM_KNN2_STATIC_SCRATCH_BYTES (held by every GPU that loads the library until exit)
+ * instead of the handle's grown-on-demand buffers, so the call issues no cudaMalloc / cudaFree / allocating routine.
+ * Limit: 256 + nchunks * nq * 8 bytes must fit the array (nchunks = database chunks of the launch plan, about
+ * 2 * SMs / ceil(nq / 1024)); on a 148-SM B200 that holds for every nq <= 200,000 whatever ndb is.  Beyond it the
+ * call returns ORBM_ERR_UNSUPPORTED with a message and launches nothing.  All calls on one device share the array:
+ * calls that overlap on the GPU (different streams, no ordering) race; calls on one stream are safe.  The first
+ * call on a device looks the array's address up (cudaGetSymbolAddress) - make it once before capturing a graph. */
+#define ORBM_KNN2_STATIC_SCRATCH_BYTES (4u << 20)
+int orbm_knn2_device_static(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                            int64_t idx_base, uint32_t* d_top2, void* stream);
 /* Merge of per-shard results d_gathered [nshards][nq][2] (the all-gather receive buffer) into d_top2 [nq][2], plus
  * the accept rule of :224-226: d_match[q] = best index if best <= th_dist && (float)best < ratio * (float)second,
  * else -1 (d_match may be NULL). */

@@ -4,6 +4,8 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include "orbm_internal.cuh"
 
@@ -283,4 +285,96 @@ extern "C" int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, con
   const int nrc = nccl->AllGather(d_local, d_gathered, (size_t)nq * 2, ncclUint32, comm, s);
   if (nrc != 0) { h->err = "ncclAllGather failed with code " + std::to_string(nrc); return ORBM_ERR_COMM; }
   return orbm_merge_top2_device(h, d_gathered, nranks, nq, th_dist, ratio, d_top2, d_match, s);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// orbm_knn2_device_static: the 2-NN of orbm_knn2_device for callers that may not allocate (CUDA graph capture, tight
+// serving loops).  No counterpart in the reference.  The per-chunk
+// partial keys and the error flag live in a file-scope device array instead of the handle's grown-on-demand buffers,
+// so the call issues no cudaMalloc / cudaFree / cudaMallocAsync.  Every GPU that loads the library holds the array
+// until exit; every call on a device shares it (calls that overlap on the GPU race: serialise them on one stream).
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kKnnStaticFlagBytes = 256;  // error flag (first int), keeps the key area 256-byte aligned
+static __device__ __align__(256) unsigned char g_knn_static_scratch[ORBM_KNN2_STATIC_SCRATCH_BYTES];
+
+constexpr int kKnnStaticMaxDev = 64;
+std::mutex g_knn_static_mu;
+unsigned char* g_knn_static_ptr[kKnnStaticMaxDev] = {};  // DEVICE address of the array on each device (set up once)
+
+// The array's name is only a host-side stand-in here: the device address comes from cudaGetSymbolAddress, looked up
+// once per device with that device current.
+int knn_static_setup(orbm_handle* h, unsigned char** out) {
+  if (h->device < 0 || h->device >= kKnnStaticMaxDev) { h->err = "device ordinal beyond the static scratch table"; return ORBM_ERR_UNSUPPORTED; }
+  std::lock_guard<std::mutex> lk(g_knn_static_mu);
+  if (!g_knn_static_ptr[h->device]) {
+    void* p = nullptr;
+    ORBM_CK(cudaGetSymbolAddress(&p, g_knn_static_scratch));
+    if (!p) { h->err = "cudaGetSymbolAddress returned a null address"; return ORBM_ERR_CUDA; }
+    g_knn_static_ptr[h->device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_knn_static_ptr[h->device];
+  return ORBM_OK;
+}
+
+}  // namespace
+
+extern "C" int orbm_knn2_device_static(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                       int64_t idx_base, uint32_t* d_top2, void* stream) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!d_q || !d_db || !d_top2 || nq < 0 || ndb < 0 || idx_base < 0) {
+    h->err = "null pointer or negative size";
+    return ORBM_ERR_ARG;
+  }
+  if (idx_base + ndb > (1 << 23)) {
+    h->err = "idx_base + ndb exceeds the 2^23 index range of the packed keys";
+    return ORBM_ERR_UNSUPPORTED;
+  }
+  if (((uintptr_t)d_q | (uintptr_t)d_db) & 15) { h->err = "descriptor arrays must be 16-byte aligned"; return ORBM_ERR_ARG; }
+  ORBM_CK(cudaSetDevice(h->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  unsigned char* scratch = nullptr;
+  const int rc = knn_static_setup(h, &scratch);
+  if (rc != ORBM_OK) return rc;
+  if (nq == 0) return ORBM_OK;
+  if (ndb == 0) { ORBM_CK(cudaMemsetAsync(d_top2, 0xFF, (size_t)nq * 8, s)); return ORBM_OK; }
+  // the chunk plan of knn2_launch (same grid => same partial keys => same result)
+  int qpt = nq > 2 * kKnnThreads ? 4 : (nq > kKnnThreads ? 2 : 1);
+  int qtiles = 0, nchunks = 0;
+  int64_t chunk_len = 0;
+  auto plan = [&](int min_tiles) {
+    qtiles = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
+    const int64_t want = std::max<int64_t>(1, (2 * (int64_t)h->num_sms + qtiles - 1) / qtiles);
+    chunk_len = (ndb + want - 1) / want;
+    chunk_len = std::max<int64_t>((chunk_len + kKnnTile - 1) / kKnnTile * kKnnTile, (int64_t)min_tiles * kKnnTile);
+    nchunks = (int)((ndb + chunk_len - 1) / chunk_len);
+  };
+  plan(8);
+  if ((int64_t)nchunks * qtiles < h->num_sms) { qpt = 1; plan(1); }
+  const size_t need = kKnnStaticFlagBytes + (size_t)nchunks * (size_t)nq * 8;
+  if (need > (size_t)ORBM_KNN2_STATIC_SCRATCH_BYTES) {
+    h->err = "orbm_knn2_device_static: " + std::to_string(nchunks) + " chunks x " + std::to_string(nq) +
+             " queries need " + std::to_string(need) + " bytes of scratch, the static array holds " +
+             std::to_string((size_t)ORBM_KNN2_STATIC_SCRATCH_BYTES) + " (use orbm_knn2_device, or fewer queries per call)";
+    return ORBM_ERR_UNSUPPORTED;
+  }
+  int* d_err = reinterpret_cast<int*>(scratch);
+  uint32_t* part = reinterpret_cast<uint32_t*>(scratch + kKnnStaticFlagBytes);
+  // the array keeps the previous call's contents: the flag must start at zero; every (chunk, query) key pair of the
+  // part area read by the merge is written by this call's knn2 CTAs
+  ORBM_CK(cudaMemsetAsync(d_err, 0, sizeof(int), s));
+  dim3 grid(nchunks, qtiles);
+  const uint4* q4 = reinterpret_cast<const uint4*>(d_q);
+  const uint4* db4 = reinterpret_cast<const uint4*>(d_db);
+  const int cl = (int)chunk_len;
+  const uint32_t ib = (uint32_t)idx_base;
+  if (qpt == 4) knn2_kernel<4, 2><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  else if (qpt == 2) knn2_kernel<2, 2><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  else knn2_kernel<1, 2><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err);
+  merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(part), nchunks, nq, 0, 0.f,
+                                                    reinterpret_cast<uint2*>(d_top2), nullptr);
+  h->launches += 2;
+  ORBM_CK(cudaGetLastError());
+  return ORBM_OK;
 }

@@ -101,6 +101,7 @@ def _bind(L):
     L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_knn2.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp]
     L.orbm_knn2_device.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp, vp]
+    L.orbm_knn2_device_static.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp, vp]
     L.orbm_merge_top2_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, f32, vp, vp, vp]
     L.orbm_knn2_sharded.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, C.c_int, vp, vp, C.c_int, f32, vp, vp, vp]
     L._orbm_bound = True
@@ -237,6 +238,10 @@ class Matcher:
 
     def knn2_device(self, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream=None):
         self._check(self._L.orbm_knn2_device(self._h, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream))
+
+    def knn2_device_static(self, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream=None):
+        """orbm_knn2_device without any device allocation (static scratch, include/orbm.h)."""
+        self._check(self._L.orbm_knn2_device_static(self._h, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream))
 
     def merge_top2_device(self, gathered_ptr, nshards, nq, th_dist, ratio, top2_ptr, match_ptr, stream=None):
         self._check(self._L.orbm_merge_top2_device(self._h, gathered_ptr, nshards, nq, th_dist, ratio, top2_ptr,
