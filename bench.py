@@ -169,7 +169,8 @@ def main():
     ap.add_argument("--no-matching", action="store_true", help="skip the Hamming-matching legs")
     ap.add_argument("--query-keyframes", type=int, default=8, help="config 5: query keyframes (x1000 descriptors) per step")
     ap.add_argument("--match-pairs", type=int, default=2048, help="config 4: frame pairs per GPU per step")
-    ap.add_argument("--all-configs", action="store_true", help="also time BASELINE configs 1 and 3 (rank 0, N=1)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip BASELINE configs 1 and 3 (rank 0, N=1 only)")
+    ap.add_argument("--all-configs", action="store_true", help=argparse.SUPPRESS)   # kept for old command lines
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -283,6 +284,40 @@ def main():
     barrier()
     assert int(h_n.sum().item()) == int(d_n.sum().item()), "e2e and device-resident legs disagree"
 
+    # ---- strong-scaling leg: config 2 as BASELINE.json words it - ONE 10,000-frame sequence split 10,000/G per rank ----
+    strong = None
+    if world > 1:
+        Fs = (F * (rank + 1)) // world - (F * rank) // world
+
+        def step_strong():
+            ex.extract_batch_device(d_frames.data_ptr(), Fs, W, H, W, H * W, d_kps.data_ptr(), d_desc.data_ptr(),
+                                    d_n.data_ptr(), stream.cuda_stream)
+
+        def step_strong_e2e():
+            ex.extract_batch_ptr(h_frames.data_ptr(), Fs, W, H, W, H * W, h_kps.data_ptr(), h_desc.data_ptr(),
+                                 h_n.data_ptr())
+        for _ in range(args.warmup):
+            step_strong()
+        ex.synchronize()
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            step_strong()
+        e1.record(stream)
+        barrier()
+        ex.synchronize()
+        s_ms = maxr(e0.elapsed_time(e1) / args.steps)
+        step_strong_e2e()
+        barrier()
+        te = time.perf_counter()
+        for _ in range(args.steps):
+            step_strong_e2e()
+        torch.cuda.synchronize()
+        s_e2e = maxr((time.perf_counter() - te) * 1e3 / args.steps)
+        barrier()
+        strong = {"frames_total": F, "frames_per_gpu": Fs, "value": F / (s_ms * 1e-3), "unit": "frames/s",
+                  "ms_per_step": s_ms, "e2e_value": F / (s_e2e * 1e-3), "e2e_ms_per_step": s_e2e, "scaling": "strong"}
+
     cpu = None
     if rank == 0 and not args.no_cpu:
         threads = os.cpu_count() or 1
@@ -315,7 +350,7 @@ def main():
             matching["is_in_frustum"] = BM.bench_frustum(args, dev, local, mt)
             matching["frontend_chain"] = BM.bench_chain(args, dev, local, mt)
     other = None
-    if args.all_configs and world == 1:
+    if not args.no_other_configs and world == 1:
         import bench_configs
         del d_frames, h_frames
         ex.close()
@@ -324,7 +359,7 @@ def main():
         dist.barrier()
     if rank == 0:
         total = F * world
-        print(json.dumps({
+        line = ({
             "metric": METRIC, "value": total / (ms_step * 1e-3), "unit": "frames/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
@@ -338,7 +373,30 @@ def main():
                     "h2d_bytes_per_step": F * H * W, "d2h_bytes_per_step": F * (NFEAT * 60 + 4),
                     "api": "orbx_extract_batch (C ABI, pinned host buffers), wall clock between device syncs"},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "matching": matching, "other_configs": other}))
+            "strong_scaling": strong, "matching": matching, "other_configs": other})
+        # compact digest, printed LAST so that it survives a truncated stdout tail: every number BASELINE.md quotes
+        sm = {"device_fps": round(line["value"]), "e2e_fps": round(line["e2e"]["value"]), "n_gpus": world,
+              "stage_ms": roofline["stage_ms_per_pass"], "roofline_frac": round(roofline["frac"], 4)}
+        if strong:
+            sm.update({"strong_scaling_fps": round(strong["value"]), "strong_scaling_e2e_fps": round(strong["e2e_value"])})
+        if matching:
+            k, i = matching["knn2_all_pairs"], matching["search_for_initialization"]
+            sm.update({"knn2_pairs_s": float(f"{k['value']:.4g}"), "knn2_ms": round(k["ms_per_step"], 3),
+                       "knn2_frac_popc": round(k["roofline"]["frac"], 3), "knn2_nranks": world,
+                       "sharded_equals_single": (k.get("check") or {}).get("sharded_equals_single"),
+                       "knn2_accepted_frac": (k.get("check") or {}).get("accepted_frac"),
+                       "init_pairs_s": round(i["value"]), "init_e2e_pairs_s": round(i["e2e"]["value"]),
+                       "init_gpu_equals_cpu": (i.get("cpu_baseline") or {}).get("gpu_equals_cpu")})
+            for name in ("frame_glue", "bow", "distinctive_descriptors", "is_in_frustum", "frontend_chain"):
+                if name in matching:
+                    sm[name + "_per_s"] = float(f"{matching[name]['value']:.4g}")
+        if other:
+            c1, c3 = other["config1_single_frame"], other["config3_1241x376_2000kp"]
+            sm.update({"config1_ms_per_call": round(c1["gpu_ms_per_call"], 4), "config1_bit_exact": c1["bit_exact"],
+                       "config3_device_fps": round(c3["gpu_device_frames_s"]), "config3_e2e_fps": round(c3["gpu_e2e_frames_s"]),
+                       "config3_bit_exact": c3["descriptors_bit_exact_on_cpu_sample"]})
+        line["summary"] = sm
+        print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 

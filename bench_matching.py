@@ -30,9 +30,16 @@ def bench_knn2(args, rank, world, dev, matcher, clocks_mhz):
     g = torch.Generator(device=dev); g.manual_seed(12345 + rank)
     db = torch.randint(0, 256, (ndb, 32), dtype=torch.uint8, device=dev, generator=g)
     nq = args.query_keyframes * KP_PER_KF
-    # queries: descriptors of the (replicated) first keyframes of rank 0's shard + 10 % bit flips; same on all ranks
+    # queries (SURVEY config 5): database descriptors + bit-flip noise (each bit w.p. 0.1), so true matches exist and
+    # the accept branch of the merge runs.  Drawn from the first keyframes of rank 0's shard (database rows 0 .. nq),
+    # replicated on every rank.
     gq = torch.Generator(device=dev); gq.manual_seed(999)
-    q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=gq)
+    q = torch.empty((nq, 32), dtype=torch.uint8, device=dev)
+    if rank == 0:
+        flips = torch.zeros((nq, 32), dtype=torch.uint8, device=dev)
+        for b in range(8):
+            flips |= (torch.rand((nq, 32), device=dev, generator=gq) < 0.1).to(torch.uint8) << b
+        q.copy_(db[:nq] ^ flips)
     if world > 1:
         dist.broadcast(q, 0)
     gathered = torch.empty((world, nq, 2), dtype=torch.int32, device=dev)
@@ -72,6 +79,30 @@ def bench_knn2(args, rank, world, dev, matcher, clocks_mhz):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     launches = matcher.kernel_launches() - l0
+    # ---- result check (outside the timed region): the sharded search (local 2-NN -> ncclAllGather -> merge) against ONE
+    # single-rank search over the whole database, which rank 0 regenerates from the ranks' seeds, on a query sample
+    check = None
+    if rank == 0:
+        ns = min(nq, 512)
+        ref = torch.empty((ns, 2), dtype=torch.int32, device=dev)
+        if world > 1:
+            parts = []
+            for r in range(world):
+                a, b = shard_range(DB_KEYFRAMES, r, world)
+                gr = torch.Generator(device=dev); gr.manual_seed(12345 + r)
+                parts.append(torch.randint(0, 256, ((b - a) * KP_PER_KF, 32), dtype=torch.uint8, device=dev, generator=gr))
+            full = torch.cat(parts); del parts
+        else:
+            full = db
+        matcher.knn2_device(q.data_ptr(), ns, full.data_ptr(), full.shape[0], 0, ref.data_ptr(), stream.cuda_stream)
+        torch.cuda.synchronize()
+        same = bool(torch.equal(ref, top2[:ns]))
+        best = ref[:, 0].to(torch.int64) & 0xFFFFFFFF
+        true_hit = float(((best & 0x7FFFFF) == torch.arange(ns, device=dev)).float().mean().item())
+        check = {"queries_checked": ns, "sharded_equals_single": same, "true_match_is_best_frac": true_hit,
+                 "accepted_frac": float((match >= 0).float().mean().item())}
+        if world > 1:
+            del full
     pairs = float(nq) * DB_KEYFRAMES * KP_PER_KF
     pps = pairs / (ms * 1e-3)
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
@@ -85,7 +116,7 @@ def bench_knn2(args, rank, world, dev, matcher, clocks_mhz):
                         "unit": "T popc32/s (8 per pair, algorithmic; the kernel issues 5 after carry-save compression)",
                         "frac": pps * 8 / popc_peak, "clock_mhz_assumed": mhz,
                         "peak_source": "16 POPC lanes/clk/SM measured by tools/popc_microbench.cu x SMs x SM clock under load"},
-           "db_bytes_read_per_step": float(ndb) * 32 * ((nq + 1023) // 1024)}
+           "db_bytes_read_per_step": float(ndb) * 32 * ((nq + 1023) // 1024), "check": check}
     if sh is not None:
         sh.close()
     return out

@@ -114,6 +114,12 @@ int orbx_debug_level_image(orbx_handle* h, int frame, int level, int which, uint
 int orbx_debug_cell_candidates(orbx_handle* h, int frame, int level, int cell, int32_t* xs, int32_t* ys,
                                float* resp, int cap, int* n);
 int orbx_debug_level_cells(orbx_handle* h, int frame, int level, int32_t* n_total, int32_t* n_retain);
+/* KeyPointsFilter::retainBest(list, keep[i]) + resize (src/ORBextractor.cc:683-685, 697-701) through the device port of
+ * libstdc++'s std::nth_element, on nlists caller-made response lists (list i = resp[start[i] .. start[i+1])).
+ * order[k] = original position, inside its list, of the record now at place k; the first min(keep, size) places of a
+ * list are what the reference keeps.  batch: 0 = the scans of select_kernel, 1 = those of select_smem_kernel. */
+int orbx_debug_retain_best(orbx_handle* h, const float* resp, const int32_t* start, const int32_t* keep, int nlists,
+                           int retain_mode, int batch, int32_t* order);
 
 /* ---- synthetic frames (bench utility; byte-identical CPU twin in oracle/synth.cc) ------------------------------ */
 /* Frame f gets seed seed0+f.  Device buffer, asynchronous on `stream`. */

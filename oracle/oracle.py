@@ -163,6 +163,16 @@ def retain_best(resp: np.ndarray, n_points: int, retain_mode: int = 0):
     return r[:n], tag[:n]
 
 
+def nth_element_killer(n: int, nth: int):
+    """Responses on which libstdc++'s nth_element (response-greater) degenerates to its depth limit -> (resp, comparisons)."""
+    L = lib()
+    L.orb_oracle_nth_element_killer.restype = C.c_long
+    L.orb_oracle_nth_element_killer.argtypes = [C.c_int, C.c_int, _f32p]
+    r = np.zeros(n, np.float32)
+    cnt = L.orb_oracle_nth_element_killer(n, nth, _ptr(r, _f32p))
+    return r, int(cnt)
+
+
 def sincos(angle_rad: float):
     c = C.c_float(); s = C.c_float()
     lib().orb_oracle_sincos(angle_rad, C.byref(c), C.byref(s))

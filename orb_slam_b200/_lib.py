@@ -54,6 +54,7 @@ def lib():
     L.orbx_debug_level_image.argtypes = [vp, C.c_int, C.c_int, C.c_int, u8p]
     L.orbx_debug_cell_candidates.argtypes = [vp, C.c_int, C.c_int, C.c_int, i32p, i32p, f32p, C.c_int, i32p]
     L.orbx_debug_level_cells.argtypes = [vp, C.c_int, C.c_int, i32p, i32p]
+    L.orbx_debug_retain_best.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]
     L.orbx_synth_frames_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_uint64, vp]
     _lib = L
     return L

@@ -50,6 +50,8 @@ struct orbm_handle {
   int64_t launches = 0;
   float last_ms = 0.f;
   int num_sms = 148;
+  int commit_mode = 0;       // 0 by job size, 1 in-order replay, 2 fixed point (ORBM_COMMIT, read at orbm_create)
+  int knn_variant = 2;       // distance arithmetic of knn2_kernel (ORBM_KNN_VARIANT, read at orbm_create)
   // workspaces
   orbm::DevBuf knn_part;     // per-chunk partial top-2 keys
   orbm::DevBuf stage_a, stage_b, stage_c;  // staging for host-pointer entry points

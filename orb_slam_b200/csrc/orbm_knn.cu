@@ -34,6 +34,9 @@ extern "C" int orbm_create(int device, orbm_handle** out) {
     cudaDeviceProp prop;
     ORBM_CK(cudaGetDeviceProperties(&prop, device));
     h->num_sms = prop.multiProcessorCount;
+    // run-time switches are per handle (a test can create one handle per setting inside one process)
+    if (const char* e = getenv("ORBM_COMMIT")) h->commit_mode = e[0] == 's' ? 1 : (e[0] == 'p' ? 2 : 0);
+    if (const char* e = getenv("ORBM_KNN_VARIANT")) h->knn_variant = std::min(2, std::max(0, atoi(e)));
     // frame-set arrays are pool allocations (orbm_alloc): keep freed blocks cached in the pool
     cudaMemPool_t pool;
     ORBM_CK(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -139,7 +142,7 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
   uint32_t* part = h->knn_part.as<uint32_t>();
   const int cl = (int)chunk_len;
   const uint32_t ib = (uint32_t)idx_base;
-  static const int dv = [] { const char* e = getenv("ORBM_KNN_VARIANT"); return e ? atoi(e) : 2; }();
+  const int dv = h->knn_variant;
 #define ORBM_KNN_LAUNCH(Q, D) knn2_kernel<Q, D><<<grid, kKnnThreads, 0, s>>>(q4, nq, db4, ndb, cl, ib, part, d_err)
 #define ORBM_KNN_DV(Q) (dv == 0 ? ORBM_KNN_LAUNCH(Q, 0) : dv == 1 ? ORBM_KNN_LAUNCH(Q, 1) : ORBM_KNN_LAUNCH(Q, 2))
   if (qpt == 4) ORBM_KNN_DV(4);

@@ -215,12 +215,11 @@ int run_job(orbm_handle* h, const HostJob& J) {
     // commit: the parallel fixed-point kernel (CTA per problem) for small jobs whose state fits in shared memory;
     // the in-order replay (warp per problem) for large jobs and oversized problems.
     // ORBM_COMMIT=serial|parallel overrides (experiments / tests).
-    static const char* force_commit = getenv("ORBM_COMMIT");
     const size_t par_smem = commit_par_smem(max_nq, max_nt);
     const bool par_ok = par_smem <= 200 * 1024;
     // crossover measured with SearchForInitialization on 1000-keypoint pairs: 0.27 vs 0.33 ms at 256 pairs, 0.43 vs
     // 0.46 at 512, 0.86 vs 0.73 at 1024 (parallel vs replay): the replay's chain is latency, the fixed point is work
-    const bool want_par = force_commit ? force_commit[0] == 'p' : np <= 512;
+    const bool want_par = h->commit_mode ? h->commit_mode == 2 : np <= 512;
     if (par_ok && want_par) {
       const int threads = np >= 148 * 4 ? 256 : (np >= 148 ? 512 : 1024);
       cudaFuncSetAttribute(commit_par_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)par_smem);

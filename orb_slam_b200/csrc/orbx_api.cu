@@ -34,6 +34,7 @@ struct orbx_handle {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
   } lane[kLanes];
   int nlanes = kDefaultLanes;
+  int select_mode = 0;              // 0 by chunk size, 1 global, 2 shared memory (ORBX_SELECT)
   int pdl_mode = 1;                 // 0 never, 1 chunks of <= kPdlMaxFrames frames, 2 always (ORBX_PDL)
   uint8_t* d_in[kLanes] = {};
   uint8_t* d_raw[kLanes] = {};   // tightly packed host rows land here first (one contiguous H2D), then D2D repitch
@@ -183,6 +184,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     h->in_pitch = (pp->max_width + 15) / 16 * 16;
     h->in_frame_bytes = (int64_t)h->in_pitch * pp->max_height;
     if (const char* e = getenv("ORBX_PDL")) h->pdl_mode = std::min(2, std::max(0, atoi(e)));
+    if (const char* e = getenv("ORBX_SELECT")) h->select_mode = e[0] == 'g' ? 1 : (e[0] == 's' ? 2 : 0);
     if (const char* e = getenv("ORBX_LANES")) h->nlanes = std::min(kLanes, std::max(1, atoi(e)));
     for (int li = 0; li < h->nlanes; li++) {
       orbx_handle::Lane& ln = h->lane[li];
@@ -286,7 +288,7 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   if (prof) {                     // serial, so that the per-stage events mean something
-    launch_select(b, dp, n, s);
+    launch_select(b, dp, n, s, h->select_mode);
     cudaEventRecord(h->ev_stage[st++], s);
     launch_blur(b, dp, h->tiles, n, s);
     cudaEventRecord(h->ev_stage[st++], s);
@@ -294,7 +296,7 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
     // select is a latency-bound kernel of a few thousand warps and blur does not depend on it: blur runs beside it
     // on s_aux (fork after FAST, whose CTAs fill the SMs' shared memory; join before describe)
     CK(cudaEventRecord(ln.ev_fork, s));
-    launch_select(b, dp, n, s);
+    launch_select(b, dp, n, s, h->select_mode);
     CK(cudaStreamWaitEvent(ln.s_aux, ln.ev_fork, 0));
     launch_blur(b, dp, h->tiles, n, ln.s_aux);
     CK(cudaEventRecord(ln.ev_join, ln.s_aux));

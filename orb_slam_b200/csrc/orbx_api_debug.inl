@@ -74,3 +74,40 @@ extern "C" int orbx_synth_frames_device(uint8_t* d_out, int nframes, int width, 
   cudaFree(tmp);
   return e == cudaSuccess && cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_ERR_CUDA;
 }
+
+// KeyPointsFilter::retainBest(list, keep) + resize(keep) through the device port of std::nth_element, for nlists
+// caller-made lists (list i = entries start[i] .. start[i+1]).  order[]: the original position (inside its list) of the
+// record now at each place; only the first min(keep, size) of a list are the reference's output.  batch != 0 selects
+// the four-keys-per-trip partition scans the shared-memory selection kernel uses.
+extern "C" int orbx_debug_retain_best(orbx_handle* h, const float* resp, const int32_t* start, const int32_t* keep,
+                                      int nlists, int retain_mode, int batch, int32_t* order) {
+  if (!h || !resp || !start || !keep || !order || nlists < 0) return ORBX_ERR_ARG;
+  if (nlists == 0) return ORBX_OK;
+  CK(cudaSetDevice(h->p.device));
+  const int total = start[nlists];
+  constexpr int kPad = 4;
+  std::vector<Cand> host((size_t)total + 2 * kPad);
+  for (auto& c : host) { c.resp = 0.f; c.xy = 0xFFFFFFFFu; }
+  std::vector<int32_t> st(nlists + 1);
+  for (int i = 0; i <= nlists; i++) st[i] = start[i] + kPad;
+  for (int i = 0; i < nlists; i++)
+    for (int k = start[i]; k < start[i + 1]; k++) { host[kPad + k].resp = resp[k]; host[kPad + k].xy = (uint32_t)(k - start[i]); }
+  Cand* d_v = nullptr; int32_t *d_st = nullptr, *d_keep = nullptr;
+  auto cleanup = [&] { cudaFree(d_v); cudaFree(d_st); cudaFree(d_keep); };
+  cudaError_t e = cudaMalloc(&d_v, host.size() * sizeof(Cand));
+  if (e == cudaSuccess) e = cudaMalloc(&d_st, st.size() * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&d_keep, (size_t)nlists * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(d_v, host.data(), host.size() * sizeof(Cand), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_st, st.data(), st.size() * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_keep, keep, (size_t)nlists * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    launch_retain_best_debug(d_v, d_st, d_keep, nlists, retain_mode, batch, nullptr);
+    h->launches++;
+    e = cudaDeviceSynchronize();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(host.data(), d_v, host.size() * sizeof(Cand), cudaMemcpyDeviceToHost);
+  cleanup();
+  if (e != cudaSuccess) { h->err = std::string("orbx_debug_retain_best: ") + cudaGetErrorString(e); return ORBX_ERR_CUDA; }
+  for (int k = 0; k < total; k++) order[k] = (int32_t)host[kPad + k].xy;
+  return ORBX_OK;
+}

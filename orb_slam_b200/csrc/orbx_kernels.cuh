@@ -42,7 +42,9 @@ void set_launch_pdl(bool on);
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s);
-void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s);
+void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s, int force);
+void launch_retain_best_debug(Cand* v, const int32_t* start, const int32_t* keep, int nlists, int retain_mode, int batch,
+                              cudaStream_t s);
 void launch_blur(const ChunkBuffers& b, const DevicePlan& hp, const BlurTiles& t, int nframes, cudaStream_t s);
 void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, orbx_keypoint* d_kps, uint8_t* d_desc,
                      int32_t* d_n_out, cudaStream_t s);

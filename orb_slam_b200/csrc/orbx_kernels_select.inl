@@ -7,7 +7,8 @@ namespace orbx {
 // __adjust_heap / __push_heap) on 8-byte Cand records with the comparator of OpenCV's KeypointResponseGreater
 // (a.response > b.response).  The reference truncates retainBest's result to n entries IN THE ORDER nth_element
 // left them (:683-685, :697-701), so the element order — not just the set — is part of the output.
-// tests/test_select.py checks this port against the real std::nth_element on random and tie-heavy lists.
+// tests/test_gpu_select.py checks this port (orbx_debug_retain_best) against the real std::nth_element on random,
+// tie-heavy, sorted and depth-limit lists.
 // ------------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool cgt(const Cand& a, const Cand& b) { return a.resp > b.resp; }
 __device__ __forceinline__ void cswap(Cand* v, int i, int j) { Cand t = v[i]; v[i] = v[j]; v[j] = t; }
@@ -360,14 +361,14 @@ __global__ void __launch_bounds__(1024) select_smem_kernel(ChunkBuffers b, int n
 // 56.00 ms with the global kernel, 57.39 with this one at kSelCap 128, 56.27 at kSelCap 64).
 constexpr int kSelectSmemMaxFrames = 32;
 
-void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s) {
+void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s, int force) {
   const int nwarps = hp.nlevels * nframes;
   int max_list = 0, max_cells = 0;
   for (int l = 0; l < hp.nlevels; l++) { max_list = std::max(max_list, hp.lv[l].list_cap); max_cells = std::max(max_cells, hp.lv[l].nCells); }
   max_list = (max_list + 1) & ~1;
   const int smem = select_smem_bytes(max_list, max_cells);
-  static const char* force = getenv("ORBX_SELECT");             // experiments: "global" / "smem"
-  const bool want_smem = force ? force[0] == 's' : nframes <= kSelectSmemMaxFrames;
+  // force: 0 = by chunk size, 1 = global, 2 = shared memory (ORBX_SELECT, read when the handle is created)
+  const bool want_smem = force ? force == 2 : nframes <= kSelectSmemMaxFrames;
   if (want_smem && smem <= 160 * 1024) {
     cudaFuncSetAttribute(select_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const int warps = std::min(32, std::max(1, max_cells));
@@ -375,6 +376,21 @@ void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cud
     return;
   }
   launch_k(select_kernel, dim3((nwarps * 32 + 127) / 128), dim3(128), 0, s, b, nwarps);
+}
+
+// Unit-test hook (orbx_debug_retain_best): retain_best_port on caller-made lists, one thread per list.  Lists lie back
+// to back behind 4 pad records on either side, so the kBatch scans' over-reads stay inside the buffer.
+template <bool kBatch>
+__global__ void retain_best_debug_kernel(Cand* v, const int32_t* start, const int32_t* keep, int nlists, int retain_mode) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlists) return;
+  retain_best_port<kBatch>(v + start[i], start[i + 1] - start[i], keep[i], retain_mode);
+}
+
+void launch_retain_best_debug(Cand* v, const int32_t* start, const int32_t* keep, int nlists, int retain_mode, int batch,
+                              cudaStream_t s) {
+  if (batch) retain_best_debug_kernel<true><<<(nlists + 63) / 64, 64, 0, s>>>(v, start, keep, nlists, retain_mode);
+  else retain_best_debug_kernel<false><<<(nlists + 63) / 64, 64, 0, s>>>(v, start, keep, nlists, retain_mode);
 }
 
 }  // namespace orbx

@@ -138,6 +138,17 @@ class ORBextractor:
         self._check(self._L.orbx_debug_level_image(self._h, frame, level, which, out.ctypes.data_as(u8p)))
         return out
 
+    def debug_retain_best(self, lists, keep, retain_mode=0, batch=0):
+        """retainBest(list, keep) + resize through the device port of std::nth_element; lists: response arrays.
+        Returns per list the original positions of the records in their new order (all of them)."""
+        start = np.concatenate([[0], np.cumsum([len(a) for a in lists])]).astype(np.int32)
+        resp = np.ascontiguousarray(np.concatenate([np.asarray(a, np.float32) for a in lists]) if lists else np.zeros(0, np.float32))
+        kp = np.ascontiguousarray(keep, np.int32)
+        order = np.zeros(max(len(resp), 1), np.int32)
+        self._check(self._L.orbx_debug_retain_best(self._h, resp.ctypes.data, start.ctypes.data, kp.ctypes.data,
+                                                   len(lists), retain_mode, batch, order.ctypes.data))
+        return [order[start[i]:start[i + 1]].copy() for i in range(len(lists))]
+
     def debug_level_cells(self, frame, level):
         i = self.debug_level_info(level)
         a = np.zeros(i["cols"] * i["rows"], np.int32)

@@ -257,3 +257,35 @@ def test_cuda_equals_reference_generated_golden():
                 assert np.array_equal(a, b), (c, mode, f)
             assert np.array_equal(d, rd), (c, mode)
             ex.close()
+
+
+@pytest.mark.parametrize("env", [
+    {"ORBX_SELECT": "global", "ORBX_PDL": "0", "ORBX_LANES": "1"},
+    {"ORBX_SELECT": "smem", "ORBX_PDL": "2", "ORBX_LANES": "3"},
+    {"ORBX_SELECT": "global", "ORBX_PDL": "2", "ORBX_LANES": "4"},
+    {"ORBX_SELECT": "smem", "ORBX_PDL": "0", "ORBX_LANES": "2"},
+])
+def test_runtime_switches_are_bit_identical(oracle, env):
+    """The run-time switches choose between code paths that must give identical results: both selection
+    kernels on single frames AND on a multi-chunk batch, programmatic dependent launch never / always, 1-4 chunk lanes.
+    They are read when the handle is created."""
+    import os
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        ex = _ex(nfeatures=700, nlevels=6, max_width=400, max_height=300, max_batch=8)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    O = oracle.OracleExtractor(700, 1.2, 6, 1, 20)
+    imgs = np.stack([oracle.synth(300, 400, 50 + s) for s in range(5)])
+    ref = [O(im) for im in imgs]
+    k, d = ex(imgs[0])
+    _cmp_final(k, d, *ref[0])
+    batch = np.concatenate([imgs] * 5)                       # 25 frames = 4 chunks of <= 8 over the lanes
+    kps, desc, n = ex.extract_batch(batch)
+    for i in range(len(batch)):
+        _cmp_final(kps[i, :n[i]], desc[i, :n[i]], *ref[i % 5])

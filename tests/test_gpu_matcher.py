@@ -15,10 +15,29 @@ def M(oracle):
     return match_oracle
 
 
-@pytest.fixture(scope="module")
-def matcher():
+def _matcher_with(env):
+    """A matcher handle created under the given run-time switches (they are read once, at orbm_create)."""
+    import os
     from orb_slam_b200 import Matcher
-    return Matcher(0)
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        return Matcher(0)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+# every test of this file runs under the default commit choice (fixed point for <= 512 problems), under the in-order
+# replay (commit_kernel) and under the fixed point forced; the 2-NN tests under each distance-arithmetic variant
+@pytest.fixture(scope="module", params=["auto", "serial+knn0", "parallel+knn1"])
+def matcher(request):
+    env = {"auto": {}, "serial+knn0": {"ORBM_COMMIT": "serial", "ORBM_KNN_VARIANT": "0"},
+           "parallel+knn1": {"ORBM_COMMIT": "parallel", "ORBM_KNN_VARIANT": "1"}}[request.param]
+    return _matcher_with(env)
 
 
 @pytest.fixture(scope="module")
@@ -375,3 +394,95 @@ def test_triangulation_fixed_point_under_long_dependency_chains(M, matcher, seed
     nm, rows = om.SearchForTriangulation(fs, fs, [0], [1], F12[None], sigma2)
     on, orow = M.search_for_triangulation(f1, f2, F12, sigma2, ori)
     assert nm[0] == on and _rows_equal(rows[0], orow) and on > 20
+
+
+def _shuffled_batch(npairs, nprob, seed):
+    rng = np.random.default_rng(seed)
+    which = np.concatenate([np.arange(npairs), rng.integers(0, npairs, nprob - npairs)])
+    rng.shuffle(which)
+    return [int(w) for w in which]
+
+
+def test_large_batches_every_kind(M, matcher, pairs):
+    """>= 600 problems per call and kind (the default path for such jobs is the in-order replay commit_kernel; the
+    fixture also forces each form): the problems repeat the 6 pairs in shuffled order and every one must equal the
+    oracle's result for its source pair."""
+    from orb_slam_b200 import ORBmatcher
+    NP = 640
+    which = _shuffled_batch(len(pairs), NP, 3)
+    sf = np.cumprod(np.concatenate([[1.0], np.full(7, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    fr1 = [MD.with_valid(p[0], MD.random_valid(p[0].n, 0.6, 110 + k)) for k, p in enumerate(pairs)]
+    fr2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.25, 120 + k)) for k, p in enumerate(pairs)]
+    s1 = matcher.upload([MD.to_matchframe(f) for f in fr1]); s2 = matcher.upload([MD.to_matchframe(f) for f in fr2])
+
+    def check(nm, rows, ref):
+        for p, w in enumerate(which):
+            assert nm[p] == ref[w][0] and _rows_equal(rows[p], ref[w][1]), (p, w)
+
+    # WindowSearch
+    om = ORBmatcher(0.8, True, matcher=matcher)
+    nm, rows = om.WindowSearch(s1, s2, which, which, 100, 0, 2**31 - 1)
+    check(nm, rows, [M.window_search(a, b, 100, 0.8, True, 0, 2**31 - 1) for a, b in zip(fr1, fr2)])
+    # SearchByProjection(F1, F2, window)
+    om = ORBmatcher(0.9, True, matcher=matcher)
+    uv = [np.stack([f.x - np.float32(p[2][0]) + 1.5, f.y - np.float32(p[2][1]) - 0.75], 1).astype(np.float32)
+          for f, p in zip(fr1, pairs)]
+    nm, rows = om.SearchByProjectionFrames(s1, s2, which, which, [uv[w] for w in which], 15)
+    check(nm, rows, [M.search_by_projection_ff(a, b, u, 15, 0.9) for a, b, u in zip(fr1, fr2, uv)])
+    # SearchByProjection, both variants
+    rng = np.random.default_rng(7)
+    for variant, ratio, ori, th in (("local_map", 0.8, False, 100), ("best", 0.9, True, 100)):
+        pts = [_points_from(p[0], p[2], rng, variant, sf) for p in pairs]
+        om = ORBmatcher(ratio, ori, matcher=matcher)
+        nm, rows = om.SearchByProjection(s2, which, [pts[w] for w in which], variant, th)
+        check(nm, rows, [M.search_by_projection(b, q, variant, th, ratio, ori) for b, q in zip(fr2, pts)])
+    # SearchByBoW, both overloads
+    for variant in ("kf_f", "kf_kf"):
+        om = ORBmatcher(0.75, True, matcher=matcher)
+        nm, rows = om.SearchByBoW(s1, s2, which, which, variant)
+        check(nm, rows, [M.search_by_bow(a, b, variant, 0.75, True) for a, b in zip(fr1, fr2)])
+    # SearchForTriangulation
+    sigma2 = (sf * sf).astype(np.float32)
+    F12 = []
+    for p in pairs:
+        t = np.array([p[2][0], p[2][1], 0.0]) + 1e-3
+        F12.append(np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]], np.float32) * np.float32(0.05))
+    g1 = [MD.with_valid(p[0], MD.random_valid(p[0].n, 0.3, 130 + k)) for k, p in enumerate(pairs)]
+    g2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.3, 140 + k)) for k, p in enumerate(pairs)]
+    t1 = matcher.upload([MD.to_matchframe(f) for f in g1]); t2 = matcher.upload([MD.to_matchframe(f) for f in g2])
+    om = ORBmatcher(0.6, True, matcher=matcher)
+    nm, rows = om.SearchForTriangulation(t1, t2, which, which, np.stack([F12[w] for w in which]), sigma2)
+    check(nm, rows, [M.search_for_triangulation(a, b, f, sigma2, True) for a, b, f in zip(g1, g2, F12)])
+    # SearchForInitialization (prev_xy updated in place per problem)
+    om = ORBmatcher(0.9, True, matcher=matcher)
+    prev = [np.stack([pairs[w][0].x, pairs[w][0].y], 1).astype(np.float32) for w in which]
+    nm, rows = om.SearchForInitialization(s1, s2, which, which, prev, 100)
+    ref = []
+    for a, b in zip(fr1, fr2):
+        op = np.stack([a.x, a.y], 1).astype(np.float32)
+        n, m = M.search_for_initialization(a, b, op, 100, 0.9, True)
+        ref.append((n, m, op))
+    for p, w in enumerate(which):
+        assert nm[p] == ref[w][0] and _rows_equal(rows[p], ref[w][1]) and np.array_equal(prev[p], ref[w][2]), (p, w)
+
+
+def test_oversized_frames_take_the_global_state_paths(M, matcher, oracle):
+    """Frames of > 2048 keypoints: the replay keeps its per-target state in global memory (kCommitSmemTargets), and the
+    fixed point does not fit shared memory above ~4000 queries and falls back to the replay."""
+    from orb_slam_b200 import ORBmatcher
+    f1, f2, shift = MD.make_pair(oracle, 9, 1241, 376, 4500)
+    assert f1.n > 4100 and f2.n > 4100
+    a = MD.with_valid(f1, MD.random_valid(f1.n, 0.7, 1)); b = MD.with_valid(f2, MD.random_valid(f2.n, 0.2, 2))
+    fs = matcher.upload([MD.to_matchframe(a), MD.to_matchframe(b)])
+    om = ORBmatcher(0.85, True, matcher=matcher)
+    nm, rows = om.WindowSearch(fs, fs, [0], [1], 60, 0, 2**31 - 1)
+    on, orow = M.window_search(a, b, 60, 0.85, True, 0, 2**31 - 1)
+    assert nm[0] == on and _rows_equal(rows[0], orow) and on > 300
+    prev = [np.stack([a.x, a.y], 1).astype(np.float32)]
+    oprev = prev[0].copy()
+    nm, rows = om.SearchForInitialization(fs, fs, [0], [1], prev, 50)
+    on, orow = M.search_for_initialization(a, b, oprev, 50, 0.85, True)
+    assert nm[0] == on and _rows_equal(rows[0], orow) and np.array_equal(prev[0], oprev)
+    nm, rows = om.SearchByBoW(fs, fs, [0], [1], "kf_f")
+    on, orow = M.search_by_bow(a, b, "kf_f", 0.85, True)
+    assert nm[0] == on and _rows_equal(rows[0], orow)
