@@ -227,12 +227,30 @@ int orbm_search_by_projection_frames(orbm_handle* h, const orbm_frameset* set1, 
  *                               when best and second share a level (`best > ratio * second` rejects)
  *  variant ORBM_PROJ_BEST       best only, accept iff best <= th_dist; rotation check when check_ori:
  *                               :1507-1620 (last frame, TH_HIGH), :1622-1746 (relocalisation, ORBdist),
- *                               :286-407 (Sim3, TH_LOW, no orientation), Fuse / SearchBySim3 inner loops
- * set valid = keypoint already has a MapPoint (skipped as candidate).  match_out[p][idx] = point index. */
-enum { ORBM_PROJ_LOCAL_MAP = 0, ORBM_PROJ_BEST = 1 };
+ *                               :286-407 (Sim3 loop closing, TH_LOW, no orientation)
+ *    For these two: set valid = keypoint already has a MapPoint (skipped as candidate), a keypoint accepted by an
+ *    earlier point is skipped by the later ones; match_out[p][idx] = point index (row of the TARGET frame).
+ *  variant ORBM_PROJ_BEST_INDEPENDENT  the best-only loops of Fuse (:1094-1113 and :1223-1242) and SearchBySim3
+ *                               (:1373-1398, :1458-1483): every grid candidate inside the level window is scored,
+ *                               keypoints that hold a MapPoint are NOT skipped, points do not see each other (two
+ *                               points may pick the same keypoint: Fuse then replaces, :1116-1131), accept iff
+ *                               best <= th_dist (TH_LOW in Fuse, TH_HIGH in SearchBySim3); no rotation check, ratio and
+ *                               set valid unused.  match_out[p][k] = best keypoint of POINT k (row of the points,
+ *                               stride >= points[p].n), nmatches[p] = accepted points (= nFused). */
+enum { ORBM_PROJ_LOCAL_MAP = 0, ORBM_PROJ_BEST = 1, ORBM_PROJ_BEST_INDEPENDENT = 2 };
 int orbm_search_by_projection(orbm_handle* h, const orbm_frameset* set, const int32_t* idx,
                               const orbm_points* points, int nproblems, int variant, int th_dist, float ratio,
                               int check_ori, int32_t* match_out, int stride, int32_t* nmatches);
+
+/* M6  SearchBySim3 (src/ORBmatcher.cc:1267-1505), both directions + the agreement check (:1487-1502) for npairs keyframe
+ * pairs (frames idx1[p], idx2[p] of one set).  points12[p]: one entry per keypoint of keyframe 1 (n == its keypoint
+ * count) - its MapPoint projected into keyframe 2 with radius th * scale[level] and level window [pred-1, pred]
+ * (:1334-1360), valid = MapPoint present, good, not already matched and inside keyframe 2's image / scale range;
+ * points21[p] likewise for keyframe 2's points in keyframe 1.  match12[p][i1] = i2 where vnMatch1[i1] == i2 and
+ * vnMatch2[i2] == i1, else -1 (stride >= keypoints of keyframe 1); nfound[p] = nFound. */
+int orbm_search_by_sim3(orbm_handle* h, const orbm_frameset* set, const int32_t* idx1, const int32_t* idx2,
+                        const orbm_points* points12, const orbm_points* points21, int npairs, int th_dist,
+                        int32_t* match12, int stride, int32_t* nfound);
 
 /* M5  SearchByBoW.  ORBM_BOW_KF_F: (KeyFrame*, Frame&) src/ORBmatcher.cc:155-284, set1 = keyframes (valid = good
  * MapPoint), match_out[p][idxF] = idxKF, accept best <= TH_LOW.  ORBM_BOW_KF_KF: (KeyFrame*, KeyFrame*) :715-850,

@@ -42,6 +42,7 @@ def lib(fast=False):
     L.mo_window_search.argtypes = [FP, FP, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp]
     L.mo_search_by_projection_ff.argtypes = [FP, FP, vp, vp, C.c_int, f32, vp]
     L.mo_search_by_projection.argtypes = [FP, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, vp]
+    L.mo_search_by_projection_independent.argtypes = [FP, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
     L.mo_search_by_bow_kf_f.argtypes = [FP, FP, VP, VP, f32, C.c_int, vp]
     L.mo_search_by_bow_kf_kf.argtypes = [FP, FP, VP, VP, f32, C.c_int, vp]
     L.mo_search_for_triangulation.argtypes = [FP, FP, VP, VP, vp, vp, C.c_int, vp]
@@ -153,6 +154,31 @@ def search_by_projection(f, pts, variant, th_dist, ratio, check_ori):
     n = lib().mo_search_by_projection(C.byref(h.s), len(u), p(u), p(v), p(r), p(mn), p(mx), p(d), p(a), p(val),
                                       0 if variant == "local_map" else 1, th_dist, ratio, int(check_ori), m.ctypes.data)
     return n, m[: h.s.n]
+
+
+def search_by_projection_independent(f, pts, th_dist):
+    """Fuse / SearchBySim3 best-only loop: per POINT the best keypoint of f within th_dist (-1 none) -> (n, best)."""
+    h = frame_struct(f)
+    g = lambda a, t: None if a is None else np.ascontiguousarray(a, t)
+    u, v, r = g(pts.u, np.float32), g(pts.v, np.float32), g(pts.radius, np.float32)
+    mn, mx = g(pts.min_level, np.int32), g(pts.max_level, np.int32)
+    d, val = g(pts.desc, np.uint8), g(pts.valid, np.uint8)
+    m = np.empty(max(len(u), 1), np.int32)
+    p = lambda z: None if z is None else z.ctypes.data
+    n = lib().mo_search_by_projection_independent(C.byref(h.s), len(u), p(u), p(v), p(r), p(mn), p(mx), p(d), p(val),
+                                                  th_dist, m.ctypes.data)
+    return n, m[: len(u)]
+
+
+def search_by_sim3(f1, f2, pts12, pts21, th_dist):
+    """SearchBySim3's two scans + agreement (src/ORBmatcher.cc:1487-1502) -> (nFound, match12[i1] = i2 or -1)."""
+    _, m1 = search_by_projection_independent(f2, pts12, th_dist)
+    _, m2 = search_by_projection_independent(f1, pts21, th_dist)
+    out = np.full(len(m1), -1, np.int32)
+    for i1, i2 in enumerate(m1):
+        if i2 >= 0 and m2[i2] == i1:
+            out[i1] = i2
+    return int((out >= 0).sum()), out
 
 
 def search_by_bow(f1, f2, variant, ratio, check_ori):

@@ -55,6 +55,10 @@ def _lib():
         L.ref_m_search_by_projection_reloc.argtypes = [_P, _P, _P, _P, _F, _I, _F, _I, _P]
         L.ref_m_search_by_projection_sim3.argtypes = [_P, _P, _P, _P, _P, _I, _I, _F, _P]
         L.ref_m_is_in_frustum.argtypes = [_P, _P, _F] + [_P] * 6
+        L.ref_m_fuse.argtypes = [_P, _P, _P, _P, _P, _I, _F, _P, _P, _P]
+        L.ref_m_fuse_sim3.argtypes = [_P, _P, _P, _P, _I, _F, _P, _P]
+        L.ref_m_search_by_sim3.argtypes = [_P, _P, _P, _P, _P, _F, _P]
+        L.ref_m_search_by_projection_ff.argtypes = [_P, _P, _P, _I, _F, _I, _P]
         L._m_ready = True
     return L
 
@@ -230,3 +234,39 @@ def is_in_frustum(view: RefFrame, src: RefFrame, cos_limit=0.5):
                                lv.ctypes.data, vc.ctypes.data)
     k = src.n
     return ret[:k], iv[:k], u[:k], v[:k], lv[:k], vc[:k]
+
+
+def fuse(kf_frame: RefFrame, src: RefFrame, sel, th):
+    """Fuse(pKF, vpMapPoints, th): pKF = kf_frame's keyframe, vpMapPoints = src's MapPoints sel[k] ->
+    (nFused, added[k], went_bad[k], repl[k]) - see oracle/ref_orbmatcher.cc::ref_m_fuse."""
+    sel = np.ascontiguousarray(sel, np.int32)
+    n = len(sel)
+    added = np.zeros(n, np.int32); bad = np.zeros(n, np.uint8); repl = np.zeros(n, np.int32)
+    r = _lib().ref_m_fuse(kf_frame.keyframe(), kf_frame._f, src._f, src.keyframe(), sel.ctypes.data, n, th,
+                          added.ctypes.data, bad.ctypes.data, repl.ctypes.data)
+    return r, added, bad, repl
+
+
+def fuse_sim3(kf_frame: RefFrame, src: RefFrame, sel, th):
+    """Fuse(pKF, Scw = identity, vpPoints, th) -> (nFused, added[k], target_went_bad[idx])."""
+    sel = np.ascontiguousarray(sel, np.int32)
+    added = np.zeros(len(sel), np.int32); tbad = np.zeros(max(kf_frame.n, 1), np.uint8)
+    r = _lib().ref_m_fuse_sim3(kf_frame.keyframe(), kf_frame._f, src._f, sel.ctypes.data, len(sel), th,
+                               added.ctypes.data, tbad.ctypes.data)
+    return r, added, tbad[:kf_frame.n]
+
+
+def search_by_sim3(f1: RefFrame, f2: RefFrame, pre12, th):
+    """SearchBySim3(pKF1, pKF2, vpMatches12, 1, I, 0, th) -> (nFound, out12[i1] = keypoint of KF2 or -1)."""
+    pre = np.ascontiguousarray(pre12, np.int32)
+    out = np.zeros(max(f1.n, 1), np.int32)
+    n = _lib().ref_m_search_by_sim3(f1.keyframe(), f1._f, f2.keyframe(), f2._f, pre.ctypes.data, th, out.ctypes.data)
+    return n, out[:f1.n]
+
+
+def search_by_projection_ff(f1: RefFrame, f2: RefFrame, pos, window, ratio, check_ori):
+    """SearchByProjection(F1, F2, windowSize, matches2), F2 pose = identity; pos [f1.n, 3] -> (n, matches21)."""
+    pos = np.ascontiguousarray(pos, np.float32)
+    m = np.zeros(max(f2.n, 1), np.int32)
+    n = _lib().ref_m_search_by_projection_ff(f1._f, f2._f, pos.ctypes.data, int(window), ratio, int(check_ori), m.ctypes.data)
+    return n, m[:f2.n]

@@ -382,6 +382,108 @@ int ref_m_search_by_projection_sim3(void* kf, void* kf_box, void* src_fb, const 
   return n;
 }
 
+// ORBmatcher::Fuse(KeyFrame* pKF, vector<MapPoint*>& vpMapPoints, float th) (src/ORBmatcher.cc:1016-1134), pKF's pose at
+// identity.  vpMapPoints = the MapPoints on src_fb's keypoints sel[k] (each observes its own keypoint in src_kf, the
+// keyframe made from src_fb: points_take_descriptors).  What the call leaves behind, per point k:
+//   added[k]    keypoint of pKF the point now observes (the AddObservation branch, :1124-1128), else -1
+//   went_bad[k] 1 if the point was good before and is bad now (the Replace branch, :1119-1122: pMP->Replace(pMPinKF))
+//   repl[k]     after a Replace the point's old observation src_kf[sel[k]] holds pMPinKF: its keypoint index in pKF's
+//               own frame kf_box; -1 when that slot was erased (pMPinKF already observed src_kf through an earlier
+//               Replace, src/MapPoint.cc:148-151) or nothing was replaced
+// Returns nFused.
+int ref_m_fuse(void* kf, void* kf_box, void* src_fb, void* src_kf, const int32_t* sel, int npts, float th,
+               int32_t* added, uint8_t* went_bad, int32_t* repl) {
+  KeyFrame* pKF = static_cast<KeyFrame*>(kf);
+  KeyFrame* sKF = static_cast<KeyFrame*>(src_kf);
+  FrameBox* bk = static_cast<FrameBox*>(kf_box);
+  FrameBox* bs = static_cast<FrameBox*>(src_fb);
+  std::vector<MapPoint*> pts(npts);
+  std::vector<char> was_bad(npts);
+  for (int k = 0; k < npts; k++) { pts[k] = bs->f->mvpMapPoints[sel[k]]; was_bad[k] = pts[k]->isBad(); }
+  ORBmatcher matcher(0.6f, true);
+  const int n = matcher.Fuse(pKF, pts, th);
+  for (int k = 0; k < npts; k++) {
+    added[k] = pts[k]->GetIndexInKeyFrame(pKF);
+    went_bad[k] = (!was_bad[k] && pts[k]->isBad()) ? 1 : 0;
+    repl[k] = -1;
+    if (went_bad[k]) {
+      MapPoint* now = sKF->GetMapPoint(sel[k]);
+      std::map<MapPoint*, int>::iterator it = now ? bk->index.find(now) : bk->index.end();
+      if (it != bk->index.end()) repl[k] = it->second;
+    }
+  }
+  return n;
+}
+
+// ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, float th) (src/ORBmatcher.cc:1136-1265)
+// with Scw = identity.  added[k] as above (:1253-1257); target_went_bad[idx] = 1 when the MapPoint on pKF's keypoint idx
+// was good before and is bad now (pMPinKF->Replace(pMP), :1248-1251).  Returns nFused.
+int ref_m_fuse_sim3(void* kf, void* kf_box, void* src_fb, const int32_t* sel, int npts, float th, int32_t* added,
+                    uint8_t* target_went_bad) {
+  KeyFrame* pKF = static_cast<KeyFrame*>(kf);
+  FrameBox* bk = static_cast<FrameBox*>(kf_box);
+  FrameBox* bs = static_cast<FrameBox*>(src_fb);
+  std::vector<MapPoint*> pts(npts);
+  for (int k = 0; k < npts; k++) pts[k] = bs->f->mvpMapPoints[sel[k]];
+  const int N = bk->f->N;
+  std::vector<MapPoint*> before(N);
+  std::vector<char> was_bad(N, 0);
+  for (int i = 0; i < N; i++) { before[i] = pKF->GetMapPoint(i); was_bad[i] = before[i] ? before[i]->isBad() : 0; }
+  ORBmatcher matcher(0.6f, true);
+  const int n = matcher.Fuse(pKF, cv::Mat::eye(4, 4, CV_32F), pts, th);
+  for (int k = 0; k < npts; k++) added[k] = pts[k]->GetIndexInKeyFrame(pKF);
+  for (int i = 0; i < N; i++) target_went_bad[i] = (before[i] && !was_bad[i] && before[i]->isBad()) ? 1 : 0;
+  return n;
+}
+
+// ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12 = 1, R12 = I, t12 = 0, th) (src/ORBmatcher.cc:1267-1505), both
+// keyframe poses at identity.  pre12[i1] >= 0: vpMatches12[i1] starts as keyframe 2's MapPoint on keypoint pre12[i1]
+// (already matched, :1301-1311).  out12[i1] = keypoint of keyframe 2 whose MapPoint vpMatches12[i1] holds afterwards
+// (pre-set entries included), else -1.  Returns nFound.
+int ref_m_search_by_sim3(void* kf1, void* box1, void* kf2, void* box2, const int32_t* pre12, float th, int32_t* out12) {
+  FrameBox* b1 = static_cast<FrameBox*>(box1);
+  FrameBox* b2 = static_cast<FrameBox*>(box2);
+  const int N1 = b1->f->N;
+  std::vector<MapPoint*> m12(N1, static_cast<MapPoint*>(nullptr));
+  for (int i = 0; i < N1; i++)
+    if (pre12[i] >= 0) m12[i] = b2->f->mvpMapPoints[pre12[i]];
+  ORBmatcher matcher(0.75f, true);
+  const float s12 = 1.0f;
+  const int n = matcher.SearchBySim3(static_cast<KeyFrame*>(kf1), static_cast<KeyFrame*>(kf2), m12, s12,
+                                     cv::Mat::eye(3, 3, CV_32F), cv::Mat::zeros(3, 1, CV_32F), th);
+  for (int i = 0; i < N1; i++) {
+    std::map<MapPoint*, int>::iterator it = m12[i] ? b2->index.find(m12[i]) : b2->index.end();
+    out12[i] = it == b2->index.end() ? -1 : it->second;
+  }
+  return n;
+}
+
+// ORBmatcher::SearchByProjection(Frame& F1, Frame& F2, int windowSize, vpMapPointMatches2) (src/ORBmatcher.cc:519-594),
+// F2's pose at identity (Rc2w*x3Dw+tc2w returns the world point; u2 = fx*x*invz+cx is the float expression of :540-550).
+// pos: F1.N x 3 world positions of F1's MapPoints.  matches21[i2] = i1 whose MapPoint was NEWLY assigned to F2's
+// keypoint i2, else -1.
+int ref_m_search_by_projection_ff(void* fb1, void* fb2, const float* pos, int window, float ratio, int check_ori,
+                                  int32_t* matches21) {
+  FrameBox* b1 = static_cast<FrameBox*>(fb1);
+  FrameBox* b2 = static_cast<FrameBox*>(fb2);
+  for (int i = 0; i < b1->f->N; i++) {
+    MapPoint* p = b1->f->mvpMapPoints[i];
+    if (!p) continue;
+    cv::Mat x(3, 1, CV_32F);
+    for (int k = 0; k < 3; k++) x.at<float>(k) = pos[3 * i + k];
+    p->SetWorldPos(x);
+  }
+  b2->f->mTcw = cv::Mat::eye(4, 4, CV_32F);
+  std::vector<MapPoint*> out;
+  ORBmatcher matcher(ratio, check_ori != 0);
+  const int n = matcher.SearchByProjection(*b1->f, *b2->f, window, out);
+  for (int i = 0; i < b2->f->N; i++) {
+    std::map<MapPoint*, int>::iterator it = (out[i] && out[i] != b2->f->mvpMapPoints[i]) ? b1->index.find(out[i]) : b1->index.end();
+    matches21[i] = it == b1->index.end() ? -1 : it->second;
+  }
+  return n;
+}
+
 // Frame::isInFrustum(pMP, viewingCosLimit) (src/Frame.cc:136-197) of frame `view_fb` (pose = identity through the
 // reference's own UpdatePoseMatrices, :129-134) for the MapPoint on every keypoint of `src_fb` (geometry from
 // ref_m_frame_set_point_geometry).  Outputs per source keypoint: the return value and the tracking fields it writes

@@ -4,6 +4,7 @@
 #include <utility>
 #include <algorithm>
 #include <cstring>
+#include <vector>
 
 #include "orbm_match.cuh"
 
@@ -59,7 +60,7 @@ int run_job(orbm_handle* h, const HostJob& J) {
   const int np = J.nproblems;
   if (np < 0 || !J.set2 || !J.idx2 || !J.out || !J.nmatches || J.stride < 1) { h->err = "bad search arguments"; return ORBM_ERR_ARG; }
   if (np == 0) return ORBM_OK;
-  const bool points = J.kind == K_PROJ_LOCAL || J.kind == K_PROJ_BEST;
+  const bool points = J.kind == K_PROJ_LOCAL || J.kind == K_PROJ_BEST || J.kind == K_PROJ_INDEP;
   const bool bow = J.kind == K_BOW_KF_F || J.kind == K_BOW_KF_KF || J.kind == K_TRIANG;
   if (!points && (!J.set1 || !J.idx1)) { h->err = "missing source frame set"; return ORBM_ERR_ARG; }
   if (points && !J.points) { h->err = "missing points"; return ORBM_ERR_ARG; }
@@ -72,7 +73,7 @@ int run_job(orbm_handle* h, const HostJob& J) {
   std::vector<Problem> prob(np);
   int64_t qtot = 0, ttot = 0, ptot = 0;
   int max_nq = 0, max_nt = 0;   // nq is an upper bound for the BoW kinds (bow_prep writes the exact count)
-  const bool per_source = J.kind == K_INIT || J.kind == K_BOW_KF_KF || J.kind == K_TRIANG;
+  const bool per_source = J.kind == K_INIT || J.kind == K_BOW_KF_KF || J.kind == K_TRIANG || J.kind == K_PROJ_INDEP;
   for (int p = 0; p < np; p++) {
     Problem& P = prob[p];
     memset(&P, 0, sizeof(P));
@@ -313,12 +314,58 @@ extern "C" int orbm_search_by_projection(orbm_handle* h, const orbm_frameset* se
                                          const orbm_points* points, int nproblems, int variant, int th_dist,
                                          float ratio, int check_ori, int32_t* match_out, int stride,
                                          int32_t* nmatches) {
-  if (h && variant != ORBM_PROJ_LOCAL_MAP && variant != ORBM_PROJ_BEST) { h->err = "unknown variant"; return ORBM_ERR_ARG; }
+  if (h && variant != ORBM_PROJ_LOCAL_MAP && variant != ORBM_PROJ_BEST && variant != ORBM_PROJ_BEST_INDEPENDENT) {
+    h->err = "unknown variant";
+    return ORBM_ERR_ARG;
+  }
   HostJob J;
-  J.kind = variant == ORBM_PROJ_LOCAL_MAP ? K_PROJ_LOCAL : K_PROJ_BEST;
+  J.kind = variant == ORBM_PROJ_LOCAL_MAP ? K_PROJ_LOCAL : (variant == ORBM_PROJ_BEST ? K_PROJ_BEST : K_PROJ_INDEP);
   J.set2 = set; J.idx2 = idx; J.points = points; J.nproblems = nproblems; J.th_dist = th_dist; J.ratio = ratio;
-  J.check_ori = check_ori; J.out = match_out; J.stride = stride; J.nmatches = nmatches;
+  J.check_ori = J.kind == K_PROJ_INDEP ? 0 : check_ori;   // Fuse / SearchBySim3 have no rotation check
+  J.out = match_out; J.stride = stride; J.nmatches = nmatches;
   return run_job(h, J);
+}
+
+extern "C" int orbm_search_by_sim3(orbm_handle* h, const orbm_frameset* set, const int32_t* idx1, const int32_t* idx2,
+                                   const orbm_points* points12, const orbm_points* points21, int npairs, int th_dist,
+                                   int32_t* match12, int stride, int32_t* nfound) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!set || !idx1 || !idx2 || !points12 || !points21 || !match12 || !nfound || npairs < 0 || stride < 1) {
+    h->err = "bad SearchBySim3 arguments";
+    return ORBM_ERR_ARG;
+  }
+  if (npairs == 0) return ORBM_OK;
+  // problem 2p: keyframe 1's points scored in keyframe 2 (vnMatch1); problem 2p + 1: keyframe 2's points in keyframe 1
+  std::vector<int32_t> tgt(2 * (size_t)npairs), nm(2 * (size_t)npairs);
+  std::vector<orbm_points> pts(2 * (size_t)npairs);
+  int row = stride;
+  for (int p = 0; p < npairs; p++) {
+    if (idx1[p] < 0 || idx1[p] >= set->nframes || idx2[p] < 0 || idx2[p] >= set->nframes) { h->err = "frame index out of range"; return ORBM_ERR_ARG; }
+    const int n1 = set->frame_off[idx1[p] + 1] - set->frame_off[idx1[p]], n2 = set->frame_off[idx2[p] + 1] - set->frame_off[idx2[p]];
+    if (points12[p].n != n1 || points21[p].n != n2) { h->err = "SearchBySim3: one point per keypoint of the source keyframe expected"; return ORBM_ERR_ARG; }
+    if (n1 > stride) { h->err = "stride smaller than a frame"; return ORBM_ERR_ARG; }
+    row = std::max(row, std::max(n1, n2));
+    tgt[2 * p] = idx2[p]; tgt[2 * p + 1] = idx1[p];
+    pts[2 * p] = points12[p]; pts[2 * p + 1] = points21[p];
+  }
+  std::vector<int32_t> best((size_t)2 * npairs * row);
+  const int rc = orbm_search_by_projection(h, set, tgt.data(), pts.data(), 2 * npairs, ORBM_PROJ_BEST_INDEPENDENT, th_dist,
+                                           0.f, 0, best.data(), row, nm.data());
+  if (rc != ORBM_OK) return rc;
+  for (int p = 0; p < npairs; p++) {          // agreement, :1487-1502
+    const int32_t* m1 = &best[(size_t)(2 * p) * row];
+    const int32_t* m2 = &best[(size_t)(2 * p + 1) * row];
+    int32_t* out = match12 + (size_t)p * stride;
+    const int n1 = points12[p].n;
+    int found = 0;
+    for (int i1 = 0; i1 < stride; i1++) {
+      int32_t r = -1;
+      if (i1 < n1 && m1[i1] >= 0 && m2[m1[i1]] == i1) { r = m1[i1]; found++; }
+      out[i1] = r;
+    }
+    nfound[p] = found;
+  }
+  return ORBM_OK;
 }
 
 extern "C" int orbm_search_by_bow(orbm_handle* h, const orbm_frameset* set1, const orbm_frameset* set2,

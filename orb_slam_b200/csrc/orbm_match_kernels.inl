@@ -17,7 +17,10 @@ namespace {
     asm volatile("griddepcontrol.wait;" ::: "memory");           \
   } while (0)
 
-enum Kind { K_INIT = 0, K_WINDOW, K_PROJ_FF, K_PROJ_LOCAL, K_PROJ_BEST, K_BOW_KF_F, K_BOW_KF_KF, K_TRIANG };
+// K_PROJ_INDEP: the best-only loops of Fuse (src/ORBmatcher.cc:1094-1113, 1223-1242) and SearchBySim3 (:1373-1398,
+// :1458-1483): no target is taken on entry, nothing an earlier point accepted is skipped, every point reports its own
+// best keypoint (two points may pick the same one) - no loop-carried state at all.
+enum Kind { K_INIT = 0, K_WINDOW, K_PROJ_FF, K_PROJ_LOCAL, K_PROJ_BEST, K_BOW_KF_F, K_BOW_KF_KF, K_TRIANG, K_PROJ_INDEP };
 
 struct Problem {
   int nq, nt;          // queries (may be rewritten by bow_prep), target keypoints
@@ -531,7 +534,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
   const int kind = a.kind;
   const float ratio = a.ratio;
   const float kIntMaxF = 2147483648.0f;  // (float)INT_MAX
-  const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL);
+  const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL && kind != K_PROJ_INDEP);
   const int kFree = 0x7fffffff;
   float F[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   if (kind == K_TRIANG)
@@ -608,6 +611,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
           if (ev < q) dmin = min(dmin, Dprev[ev]);
         return dmin <= d;
       }
+      if (kind == K_PROJ_INDEP) return false;                   // Fuse / SearchBySim3 scan every candidate
       return s_link[t] < q;                                     // `if (taken) continue`
     };
     auto decide = [&](int q, uint32_t b, uint32_t sk, int tb, int tsec) -> bool {
@@ -626,7 +630,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
               ok = !(l1 == l2 && (float)bd > __fmul_rn(ratio, sdf));
             }
             break;
-          case K_PROJ_BEST: ok = bd <= a.th_dist; break;                                               // :1576, :1702, :398
+          case K_PROJ_BEST: case K_PROJ_INDEP: ok = bd <= a.th_dist; break;                            // :1576, :1702, :398; :1116, :1245, :1395, :1480
           case K_BOW_KF_F: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;          // :224-226
           default: ok = bd < ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;                   // :791-793
         }
@@ -773,7 +777,7 @@ __global__ void __launch_bounds__(1024) commit_par_kernel(SearchArgs a, int max_
         for (int ev = s_link[t]; ev >= 0; ev = s_next[ev]) owner = max(owner, ev);
         if (owner == q) gts[t] = make_int2(qr[q].src, Dcur[q]);
         else match = -1;
-      } else {
+      } else if (kind != K_PROJ_INDEP) {       // (independent points leave the targets free)
         gts[t] = make_int2(qr[q].src, Dcur[q]);
       }
     }
@@ -819,7 +823,7 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
   const int kind = a.kind;
   const float ratio = a.ratio;
   const float kIntMaxF = 2147483648.0f;  // (float)INT_MAX
-  const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL);
+  const bool use_hist = kind == K_WINDOW || (a.check_ori && kind != K_PROJ_FF && kind != K_PROJ_LOCAL && kind != K_PROJ_INDEP);
   float F[9];
   if (kind == K_TRIANG)
     for (int k = 0; k < 9; k++) F[k] = a.F12[(int64_t)p * 9 + k];
@@ -875,7 +879,7 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
           const uint32_t e = j < 32 ? cb[i * 32 + lane] : cand[off + j];
           const int t = (int)(e & kCandMask), d = (int)(e >> kCandShift);
           const int2 st = ts[t];
-          const bool skip = kind == K_INIT ? st.y <= d : st.x != -1;  // :637 / `if (taken) continue`
+          const bool skip = kind == K_INIT ? st.y <= d : (kind == K_PROJ_INDEP ? false : st.x != -1);  // :637 / `if (taken) continue`
           if (!skip) {
             const uint32_t key = ((uint32_t)d << kCandShift) | (uint32_t)j;
             if (key < b) { s = b; tsec = tb; b = key; tb = t; }
@@ -903,7 +907,7 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
               }
               break;
             }
-            case K_PROJ_BEST: ok = bd <= a.th_dist; break;                                               // :1576, :1702, :398
+            case K_PROJ_BEST: case K_PROJ_INDEP: ok = bd <= a.th_dist; break;                            // :1576, :1702, :398; :1116, :1245, :1395, :1480
             case K_BOW_KF_F: ok = bd <= ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;          // :224-226
             default: ok = bd < ORBM_TH_LOW && (float)bd < __fmul_rn(ratio, sdf); break;                   // :791-793
           }
@@ -940,7 +944,7 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
           const int prev = ts[accept_t].x;
           if (prev >= 0) qr[prev].match = -1;
         }
-        ts[accept_t] = make_int2(src, accept_d);
+        if (kind != K_PROJ_INDEP) ts[accept_t] = make_int2(src, accept_d);
         qr[q].match = accept_t;
         qr[q].bin = use_hist ? accept_t : -1;   // the accepted target; turned into its rotation bin after the loop
       }
@@ -954,7 +958,7 @@ __global__ void __launch_bounds__(32 * kCommitWarps) commit_kernel(SearchArgs a)
   commit_tail(a, P, p, qr, ts, ts_in_smem ? gts : nullptr, s_hist[warp], use_hist, lane);
 }
 
-// output rows (include/orbm.h): per-source for K_INIT / K_BOW_KF_KF / K_TRIANG, per-target otherwise
+// output rows (include/orbm.h): per-source for K_INIT / K_BOW_KF_KF / K_TRIANG / K_PROJ_INDEP, per-target otherwise
 __global__ void __launch_bounds__(128) emit_kernel(SearchArgs a) {
   ORBM_PDL_ENTRY();
   const int p = blockIdx.x;
@@ -962,7 +966,7 @@ __global__ void __launch_bounds__(128) emit_kernel(SearchArgs a) {
   int32_t* out = a.out + (int64_t)p * a.stride;
   const QRec* qr = a.q + P.qstart;
   const int2* ts = a.tstate + P.tstart;
-  const bool per_source = a.kind == K_INIT || a.kind == K_BOW_KF_KF || a.kind == K_TRIANG;
+  const bool per_source = a.kind == K_INIT || a.kind == K_BOW_KF_KF || a.kind == K_TRIANG || a.kind == K_PROJ_INDEP;
   if (per_source) {
     for (int i = threadIdx.x; i < a.stride; i += blockDim.x) out[i] = -1;
     __syncthreads();

@@ -97,6 +97,7 @@ def _bind(L):
     L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_search_by_projection_frames.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, vp, vp]
     L.orbm_search_by_projection.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, f32, C.c_int, vp, C.c_int, vp]
+    L.orbm_search_by_sim3.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_search_by_bow.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, vp, C.c_int, vp]
     L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_knn2.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp]
@@ -499,6 +500,14 @@ class ProjectedPoints:
         radius = (np.float32(int(th)) * np.asarray(scale_factors, np.float32)[level]).astype(np.float32)
         return cls(u, v, radius, level - 1, level, desc, None, valid)
 
+    @classmethod
+    def for_fuse(cls, u, v, level, desc, scale_factors, th, valid=None):
+        """Fuse (src/ORBmatcher.cc:1078-1086, :1207-1215) and SearchBySim3 (:1353-1360, :1438-1445): radius = th *
+        scale[predicted level] (th is a float there), candidates on levels [pred-1, pred]; use variant 'independent'."""
+        level = _i32(level)
+        radius = (np.float32(th) * np.asarray(scale_factors, np.float32)[level]).astype(np.float32)
+        return cls(u, v, radius, level - 1, level, desc, None, valid)
+
 
 def predict_scale_level(dist, min_distance, scale_factors):
     """`ratio = dist / minDistance; lower_bound(mvScaleFactors, ratio)` clamped to nLevels-1, all in float
@@ -594,13 +603,31 @@ class ORBmatcher:
         :286-407).  points: list of ProjectedPoints, one per problem.  Returns (nmatches, rows[idx] = point)."""
         ii = _i32(np.atleast_1d(idx))
         arr = (_Points * len(points))(*[p.c_struct() for p in points])
-        stride = max(fset.max_n, 1)
+        v = {"local_map": 0, "best": 1, "independent": 2}[variant]
+        # 'independent' (Fuse / SearchBySim3 loops) reports per POINT, the others per keypoint of the target frame
+        stride = max([p.n for p in points] + [1]) if v == 2 else max(fset.max_n, 1)
         out = np.empty((len(ii), stride), np.int32); nm = np.empty(len(ii), np.int32)
-        v = 0 if variant == "local_map" else 1
         self.m._check(self._L.orbm_search_by_projection(self.m._h, fset._s, ii.ctypes.data, arr, len(ii), v,
                                                         int(th_dist), self.mfNNratio, int(self.mbCheckOrientation),
                                                         out.ctypes.data, stride, nm.ctypes.data))
         return nm, out
+
+    def Fuse(self, fset, idx, points, th_dist=TH_LOW):
+        """Candidate scoring of ORBmatcher::Fuse (both overloads, src/ORBmatcher.cc:1016-1134, :1136-1265): per problem
+        (nFused, rows[k] = bestIdx of point k or -1).  What the reference then does with (point, bestIdx) - Replace or
+        AddObservation, :1116-1131 - is pointer bookkeeping and stays with the caller."""
+        return self.SearchByProjection(fset, idx, points, "independent", th_dist)
+
+    def SearchBySim3(self, fset, idx1, idx2, points12, points21, th_dist=TH_HIGH):
+        """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1267-1505): both scans + agreement -> (nFound, match12 rows)."""
+        i1, i2 = self._pairs(idx1, idx2)
+        a12 = (_Points * len(points12))(*[p.c_struct() for p in points12])
+        a21 = (_Points * len(points21))(*[p.c_struct() for p in points21])
+        stride = max(fset.max_n, 1)
+        out = np.empty((len(i1), stride), np.int32); nf = np.empty(len(i1), np.int32)
+        self.m._check(self._L.orbm_search_by_sim3(self.m._h, fset._s, i1.ctypes.data, i2.ctypes.data, a12, a21, len(i1),
+                                                  int(th_dist), out.ctypes.data, stride, nf.ctypes.data))
+        return nf, out
 
     def SearchByBoW(self, set1, set2, idx1, idx2, variant="kf_f"):
         """'kf_f': SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:155-284, rows[idxF] = idxKF;

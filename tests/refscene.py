@@ -144,3 +144,151 @@ def projection_cases(oracle, RF, seed, cam, nfeatures=400):
                                        valid=(v1[sel] == 1) & (pre < 0) & ok[sel])
         yield dict(name=f"sim3:{th}", target=target(taken), points=pts, variant="best", th_dist=50, ratio=0.9,
                    ori=False, ref_n=rn, ref_m=rm)
+
+
+def _point_cloud(rng, rf, du, dv, cam, sf, nlevels=6):
+    """World points (camera frame == world frame) for the MapPoints of frame rf so that they project near
+    (x + du, y + dv); some behind the camera, outside the image, out of the scale range or seen from behind."""
+    n = rf.n
+    fx, fy, cx, cy = (np.float32(c) for c in cam[:4])
+    z = rng.uniform(1.0, 8.0, n).astype(np.float32)
+    z[5:10] = -2.0
+    tu = rf.xu + du + rng.normal(0, 2, n); tv = rf.yu + dv + rng.normal(0, 2, n)
+    tu[:5] = -400.0
+    pos = np.stack([(tu - cx) / fx * z, (tv - cy) / fy * z, z], 1).astype(np.float32)
+    dist = _norm3(pos)
+    lvl_true = np.clip(rf.kps["octave"] + rng.integers(-1, 2, n), 0, nlevels - 1)
+    min_dist = (dist / (sf[lvl_true] * rng.uniform(0.85, 0.999, n).astype(np.float32))).astype(np.float32)
+    max_dist = (min_dist * np.float32(1.2 ** nlevels)).astype(np.float32)
+    min_dist[10:14] = dist[10:14] * np.float32(1.5)
+    max_dist[14:18] = dist[14:18] * np.float32(0.5)
+    normal = (pos / dist[:, None]).astype(np.float32)
+    flip = rng.random(n) < 0.1
+    normal[flip] = -normal[flip]
+    return pos, dist, min_dist, max_dist, normal
+
+
+def _project_kf(pos, dist, min_dist, max_dist, normal, cam, bounds, sf, check_normal):
+    """Caller-side float expressions shared by Fuse (src/ORBmatcher.cc:1043-1083, :1171-1212) and SearchBySim3
+    (:1325-1357, :1410-1442) at identity pose: (u, v, predicted level, passes-all-tests)."""
+    from orb_slam_b200.matcher import predict_scale_level
+    fx, fy, cx, cy = (np.float32(c) for c in cam[:4])
+    b = bounds
+    invz = (np.float32(1) / pos[:, 2]).astype(np.float32)
+    x = (pos[:, 0] * invz).astype(np.float32); y = (pos[:, 1] * invz).astype(np.float32)
+    u = fx * x + cx; v = fy * y + cy
+    in_img = (u >= np.float32(b[0])) & (u < np.float32(b[1])) & (v >= np.float32(b[2])) & (v < np.float32(b[3]))
+    ok = (~(pos[:, 2] < 0)) & in_img & ~((dist < min_dist) | (dist > max_dist))
+    if check_normal:
+        dot = (pos.astype(np.float64) * normal.astype(np.float64)).sum(1)
+        ok &= ~(dot < 0.5 * dist.astype(np.float64))
+    return u, v, predict_scale_level(dist, min_dist, sf), ok
+
+
+def fuse_cases(oracle, RF, seed, cam, nfeatures=400):
+    """ORBmatcher::Fuse (both overloads), SearchBySim3 and SearchByProjection(F1, F2, window) run by the COMPILED
+    REFERENCE on its own objects.  Yields dicts: `kind` in {fuse, fuse_sim3, sim3, proj_ff}, the flat-array inputs of the
+    oracle / CUDA form and everything the reference's call leaves observable."""
+    from orb_slam_b200.matcher import ProjectedPoints
+    w = RF.World(None, nfeatures, 1.2, 6, 1, 20)
+    ims = images(oracle, seed)
+    f1 = w.frame(ims[0], K_of(cam), cam[4:9], reset_static=True)
+    f2 = w.frame(ims[1], K_of(cam), cam[4:9])
+    sf = np.cumprod(np.concatenate([[1.0], np.full(5, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    rng = np.random.default_rng(seed)
+    v1, v2 = valid_flags(f1.n, seed + 2), valid_flags(f2.n, seed + 1)
+    g1 = _point_cloud(rng, f1, -11, -6, cam, sf)      # f1's points, seen in f2
+    g2 = _point_cloud(rng, f2, +11, +6, cam, sf)      # f2's points, seen in f1
+
+    def fresh():
+        """New MapPoint objects on both frames (the calls below mutate them)."""
+        f1.set_valid(v1); f1.set_point_geometry(g1[0], g1[2], g1[3], g1[4]); f1.points_take_descriptors()
+        f2.set_valid(v2); f2.set_point_geometry(g2[0], g2[2], g2[3], g2[4]); f2.points_take_descriptors()
+
+    def frame_of(rf, v):
+        t = match_frame(rf, v, None)
+        t.valid = (np.asarray(v) != 0).astype(np.uint8)
+        return t
+
+    sel = np.flatnonzero(v1 != 0).astype(np.int32)     # every MapPoint of f1, good and bad
+    rng.shuffle(sel)
+    # ---- Fuse(pKF, vpMapPoints, th) :1016-1134 ------------------------------------------------------------------------
+    u, v, level, ok = _project_kf(*g1, cam, f2.bounds, sf, True)
+    for th in (2.5, 6.0):
+        fresh()
+        n, added, went_bad, repl = RF.fuse(f2, f1, sel, th)
+        pts = ProjectedPoints.for_fuse(u[sel], v[sel], level[sel], f1.desc[sel], sf, th, valid=(v1[sel] == 1) & ok[sel])
+        yield dict(kind="fuse", name=f"fuse:{th}", target=frame_of(f2, v2), tvalid=v2.copy(), points=pts, th_dist=50,
+                   ref_n=n, added=added, went_bad=went_bad, repl=repl)
+    # ---- Fuse(pKF, Scw, vpPoints, th) :1136-1265 ------------------------------------------------------------------------
+    for th in (4.0, 8.0):
+        fresh()
+        n, added, tbad = RF.fuse_sim3(f2, f1, sel, th)
+        pts = ProjectedPoints.for_fuse(u[sel], v[sel], level[sel], f1.desc[sel], sf, th, valid=(v1[sel] == 1) & ok[sel])
+        yield dict(kind="fuse_sim3", name=f"fuse_sim3:{th}", target=frame_of(f2, v2), tvalid=v2.copy(), points=pts,
+                   th_dist=50, ref_n=n, added=added, target_went_bad=tbad)
+    # ---- SearchBySim3 :1267-1505 ----------------------------------------------------------------------------------------
+    u12, v12, l12, ok12 = _project_kf(*g1, cam, f2.bounds, sf, False)
+    u21, v21, l21, ok21 = _project_kf(*g2, cam, f1.bounds, sf, False)
+    for th in (7.5, 3.0):
+        fresh()
+        pre = np.full(f1.n, -1, np.int32)              # vpMatches12 on entry: some pairs already matched
+        c1 = rng.choice(np.flatnonzero(v1 == 1), 20, replace=False)
+        pre[c1] = rng.choice(np.flatnonzero(v2 != 0), 20, replace=False)
+        n, out12 = RF.search_by_sim3(f1, f2, pre, th)
+        already2 = np.zeros(f2.n, bool); already2[pre[pre >= 0]] = True
+        p12 = ProjectedPoints.for_fuse(u12, v12, l12, f1.desc, sf, th, valid=(v1 == 1) & (pre < 0) & ok12)
+        p21 = ProjectedPoints.for_fuse(u21, v21, l21, f2.desc, sf, th, valid=(v2 == 1) & ~already2 & ok21)
+        yield dict(kind="sim3", name=f"sim3:{th}", f1=frame_of(f1, v1), f2=frame_of(f2, v2), p12=p12, p21=p21, pre=pre,
+                   th_dist=100, ref_n=n, ref_m=out12)
+    # ---- SearchByProjection(F1, F2, window, matches2) :519-594 ----------------------------------------------------------
+    fx, fy, cx, cy = (np.float32(c) for c in cam[:4])
+    pos = g1[0]
+    invz = (1.0 / pos[:, 2].astype(np.float64)).astype(np.float32)          # const float invzc2 = 1.0/z
+    uu = (fx * pos[:, 0]) * invz + cx; vv = (fy * pos[:, 1]) * invz + cy     # F2.fx*xc2*invzc2+F2.cx, left to right
+    for window, ratio in ((15, 0.8), (50, 0.9)):
+        fresh()
+        n, m21 = RF.search_by_projection_ff(f1, f2, pos, window, ratio, True)
+        a = match_frame(f1, v1, None)                   # valid = good MapPoint (none of them is in F2 yet)
+        yield dict(kind="proj_ff", name=f"proj_ff:{window}", f1=a, f2=frame_of(f2, v2),
+                   uv=np.stack([uu, vv], 1).astype(np.float32), window=window, ratio=ratio, ref_n=n, ref_m=m21)
+
+
+def fuse_expectation(case, best):
+    """What the reference's Fuse leaves observable, predicted from the per-point best keypoints `best` (oracle or CUDA)
+    and the state of the target keypoints (`tvalid`: 0 no MapPoint, 1 good, 2 bad) by replaying ONLY the pointer
+    bookkeeping of src/ORBmatcher.cc:1116-1131 / :1245-1260 and MapPoint::Replace (src/MapPoint.cc:124-158)."""
+    tv = case["tvalid"]
+    n = len(best)
+    if case["kind"] == "fuse":
+        added = np.full(n, -1, np.int32); bad = np.zeros(n, np.uint8); repl = np.full(n, -1, np.int32)
+        holder = {}                     # keypoint -> 'own' (the keyframe's good MapPoint) or a point index
+        seen_src = set()                # MapPoints in the keyframe that already observe the source keyframe
+        for k in range(n):
+            t = int(best[k])
+            if t < 0:
+                continue
+            h = holder.get(t, "own" if tv[t] == 1 else ("badown" if tv[t] == 2 else None))
+            if h is None:               # free keypoint: AddObservation + AddMapPoint
+                added[k] = t; holder[t] = k; seen_src.add(("p", k))
+            elif h == "badown":         # a bad MapPoint sits there: counted, nothing done
+                pass
+            else:                       # pMP->Replace(pMPinKF): the point dies, its source observation moves over
+                bad[k] = 1
+                key = ("own", t) if h == "own" else ("p", h)
+                if key not in seen_src:
+                    seen_src.add(key)
+                    if h == "own":
+                        repl[k] = t     # observable through the keyframe's own frame index
+        return dict(added=added, went_bad=bad, repl=repl)
+    added = np.full(n, -1, np.int32); tbad = np.zeros(len(tv), np.uint8)
+    last = {}
+    for k in range(n):
+        t = int(best[k])
+        if t >= 0 and tv[t] != 2:
+            last[t] = k                 # pMPinKF->Replace(pMP): the newest point takes over the observation
+            if tv[t] == 1:
+                tbad[t] = 1
+    for t, k in last.items():
+        added[k] = t
+    return dict(added=added, target_went_bad=tbad)

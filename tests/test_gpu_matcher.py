@@ -486,3 +486,68 @@ def test_oversized_frames_take_the_global_state_paths(M, matcher, oracle):
     nm, rows = om.SearchByBoW(fs, fs, [0], [1], "kf_f")
     on, orow = M.search_by_bow(a, b, "kf_f", 0.85, True)
     assert nm[0] == on and _rows_equal(rows[0], orow)
+
+
+def test_cuda_equals_reference_generated_fuse_golden(matcher):
+    """The CUDA matcher against vectors produced by the reference's OWN Fuse (both overloads, src/ORBmatcher.cc:1016-1265),
+    SearchBySim3 (:1267-1505) and SearchByProjection(F1, F2, window) (:519-594) (tests/golden/make_ref_fuse_golden.py):
+    ORBM_PROJ_BEST_INDEPENDENT, orbm_search_by_sim3, orbm_search_by_projection_frames."""
+    import refgolden as RG
+    import refscene as RS
+    from orb_slam_b200 import ORBmatcher
+    om = ORBmatcher(0.9, True, matcher=matcher)
+    cases = list(RG.fuse_cases())
+    fus = [c for c in cases if c["kind"] in ("fuse", "fuse_sim3")]
+    fs = matcher.upload([c["target"] for c in fus])
+    nm, rows = om.Fuse(fs, list(range(len(fus))), [c["points"] for c in fus], 50)       # all 8 calls in one batch
+    for k, c in enumerate(fus):
+        assert nm[k] == c["ref_n"], c["name"]
+        best = rows[k, :c["points"].n]
+        assert np.all(rows[k, c["points"].n:] == -1)
+        for key, val in RS.fuse_expectation(c, best).items():
+            assert np.array_equal(val, c[key]), (c["name"], key)
+    sim = [c for c in cases if c["kind"] == "sim3"]
+    fs = matcher.upload([f for c in sim for f in (c["f1"], c["f2"])])
+    i1 = list(range(0, 2 * len(sim), 2)); i2 = [i + 1 for i in i1]
+    nf, rows = om.SearchBySim3(fs, i1, i2, [c["p12"] for c in sim], [c["p21"] for c in sim], 100)
+    for k, c in enumerate(sim):
+        m12 = rows[k, :c["f1"].n]
+        assert nf[k] == c["ref_n"] and np.array_equal(np.where(c["pre"] >= 0, c["pre"], m12), c["ref_m"]), c["name"]
+    for c in (c for c in cases if c["kind"] == "proj_ff"):
+        fs = matcher.upload([c["f1"], c["f2"]])
+        o2 = ORBmatcher(c["ratio"], True, matcher=matcher)
+        nm, rows = o2.SearchByProjectionFrames(fs, fs, [0], [1], [c["uv"]], c["window"])
+        assert nm[0] == c["ref_n"] and _rows_equal(rows[0], c["ref_m"]), c["name"]
+
+
+def test_fuse_and_sim3_scoring_large_batches(M, matcher, pairs):
+    """ORBM_PROJ_BEST_INDEPENDENT / orbm_search_by_sim3 against the oracle on 1000-keypoint frames, 6 problems (fixed
+    point commit) and 640 problems (replay commit)."""
+    from orb_slam_b200 import ORBmatcher, ProjectedPoints
+    sf = np.cumprod(np.concatenate([[1.0], np.full(7, np.float32(1.2))]).astype(np.float32)).astype(np.float32)
+    rng = np.random.default_rng(77)
+    fr1 = [MD.with_valid(p[0], MD.random_valid(p[0].n, 0.5, 210 + k)) for k, p in enumerate(pairs)]
+    fr2 = [MD.with_valid(p[1], MD.random_valid(p[1].n, 0.5, 220 + k)) for k, p in enumerate(pairs)]
+    fs = matcher.upload([MD.to_matchframe(f) for f in fr1 + fr2])
+    P = len(pairs)
+
+    def proj(src, shift, sign):
+        n = src.n
+        u = (src.x - sign * np.float32(shift[0]) + rng.uniform(-2, 2, n)).astype(np.float32)
+        v = (src.y - sign * np.float32(shift[1]) + rng.uniform(-2, 2, n)).astype(np.float32)
+        level = np.clip(src.octave + rng.integers(0, 2, n), 0, 7)
+        return ProjectedPoints.for_fuse(u, v, level, src.desc, sf, float(rng.choice([2.5, 4.0, 7.5])),
+                                        valid=(rng.random(n) < 0.85).astype(np.uint8))
+    p12 = [proj(fr1[k], pairs[k][2], 1) for k in range(P)]
+    p21 = [proj(fr2[k], pairs[k][2], -1) for k in range(P)]
+    om = ORBmatcher(0.9, True, matcher=matcher)
+    ref_f = [M.search_by_projection_independent(fr2[k], p12[k], 50) for k in range(P)]
+    ref_s = [M.search_by_sim3(fr1[k], fr2[k], p12[k], p21[k], 100) for k in range(P)]
+    assert sum(r[0] for r in ref_f) > 600 and sum(r[0] for r in ref_s) > 300
+    for which in (list(range(P)), _shuffled_batch(P, 640, 5)):
+        nm, rows = om.Fuse(fs, [P + w for w in which], [p12[w] for w in which], 50)
+        for p, w in enumerate(which):
+            assert nm[p] == ref_f[w][0] and _rows_equal(rows[p], ref_f[w][1]), (p, w)
+        nf, rows = om.SearchBySim3(fs, which, [P + w for w in which], [p12[w] for w in which], [p21[w] for w in which], 100)
+        for p, w in enumerate(which):
+            assert nf[p] == ref_s[w][0] and _rows_equal(rows[p], ref_s[w][1]), (p, w)

@@ -221,3 +221,53 @@ def test_search_for_triangulation_equals_compiled_reference(oracle, M, tmp_path,
         rn, rm = RF.search_for_triangulation(rfs[0], rfs[1], F12, ratio, ori)
         on, om = M.search_for_triangulation(ofr[0], ofr[1], F12, sigma2, ori)
         assert rn == on and np.array_equal(rm, om) and on > 20, (ratio, ori)
+
+
+@pytest.mark.parametrize("seed,cam", [(41, RS.CAM_SHIPPED), (42, RS.CAM_PINHOLE)])
+def test_fuse_sim3_projection_frames_equal_compiled_reference(oracle, M, seed, cam):
+    """The rest of M6 and M4: ORBmatcher::Fuse (src/ORBmatcher.cc:1016-1134 and :1136-1265), SearchBySim3 (:1267-1505) and
+    SearchByProjection(F1, F2, window) (:519-594) run by the compiled reference on its own KeyFrame / MapPoint objects,
+    against the oracle's independent best-only scoring.  Fuse returns only a count; the per-point keypoints are read
+    off what it does to the object graph (observations added, points / keyframe points replaced), which
+    refscene.fuse_expectation predicts from the oracle's per-point result."""
+    RF = _rf()
+    seen = {}
+    for c in RS.fuse_cases(oracle, RF, seed, cam):
+        kind = c["kind"]
+        seen[kind] = seen.get(kind, 0) + 1
+        if kind in ("fuse", "fuse_sim3"):
+            n, best = M.search_by_projection_independent(c["target"], c["points"], c["th_dist"])
+            assert n == c["ref_n"] and n > 40, (c["name"], n, c["ref_n"])
+            exp = RS.fuse_expectation(c, best)
+            for key, val in exp.items():
+                assert np.array_equal(val, c[key]), (c["name"], key)
+            tv = c["tvalid"][best[best >= 0]]
+            assert (tv == 0).sum() > 5 and (tv == 1).sum() > 5           # both branches taken
+            assert len(np.unique(best[best >= 0])) < (best >= 0).sum()   # two points chose one keypoint
+        elif kind == "sim3":
+            n, m12 = M.search_by_sim3(c["f1"], c["f2"], c["p12"], c["p21"], c["th_dist"])
+            exp = np.where(c["pre"] >= 0, c["pre"], m12)                 # pre-set entries stay (vpMatches12 in/out)
+            assert n == c["ref_n"] and np.array_equal(exp, c["ref_m"]) and n > 15, (c["name"], n, c["ref_n"])
+        else:
+            n, m21 = M.search_by_projection_ff(c["f1"], c["f2"], c["uv"], c["window"], c["ratio"])
+            assert n == c["ref_n"] and np.array_equal(m21, c["ref_m"]) and n > 15, (c["name"], n, c["ref_n"])
+    assert seen == {"fuse": 2, "fuse_sim3": 2, "sim3": 2, "proj_ff": 2}
+
+
+def test_oracle_reproduces_reference_fuse_golden(M):
+    """Runs anywhere (no compiled reference needed): the oracle against tests/golden/ref_fuse.npz."""
+    kinds = {}
+    for c in RG.fuse_cases():
+        kinds[c["kind"]] = kinds.get(c["kind"], 0) + 1
+        if c["kind"] in ("fuse", "fuse_sim3"):
+            n, best = M.search_by_projection_independent(c["target"], c["points"], c["th_dist"])
+            assert n == c["ref_n"], c["name"]
+            for key, val in RS.fuse_expectation(c, best).items():
+                assert np.array_equal(val, c[key]), (c["name"], key)
+        elif c["kind"] == "sim3":
+            n, m12 = M.search_by_sim3(c["f1"], c["f2"], c["p12"], c["p21"], c["th_dist"])
+            assert n == c["ref_n"] and np.array_equal(np.where(c["pre"] >= 0, c["pre"], m12), c["ref_m"]), c["name"]
+        else:
+            n, m21 = M.search_by_projection_ff(c["f1"], c["f2"], c["uv"], c["window"], c["ratio"])
+            assert n == c["ref_n"] and np.array_equal(m21, c["ref_m"]), c["name"]
+    assert kinds == {"fuse": 4, "fuse_sim3": 4, "sim3": 4, "proj_ff": 4}
