@@ -7,6 +7,7 @@ bounds and grid binning are all the reference's code.  Authoring container only;
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import os
 
@@ -28,37 +29,61 @@ def available() -> bool:
     return True
 
 
+DROPIN_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_dropin.so")
+
+
+@contextlib.contextmanager
+def library(path):
+    """Run the same wrappers against another build of them: DROPIN_LIB = the reference's Frame / KeyFrame / MapPoint
+    sources compiled against include/shim/ORBextractor.h + ORBmatcher.h and liborbx.so (oracle/Makefile ref_dropin) -
+    the CUDA path behind the reference's own classes.  Objects remember the library they were created with."""
+    global LIB
+    old, LIB = LIB, path
+    try:
+        yield
+    finally:
+        LIB = old
+
+
 def _lib():
     L = RE._lib(LIB)
     if not getattr(L, "_m_ready", False):
-        L.ref_m_world_create.restype = _P; L.ref_m_world_create.argtypes = [C.c_char_p]
-        L.ref_m_frame_create.restype = _P; L.ref_m_frame_create.argtypes = [_P, _P, _P, _I, _I, _P, _P, _I]
-        L.ref_m_frame_n.argtypes = [_P]
-        L.ref_m_frame_bounds.argtypes = [_P, _P, _P]
-        L.ref_m_frame_read.argtypes = [_P, _P, _P, _P, _P]
-        L.ref_m_frame_grid.argtypes = [_P, _P, _P]
-        L.ref_m_features_in_area.argtypes = [_P, _F, _F, _F, _I, _I, _P]
-        L.ref_m_search_for_initialization.argtypes = [_P, _P, _P, _P, _I, _F, _I]
-        L.ref_m_frame_set_valid.argtypes = [_P, _P]
-        L.ref_m_window_search.argtypes = [_P, _P, _I, _I, _I, _F, _I, _P]
-        L.ref_m_frame_compute_bow.argtypes = [_P]
-        L.ref_m_frame_bow.argtypes = [_P] + [_P] * 7
-        L.ref_m_keyframe_create.restype = _P; L.ref_m_keyframe_create.argtypes = [_P]
-        L.ref_m_search_by_bow_kf_f.argtypes = [_P, _P, _P, _F, _I, _P]
-        L.ref_m_search_by_bow_kf_kf.argtypes = [_P, _P, _P, _I, _F, _I, _P]
-        L.ref_m_distinctive_desc.argtypes = [_P, _P, _P, _I, _P, _P]
-        L.ref_m_search_by_projection_local.argtypes = [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P]
-        L.ref_m_search_by_projection_last.argtypes = [_P, _P, _P, _F, _F, _I, _P]
-        L.ref_m_search_for_triangulation.argtypes = [_P, _P, _P, _I, _F, _I, _P]
-        L.ref_m_frame_set_point_geometry.argtypes = [_P, _P, _P, _P, _P]
-        L.ref_m_frame_points_take_descriptors.argtypes = [_P, _P]
-        L.ref_m_search_by_projection_reloc.argtypes = [_P, _P, _P, _P, _F, _I, _F, _I, _P]
-        L.ref_m_search_by_projection_sim3.argtypes = [_P, _P, _P, _P, _P, _I, _I, _F, _P]
-        L.ref_m_is_in_frustum.argtypes = [_P, _P, _F] + [_P] * 6
-        L.ref_m_fuse.argtypes = [_P, _P, _P, _P, _P, _I, _F, _P, _P, _P]
-        L.ref_m_fuse_sim3.argtypes = [_P, _P, _P, _P, _I, _F, _P, _P]
-        L.ref_m_search_by_sim3.argtypes = [_P, _P, _P, _P, _P, _F, _P]
-        L.ref_m_search_by_projection_ff.argtypes = [_P, _P, _P, _I, _F, _I, _P]
+        sig = [
+            ("ref_m_world_create", "restype", _P),
+            ("ref_m_world_create", "argtypes", [C.c_char_p]),
+            ("ref_m_frame_create", "restype", _P),
+            ("ref_m_frame_create", "argtypes", [_P, _P, _P, _I, _I, _P, _P, _I]),
+            ("ref_m_frame_n", "argtypes", [_P]),
+            ("ref_m_frame_bounds", "argtypes", [_P, _P, _P]),
+            ("ref_m_frame_read", "argtypes", [_P, _P, _P, _P, _P]),
+            ("ref_m_frame_grid", "argtypes", [_P, _P, _P]),
+            ("ref_m_features_in_area", "argtypes", [_P, _F, _F, _F, _I, _I, _P]),
+            ("ref_m_search_for_initialization", "argtypes", [_P, _P, _P, _P, _I, _F, _I]),
+            ("ref_m_frame_set_valid", "argtypes", [_P, _P]),
+            ("ref_m_window_search", "argtypes", [_P, _P, _I, _I, _I, _F, _I, _P]),
+            ("ref_m_frame_compute_bow", "argtypes", [_P]),
+            ("ref_m_frame_bow", "argtypes", [_P] + [_P] * 7),
+            ("ref_m_keyframe_create", "restype", _P),
+            ("ref_m_keyframe_create", "argtypes", [_P]),
+            ("ref_m_search_by_bow_kf_f", "argtypes", [_P, _P, _P, _F, _I, _P]),
+            ("ref_m_search_by_bow_kf_kf", "argtypes", [_P, _P, _P, _I, _F, _I, _P]),
+            ("ref_m_distinctive_desc", "argtypes", [_P, _P, _P, _I, _P, _P]),
+            ("ref_m_search_by_projection_local", "argtypes", [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P]),
+            ("ref_m_search_by_projection_last", "argtypes", [_P, _P, _P, _F, _F, _I, _P]),
+            ("ref_m_search_for_triangulation", "argtypes", [_P, _P, _P, _I, _F, _I, _P]),
+            ("ref_m_frame_set_point_geometry", "argtypes", [_P, _P, _P, _P, _P]),
+            ("ref_m_frame_points_take_descriptors", "argtypes", [_P, _P]),
+            ("ref_m_search_by_projection_reloc", "argtypes", [_P, _P, _P, _P, _F, _I, _F, _I, _P]),
+            ("ref_m_search_by_projection_sim3", "argtypes", [_P, _P, _P, _P, _P, _I, _I, _F, _P]),
+            ("ref_m_is_in_frustum", "argtypes", [_P, _P, _F] + [_P] * 6),
+            ("ref_m_fuse", "argtypes", [_P, _P, _P, _P, _P, _I, _F, _P, _P, _P]),
+            ("ref_m_fuse_sim3", "argtypes", [_P, _P, _P, _P, _I, _F, _P, _P]),
+            ("ref_m_search_by_sim3", "argtypes", [_P, _P, _P, _P, _P, _F, _P]),
+            ("ref_m_search_by_projection_ff", "argtypes", [_P, _P, _P, _I, _F, _I, _P]),
+        ]
+        for name, kind, val in sig:          # the drop-in build leaves out the routines its shim does not cover
+            if hasattr(L, name):
+                setattr(getattr(L, name), kind, val)
         L._m_ready = True
     return L
 

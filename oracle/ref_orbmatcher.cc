@@ -245,6 +245,7 @@ int ref_m_search_by_bow_kf_kf(void* kf1, void* kf2, void* kf2_box, int n1, float
 // Point k: a MapPoint whose descriptor is keypoint desc_idx[k] of the keyframe made from `desc_fb` (one observation ->
 // ComputeDistinctiveDescriptors picks it), with the tracking fields isInFrustum would have written.
 // matchesF[i] = index of the point newly hung on keypoint i of F, else -1.
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_search_by_projection_local(void* fb, void* desc_fb, int npts, const float* u, const float* v,
                                      const int32_t* level, const float* view_cos, const uint8_t* in_view,
                                      const uint8_t* bad, const int32_t* desc_idx, float th, float ratio,
@@ -278,11 +279,13 @@ int ref_m_search_by_projection_local(void* fb, void* desc_fb, int npts, const fl
   }
   return n;
 }
+#endif
 
 // SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th) (src/ORBmatcher.cc:1507-1622) with the current
 // pose left at identity, so that Rcw*x3Dw+tcw returns the world point unchanged (adding zeros is exact) and
 // u = fx*x/z + cx is the float expression of :1535-1538 only.  pos: last.N x 3 world positions for last's MapPoints.
 // matchesCur[i2] = index in the last frame, else -1 (only matches made by this call).
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_search_by_projection_last(void* cur_fb, void* last_fb, const float* pos, float th, float ratio, int check_ori,
                                     int32_t* matchesCur) {
   FrameBox* bc = static_cast<FrameBox*>(cur_fb);
@@ -303,6 +306,7 @@ int ref_m_search_by_projection_last(void* cur_fb, void* last_fb, const float* po
   }
   return n;
 }
+#endif
 
 // Geometry state of the MapPoint on keypoint i of `fb` (protected members; this file is compiled with
 // -fno-access-control): world position, scale-invariance distances (what UpdateNormalAndDepth writes,
@@ -340,6 +344,7 @@ void ref_m_frame_points_take_descriptors(void* fb, void* kf) {
 // world point unchanged, so the float projection (:1652-1653), the bounds tests, dist3D/minDistance -> lower_bound level
 // prediction (:1660-1667), the radius, the area query, the best-only scan and the rotation check are the reference's.
 // already[i] != 0 -> keyframe MapPoint i is in sAlreadyFound.  matchesCur[i2] = keyframe keypoint index, else -1.
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_search_by_projection_reloc(void* cur_fb, void* kf, void* kf_box, const uint8_t* already, float th,
                                      int orb_dist, float ratio, int check_ori, int32_t* matchesCur) {
   FrameBox* bc = static_cast<FrameBox*>(cur_fb);
@@ -357,12 +362,14 @@ int ref_m_search_by_projection_reloc(void* cur_fb, void* kf, void* kf_box, const
   }
   return n;
 }
+#endif
 
 // SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:286-407, loop closing)
 // with Scw = identity (scw = 1).  vpPoints = the MapPoints of src_fb's keypoints sel[0..npts) (in that order);
 // vpMatched starts as the MapPoints already on the keyframe's own frame kf_box (set_valid) plus, for pre[k] >= 0, point
 // sel[k] pre-assigned to keyframe keypoint pre[k] ("already found").  matched[idx] = position k in sel of the point
 // NEWLY matched to keyframe keypoint idx, else -1.
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_search_by_projection_sim3(void* kf, void* kf_box, void* src_fb, const int32_t* sel, const int32_t* pre,
                                     int npts, int th, float ratio, int32_t* matched) {
   FrameBox* bk = static_cast<FrameBox*>(kf_box);
@@ -381,6 +388,7 @@ int ref_m_search_by_projection_sim3(void* kf, void* kf_box, void* src_fb, const 
   for (int i = 0; i < bk->f->N; i++) matched[i] = (vm[i] && vm[i] != before[i]) ? which.at(vm[i]) : -1;
   return n;
 }
+#endif
 
 // ORBmatcher::Fuse(KeyFrame* pKF, vector<MapPoint*>& vpMapPoints, float th) (src/ORBmatcher.cc:1016-1134), pKF's pose at
 // identity.  vpMapPoints = the MapPoints on src_fb's keypoints sel[k] (each observes its own keypoint in src_kf, the
@@ -391,6 +399,7 @@ int ref_m_search_by_projection_sim3(void* kf, void* kf_box, void* src_fb, const 
 //               own frame kf_box; -1 when that slot was erased (pMPinKF already observed src_kf through an earlier
 //               Replace, src/MapPoint.cc:148-151) or nothing was replaced
 // Returns nFused.
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_fuse(void* kf, void* kf_box, void* src_fb, void* src_kf, const int32_t* sel, int npts, float th,
                int32_t* added, uint8_t* went_bad, int32_t* repl) {
   KeyFrame* pKF = static_cast<KeyFrame*>(kf);
@@ -414,10 +423,12 @@ int ref_m_fuse(void* kf, void* kf_box, void* src_fb, void* src_kf, const int32_t
   }
   return n;
 }
+#endif
 
 // ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, float th) (src/ORBmatcher.cc:1136-1265)
 // with Scw = identity.  added[k] as above (:1253-1257); target_went_bad[idx] = 1 when the MapPoint on pKF's keypoint idx
 // was good before and is bad now (pMPinKF->Replace(pMP), :1248-1251).  Returns nFused.
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_fuse_sim3(void* kf, void* kf_box, void* src_fb, const int32_t* sel, int npts, float th, int32_t* added,
                     uint8_t* target_went_bad) {
   KeyFrame* pKF = static_cast<KeyFrame*>(kf);
@@ -435,11 +446,13 @@ int ref_m_fuse_sim3(void* kf, void* kf_box, void* src_fb, const int32_t* sel, in
   for (int i = 0; i < N; i++) target_went_bad[i] = (before[i] && !was_bad[i] && before[i]->isBad()) ? 1 : 0;
   return n;
 }
+#endif
 
 // ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12 = 1, R12 = I, t12 = 0, th) (src/ORBmatcher.cc:1267-1505), both
 // keyframe poses at identity.  pre12[i1] >= 0: vpMatches12[i1] starts as keyframe 2's MapPoint on keypoint pre12[i1]
 // (already matched, :1301-1311).  out12[i1] = keypoint of keyframe 2 whose MapPoint vpMatches12[i1] holds afterwards
 // (pre-set entries included), else -1.  Returns nFound.
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_search_by_sim3(void* kf1, void* box1, void* kf2, void* box2, const int32_t* pre12, float th, int32_t* out12) {
   FrameBox* b1 = static_cast<FrameBox*>(box1);
   FrameBox* b2 = static_cast<FrameBox*>(box2);
@@ -457,6 +470,7 @@ int ref_m_search_by_sim3(void* kf1, void* box1, void* kf2, void* box2, const int
   }
   return n;
 }
+#endif
 
 // ORBmatcher::SearchByProjection(Frame& F1, Frame& F2, int windowSize, vpMapPointMatches2) (src/ORBmatcher.cc:519-594),
 // F2's pose at identity (Rc2w*x3Dw+tc2w returns the world point; u2 = fx*x*invz+cx is the float expression of :540-550).
@@ -506,6 +520,7 @@ void ref_m_is_in_frustum(void* view_fb, void* src_fb, float cos_limit, uint8_t* 
 
 // SearchForTriangulation(pKF1, pKF2, F12, vMatchedKeys1, vMatchedKeys2, vMatchedPairs) (src/ORBmatcher.cc:852-1014):
 // match12[i1] = i2 from vMatchedPairs, else -1
+#ifndef REF_DROPIN   // not part of include/shim/ORBmatcher.h (served through the flat views of orbm.h)
 int ref_m_search_for_triangulation(void* kf1, void* kf2, const float* F12, int n1, float ratio, int check_ori,
                                    int32_t* match12) {
   cv::Mat F = mat_from(F12, 3, 3);
@@ -517,6 +532,7 @@ int ref_m_search_for_triangulation(void* kf1, void* kf2, const float* F12, int n
   for (size_t k = 0; k < pairs.size(); k++) match12[pairs[k].first] = (int32_t)pairs[k].second;
   return n;
 }
+#endif
 
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:185-250) for a MapPoint observed at keypoint idx[k] of
 // keyframe kfs[k].  The reference walks its std::map<KeyFrame*, size_t> in POINTER order; `order` reports that order

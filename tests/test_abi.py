@@ -43,3 +43,18 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inl", ".h")):
                 s = open(os.path.join(dp, f), errors="ignore").read()
                 assert "import oracle" not in s and "from oracle" not in s and "liborb_oracle" not in s, f
+
+
+def test_headers_are_plain_c(tmp_path):
+    """include/orbx.h and include/orbm.h compile as C99 (no C++ in the ABI headers) and every declared function links."""
+    import subprocess
+    from orb_slam_b200 import build
+    lib = build.build()
+    src = tmp_path / "t.c"
+    names = _declared("orbx.h") + _declared("orbm.h")
+    body = "\n".join(f"  p[{i}] = (void*){n};" for i, n in enumerate(names))
+    src.write_text('#include "orbx.h"\n#include "orbm.h"\nint main(void) {\n  void* p[%d];\n%s\n  return p[0] == 0;\n}\n'
+                   % (len(names), body))
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-Wno-pedantic", "-I", os.path.join(ROOT, "include"), str(src),
+                    "-o", str(tmp_path / "t"), "-L", os.path.dirname(lib), "-lorbx",
+                    f"-Wl,-rpath,{os.path.dirname(lib)}"], check=True)
