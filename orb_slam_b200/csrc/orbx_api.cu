@@ -32,7 +32,18 @@ struct orbx_handle {
     int32_t *d_n_total = nullptr, *d_n_retain = nullptr, *d_kp_count = nullptr;
     cudaStream_t s_main = nullptr, s_aux = nullptr;                       // blur runs beside select on s_aux
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
+    cudaEvent_t ev_last = nullptr;      // end of the last chunk that used this scratch set, on whatever stream it ran
+    cudaStream_t last_s = nullptr;
+    bool used = false;
+    // tensor maps of the TMA-staged FAST kernel: levels >= 1 point into d_pyr (valid for one plan), level 0 into the
+    // caller's frames (re-encoded when pointer / strides change)
+    FastTma tma;
+    int tma_plan = -1;
+    const uint8_t* tma_lv0 = nullptr;
+    size_t tma_stride = 0, tma_frame_stride = 0;
   } lane[kLanes];
+  int plan_version = 0;
+  int fast_mode = 0;                // 0 TMA kernel when the buffers allow it, 1 legacy kernel only (ORBX_FAST=legacy)
   int nlanes = kDefaultLanes;
   int select_mode = 0;              // 0 by chunk size, 1 global, 2 shared memory (ORBX_SELECT)
   int pdl_mode = 1;                 // 0 never, 1 chunks of <= kPdlMaxFrames frames, 2 always (ORBX_PDL)
@@ -115,6 +126,63 @@ extern "C" int orbx_params_from_yaml(const char* path, orbx_params* p) {
   return ORBX_OK;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// 3-D byte tensor (x, y, frame) with rows `pitch` and frames `frame_bytes` apart; box = bw x bh x 1, zero fill outside
+static bool encode_level_map(CUtensorMap* m, const void* base, int w, int hgt, int nframes, size_t pitch, size_t frame_bytes,
+                             int bw, int bh) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn || (reinterpret_cast<uintptr_t>(base) & 15) || (pitch & 15) || (frame_bytes & 15) || bw > 256 || bh > 256) return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)hgt, (cuuint64_t)nframes};
+  const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_bytes};
+  const cuuint32_t box[3] = {(cuuint32_t)bw, (cuuint32_t)bh, 1};
+  const cuuint32_t es[3] = {1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// Tensor maps of one chunk; false = this chunk takes the legacy kernel (misaligned caller buffer, oversized cells, ...)
+static bool prepare_fast_tma(orbx_handle* h, orbx_handle::Lane& ln, const uint8_t* lv0, size_t stride, size_t frame_stride) {
+  const HostPlan& hp = h->hp;
+  if (h->fast_mode == 1 || !hp.fast_tma_ok || hp.fast_tma_smem_bytes > 200 * 1024) return false;
+  const DevicePlan& dp = hp.dp;
+  const int B = h->p.max_batch;
+  if (ln.tma_plan != h->plan_version) {
+    for (int l = 1; l < dp.nlevels; l++) {
+      if (!hp.fast_box_w[l]) continue;                               // level without a scored cell: never addressed
+      if (!encode_level_map(&ln.tma.map[l], ln.d_pyr + dp.lv[l].off, dp.lv[l].w, dp.lv[l].h, B, dp.lv[l].pitch,
+                            (size_t)dp.pyr_frame_bytes, hp.fast_box_w[l], hp.fast_box_h[l]))
+        return false;
+    }
+    for (int l = 0; l < kMaxLevels; l++) { ln.tma.box_w[l] = hp.fast_box_w[l]; ln.tma.box_h[l] = hp.fast_box_h[l]; }
+    ln.tma.smem_bytes = hp.fast_tma_smem_bytes;
+    ln.tma_plan = h->plan_version;
+    ln.tma_lv0 = nullptr;
+  }
+  if (ln.tma_lv0 != lv0 || ln.tma_stride != stride || ln.tma_frame_stride != frame_stride) {
+    ln.tma_lv0 = nullptr;
+    if (hp.fast_box_w[0] &&
+        !encode_level_map(&ln.tma.map[0], lv0, dp.lv[0].w, dp.lv[0].h, B, stride, frame_stride, hp.fast_box_w[0], hp.fast_box_h[0]))
+      return false;
+    ln.tma_lv0 = lv0; ln.tma_stride = stride; ln.tma_frame_stride = frame_stride;
+  }
+  return true;
+}
+
 static int upload_plan(orbx_handle* h, int w, int hgt) {
   if (h->plan_w == w && h->plan_h == hgt) return ORBX_OK;
   int rc = build_plan(h->p, w, hgt, &h->hp, &h->err);
@@ -130,7 +198,13 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     h->err = "cell too large for the shared-memory FAST tile (cell area > ~100k px)";
     return ORBX_ERR_UNSUPPORTED;
   }
-  for (int li = 0; li < h->nlanes; li++) CK(cudaStreamSynchronize(h->lane[li].s_main));
+  // the tables below are read by kernels of earlier calls, which may still run on the lanes' streams or - single-chunk
+  // device-API calls - on a caller's stream (ev_last): wait for all of them before overwriting
+  for (int li = 0; li < h->nlanes; li++) {
+    CK(cudaStreamSynchronize(h->lane[li].s_main));
+    if (h->lane[li].used) CK(cudaEventSynchronize(h->lane[li].ev_last));
+  }
+  h->plan_version++;
   CK(cudaMemcpy(h->d_plan, &dp, sizeof(dp), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(h->d_cells, h->hp.cells.data(), h->hp.cells.size() * sizeof(CellPlan), cudaMemcpyHostToDevice));
   if (!h->hp.rx.empty()) {
@@ -185,6 +259,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     h->in_frame_bytes = (int64_t)h->in_pitch * pp->max_height;
     if (const char* e = getenv("ORBX_PDL")) h->pdl_mode = std::min(2, std::max(0, atoi(e)));
     if (const char* e = getenv("ORBX_SELECT")) h->select_mode = e[0] == 'g' ? 1 : (e[0] == 's' ? 2 : 0);
+    if (const char* e = getenv("ORBX_FAST")) h->fast_mode = e[0] == 'l' ? 1 : 0;
     if (const char* e = getenv("ORBX_LANES")) h->nlanes = std::min(kLanes, std::max(1, atoi(e)));
     for (int li = 0; li < h->nlanes; li++) {
       orbx_handle::Lane& ln = h->lane[li];
@@ -201,6 +276,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
       CK(cudaEventCreateWithFlags(&ln.ev_fork, cudaEventDisableTiming));
       CK(cudaEventCreateWithFlags(&ln.ev_join, cudaEventDisableTiming));
       CK(cudaEventCreateWithFlags(&ln.ev_done, cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&ln.ev_last, cudaEventDisableTiming));
     }
     CK(cudaMalloc(&h->d_err, sizeof(int32_t)));
     CK(cudaMemset(h->d_err, 0, sizeof(int32_t)));
@@ -251,6 +327,7 @@ extern "C" void orbx_destroy(orbx_handle* h) {
     if (ln.ev_fork) cudaEventDestroy(ln.ev_fork);
     if (ln.ev_join) cudaEventDestroy(ln.ev_join);
     if (ln.ev_done) cudaEventDestroy(ln.ev_done);
+    if (ln.ev_last) cudaEventDestroy(ln.ev_last);
   }
   if (h->s_in) {
     cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
@@ -277,6 +354,9 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   b.pyr = ln.d_pyr; b.blur = ln.d_blur; b.cand = ln.d_cand; b.n_total = ln.d_n_total; b.n_retain = ln.d_n_retain;
   b.list = ln.d_list; b.kp = ln.d_kp; b.kp_count = ln.d_kp_count; b.err_flag = h->d_err;
   b.plan = h->d_plan; b.cells = h->d_cells; b.rx = h->d_rx; b.ry = h->d_ry;
+  // this scratch set was last used on another stream (a caller's, or the lane's own): order behind that chunk
+  if (ln.used && ln.last_s != s) CK(cudaStreamWaitEvent(s, ln.ev_last, 0));
+  const bool fast_tma = prepare_fast_tma(h, ln, d_imgs, stride, frame_stride);
   const bool prof = h->profiling;
   // launch-latency-bound chains (a few frames per chunk) use programmatic dependent launch; full chunks keep the
   // plain stream order, where the other lane's kernels already fill the tails (ORBX_PDL=0 never / 2 always)
@@ -285,7 +365,8 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   for (int l = 1; l < dp.nlevels; l++) launch_resize_level(b, dp, l, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
-  launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);
+  if (fast_tma) launch_fast_cells_tma(b, dp, ln.tma, n, s);
+  else launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   if (prof) {                     // serial, so that the per-stage events mean something
     launch_select(b, dp, n, s, h->select_mode);
@@ -316,6 +397,8 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
       h->prof_launch[i] += nl[i];
     }
   }
+  CK(cudaEventRecord(ln.ev_last, s));
+  ln.last_s = s; ln.used = true;
   h->last = b; h->last_frames = n;
   return ORBX_OK;
 }
@@ -347,7 +430,7 @@ static int check_err_flag(orbx_handle* h) {
   const int32_t flag = *h->h_err;
   if (flag) {
     cudaMemset(h->d_err, 0, sizeof(flag));
-    h->err = flag == 1 ? "cell candidate list overflow" : "level list overflow";
+    h->err = flag == 1 ? "cell candidate list overflow" : (flag == 3 ? "FAST tile never arrived (TMA wait timed out)" : "level list overflow");
     return ORBX_ERR_OVERFLOW;
   }
   return ORBX_OK;

@@ -52,6 +52,20 @@ struct CellPlan {
   uint32_t m_grp;        // staging groups (8 px) per sub-image row      = fast_ngrp(rw + 6)
   uint32_t m_g8;         // reject groups (8 px) per scored row          = (rw + 7) / 8
   uint32_t m_wpr;        // bitmap words (32 px) per scored row          = (rw + 31) / 32
+  // fast_cells_tma_kernel: a tensor copy must start on a 16-byte boundary of the image row, so the box starts `lead`
+  // columns left of x0 - 8 and the kernel works in shifted coordinates xs = x + lead over rows of lead + rw columns
+  // Everything below is computed once on the host so that the kernel's prologue is one record load.
+  int16_t lead;          // x0 & 15
+  int16_t rwt;           // lead + rw: columns per shifted row
+  int16_t g16;           // 16-pixel reject groups per shifted row = (rwt + 15) / 16
+  int16_t scp;           // score-map pitch  = fast_scp(rwt)
+  int16_t wpr;           // bitmap words per shifted row = (rwt + 31) / 32
+  int16_t nbw;           // bitmap words = wpr * rh
+  int32_t ngrp;          // reject groups = g16 * rh
+  int32_t nz16;          // uint4 stores that clear score map + bitmaps A, B
+  int32_t off_sc, off_bm, off_q;   // shared-memory byte offsets (raw image at 0): score map, bitmaps A + B, lists
+  uint32_t m_g16;        // fast_magic(g16)
+  uint32_t m_wprt;       // fast_magic(wpr)
 };
 
 struct ResizeX {  // per destination column: source column and the two 11-bit weights (cv::resize INTER_LINEAR)
@@ -80,6 +94,11 @@ struct HostPlan {
   std::vector<ResizeX> rx;
   std::vector<ResizeY> ry;
   int fast_smem_bytes;       // dynamic shared memory of the FAST kernel: max over cells of fast_cell_smem()
+  // TMA-staged FAST kernel (fast_cells_tma_kernel): per level the tensor-copy box (the level's largest cell incl. the
+  // 8-byte lead-in and the reject's over-read), its shared-memory footprint, and whether every level fits a box
+  int fast_box_w[kMaxLevels], fast_box_h[kMaxLevels];
+  int fast_tma_smem_bytes;
+  bool fast_tma_ok;
 };
 
 // Shared-memory geometry of fast_cells_kernel for a cell sub-image of cw x ch pixels (scored region (cw-6) x (ch-6)):
@@ -100,6 +119,10 @@ inline __host__ __device__ int fast_cell_smem(int cw, int ch) {
   return fast_img_bytes(cw, ch) + fast_h8_bytes(cw, ch) + fast_sc_bytes(cw - 6, ch - 6) +
          16 * fast_bm_words(cw - 6, ch - 6) + 16;
 }
+// fast_cells_tma_kernel: box width for a level whose widest scored region is rw (scored pixel x at byte 8 + x; the last
+// 8-pixel reject group reads 4 bytes beyond its 8), multiple of 16 as the tensor map wants
+inline __host__ __device__ int fast_tma_box_w(int rwt) { return 16 * ((rwt + 15) >> 4) + 32; }   // rwt = lead + rw; position xs at byte 16 + xs
+constexpr int kFastTmaListBytes = (1024 + 1024) * 4;   // kFastQ1 + kFastQ2 entries
 // floor(i / d) == umulhi(i, fast_magic(d)) for i * d < 2^32; d == 1 gives 0, which magic_div() reads as "i itself"
 inline uint32_t fast_magic(uint32_t d) { return 0xffffffffu / d + 1u; }
 

@@ -1,5 +1,7 @@
 // Kernel launch interface between orbx_api.cu and orbx_kernels.cu.
 #pragma once
+#include <cuda.h>   // CUtensorMap (type only; the encoder is resolved at run time, no -lcuda)
+
 #include "orbx_internal.cuh"
 
 namespace orbx {
@@ -24,6 +26,14 @@ struct ChunkBuffers {
   const ResizeY* ry;
 };
 
+// Tensor maps of fast_cells_tma_kernel, passed by value (__grid_constant__): one 3-D map (x, y, frame) of bytes per
+// pyramid level, box = the level's largest cell sub-image.
+struct FastTma {
+  CUtensorMap map[kMaxLevels];
+  int box_w[kMaxLevels], box_h[kMaxLevels];
+  int smem_bytes;
+};
+
 struct BlurTiles {            // everything blur7_kernel needs per level, passed by value (constant bank, no global loads)
   int nlevels, blur_mode;
   int base[kMaxLevels + 1];   // prefix of tiles per level
@@ -42,6 +52,7 @@ void set_launch_pdl(bool on);
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s);
+void launch_fast_cells_tma(const ChunkBuffers& b, const DevicePlan& hp, const FastTma& tm, int nframes, cudaStream_t s);
 void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s, int force);
 void launch_retain_best_debug(Cand* v, const int32_t* start, const int32_t* keep, int nlists, int retain_mode, int batch,
                               cudaStream_t s);

@@ -459,5 +459,7 @@ void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_byt
   launch_k(kern, grid, dim3(kFastThreads), (size_t)smem_bytes, s, b, fl);
 }
 
+#include "orbx_kernels_detect_tma.inl"
+
 }  // namespace orbx
 #include "orbx_kernels_select.inl"

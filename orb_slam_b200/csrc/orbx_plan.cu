@@ -99,6 +99,9 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
   int64_t pyr_off = 0, blur_off = 0, cand_off = 0;
   int cell_base = 0, kp_base = 0, list_base = 0;
   hp.fast_smem_bytes = 0;
+  hp.fast_tma_smem_bytes = 0;
+  hp.fast_tma_ok = true;
+  for (int l = 0; l < kMaxLevels; l++) hp.fast_box_w[l] = hp.fast_box_h[l] = 0;
   for (int level = 0; level < nlevels; level++) {
     LevelPlan& L = dp.lv[level];
     float scale = mvInvScaleFactor[level];
@@ -143,6 +146,7 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
     L.list_cap = 2 * nCells * L.quota + 2 * nCells + 8;
     list_base += L.list_cap;
 
+    int max_rw = 0, max_rh = 0;   // this level's largest shifted scored region (TMA kernel)
     // cell loop :558-599
     std::vector<int> iniXCol(levelCols);
     float hY = cellH + 6;
@@ -187,10 +191,35 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
             c.m_g8 = fast_magic((c.rw + 7) / 8);
             c.m_wpr = fast_magic((c.rw + 31) / 32);
             hp.fast_smem_bytes = std::max(hp.fast_smem_bytes, fast_cell_smem(cw, ch));
+            c.lead = (int16_t)(c.x0 & 15);
+            c.rwt = (int16_t)(c.lead + c.rw);
+            c.g16 = (int16_t)((c.rwt + 15) / 16);
+            c.scp = (int16_t)fast_scp(c.rwt);
+            c.wpr = (int16_t)((c.rwt + 31) / 32);
+            c.nbw = (int16_t)(c.wpr * c.rh);
+            c.ngrp = c.g16 * c.rh;
+            c.m_g16 = fast_magic(c.g16);
+            c.m_wprt = fast_magic(c.wpr);
+            max_rw = std::max(max_rw, (int)c.rwt); max_rh = std::max(max_rh, (int)c.rh);
           }
         }
         cand_off += c.cand_cap;
         hp.cells.push_back(c);
+      }
+    }
+    if (max_rw > 0) {
+      const int bw = fast_tma_box_w(max_rw), bh = max_rh + 6;
+      hp.fast_box_w[level] = bw; hp.fast_box_h[level] = bh;
+      if (bw > 256 || bh > 256) hp.fast_tma_ok = false;          // the tensor-copy box is limited to 256 per dimension
+      for (size_t k = hp.cells.size() - (size_t)nCells; k < hp.cells.size(); k++) {
+        CellPlan& c = hp.cells[k];
+        if (c.rw <= 0) continue;
+        const int sc = fast_sc_bytes(c.rwt, c.rh);
+        c.off_sc = bw * bh; c.off_bm = c.off_sc + sc;
+        c.off_q = (c.off_bm + 8 * c.nbw + 15) & ~15;
+        c.nz16 = (sc + 8 * c.nbw + 15) / 16;
+        if (4 * c.ngrp > 4 * 1024) hp.fast_tma_ok = false;        // the flag words share list 2's bytes (kFastQ2 entries)
+        hp.fast_tma_smem_bytes = std::max(hp.fast_tma_smem_bytes, c.off_q + kFastTmaListBytes);
       }
     }
   }
