@@ -159,6 +159,7 @@ static bool encode_level_map(CUtensorMap* m, const void* base, int w, int hgt, i
 static bool prepare_fast_tma(orbx_handle* h, orbx_handle::Lane& ln, const uint8_t* lv0, size_t stride, size_t frame_stride) {
   const HostPlan& hp = h->hp;
   if (h->fast_mode == 1 || !hp.fast_tma_ok || hp.fast_tma_smem_bytes > 200 * 1024) return false;
+  if (h->p.fast_th > 120) return false;          // its byte-SIMD reject assumes threshold + 1 < 128
   const DevicePlan& dp = hp.dp;
   const int B = h->p.max_batch;
   if (ln.tma_plan != h->plan_version) {

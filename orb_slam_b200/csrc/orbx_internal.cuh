@@ -41,7 +41,7 @@ struct LevelPlan {
   int tab_x, tab_y;      // offsets of this level's resize tables (xofs/alpha, yofs/beta)
 };
 
-struct CellPlan {
+struct alignas(16) CellPlan {   // 16-byte aligned: a kernel reads its record with five 128-bit loads
   int16_t level;
   int16_t x0, y0;        // first scored pixel of the cell (= iniX + 3, iniY + 3) in level coordinates
   int16_t rw, rh;        // scored region size; 0 when the reference skips the cell (hX <= 0 / hY <= 0 / < 7 px)

@@ -8,13 +8,19 @@
 //             must start on a 16-byte boundary of the image row, so the kernel works in shifted coordinates
 //             xs = x + lead - out-of-image bytes zero-filled by the engine.  No per-thread address math, no misalignment shifts, no global loads on
 //             the issue stream.  The u16 copy of the image is gone: the ladder expands ring bytes with PRMT as it
-//             loads them, and the reject halves its bytes after loading them: ONE copy of the cell in shared memory.
+//             loads them, and the reject tests the raw bytes directly: ONE copy of the cell in shared memory.
 //   queues    flagged pixel pairs / pixels above the threshold are appended to CTA-wide lists with one shared-memory
 //             atomicAdd per thread that has any (sparse), then consumed thread = entry by full warps; the per-warp
 //             bit queues with their prefix scans over every bitmap word are gone.  A list that overflows (noise
 //             images) switches that phase to a dense walk over the cell - slower, same result.
 //   emission  one warp: each lane owns a contiguous run of bitmap words, one shuffle scan gives its output offset.
 // ------------------------------------------------------------------------------------------------------------------
+// 128 threads: with one 35 KB copy of the cell per CTA six CTAs share an SM, and the sparse phases (few entries per
+// cell) leave fewer idle warps at the barriers than 256-thread CTAs did: 14.6 instead of 15.4 ms per 10k frames
+#ifndef ORBX_FAST_TMA_THREADS
+#define ORBX_FAST_TMA_THREADS 128
+#endif
+constexpr int kFastTmaThreads = ORBX_FAST_TMA_THREADS;
 constexpr int kFastQ1 = 1024, kFastQ2 = 1024;   // list capacities (entries): flagged pairs / pixels with S >= tmin
 
 __device__ __forceinline__ uint32_t ft_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -64,7 +70,7 @@ __device__ __forceinline__ uint32_t fast_pair_score_u8(const uint8_t* raw, int r
 }
 
 template <bool kHarris>
-__global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads)
+__global__ void __launch_bounds__(kFastTmaThreads, 1024 / kFastTmaThreads)
 fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ FastTma tm) {
   ORBX_PDL_ENTRY();
   extern __shared__ __align__(128) uint8_t smem_tma[];
@@ -107,7 +113,7 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
         : "memory");
   }
   const int nz = c.nz16;                                         // score map + bitmaps A, B (contiguous)
-  for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < nz; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
   if (tid < 4) s_cnt[tid] = 0;
   __syncthreads();                                               // barrier initialised before anybody polls it
   {
@@ -127,33 +133,35 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
   int tmin = max(tA > tB ? tA : min(tA, tB), 1);
   bool useA;
   for (;;) {
-    // ---- 1a  reject, 16 pixels per thread on the halved bytes, branch-free: one flag word per group -------------------
+    // ---- 1a  reject, 16 pixels per thread on the raw bytes, branch-free: one flag word per group ------------------------
     // An arc of 9 ring pixels holds one pixel of every opposite pair, so a corner at threshold t needs
-    // (|up-v| > t or |down-v| > t) and (|left-v| > t or |right-v| > t); on the halved image that is implied by
-    // |a'-v'| >= ceil(t/2), and adding (0x80 - ceil(t/2)) to a VABSDIFF4 result raises bit 7 exactly then.  The four
-    // result words (bit 7 of byte k = pixel 4j + k of word j) are folded into one: bit 8k + j = pixel 4j + k.
+    // (|up-v| > t or |down-v| > t) and (|left-v| > t or |right-v| > t): VABSDIFF4 + one add per direction and 4 pixels.
+    // The four result words (bit 7 of byte k = pixel 4j + k of word j) are folded into one: bit 8k + j = pixel 4j + k.
     {
       const int G16 = c.g16, ng = c.ngrp;
-      const uint32_t bias4 = (0x80u - (uint32_t)((tmin + 1) >> 1)) * 0x01010101u;
-      const int sy = magic_div(kFastThreads, c.m_g16), sg = kFastThreads - sy * G16;
+      const uint32_t bias4 = (0x7fu - (uint32_t)tmin) * 0x01010101u;
+      const int sy = magic_div(kFastTmaThreads, c.m_g16), sg = kFastTmaThreads - sy * G16;
       int y = magic_div(tid, c.m_g16), g = tid - y * G16;
-      for (int i = tid; i < ng; i += kFastThreads) {
+      for (int i = tid; i < ng; i += kFastTmaThreads) {
         const uint8_t* ctr = s_raw + (y + 3) * rp + 16 * g + 16;  // centre bytes of positions 16g .. 16g+15
-        uint4 C = *reinterpret_cast<const uint4*>(ctr);
-        uint4 U = *reinterpret_cast<const uint4*>(ctr - 3 * rp), D = *reinterpret_cast<const uint4*>(ctr + 3 * rp);
-        uint32_t W0 = *reinterpret_cast<const uint32_t*>(ctr - 4), W5 = *reinterpret_cast<const uint32_t*>(ctr + 16);
-#define ORBX_H(v) v = ((v) >> 1) & 0x7f7f7f7fu                      /* the halved image, made on the fly */
-        ORBX_H(C.x); ORBX_H(C.y); ORBX_H(C.z); ORBX_H(C.w); ORBX_H(U.x); ORBX_H(U.y); ORBX_H(U.z); ORBX_H(U.w);
-        ORBX_H(D.x); ORBX_H(D.y); ORBX_H(D.z); ORBX_H(D.w); ORBX_H(W0); ORBX_H(W5);
-#undef ORBX_H
-#define ORBX_REJ(u, d, l, r, cc)                                                                   \
-  (((__vabsdiffu4(u, cc) + bias4) | (__vabsdiffu4(d, cc) + bias4)) &                                \
-   ((__vabsdiffu4(l, cc) + bias4) | (__vabsdiffu4(r, cc) + bias4)) & 0x80808080u)
-        const uint32_t m0 = ORBX_REJ(U.x, D.x, __byte_perm(W0, C.x, 0x4321), __byte_perm(C.x, C.y, 0x6543), C.x);
-        const uint32_t m1 = ORBX_REJ(U.y, D.y, __byte_perm(C.x, C.y, 0x4321), __byte_perm(C.y, C.z, 0x6543), C.y);
-        const uint32_t m2 = ORBX_REJ(U.z, D.z, __byte_perm(C.y, C.z, 0x4321), __byte_perm(C.z, C.w, 0x6543), C.z);
-        const uint32_t m3 = ORBX_REJ(U.w, D.w, __byte_perm(C.z, C.w, 0x4321), __byte_perm(C.w, W5, 0x6543), C.w);
+        const uint4 C = *reinterpret_cast<const uint4*>(ctr);
+        const uint4 U = *reinterpret_cast<const uint4*>(ctr - 3 * rp), D = *reinterpret_cast<const uint4*>(ctr + 3 * rp);
+        const uint32_t W0 = *reinterpret_cast<const uint32_t*>(ctr - 4), W5 = *reinterpret_cast<const uint32_t*>(ctr + 16);
+        // d = |a - v| per byte; d > t  <=>  bit 7 of (d + 0x7f - t), as long as that sum stays below 256, i.e. d < 128;
+        // a byte with d >= 128 (> t: fastTh <= 120 here) is caught by its own bit 7, and the carry it may send into the
+        // next byte can only ADD a flag there (the reject is conservative by design)
+#define ORBX_GT(a, cc, out)                                            \
+  { const uint32_t d_ = __vabsdiffu4(a, cc); out = (d_ + bias4) | d_; }
+#define ORBX_REJ(u, d, l, r, cc, out)                                  \
+  { uint32_t a_, b_, c_, e_; ORBX_GT(u, cc, a_) ORBX_GT(d, cc, b_) ORBX_GT(l, cc, c_) ORBX_GT(r, cc, e_)   \
+    out = (a_ | b_) & (c_ | e_) & 0x80808080u; }
+        uint32_t m0, m1, m2, m3;
+        ORBX_REJ(U.x, D.x, __byte_perm(W0, C.x, 0x4321), __byte_perm(C.x, C.y, 0x6543), C.x, m0)
+        ORBX_REJ(U.y, D.y, __byte_perm(C.x, C.y, 0x4321), __byte_perm(C.y, C.z, 0x6543), C.y, m1)
+        ORBX_REJ(U.z, D.z, __byte_perm(C.y, C.z, 0x4321), __byte_perm(C.z, C.w, 0x6543), C.z, m2)
+        ORBX_REJ(U.w, D.w, __byte_perm(C.z, C.w, 0x4321), __byte_perm(C.w, W5, 0x6543), C.w, m3)
 #undef ORBX_REJ
+#undef ORBX_GT
         s_flag[i] = (m0 >> 7) | (m1 >> 6) | (m2 >> 5) | (m3 >> 4);
         y += sy; g += sg;
         if (g >= G16) { g -= G16; y++; }
@@ -163,20 +171,12 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
     // ---- 1b  flag words -> list 1 of pixel PAIRS (xs even) with either pixel flagged and inside the scored region ------
     {
       const int G16 = c.g16, ng = c.ngrp;
-      for (int i = tid; i < ng; i += kFastThreads) {
+      for (int i = tid; i < ng; i += kFastTmaThreads) {
         const uint32_t t = s_flag[i];
         uint32_t pr = (t | (t >> 8)) & 0x000f000fu;             // bit j: pair at 4j (pixels 4j, 4j+1); bit 16+j: pair at 4j+2
         if (pr) {
           const int y = magic_div(i, c.m_g16), x0g = 16 * (i - y * G16);
-          // pairs outside [lead, rw) were computed from padding / neighbour cells
-          uint32_t keep = 0;
-#pragma unroll
-          for (int j = 0; j < 4; j++) {
-            const int xa = x0g + 4 * j, xb = xa + 2;
-            if (xa + 1 >= lead && xa < rw) keep |= 1u << j;
-            if (xb + 1 >= lead && xb < rw) keep |= 0x10000u << j;
-          }
-          pr &= keep;
+          // (pairs outside [lead, rw) - padding / the neighbour cell - are dropped by the scorer: cheaper than masking here)
           if (pr) {
             int off = atomicAdd(&s_cnt[2], __popc(pr));
             const uint32_t base = ((uint32_t)y << 16) | (uint32_t)x0g;
@@ -195,10 +195,11 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
     // ---- 2  full score of the flagged pairs; pixels with S >= tmin go to list 2 ------------------------------------------
     {
       auto heavy = [&](int x, int y) {
+        if (x + 1 < lead || x >= rw) return;                    // a pair of the padding / the neighbour cell
         const uint32_t s2 = fast_pair_score_u8(s_raw, rp, x, y);
         uint32_t two = __byte_perm(s2, 0, 0x4420);               // (S(x), S(x+1)) as two bytes
         if (x + 1 >= rw) two &= 0xff;
-        if (x < lead) two &= x + 1 < lead ? 0u : 0xff00u;      // (whole pairs left of the region: dense walk only)
+        if (x < lead) two &= 0xff00;
         if (two) {
           *reinterpret_cast<uint16_t*>(s_sc + (y + 1) * scp + 4 + x) = (uint16_t)two;
           const bool m0 = (int)(two & 0xff) >= tmin, m1 = (int)(two >> 8) >= tmin;
@@ -212,10 +213,10 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
       };
       const int n1 = s_cnt[2];
       if (n1 <= kFastQ1) {
-        for (int i = tid; i < n1; i += kFastThreads) { const uint32_t e = s_q1[i]; heavy((int)(e & 0xffff), (int)(e >> 16)); }
+        for (int i = tid; i < n1; i += kFastTmaThreads) { const uint32_t e = s_q1[i]; heavy((int)(e & 0xffff), (int)(e >> 16)); }
       } else {                                                   // list 1 overflowed: every pair of the cell
         const int hp = (rw + 1) >> 1, np = hp * rh;
-        for (int i = tid; i < np; i += kFastThreads) { const int y = i / hp; heavy(2 * (i - y * hp), y); }
+        for (int i = tid; i < np; i += kFastTmaThreads) { const int y = i / hp; heavy(2 * (i - y * hp), y); }
       }
     }
     __syncthreads();
@@ -236,9 +237,9 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
       };
       const int n2 = s_cnt[3];
       if (n2 <= kFastQ2) {
-        for (int i = tid; i < n2; i += kFastThreads) { const uint32_t e = s_q2[i]; nms((int)(e & 0xffff), (int)(e >> 16)); }
+        for (int i = tid; i < n2; i += kFastTmaThreads) { const uint32_t e = s_q2[i]; nms((int)(e & 0xffff), (int)(e >> 16)); }
       } else {                                                   // list 2 overflowed: every pixel of the score map
-        for (int i = tid; i < rw * rh; i += kFastThreads) {        // (columns < lead hold zeros)
+        for (int i = tid; i < rw * rh; i += kFastTmaThreads) {        // (columns < lead hold zeros)
           const int y = i / rw, x = i - y * rw;
           if ((int)s_sc[(y + 1) * scp + 4 + x] >= tmin) nms(x, y);
         }
@@ -252,7 +253,7 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
     if (useA || tmin <= tB) break;
     // retry at 7: forget this pass's scores, bitmaps and lists
     __syncthreads();                              // everyone has read s_cnt
-    for (int i = tid; i < nz; i += kFastThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < nz; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
     if (tid < 4) s_cnt[tid] = 0;
     tmin = tB;
     __syncthreads();
@@ -314,5 +315,5 @@ void launch_fast_cells_tma(const ChunkBuffers& b, const DevicePlan& hp, const Fa
   fl.cand_per_frame = hp.cand_per_frame; fl.frame_bytes = hp.pyr_frame_bytes;
   for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
   dim3 grid(hp.total_cells, nframes);
-  launch_k(kern, grid, dim3(kFastThreads), (size_t)tm.smem_bytes, s, b, fl, tm);
+  launch_k(kern, grid, dim3(kFastTmaThreads), (size_t)tm.smem_bytes, s, b, fl, tm);
 }

@@ -289,3 +289,30 @@ def test_runtime_switches_are_bit_identical(oracle, env):
     kps, desc, n = ex.extract_batch(batch)
     for i in range(len(batch)):
         _cmp_final(kps[i, :n[i]], desc[i, :n[i]], *ref[i % 5])
+
+
+def test_fast_kernels_agree(oracle):
+    """The TMA-staged FAST kernel (default where the buffers allow it) and the legacy kernel (ORBX_FAST=legacy; also the
+    fallback for misaligned caller buffers) on scenes that take every branch: list overflow (noise), retry at 7 (flat /
+    low contrast), odd sizes whose cells straddle the tensor-copy alignment, a row pitch that is not a multiple of 16."""
+    import os
+    rng = np.random.default_rng(11)
+    cases = [(640, 480, 1000, 8, 20, "scene"), (333, 251, 700, 5, 9, "noise"), (459, 193, 2000, 6, 20, "low"),
+             (1241, 376, 2000, 8, 20, "half"), (401, 301, 300, 4, 5, "scene")]
+    for w, h, nf, nl, th, kind in cases:
+        base = oracle.synth(h, w, 77)
+        img = {"scene": base, "noise": rng.integers(0, 256, (h, w), dtype=np.uint8),
+               "low": (base // 9 + 60).astype(np.uint8),
+               "half": np.where(np.arange(w)[None, :] < w // 2, 90, rng.integers(0, 256, (h, w))).astype(np.uint8)}[kind]
+        ok, od = oracle.OracleExtractor(nf, 1.2, nl, 1, th)(img)
+        for mode in ("tma", "legacy"):
+            os.environ["ORBX_FAST"] = mode
+            try:
+                ex = _ex(nfeatures=nf, nlevels=nl, fastTh=th, max_width=w, max_height=h, max_batch=3)
+            finally:
+                os.environ.pop("ORBX_FAST", None)
+            k, d = ex(img)
+            _cmp_final(k, d, ok, od)
+            kps, desc, n = ex.extract_batch(np.stack([img] * 5))       # 2 chunks, both lanes
+            for i in range(5):
+                _cmp_final(kps[i, :n[i]], desc[i, :n[i]], ok, od)
