@@ -38,12 +38,19 @@ struct orbx_handle {
     // tensor maps of the TMA-staged FAST kernel: levels >= 1 point into d_pyr (valid for one plan), level 0 into the
     // caller's frames (re-encoded when pointer / strides change)
     FastTma tma;
+    ResizeTma rtma;                     // source boxes of resize_tma_kernel; rtma_ok[l]: level l has a valid map
+    bool rtma_ok[kMaxLevels] = {};
     int tma_plan = -1;
     const uint8_t* tma_lv0 = nullptr;
     size_t tma_stride = 0, tma_frame_stride = 0;
+    int rtma_plan = -1;
+    const uint8_t* rtma_lv0 = nullptr;
+    size_t rtma_stride = 0, rtma_frame_stride = 0;
+    bool rtma_lv0_valid = false;
   } lane[kLanes];
   int plan_version = 0;
   int fast_mode = 0;                // 0 TMA kernel when the buffers allow it, 1 legacy kernel only (ORBX_FAST=legacy)
+  int resize_mode = 0;              // the same for the pyramid kernels (ORBX_RESIZE=legacy)
   int nlanes = kDefaultLanes;
   int select_mode = 0;              // 0 by chunk size, 1 global, 2 shared memory (ORBX_SELECT)
   int pdl_mode = 1;                 // 0 never, 1 chunks of <= kPdlMaxFrames frames, 2 always (ORBX_PDL)
@@ -184,6 +191,31 @@ static bool prepare_fast_tma(orbx_handle* h, orbx_handle::Lane& ln, const uint8_
   return true;
 }
 
+// Source maps of resize_tma_kernel for this chunk (ln.rtma_ok[l] says which levels have one; the others take
+// resize_level_kernel).  Levels >= 2 read the lane's own pyramid slab, level 1 the caller's frames.
+static void prepare_resize_tma(orbx_handle* h, orbx_handle::Lane& ln, const uint8_t* lv0, size_t stride, size_t frame_stride) {
+  const HostPlan& hp = h->hp;
+  const DevicePlan& dp = hp.dp;
+  const int B = h->p.max_batch;
+  if (ln.rtma_plan != h->plan_version) {
+    for (int l = 0; l < kMaxLevels; l++) { ln.rtma_ok[l] = false; ln.rtma.box_w[l] = hp.resize_box_w[l]; ln.rtma.box_h[l] = hp.resize_box_h[l]; }
+    if (h->resize_mode != 1)
+      for (int l = 2; l < dp.nlevels; l++)
+        ln.rtma_ok[l] = hp.resize_box_w[l] > 0 &&
+                        encode_level_map(&ln.rtma.map[l], ln.d_pyr + dp.lv[l - 1].off, dp.lv[l - 1].w, dp.lv[l - 1].h, B,
+                                         dp.lv[l - 1].pitch, (size_t)dp.pyr_frame_bytes, hp.resize_box_w[l], hp.resize_box_h[l]);
+    ln.rtma_plan = h->plan_version;
+    ln.rtma_lv0 = nullptr;
+    ln.rtma_lv0_valid = false;
+  }
+  if (dp.nlevels > 1 && (!ln.rtma_lv0_valid || ln.rtma_lv0 != lv0 || ln.rtma_stride != stride || ln.rtma_frame_stride != frame_stride)) {
+    ln.rtma_ok[1] = h->resize_mode != 1 && hp.resize_box_w[1] > 0 &&
+                    encode_level_map(&ln.rtma.map[1], lv0, dp.lv[0].w, dp.lv[0].h, B, stride, frame_stride, hp.resize_box_w[1],
+                                     hp.resize_box_h[1]);
+    ln.rtma_lv0 = lv0; ln.rtma_stride = stride; ln.rtma_frame_stride = frame_stride; ln.rtma_lv0_valid = true;
+  }
+}
+
 static int upload_plan(orbx_handle* h, int w, int hgt) {
   if (h->plan_w == w && h->plan_h == hgt) return ORBX_OK;
   int rc = build_plan(h->p, w, hgt, &h->hp, &h->err);
@@ -261,6 +293,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     if (const char* e = getenv("ORBX_PDL")) h->pdl_mode = std::min(2, std::max(0, atoi(e)));
     if (const char* e = getenv("ORBX_SELECT")) h->select_mode = e[0] == 'g' ? 1 : (e[0] == 's' ? 2 : 0);
     if (const char* e = getenv("ORBX_FAST")) h->fast_mode = e[0] == 'l' ? 1 : 0;
+    if (const char* e = getenv("ORBX_RESIZE")) h->resize_mode = e[0] == 'l' ? 1 : 0;
     if (const char* e = getenv("ORBX_LANES")) h->nlanes = std::min(kLanes, std::max(1, atoi(e)));
     for (int li = 0; li < h->nlanes; li++) {
       orbx_handle::Lane& ln = h->lane[li];
@@ -358,13 +391,17 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   // this scratch set was last used on another stream (a caller's, or the lane's own): order behind that chunk
   if (ln.used && ln.last_s != s) CK(cudaStreamWaitEvent(s, ln.ev_last, 0));
   const bool fast_tma = prepare_fast_tma(h, ln, d_imgs, stride, frame_stride);
+  prepare_resize_tma(h, ln, d_imgs, stride, frame_stride);
   const bool prof = h->profiling;
   // launch-latency-bound chains (a few frames per chunk) use programmatic dependent launch; full chunks keep the
   // plain stream order, where the other lane's kernels already fill the tails (ORBX_PDL=0 never / 2 always)
   set_launch_pdl(h->pdl_mode == 2 || (h->pdl_mode == 1 && n <= kPdlMaxFrames));
   int st = 0;
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
-  for (int l = 1; l < dp.nlevels; l++) launch_resize_level(b, dp, l, n, s);
+  for (int l = 1; l < dp.nlevels; l++) {
+    if (ln.rtma_ok[l]) launch_resize_level_tma(b, dp, ln.rtma, l, n, s);
+    else launch_resize_level(b, dp, l, n, s);
+  }
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   if (fast_tma) launch_fast_cells_tma(b, dp, ln.tma, n, s);
   else launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);

@@ -99,6 +99,8 @@ struct HostPlan {
   int fast_box_w[kMaxLevels], fast_box_h[kMaxLevels];
   int fast_tma_smem_bytes;
   bool fast_tma_ok;
+  // TMA-staged resize (resize_tma_kernel): source box of a 128 x 64 destination tile of level l, 0 = not available
+  int resize_box_w[kMaxLevels], resize_box_h[kMaxLevels];
 };
 
 // Shared-memory geometry of fast_cells_kernel for a cell sub-image of cw x ch pixels (scored region (cw-6) x (ch-6)):

@@ -34,6 +34,14 @@ struct FastTma {
   int smem_bytes;
 };
 
+// Tensor maps of resize_tma_kernel: map[l] describes the SOURCE of level l (= level l - 1; level 0 = the caller's frames)
+// as a 3-D byte tensor (x, y, frame) with the box one CTA tile needs.
+struct ResizeTma {
+  CUtensorMap map[kMaxLevels];
+  int box_w[kMaxLevels], box_h[kMaxLevels];
+};
+constexpr int kResizeTileW = 128, kResizeTileH = 64;   // destination tile of one resize_tma_kernel CTA (4 warps x 16 rows)
+
 struct BlurTiles {            // everything blur7_kernel needs per level, passed by value (constant bank, no global loads)
   int nlevels, blur_mode;
   int base[kMaxLevels + 1];   // prefix of tiles per level
@@ -51,6 +59,8 @@ struct BlurTiles {            // everything blur7_kernel needs per level, passed
 void set_launch_pdl(bool on);
 
 void launch_resize_level(const ChunkBuffers& b, const DevicePlan& hp, int level, int nframes, cudaStream_t s);
+void launch_resize_level_tma(const ChunkBuffers& b, const DevicePlan& hp, const ResizeTma& tm, int level, int nframes,
+                             cudaStream_t s);
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s);
 void launch_fast_cells_tma(const ChunkBuffers& b, const DevicePlan& hp, const FastTma& tm, int nframes, cudaStream_t s);
 void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s, int force);

@@ -122,7 +122,24 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
     kp_base += L.nDesired;
     L.tab_x = (int)hp.rx.size();
     L.tab_y = (int)hp.ry.size();
-    if (level > 0) resize_tables(dp.lv[level - 1].w, dp.lv[level - 1].h, L.w, L.h, &hp.rx, &hp.ry);
+    hp.resize_box_w[level] = hp.resize_box_h[level] = 0;
+    if (level > 0) {
+      resize_tables(dp.lv[level - 1].w, dp.lv[level - 1].h, L.w, L.h, &hp.rx, &hp.ry);
+      // source box of a 128 x 64 destination tile: columns from the 16-byte boundary at or below sx(first column) to
+      // sx(last column) + 1, rows sy0(first row) .. sy1(last row); 4 consecutive columns must span <= 8 source bytes
+      const ResizeX* rx = hp.rx.data() + L.tab_x;
+      const ResizeY* ry = hp.ry.data() + L.tab_y;
+      int bw = 0, bh = 0;
+      bool ok = true;
+      for (int x0 = 0; x0 < L.w; x0 += 128) {
+        const int x1 = std::min(x0 + 127, L.w - 1);
+        bw = std::max(bw, rx[x1].sx + 1 - (rx[x0].sx & ~15) + 1);
+      }
+      for (int x0 = 0; x0 < L.w; x0 += 4) ok = ok && rx[std::min(x0 + 3, L.w - 1)].sx + 1 - rx[x0].sx <= 7;
+      for (int y0 = 0; y0 < L.h; y0 += 64) bh = std::max(bh, ry[std::min(y0 + 63, L.h - 1)].sy1 - ry[y0].sy0 + 1);
+      bw = (bw + 12 + 15) & ~15;                    // + the aligned 12-byte read of the last column group
+      if (ok && bw <= 256 && bh <= 256) { hp.resize_box_w[level] = bw; hp.resize_box_h[level] = bh; }
+    }
 
     // grid geometry :531-547
     const int nDesiredFeatures = L.nDesired;

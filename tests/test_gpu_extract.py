@@ -292,8 +292,8 @@ def test_runtime_switches_are_bit_identical(oracle, env):
 
 
 def test_fast_kernels_agree(oracle):
-    """The TMA-staged FAST kernel (default where the buffers allow it) and the legacy kernel (ORBX_FAST=legacy; also the
-    fallback for misaligned caller buffers) on scenes that take every branch: list overflow (noise), retry at 7 (flat /
+    """The TMA-staged FAST / pyramid kernels (default where the buffers allow it) and the legacy kernels (ORBX_FAST=legacy,
+    ORBX_RESIZE=legacy; also the fallback for misaligned caller buffers) on scenes that take every branch: list overflow (noise), retry at 7 (flat /
     low contrast), odd sizes whose cells straddle the tensor-copy alignment, a row pitch that is not a multiple of 16."""
     import os
     rng = np.random.default_rng(11)
@@ -306,11 +306,11 @@ def test_fast_kernels_agree(oracle):
                "half": np.where(np.arange(w)[None, :] < w // 2, 90, rng.integers(0, 256, (h, w))).astype(np.uint8)}[kind]
         ok, od = oracle.OracleExtractor(nf, 1.2, nl, 1, th)(img)
         for mode in ("tma", "legacy"):
-            os.environ["ORBX_FAST"] = mode
+            os.environ["ORBX_FAST"] = os.environ["ORBX_RESIZE"] = mode     # FAST and pyramid kernels alike
             try:
                 ex = _ex(nfeatures=nf, nlevels=nl, fastTh=th, max_width=w, max_height=h, max_batch=3)
             finally:
-                os.environ.pop("ORBX_FAST", None)
+                os.environ.pop("ORBX_FAST", None); os.environ.pop("ORBX_RESIZE", None)
             k, d = ex(img)
             _cmp_final(k, d, ok, od)
             kps, desc, n = ex.extract_batch(np.stack([img] * 5))       # 2 chunks, both lanes
