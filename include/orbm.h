@@ -292,6 +292,20 @@ int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* 
 #define ORBM_KNN2_STATIC_SCRATCH_BYTES (4u << 20)
 int orbm_knn2_device_static(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
                             int64_t idx_base, uint32_t* d_top2, void* stream);
+/* The same search for databases beyond the 2^23 indices of the 32-bit keys: d_top2 [nq][2] receives 64-bit keys
+ * (dist << 40) | (idx_base + index), all ones = none; idx_base + ndb < 2^40.  The database is searched in segments of
+ * 2^23 descriptors with the kernels above and merged on the device. */
+#define ORBM_KEY64_NONE 0xFFFFFFFFFFFFFFFFull
+#define ORBM_KEY64_DIST(k) ((int)((k) >> 40))
+#define ORBM_KEY64_INDEX(k) ((int64_t)((k) & 0xFFFFFFFFFFull))
+int orbm_knn2_device64(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int64_t idx_base,
+                       uint64_t* d_top2, void* stream);
+/* Waits for the handle's stream and reports what the asynchronous entry points above and below could not return: a
+ * database tile that never arrived in knn2_kernel (ORBM_ERR_CUDA; the affected queries hold ORBM_KEY_NONE keys) and an
+ * asynchronous NCCL error on the communicator last used by orbm_knn2_sharded (ncclCommGetAsyncError, ORBM_ERR_COMM).
+ * Work enqueued on a caller's stream must have been synchronised by the caller first.  The counterpart of
+ * orbx_synchronize. */
+int orbm_synchronize(orbm_handle* h);
 /* Merge of per-shard results d_gathered [nshards][nq][2] (the all-gather receive buffer) into d_top2 [nq][2], plus
  * the accept rule of :224-226: d_match[q] = best index if best <= th_dist && (float)best < ratio * (float)second,
  * else -1 (d_match may be NULL). */
@@ -306,6 +320,7 @@ int orbm_merge_top2_device(orbm_handle* h, const uint32_t* d_gathered, int nshar
 int orbm_comm_unique_id(uint8_t id[ORBM_COMM_ID_BYTES]);
 int orbm_comm_init_rank(orbm_handle* h, int nranks, const uint8_t id[ORBM_COMM_ID_BYTES], int rank, void** comm);
 void orbm_comm_destroy(void* comm);
+void orbm_comm_release(orbm_handle* h, void* comm); /* destroy + make orbm_synchronize(h) forget it */
 int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db_shard, int64_t ndb_shard,
                       int64_t idx_base, int nranks, void* comm, uint32_t* d_gathered, int th_dist, float ratio,
                       uint32_t* d_top2, int32_t* d_match, void* stream);

@@ -59,6 +59,10 @@ struct orbm_handle {
   orbm::DevBuf ws_bow;       // per-keypoint descent results + uncompacted per-frame vectors (orbm_bow.cu)
   void* pinned = nullptr;    // pinned host staging (1 MB): small inputs go up / small results come back through it
   size_t pinned_cap = 0;
+  void* pinned_big = nullptr;       // pinned gather block of large projected-point batches (grown on demand)
+  size_t pinned_big_cap = 0;
+  cudaMemPool_t pool = nullptr;     // private stream-ordered pool of the frame-set arrays
+  void* last_comm = nullptr;        // communicator of the last orbm_knn2_sharded (asynchronous NCCL errors, orbm_synchronize)
   cudaEvent_t ev_order = nullptr;   // orders the handle's stream behind a caller's stream (created on first use)
 };
 
@@ -88,12 +92,15 @@ struct orbm_frameset {
   bool bow_sized = false;           // the feature / bow vector arrays have their upper-bound sizes (reusable)
 };
 
-// Frame-set arrays come from the device's stream-ordered pool (cudaMallocAsync on the handle's stream; the pool's
-// release threshold is lifted at orbm_create so freed blocks are reused instead of returned to the driver): creating
-// and destroying a frame set per tracked batch then costs microseconds, not a dozen cudaMalloc/cudaFree round trips.
-inline cudaError_t orbm_alloc(orbm_handle* h, void** p, size_t bytes) { return cudaMallocAsync(p, bytes, h->stream); }
+// Frame-set arrays come from a stream-ordered pool PRIVATE to the handle (cudaMemPoolCreate at orbm_create, release
+// threshold lifted so freed blocks are reused instead of returned to the driver, destroyed with the handle; the
+// device's default pool, which other cudaMallocAsync users of the process share, is left alone): creating and
+// destroying a frame set per tracked batch then costs microseconds, not a dozen cudaMalloc/cudaFree round trips.
+inline cudaError_t orbm_alloc(orbm_handle* h, void** p, size_t bytes) {
+  return cudaMallocFromPoolAsync(p, bytes, h->pool, h->stream);
+}
 template <class T> inline cudaError_t orbm_alloc(orbm_handle* h, T** p, size_t bytes) {
-  return cudaMallocAsync(reinterpret_cast<void**>(p), bytes, h->stream);
+  return cudaMallocFromPoolAsync(reinterpret_cast<void**>(p), bytes, h->pool, h->stream);
 }
 inline void orbm_free(orbm_handle* h, void* p) { if (p) cudaFreeAsync(p, h->stream); }
 constexpr size_t kOrbmPinnedBytes = 1u << 20;

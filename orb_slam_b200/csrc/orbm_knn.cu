@@ -35,13 +35,19 @@ extern "C" int orbm_create(int device, orbm_handle** out) {
     ORBM_CK(cudaGetDeviceProperties(&prop, device));
     h->num_sms = prop.multiProcessorCount;
     // run-time switches are per handle (a test can create one handle per setting inside one process)
+    ORBM_CK(h->ws_misc.reserve(256));
+    ORBM_CK(cudaMemset(h->ws_misc.p, 0, 256));          // [0] sticky knn2 error flag, [2..3] search arena cursor
     if (const char* e = getenv("ORBM_COMMIT")) h->commit_mode = e[0] == 's' ? 1 : (e[0] == 'p' ? 2 : 0);
     if (const char* e = getenv("ORBM_KNN_VARIANT")) h->knn_variant = std::min(2, std::max(0, atoi(e)));
-    // frame-set arrays are pool allocations (orbm_alloc): keep freed blocks cached in the pool
-    cudaMemPool_t pool;
-    ORBM_CK(cudaDeviceGetDefaultMemPool(&pool, device));
+    // frame-set arrays are pool allocations (orbm_alloc) from a pool of the handle's own: freed blocks stay cached in it
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    ORBM_CK(cudaMemPoolCreate(&h->pool, &props));
     unsigned long long keep = ~0ull;
-    ORBM_CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    ORBM_CK(cudaMemPoolSetAttribute(h->pool, cudaMemPoolAttrReleaseThreshold, &keep));
     return ORBM_OK;
   };
   int rc = body();
@@ -58,10 +64,12 @@ extern "C" void orbm_destroy(orbm_handle* h) {
                     &h->ws_target, &h->ws_cand, &h->ws_misc, &h->ws_io, &h->ws_bow};
   for (DevBuf* b : bufs) b->release();
   if (h->pinned) cudaFreeHost(h->pinned);
+  if (h->pinned_big) cudaFreeHost(h->pinned_big);
   if (h->ev_order) cudaEventDestroy(h->ev_order);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->pool) cudaMemPoolDestroy(h->pool);       // frame sets still alive lose their memory with their handle
   delete h;
 }
 
@@ -114,9 +122,8 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
     return ORBM_ERR_UNSUPPORTED;
   }
   if (((uintptr_t)d_q | (uintptr_t)d_db) & 15) { h->err = "descriptor arrays must be 16-byte aligned"; return ORBM_ERR_ARG; }
-  ORBM_CK(h->ws_misc.reserve(256));
+  // sticky: set by a CTA whose TMA tile never arrived, read and cleared by orbm_knn2 / orbm_synchronize
   int* d_err = h->ws_misc.as<int>();
-  ORBM_CK(cudaMemsetAsync(d_err, 0, sizeof(int), s));
   if (nq == 0) return ORBM_OK;
   if (ndb == 0) { ORBM_CK(cudaMemsetAsync(d_top2, 0xFF, (size_t)nq * 8, s)); return ORBM_OK; }
   // chunks: about 2 CTAs per SM over the whole grid; each chunk a whole number of tiles and >= 8 tiles (the TMA ring
@@ -158,9 +165,15 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
 int knn_check_err(orbm_handle* h) {  // call after the stream has been synchronised
   int flag = 0;
   ORBM_CK(cudaMemcpy(&flag, h->ws_misc.p, sizeof(int), cudaMemcpyDeviceToHost));
-  if (flag) { h->err = "knn2: TMA tile never arrived (mbarrier wait timed out)"; return ORBM_ERR_CUDA; }
+  if (flag) {
+    cudaMemset(h->ws_misc.p, 0, sizeof(int));
+    h->err = "knn2: TMA tile never arrived (mbarrier wait timed out); the affected queries hold 'none' keys";
+    return ORBM_ERR_CUDA;
+  }
   return ORBM_OK;
 }
+
+int nccl_check_async(orbm_handle* h, void* comm);
 
 }  // namespace
 
@@ -169,6 +182,55 @@ extern "C" int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, cons
   if (!h) return ORBM_ERR_ARG;
   ORBM_CK(cudaSetDevice(h->device));
   return knn2_launch(h, d_q, nq, d_db, ndb, idx_base, d_top2, stream ? (cudaStream_t)stream : h->stream);
+}
+
+// ---- databases beyond the 2^23 indices of the packed 32-bit keys: 64-bit keys (dist << 40) | index ----------------------
+// The database is searched in segments of 2^23 descriptors with the 32-bit kernels (segment-local indices); one small
+// kernel per segment widens the keys with the segment's base and folds them into the running (best, second) pair.
+// Key order is still (distance, index) order, so the result equals one sequential scan with strict `<`.
+namespace {
+__global__ void __launch_bounds__(256) widen_merge_kernel(const uint2* __restrict__ seg, int nq, uint64_t base, int first,
+                                                          ulonglong2* __restrict__ io) {
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= nq) return;
+  ulonglong2 r = first ? make_ulonglong2(~0ull, ~0ull) : io[qi];
+  const uint2 v = seg[qi];
+  const uint32_t ks[2] = {v.x, v.y};
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    if (ks[k] == kNone) continue;
+    const uint64_t key = ((uint64_t)(ks[k] >> 23) << 40) | (base + (uint64_t)(ks[k] & 0x7FFFFFu));
+    const uint64_t hi = r.x > key ? r.x : key;
+    r.y = r.y < hi ? r.y : hi;
+    r.x = r.x < key ? r.x : key;
+  }
+  io[qi] = r;
+}
+}  // namespace
+
+extern "C" int orbm_knn2_device64(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                  int64_t idx_base, uint64_t* d_top2, void* stream) {
+  if (!h) return ORBM_ERR_ARG;
+  if (!d_q || !d_db || !d_top2 || nq < 0 || ndb < 0 || idx_base < 0 || idx_base + ndb >= (1ll << 40)) {
+    h->err = "null pointer, negative size or index beyond 2^40";
+    return ORBM_ERR_ARG;
+  }
+  if (nq == 0) return ORBM_OK;
+  ORBM_CK(cudaSetDevice(h->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  if (ndb == 0) { ORBM_CK(cudaMemsetAsync(d_top2, 0xFF, (size_t)nq * 16, s)); return ORBM_OK; }
+  ORBM_CK(h->stage_c.reserve((size_t)nq * 8 + 16));
+  const int64_t kSeg = 1ll << 23;
+  for (int64_t o = 0; o < ndb; o += kSeg) {
+    const int64_t len = std::min(kSeg, ndb - o);
+    const int rc = knn2_launch(h, d_q, nq, d_db + o * 32, len, 0, h->stage_c.as<uint32_t>(), s);
+    if (rc != ORBM_OK) return rc;
+    widen_merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(h->stage_c.as<uint2>(), nq, (uint64_t)(idx_base + o), o == 0,
+                                                       reinterpret_cast<ulonglong2*>(d_top2));
+    h->launches++;
+  }
+  ORBM_CK(cudaGetLastError());
+  return ORBM_OK;
 }
 
 extern "C" int orbm_knn2(orbm_handle* h, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int64_t idx_base,
@@ -191,6 +253,20 @@ extern "C" int orbm_knn2(orbm_handle* h, const uint8_t* q, int nq, const uint8_t
   ORBM_CK(cudaStreamSynchronize(h->stream));
   cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
   return knn_check_err(h);
+}
+
+// Waits for the handle's stream and reports what the asynchronous entry points (orbm_knn2_device,
+// orbm_knn2_device_static, orbm_knn2_sharded, orbm_merge_top2_device) could not return: the sticky "tile never arrived"
+// flag of knn2_kernel and an asynchronous NCCL error of the communicator last used by orbm_knn2_sharded.  Work launched
+// on a CALLER'S stream must have been synchronised by the caller first.
+extern "C" int orbm_synchronize(orbm_handle* h) {
+  if (!h) return ORBM_ERR_ARG;
+  ORBM_CK(cudaSetDevice(h->device));
+  ORBM_CK(cudaStreamSynchronize(h->stream));
+  int rc = knn_check_err(h);
+  if (rc != ORBM_OK) return rc;
+  if (h->last_comm) return nccl_check_async(h, h->last_comm);
+  return ORBM_OK;
 }
 
 extern "C" int orbm_merge_top2_device(orbm_handle* h, const uint32_t* d_gathered, int nshards, int nq, int th_dist,
@@ -216,6 +292,7 @@ struct NcclApi {
   int (*GetUniqueId)(void*) = nullptr;
   int (*CommInitRank)(void**, int, NcclUid, int) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
+  int (*CommGetAsyncError)(void*, int*) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
   bool ok = false;
 };
@@ -238,8 +315,26 @@ NcclApi* nccl_api() {
   *(void**)&api.CommInitRank = sym("ncclCommInitRank");
   *(void**)&api.CommDestroy = sym("ncclCommDestroy");
   *(void**)&api.GetErrorString = sym("ncclGetErrorString");
+  *(void**)&api.CommGetAsyncError = sym("ncclCommGetAsyncError");
   api.ok = api.AllGather && api.GetUniqueId && api.CommInitRank && api.CommDestroy;
   return api.ok ? &api : nullptr;
+}
+}  // namespace
+
+namespace {
+// ncclCommGetAsyncError: errors of collectives already enqueued (a peer died, a transport failed) that no enqueue call
+// returned.  ncclSuccess (0) and ncclInProgress (7) are not errors.
+int nccl_check_async(orbm_handle* h, void* comm) {
+  NcclApi* n = nccl_api();
+  if (!n || !n->CommGetAsyncError || !comm) return ORBM_OK;
+  int async = 0;
+  const int rc = n->CommGetAsyncError(comm, &async);
+  if (rc != 0 || (async != 0 && async != 7)) {
+    const int code = rc != 0 ? rc : async;
+    h->err = std::string("NCCL asynchronous error: ") + (n->GetErrorString ? n->GetErrorString(code) : std::to_string(code).c_str());
+    return ORBM_ERR_COMM;
+  }
+  return ORBM_OK;
 }
 }  // namespace
 
@@ -266,6 +361,11 @@ extern "C" int orbm_comm_init_rank(orbm_handle* h, int nranks, const uint8_t id[
   return ORBM_OK;
 }
 
+extern "C" void orbm_comm_release(orbm_handle* h, void* comm) {   // destroy + forget (orbm_synchronize queries last_comm)
+  if (h && h->last_comm == comm) h->last_comm = nullptr;
+  orbm_comm_destroy(comm);
+}
+
 extern "C" void orbm_comm_destroy(void* comm) {
   NcclApi* n = nccl_api();
   if (n && comm) n->CommDestroy(comm);
@@ -287,6 +387,9 @@ extern "C" int orbm_knn2_sharded(orbm_handle* h, const uint8_t* d_q, int nq, con
   const int ncclUint32 = 3;
   const int nrc = nccl->AllGather(d_local, d_gathered, (size_t)nq * 2, ncclUint32, comm, s);
   if (nrc != 0) { h->err = "ncclAllGather failed with code " + std::to_string(nrc); return ORBM_ERR_COMM; }
+  h->last_comm = comm;
+  rc = nccl_check_async(h, comm);                 // errors of EARLIER collectives on this communicator
+  if (rc != ORBM_OK) return rc;
   return orbm_merge_top2_device(h, d_gathered, nranks, nq, th_dist, ratio, d_top2, d_match, s);
 }
 

@@ -156,7 +156,11 @@ __global__ void __launch_bounds__(kKnnThreads) knn2_kernel(const uint4* __restri
       issue(it - 1 + kKnnStages, ps);
     }
   }
-  if (!ok) { atomicExch(err, 3); return; }
+  if (!ok) {                       // a lost tile: report it and leave 'none' keys, never stale ones, for the merge
+    atomicExch(err, 3);
+#pragma unroll
+    for (int k = 0; k < QPT; k++) { best[k] = kNone; second[k] = kNone; }
+  }
 #pragma unroll
   for (int k = 0; k < QPT; k++) {
     const int qi = (qtile * QPT + k) * kKnnThreads + tid;

@@ -102,6 +102,10 @@ def _bind(L):
     L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_knn2.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp]
     L.orbm_knn2_device.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp, vp]
+    L.orbm_knn2_device64.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp, vp]
+    L.orbm_synchronize.argtypes = [vp]
+    L.orbm_comm_release.argtypes = [vp, vp]
+    L.orbm_comm_release.restype = None
     L.orbm_knn2_device_static.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, vp, vp]
     L.orbm_merge_top2_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, f32, vp, vp, vp]
     L.orbm_knn2_sharded.argtypes = [vp, vp, C.c_int, vp, C.c_int64, C.c_int64, C.c_int, vp, vp, C.c_int, f32, vp, vp, vp]
@@ -239,6 +243,14 @@ class Matcher:
 
     def knn2_device(self, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream=None):
         self._check(self._L.orbm_knn2_device(self._h, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream))
+
+    def knn2_device64(self, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream=None):
+        """64-bit keys (dist << 40 | index) for databases beyond 2^23 descriptors; top2: [nq, 2] uint64 on the device."""
+        self._check(self._L.orbm_knn2_device64(self._h, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream))
+
+    def synchronize(self):
+        """orbm_synchronize: waits for the handle's stream, raises on a deferred knn2 / NCCL error."""
+        self._check(self._L.orbm_synchronize(self._h))
 
     def knn2_device_static(self, q_ptr, nq, db_ptr, ndb, idx_base, top2_ptr, stream=None):
         """orbm_knn2_device without any device allocation (static scratch, include/orbm.h)."""
@@ -696,7 +708,7 @@ class ShardedKnn2:
 
     def close(self):
         if getattr(self, "_comm", None) and getattr(self.m, "_h", None):
-            self.m._L.orbm_comm_destroy(self._comm)
+            self.m._L.orbm_comm_release(self.m._h, self._comm)
         self._comm = None
 
     def search(self, q_ptr, nq, db_shard_ptr, ndb_shard, idx_base, gathered_ptr, top2_ptr, match_ptr, th_dist=TH_LOW,

@@ -316,3 +316,27 @@ def test_fast_kernels_agree(oracle):
             kps, desc, n = ex.extract_batch(np.stack([img] * 5))       # 2 chunks, both lanes
             for i in range(5):
                 _cmp_final(kps[i, :n[i]], desc[i, :n[i]], ok, od)
+
+
+def test_device_api_with_unaligned_rows_takes_the_legacy_kernels(oracle):
+    """orbx_extract_batch_device on a caller buffer whose row pitch (333) and frame stride are not multiples of 16: the
+    tensor maps of the TMA kernels cannot describe it, so the chunk runs on the legacy kernels - same results."""
+    import torch
+    from orb_slam_b200 import KP_DTYPE
+    w, h, nf = 333, 251, 700
+    imgs = np.stack([oracle.synth(h, w, 90 + s) for s in range(3)])
+    ex = _ex(nfeatures=nf, nlevels=5, fastTh=9, max_width=w, max_height=h, max_batch=4)
+    d = torch.from_numpy(imgs).cuda()
+    assert d.stride(1) == 333
+    d_k = torch.zeros((3, nf, 28), dtype=torch.uint8, device="cuda")
+    d_d = torch.zeros((3, nf, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(3, dtype=torch.int32, device="cuda")
+    ex.extract_batch_device(d.data_ptr(), 3, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(),
+                            torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ex.synchronize()
+    n = d_n.cpu().numpy(); k = d_k.cpu().numpy().view(KP_DTYPE).reshape(3, nf); dd = d_d.cpu().numpy()
+    O = oracle.OracleExtractor(nf, 1.2, 5, 1, 9)
+    for f in range(3):
+        ok, od = O(imgs[f])
+        _cmp_final(k[f, :n[f]], dd[f, :n[f]], ok, od)

@@ -118,3 +118,46 @@ def test_config5_5m_database_planted_split_and_sample(oracle):
     sample = np.arange(0, NQ, NQ // 48)
     ref = M.knn2(q[sample], db, threads=16)
     assert np.array_equal(got[sample], ref)
+
+
+def test_knn2_64bit_keys_beyond_2_23_descriptors(oracle):
+    """orbm_knn2_device64: a database of 2^23 + 300,000 descriptors (more than the 32-bit keys can index).  Planted
+    near-duplicates in BOTH segments come back as best matches with their 40-bit indices and exact distances, a duplicate
+    row that exists in both segments resolves to the lower index, and the result equals the two halves searched with the
+    32-bit entry point and merged on the host; a query sample equals the oracle over the tail segment."""
+    import torch
+    from oracle import match_oracle as M
+    from orb_slam_b200 import Matcher
+    M.lib()
+    m = Matcher(0)
+    ndb, nq = (1 << 23) + 300_000, 512
+    g = torch.Generator(device="cuda").manual_seed(5)
+    db = torch.randint(0, 256, (ndb, 32), dtype=torch.uint8, device="cuda", generator=g)
+    pick = torch.randint(0, ndb, (nq,), device="cuda", generator=g)
+    pick[:64] = torch.randint(1 << 23, ndb, (64,), device="cuda", generator=g)         # the tail segment for sure
+    q = db[pick].clone()
+    q[:, 3] ^= 0x81                                                                    # distance 2 to the planted row
+    db[(1 << 23) + 77] = db[1234]; q[100] = db[1234]; pick[100] = 1234                 # same row in both segments
+    out = torch.empty((nq, 2), dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    m.knn2_device64(q.data_ptr(), nq, db.data_ptr(), ndb, 0, out.data_ptr(), st)
+    torch.cuda.synchronize()
+    m.synchronize()
+    k = out.cpu().numpy().view(np.uint64)
+    dist, idx = (k >> np.uint64(40)).astype(np.int64), (k & np.uint64(0xFFFFFFFFFF)).astype(np.int64)
+    p = pick.cpu().numpy()
+    assert np.array_equal(idx[:, 0], p) and (dist[np.arange(nq) != 100, 0] == 2).all() and dist[100, 0] == 0
+    assert idx[100, 1] == (1 << 23) + 77 and dist[100, 1] == 0
+    # against the 32-bit path on the two segments, merged on the host in (distance, index) order
+    a = torch.empty((nq, 2), dtype=torch.int32, device="cuda"); b = torch.empty((nq, 2), dtype=torch.int32, device="cuda")
+    m.knn2_device(q.data_ptr(), nq, db.data_ptr(), 1 << 23, 0, a.data_ptr(), st)
+    m.knn2_device(q.data_ptr(), nq, db[1 << 23:].data_ptr(), ndb - (1 << 23), 0, b.data_ptr(), st)
+    torch.cuda.synchronize()
+    ka, kb = a.cpu().numpy().view(np.uint32).astype(np.uint64), b.cpu().numpy().view(np.uint32).astype(np.uint64)
+    wide = lambda kk, base: ((kk >> np.uint64(23)) << np.uint64(40)) | ((kk & np.uint64(0x7FFFFF)) + np.uint64(base))
+    allk = np.sort(np.concatenate([wide(ka, 0), wide(kb, 1 << 23)], axis=1), axis=1)[:, :2]
+    assert np.array_equal(k, allk)
+    # oracle over the tail segment for the queries planted there
+    tail = db[1 << 23:].cpu().numpy()
+    ref = M.knn2(q[:64].cpu().numpy(), tail, threads=8)
+    assert np.array_equal(kb[:64].astype(np.uint32), ref)
