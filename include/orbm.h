@@ -190,6 +190,27 @@ int orbm_is_in_frustum(orbm_handle* h, const orbm_frustum_view* views, int nview
                        const float* normal /* n x 3 */, const float* min_dist, const float* max_dist, int n,
                        float cos_limit, uint8_t* in_view, float* u, float* v, int32_t* level, float* view_cos);
 
+/* ---- N4: KeyFrameDatabase candidate scoring ------------------------------------------------------
+ * KeyFrameDatabase::DetectRelocalisationCandidates (src/KeyFrameDatabase.cc:198-308) and ::DetectLoopCandidates
+ * (:75-196) up to the point where they start walking the covisibility graph: for every query frame and every keyframe
+ * of the database the number of shared vocabulary words (mnRelocWords / mnLoopWords, via the inverted file of
+ * KeyFrameDatabase::add, :40-46), maxCommonWords over the candidates, minCommonWords = (int)(maxCommonWords * 0.8f)
+ * (:231-238) and mpVoc->score(query, keyframe) - L1Scoring::score as the float the reference stores - for candidates
+ * with more than minCommonWords shared words (:247-255).
+ *   orbm_bowdb_create   builds the inverted file of a keyframe set that holds BowVectors (orbm_frameset_compute_bow);
+ *                       the set must outlive the database
+ *   orbm_bowdb_query    queries = frames qidx[0..nq) of a set with BowVectors.  exclude [nq][nkf] (may be NULL): != 0 =
+ *                       the keyframe is no candidate for that query (DetectLoopCandidates drops the query's connected
+ *                       keyframes, :95).  Outputs, HOST: common [nq][nkf] shared words (0 = none; counted for excluded
+ *                       keyframes too), max_common / min_common [nq], score [nq][nkf] = the score where
+ *                       common > min_common and not excluded, else -1.
+ * Accumulating the scores over GetBestCovisibilityKeyFrames(10) and the 0.75 * best cut (:262-305) stay with the host. */
+typedef struct orbm_bowdb orbm_bowdb;
+int orbm_bowdb_create(orbm_handle* h, const orbm_frameset* keyframes, orbm_bowdb** out);
+void orbm_bowdb_destroy(orbm_bowdb* d);
+int orbm_bowdb_query(orbm_bowdb* d, const orbm_frameset* queries, const int32_t* qidx, int nq, const uint8_t* exclude,
+                     int32_t* common, int32_t* max_common, int32_t* min_common, float* score);
+
 /* ---- N4: MapPoint::ComputeDistinctiveDescriptors batched (src/MapPoint.cc:185-250) ---------------------------
  * Point p observes the descriptors desc[start[p] .. start[p+1]) (HOST buffers; the caller has already dropped bad
  * keyframes, :205-209).  best[p] = index inside the point's list of the descriptor with the least median Hamming

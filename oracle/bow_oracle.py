@@ -109,6 +109,25 @@ def score_l1(b1, b2) -> float:
     return float(_lib().bo_score_l1(w1.ctypes.data, v1.ctypes.data, len(w1), w2.ctypes.data, v2.ctypes.data, len(w2)))
 
 
+def kfdb_candidates(query_bow, db_bows, exclude=None):
+    """The candidate scoring of KeyFrameDatabase::DetectRelocalisationCandidates / DetectLoopCandidates (reference
+    src/KeyFrameDatabase.cc:198-255, :75-139) on flat BowVectors (word ids ascending, weights): shared-word count per
+    keyframe (what walking the inverted file accumulates in mnRelocWords / mnLoopWords), maxCommonWords over the keyframes
+    that are not excluded, minCommonWords = int(float(max) * 0.8f), and float(L1Scoring::score) for keyframes with
+    more than minCommonWords shared words.  Returns (common, max_common, min_common, score[-1 where not scored])."""
+    n = len(db_bows)
+    qw = np.asarray(query_bow[0], np.int32)
+    common = np.array([len(np.intersect1d(qw, np.asarray(b[0], np.int32), assume_unique=True)) for b in db_bows], np.int32)
+    ex = np.zeros(n, bool) if exclude is None else np.asarray(exclude).astype(bool)
+    mx = int(common[~ex].max()) if (~ex).any() else 0
+    mn = int(np.float32(mx) * np.float32(0.8))
+    score = np.full(n, -1, np.float32)
+    for k in range(n):
+        if not ex[k] and common[k] > mn:
+            score[k] = np.float32(score_l1(query_bow, db_bows[k]))
+    return common, mx, mn, score
+
+
 def save_text(path, k, L, scoring, weighting, parent, desc, weight, is_leaf, trailing_newline=False):
     """Writes the ORBvoc.txt layout saveToTextFile produces (TemplatedVocabulary.h:1429-1449); weights with 17
     significant digits so a round trip is exact."""

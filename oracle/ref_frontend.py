@@ -76,6 +76,11 @@ def _lib():
             ("ref_m_search_by_projection_reloc", "argtypes", [_P, _P, _P, _P, _F, _I, _F, _I, _P]),
             ("ref_m_search_by_projection_sim3", "argtypes", [_P, _P, _P, _P, _P, _I, _I, _F, _P]),
             ("ref_m_is_in_frustum", "argtypes", [_P, _P, _F] + [_P] * 6),
+            ("ref_m_kfdb_add", "argtypes", [_P, _P]),
+            ("ref_m_detect_reloc", "argtypes", [_P, _P, _P, _I, _P, _P, _P, _P]),
+            ("ref_m_detect_loop", "argtypes", [_P, _P, _P, _I, _P, _F, _P, _P, _P, _P]),
+            ("ref_m_frame_id", "argtypes", [_P]),
+            ("ref_m_keyframe_id", "argtypes", [_P]),
             ("ref_m_fuse", "argtypes", [_P, _P, _P, _P, _P, _I, _F, _P, _P, _P]),
             ("ref_m_fuse_sim3", "argtypes", [_P, _P, _P, _P, _I, _F, _P, _P]),
             ("ref_m_search_by_sim3", "argtypes", [_P, _P, _P, _P, _P, _F, _P]),
@@ -295,3 +300,33 @@ def search_by_projection_ff(f1: RefFrame, f2: RefFrame, pos, window, ratio, chec
     m = np.zeros(max(f2.n, 1), np.int32)
     n = _lib().ref_m_search_by_projection_ff(f1._f, f2._f, pos.ctypes.data, int(window), ratio, int(check_ori), m.ctypes.data)
     return n, m[:f2.n]
+
+
+def kfdb_add(world: World, frames):
+    """KeyFrameDatabase::add for the keyframes of `frames` (after compute_bow)."""
+    for f in frames:
+        _lib().ref_m_kfdb_add(world._w, f.keyframe())
+
+
+def _kf_array(frames):
+    return (C.c_void_p * len(frames))(*[f.keyframe() for f in frames])
+
+
+def detect_relocalisation_candidates(world: World, query: RefFrame, frames):
+    """KeyFrameDatabase::DetectRelocalisationCandidates(F) -> (ncand, touched, words, score, cand) per keyframe of `frames`."""
+    n = len(frames)
+    t = np.zeros(n, np.uint8); w = np.zeros(n, np.int32); s = np.zeros(n, np.float32); c = np.zeros(n, np.uint8)
+    assert _lib().ref_m_frame_id(query._f) != 0
+    r = _lib().ref_m_detect_reloc(world._w, query._f, _kf_array(frames), n, t.ctypes.data, w.ctypes.data, s.ctypes.data, c.ctypes.data)
+    return r, t, w, s, c
+
+
+def detect_loop_candidates(world: World, query: RefFrame, frames, connected, min_score):
+    """KeyFrameDatabase::DetectLoopCandidates(pKF, minScore); connected[k] != 0 -> frames[k] is a covisibility neighbour."""
+    n = len(frames)
+    con = np.ascontiguousarray(connected, np.uint8)
+    t = np.zeros(n, np.uint8); w = np.zeros(n, np.int32); s = np.zeros(n, np.float32); c = np.zeros(n, np.uint8)
+    assert _lib().ref_m_keyframe_id(query.keyframe()) != 0
+    r = _lib().ref_m_detect_loop(world._w, query.keyframe(), _kf_array(frames), n, con.ctypes.data, min_score, t.ctypes.data,
+                                 w.ctypes.data, s.ctypes.data, c.ctypes.data)
+    return r, t, w, s, c

@@ -498,6 +498,49 @@ int ref_m_search_by_projection_ff(void* fb1, void* fb2, const float* pos, int wi
   return n;
 }
 
+// KeyFrameDatabase (src/KeyFrameDatabase.cc): add(pKF) puts the keyframe into the inverted file (:40-46).
+void ref_m_kfdb_add(void* world, void* kf) { static_cast<World*>(world)->db->add(static_cast<KeyFrame*>(kf)); }
+
+// DetectRelocalisationCandidates(F) (:198-308) for the frame in `fb` against everything add()ed.  For each of the nkf
+// keyframes in kfs: touched[k] = 1 when the call counted it (mnRelocQuery == F.mnId), words[k] = mnRelocWords,
+// score[k] = mRelocScore (meaningful only above the cut), cand[k] = 1 when the keyframe is among the returned candidates.
+// Returns the number of candidates.  The frame's mnId must not be 0 (keyframes start with mnRelocQuery == 0).
+int ref_m_detect_reloc(void* world, void* fb, void** kfs, int nkf, uint8_t* touched, int32_t* words, float* score,
+                       uint8_t* cand) {
+  World* w = static_cast<World*>(world);
+  Frame* F = static_cast<FrameBox*>(fb)->f;
+  std::vector<KeyFrame*> r = w->db->DetectRelocalisationCandidates(F);
+  std::set<KeyFrame*> rs(r.begin(), r.end());
+  for (int k = 0; k < nkf; k++) {
+    KeyFrame* p = static_cast<KeyFrame*>(kfs[k]);
+    touched[k] = p->mnRelocQuery == F->mnId ? 1 : 0;
+    words[k] = p->mnRelocWords; score[k] = p->mRelocScore; cand[k] = rs.count(p) ? 1 : 0;
+  }
+  return (int)r.size();
+}
+
+// DetectLoopCandidates(pKF, minScore) (:75-196); connected[k] != 0: keyframe k is made a covisibility neighbour of the
+// query first (KeyFrame::AddConnection), which the search then skips (:95).  Outputs as above from mnLoopQuery /
+// mnLoopWords / mLoopScore.
+int ref_m_detect_loop(void* world, void* query_kf, void** kfs, int nkf, const uint8_t* connected, float min_score,
+                      uint8_t* touched, int32_t* words, float* score, uint8_t* cand) {
+  World* w = static_cast<World*>(world);
+  KeyFrame* q = static_cast<KeyFrame*>(query_kf);
+  for (int k = 0; k < nkf; k++)
+    if (connected[k]) q->AddConnection(static_cast<KeyFrame*>(kfs[k]), 20);
+  std::vector<KeyFrame*> r = w->db->DetectLoopCandidates(q, min_score);
+  std::set<KeyFrame*> rs(r.begin(), r.end());
+  for (int k = 0; k < nkf; k++) {
+    KeyFrame* p = static_cast<KeyFrame*>(kfs[k]);
+    touched[k] = p->mnLoopQuery == q->mnId ? 1 : 0;
+    words[k] = p->mnLoopWords; score[k] = p->mLoopScore; cand[k] = rs.count(p) ? 1 : 0;
+  }
+  return (int)r.size();
+}
+
+int ref_m_frame_id(void* fb) { return (int)static_cast<FrameBox*>(fb)->f->mnId; }
+int ref_m_keyframe_id(void* kf) { return (int)static_cast<KeyFrame*>(kf)->mnId; }
+
 // Frame::isInFrustum(pMP, viewingCosLimit) (src/Frame.cc:136-197) of frame `view_fb` (pose = identity through the
 // reference's own UpdatePoseMatrices, :129-134) for the MapPoint on every keypoint of `src_fb` (geometry from
 // ref_m_frame_set_point_geometry).  Outputs per source keypoint: the return value and the tracking fields it writes

@@ -4,6 +4,6 @@ Product surface: the C ABI in include/orbx.h / include/orbm.h (liborbx.so) and t
 reference classes.  Nothing here imports oracle/ and nothing falls back to a CPU path.
 """
 from .extractor import KP_DTYPE, ORBextractor, OrbxError, synth_frames_device  # noqa: F401
-from .matcher import (Camera, FrameSet, FrustumView, Matcher, image_bounds, MatchFrame, ORBmatcher, OrbmError, ORBVocabulary,
+from .matcher import (BowDatabase, Camera, FrameSet, FrustumView, Matcher, image_bounds, MatchFrame, ORBmatcher, OrbmError, ORBVocabulary,
                       ProjectedPoints, ShardedKnn2,
                       shard_range)  # noqa: F401,E402

@@ -97,6 +97,10 @@ def _bind(L):
     L.orbm_window_search.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_search_by_projection_frames.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, f32, vp, vp]
     L.orbm_search_by_projection.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, f32, C.c_int, vp, C.c_int, vp]
+    L.orbm_bowdb_create.argtypes = [vp, vp, C.POINTER(vp)]
+    L.orbm_bowdb_destroy.argtypes = [vp]
+    L.orbm_bowdb_destroy.restype = None
+    L.orbm_bowdb_query.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp]
     L.orbm_search_by_sim3.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orbm_search_by_bow.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, f32, C.c_int, vp, C.c_int, vp]
     L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int, vp]
@@ -356,6 +360,7 @@ class FrameSet:
         self._s = C.c_void_p()
         matcher._check(self._L.orbm_frameset_create(matcher._h, arr, fvs, len(self.frames), C.byref(self._s)))
         self.max_n = max(f.n for f in self.frames)
+        self.nframes = len(self.frames)
 
     @classmethod
     def from_extractor(cls, matcher: Matcher, kps_ptr, desc_ptr, n_ptr, nframes, kp_stride, camera: Camera,
@@ -367,6 +372,7 @@ class FrameSet:
         self._s = C.c_void_p()
         matcher._check(self._L.orbm_frameset_from_extractor(matcher._h, kps_ptr, desc_ptr, n_ptr, nframes, kp_stride,
                                                             C.byref(camera), stream, C.byref(self._s)))
+        self.nframes = nframes
         self.counts = np.zeros(nframes, np.int32)
         matcher._check(self._L.orbm_frameset_counts(self._s, self.counts.ctypes.data))
         self.max_n = int(self.counts.max()) if nframes else 0
@@ -664,6 +670,39 @@ class ORBmatcher:
                                                             int(self.mbCheckOrientation), out.ctypes.data, stride,
                                                             nm.ctypes.data))
         return nm, out
+
+
+class BowDatabase:
+    """KeyFrameDatabase candidate scoring (reference src/KeyFrameDatabase.cc:75-308) over a resident keyframe set with
+    BowVectors: inverted file on the device, shared-word counts, the 0.8 * max cut and the L1 scores of the survivors."""
+
+    def __init__(self, matcher: "Matcher", keyframes: "FrameSet"):
+        self.m, self.keyframes = matcher, keyframes
+        p = C.c_void_p()
+        matcher._check(matcher._L.orbm_bowdb_create(matcher._h, keyframes._s, C.byref(p)))
+        self._d = p
+
+    def query(self, queries: "FrameSet", qidx, exclude=None):
+        """-> (common [nq, nkf], max_common [nq], min_common [nq], score [nq, nkf] (-1 below the cut / excluded))."""
+        qi = _i32(np.atleast_1d(qidx))
+        nq, nkf = len(qi), self.keyframes.nframes
+        common = np.zeros((nq, max(nkf, 1)), np.int32); score = np.full((nq, max(nkf, 1)), -1, np.float32)
+        mx = np.zeros(nq, np.int32); mn = np.zeros(nq, np.int32)
+        ex = None if exclude is None else np.ascontiguousarray(exclude, np.uint8).reshape(nq, nkf)
+        self.m._check(self.m._L.orbm_bowdb_query(self._d, queries._s, qi.ctypes.data, nq, None if ex is None else ex.ctypes.data,
+                                                 common.ctypes.data, mx.ctypes.data, mn.ctypes.data, score.ctypes.data))
+        return common[:, :nkf], mx, mn, score[:, :nkf]
+
+    def close(self):
+        if self._d:
+            self.m._L.orbm_bowdb_destroy(self._d)
+            self._d = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def shard_range(n_units, rank, world):

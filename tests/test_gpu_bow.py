@@ -193,3 +193,42 @@ def test_extractor_to_bow_on_device(B, oracle, matcher):
         w, v = fs.bow_vector(f)
         assert n[f] > 100 and np.array_equal(w, ow) and same_f64(v, ov)
         assert all(np.array_equal(x, y) for x, y in zip(fs.feature_vector(f), ofv))
+
+
+def test_keyframe_database_candidate_scoring(matcher, B):
+    """N4: orbm_bowdb_* (inverted file, shared-word counts, 0.8 * max cut, L1 scores of the survivors) against the oracle
+    restatement of KeyFrameDatabase::DetectRelocalisationCandidates / DetectLoopCandidates (src/KeyFrameDatabase.cc:75-308),
+    which tests/test_ref_matcher.py pins to the compiled reference: 60 keyframes, 9 queries, with and without excluded
+    (covisible) keyframes; counts exact, scores compared as float bits."""
+    from orb_slam_b200 import BowDatabase, MatchFrame, ORBVocabulary
+    V = B.synth_vocabulary_fast(k=6, L=4, seed=3)
+    ovoc = B.Vocabulary.from_arrays(**{k: V[k] for k in KEYS})
+    voc = ORBVocabulary.from_arrays(matcher, **{k: V[k] for k in KEYS})
+    rng = np.random.default_rng(8)
+    leaves = V["desc"][V["is_leaf"] == 1]
+
+    def frame(n, pool):
+        d = leaves[rng.choice(pool, n)].copy()
+        flip = rng.integers(0, 256, (n, 2))
+        for c in range(2):
+            d[np.arange(n), flip[:, c] >> 3] ^= (1 << (flip[:, c] & 7)).astype(np.uint8)
+        z = np.zeros(n, np.float32)
+        return MatchFrame(z, z, z, np.zeros(n, np.int32), d)
+    pools = [rng.choice(len(leaves), 400, replace=False) for _ in range(6)]      # six "places" with their own words
+    kfs = [frame(int(rng.integers(200, 900)), pools[k % 6]) for k in range(60)]
+    kfs.append(frame(5, pools[0])); kfs.append(MatchFrame(*(np.zeros(0, np.float32),) * 3, np.zeros(0, np.int32), np.zeros((0, 32), np.uint8)))
+    qs = [frame(int(rng.integers(300, 800)), pools[k % 6]) for k in range(9)]
+    ks, qset = matcher.upload(kfs), matcher.upload(qs)
+    ks.compute_bow(voc, 4); qset.compute_bow(voc, 4)
+    kb = [ovoc.transform(f.desc, 4)[0] for f in kfs]; qb = [ovoc.transform(f.desc, 4)[0] for f in qs]
+    db = BowDatabase(matcher, ks)
+    order = [3, 0, 8, 1, 2, 4, 5, 6, 7, 3]                                        # any order, repeats allowed
+    for exclude in (None, (rng.random((len(order), len(kfs))) < 0.2).astype(np.uint8)):
+        common, mx, mn, score = db.query(qset, order, exclude)
+        for r, q in enumerate(order):
+            oc, omx, omn, osc = B.kfdb_candidates(qb[q], kb, None if exclude is None else exclude[r])
+            assert np.array_equal(common[r], oc) and mx[r] == omx and mn[r] == omn, (r, q)
+            assert np.array_equal(score[r].view(np.uint32), osc.view(np.uint32)), (r, q)
+            assert (osc >= 0).sum() >= 3 and (osc < 0).sum() >= 30
+    assert matcher.last_kernel_ms() > 0
+    db.close()

@@ -271,3 +271,51 @@ def test_oracle_reproduces_reference_fuse_golden(M):
             n, m21 = M.search_by_projection_ff(c["f1"], c["f2"], c["uv"], c["window"], c["ratio"])
             assert n == c["ref_n"] and np.array_equal(m21, c["ref_m"]), c["name"]
     assert kinds == {"fuse": 4, "fuse_sim3": 4, "sim3": 4, "proj_ff": 4}
+
+
+def _kfdb_scene(oracle, RF, tmp_path, seed, nkf=7):
+    """nkf keyframes + one query view of synthetic scenes (two scenes, several shifts) with a 5^4-word vocabulary."""
+    from oracle import bow_oracle as B
+    V = B.synth_vocabulary(k=5, L=4, seed=seed, stop_frac=0.0)
+    vpath = str(tmp_path / "voc.txt")
+    B.save_text(vpath, **V)
+    w = RF.World(vpath, 300, 1.2, 6, 1, 20)
+    cam = RS.CAM_PINHOLE
+    frames = []
+    for k in range(nkf + 1):
+        a, b = RS.images(oracle, seed + (k % 3), shift=(3 * k, 2 * k))
+        f = w.frame(b if k % 2 else a, RS.K_of(cam), cam[4:9], reset_static=(k == 0))
+        frames.append(f)
+    bows = [f.compute_bow()[0] for f in frames]                # Frame::ComputeBoW -> (words, weights)
+    return w, frames, bows
+
+
+def test_keyframe_database_candidate_scoring_equals_compiled_reference(oracle, tmp_path):
+    """N4: the compiled KeyFrameDatabase (add, DetectRelocalisationCandidates :198-308, DetectLoopCandidates :75-196) on
+    real KeyFrames against oracle/bow_oracle.py::kfdb_candidates: shared-word counts, the 0.8 * max cut, float scores;
+    without covisibility links the returned candidates are the keyframes whose score exceeds 0.75 * the best score."""
+    RF = _rf()
+    from oracle import bow_oracle as B
+    w, frames, bows = _kfdb_scene(oracle, RF, tmp_path, 51)
+    kfs, query = frames[:-1], frames[-1]
+    RF.kfdb_add(w, kfs)
+    n, touched, words, score, cand = RF.detect_relocalisation_candidates(w, query, kfs)
+    common, mx, mn, osc = B.kfdb_candidates(bows[-1], bows[:-1])
+    assert np.array_equal(touched.astype(bool), common > 0) and np.array_equal(words[common > 0], common[common > 0])
+    above = common > mn
+    assert above.sum() >= 2 and (~above).sum() >= 1 and mx > 20
+    assert np.array_equal(score[above].view(np.uint32), osc[above].view(np.uint32))          # float bits
+    best = osc[above].max()
+    assert np.array_equal(cand.astype(bool), above & (osc > np.float32(0.75) * best)) and n == int(cand.sum())
+    # loop detection: the query is keyframe 2 (mnId != 0: keyframes start with mnLoopQuery == 0), keyframes 1 and 3 are its
+    # covisibility neighbours (skipped, :95)
+    connected = np.zeros(len(kfs), np.uint8); connected[[1, 3]] = 1
+    connected[2] = 1                                            # the query itself shares every word with itself
+    n, touched, words, score, cand = RF.detect_loop_candidates(w, kfs[2], kfs, connected, 0.0)
+    common, mx, mn, osc = B.kfdb_candidates(bows[2], bows[:-1], exclude=connected)
+    free = connected == 0
+    assert np.array_equal(touched[free].astype(bool), common[free] > 0) and not touched[~free].any()
+    assert np.array_equal(words[free & (common > 0)], common[free & (common > 0)])
+    above = free & (common > mn)
+    assert above.sum() >= 1
+    assert np.array_equal(score[above].view(np.uint32), osc[above].view(np.uint32))
