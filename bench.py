@@ -169,6 +169,7 @@ def main():
     ap.add_argument("--no-matching", action="store_true", help="skip the Hamming-matching legs")
     ap.add_argument("--query-keyframes", type=int, default=8, help="config 5: query keyframes (x1000 descriptors) per step")
     ap.add_argument("--match-pairs", type=int, default=2048, help="config 4: frame pairs per GPU per step")
+    ap.add_argument("--host-wc", action="store_true", help="e2e leg: input frames in WRITE-COMBINED pinned memory (orbx_host_alloc)")
     ap.add_argument("--no-other-configs", action="store_true", help="skip BASELINE configs 1 and 3 (rank 0, N=1 only)")
     ap.add_argument("--all-configs", action="store_true", help=argparse.SUPPRESS)   # kept for old command lines
     args = ap.parse_args()
@@ -198,8 +199,22 @@ def main():
     d_desc = torch.empty((F, NFEAT, 32), dtype=torch.uint8, device=dev)
     d_n = torch.zeros(F, dtype=torch.int32, device=dev)
     # host side of the e2e leg: pinned frames in, pinned results out
-    h_frames = torch.empty((F, H, W), dtype=torch.uint8, pin_memory=True)
-    h_frames.copy_(d_frames)
+    wc_ptr = None
+    if args.host_wc:
+        import ctypes
+        from orb_slam_b200._lib import lib as _orbx_lib
+        wc_ptr = ctypes.c_void_p()
+        assert _orbx_lib().orbx_host_alloc(F * H * W, 1, ctypes.byref(wc_ptr)) == 0
+        h_frames = torch.from_numpy(np.ctypeslib.as_array(ctypes.cast(wc_ptr, ctypes.POINTER(ctypes.c_uint8)), shape=(F, H, W)))
+        stage = torch.empty((min(F, 512), H, W), dtype=torch.uint8, pin_memory=True)
+        for f0 in range(0, F, stage.shape[0]):                        # fill through a pinned bounce buffer (CPU WRITES only)
+            n_ = min(stage.shape[0], F - f0)
+            stage[:n_].copy_(d_frames[f0:f0 + n_])
+            h_frames[f0:f0 + n_] = stage[:n_]
+        del stage
+    else:
+        h_frames = torch.empty((F, H, W), dtype=torch.uint8, pin_memory=True)
+        h_frames.copy_(d_frames)
     h_kps = torch.empty((F, NFEAT, 28), dtype=torch.uint8, pin_memory=True)
     h_desc = torch.empty((F, NFEAT, 32), dtype=torch.uint8, pin_memory=True)
     h_n = torch.zeros(F, dtype=torch.int32, pin_memory=True)
@@ -260,16 +275,40 @@ def main():
     dom = max(prof, key=lambda s: prof[s][0])
     dom_ms, dom_launches = prof[dom]
     dom_gbs = ALGO[dom] * F / (dom_ms * 1e-3) / 1e9
-    traffic = None
+    # per-kernel counters of one ncu --set full capture (profiles/r2_ncu_full_extract.csv -> tools/ncu_counters.py):
+    # executed warp instructions and DRAM bytes per frame do not depend on clocks or co-running kernels, so together with
+    # the LIVE stage times they give the roof these integer kernels actually sit under: the SM's issue rate (4 warp
+    # instructions / clk / SM) and the busiest execution pipe (ALU class: 2 / clk / SM, tools/int_ops_microbench.cu)
+    counters = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+        counters = json.load(open(os.path.join(ROOT, "profiles", "r2_kernel_counters.json")))["stages"]
     except Exception:
         pass
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    clk = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
+    stages = {}
+    for s_ in prof:
+        t = prof[s_][0] * 1e-3
+        e = {"ms": round(prof[s_][0], 3)}
+        if ALGO[s_]:
+            e["hbm_frac"] = round(ALGO[s_] * F / t / 1e9 / peak, 4)
+        c = counters.get(s_)
+        if c and t > 0:
+            e["issue_frac"] = round(c["warp_inst_per_frame"] * F / (sms * 4 * clk * t), 3)
+            e["pipe"] = c["busiest_pipe"]
+            e["pipe_frac"] = round(c["ncu_busiest_pipe_pct"] / 100 * (c["ncu_us_per_frame"] * 1e-6 * F) / t, 3)
+            e["thread_inst_per_algo_byte"] = round(32 * c["warp_inst_per_frame"] / ALGO[s_], 1) if ALGO[s_] else None
+            e["dram_over_algo"] = round(c["dram_bytes_per_frame"] / ALGO[s_], 2) if ALGO[s_] else None
+        stages[s_] = e
+    traffic = int(counters[dom]["dram_bytes_per_frame"] * args.batch) if dom in counters else None
     roofline = {"bound": "hbm", "kernel": dom, "achieved": dom_gbs, "peak": peak, "unit": "GB/s",
                 "frac": dom_gbs / peak, "traffic": traffic, "peak_source": peak_src,
                 "avg_launch_ms": dom_ms / max(dom_launches, 1), "launches_per_pass": dom_launches,
                 "algorithmic_bytes_per_frame": ALGO[dom],
-                "stage_ms_per_pass": {s: round(prof[s][0], 3) for s in prof},
+                "note": "frac is the contractual HBM fraction of the dominant kernel; the kernels are integer-issue bound "
+                        "(stages[*].issue_frac = executed warp instructions / (SMs x 4 x clk x time), pipe_frac = busiest "
+                        "execution pipe), traffic = DRAM bytes of one launch from ncu (profiles/r2_ncu_full_extract.csv)",
+                "stage_ms_per_pass": {s: round(prof[s][0], 3) for s in prof}, "stages": stages,
                 "whole_pipeline_frac": ALGO_FRAME * F / (ms_step * 1e-3) / 1e9 / peak}
 
     # ---- end-to-end leg (host pinned -> H2D -> kernels -> D2H) ----------------------------------------------------
@@ -283,6 +322,30 @@ def main():
     e2e_ms = maxr((time.perf_counter() - te) * 1e3 / args.steps)
     barrier()
     assert int(h_n.sum().item()) == int(d_n.sum().item()), "e2e and device-resident legs disagree"
+    # ---- what the host <-> device fabric gives when the copies ARE the step: the same bytes, plain cudaMemcpyAsync, all
+    # ranks at once, both directions in flight (the ceiling of the e2e leg; on a multi-GPU VM it is shared by the ranks)
+    fabric = None
+    if not args.host_wc:
+        s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        d_out = torch.empty(F * (NFEAT * 60 + 4), dtype=torch.uint8, device=dev)
+        h_out = torch.empty(F * (NFEAT * 60 + 4), dtype=torch.uint8, pin_memory=True)
+
+        def copies():
+            with torch.cuda.stream(s_in):
+                d_frames.copy_(h_frames, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                h_out.copy_(d_out, non_blocking=True)
+        copies()
+        barrier()
+        tf = time.perf_counter()
+        for _ in range(3):
+            copies()
+        torch.cuda.synchronize()
+        fab_ms = maxr((time.perf_counter() - tf) * 1e3 / 3)
+        barrier()
+        fabric = {"h2d_gbs": world * F * H * W / fab_ms / 1e6, "d2h_gbs": world * F * (NFEAT * 60 + 4) / fab_ms / 1e6,
+                  "ms_per_step": fab_ms, "frames_s_if_copies_were_the_step": world * F / (fab_ms * 1e-3)}
+        del d_out, h_out
 
     # ---- strong-scaling leg: config 2 as BASELINE.json words it - ONE 10,000-frame sequence split 10,000/G per rank ----
     strong = None
@@ -371,12 +434,18 @@ def main():
                        "keypoints_per_frame": kp_mean},
             "e2e": {"value": total / (e2e_ms * 1e-3), "unit": "frames/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": F * H * W, "d2h_bytes_per_step": F * (NFEAT * 60 + 4),
-                    "api": "orbx_extract_batch (C ABI, pinned host buffers), wall clock between device syncs"},
+                    "api": "orbx_extract_batch (C ABI, pinned host buffers), wall clock between device syncs",
+                    "host_memory": "write-combined pinned (orbx_host_alloc)" if args.host_wc else "pinned",
+                    "host_fabric": fabric,
+                    "frac_of_host_fabric": (fab_ms / e2e_ms) if fabric else None},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
             "strong_scaling": strong, "matching": matching, "other_configs": other})
         # compact digest, printed LAST so that it survives a truncated stdout tail: every number BASELINE.md quotes
         sm = {"device_fps": round(line["value"]), "e2e_fps": round(line["e2e"]["value"]), "n_gpus": world,
-              "stage_ms": roofline["stage_ms_per_pass"], "roofline_frac": round(roofline["frac"], 4)}
+              "stage_ms": roofline["stage_ms_per_pass"], "roofline_frac": round(roofline["frac"], 4),
+              "e2e_frac_of_host_fabric": round(line["e2e"]["frac_of_host_fabric"], 3) if line["e2e"]["frac_of_host_fabric"] else None,
+              "issue_frac": {s_: v.get("issue_frac") for s_, v in roofline["stages"].items()},
+              "pipe_frac": {s_: v.get("pipe_frac") for s_, v in roofline["stages"].items()}}
         if strong:
             sm.update({"strong_scaling_fps": round(strong["value"]), "strong_scaling_e2e_fps": round(strong["e2e_value"])})
         if matching:

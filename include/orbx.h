@@ -96,6 +96,13 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int nframes
 /* Waits for the handle's streams and reports deferred device-side errors (list overflow). */
 int orbx_synchronize(orbx_handle* h);
 
+/* Pinned (page-locked) host memory for the buffers handed to orbx_extract_batch, for hosts that do not link a CUDA
+ * runtime of their own: copies from / to pinned memory are asynchronous and run at the link's speed.  write_combined != 0
+ * asks for write-combined pages (fast for the DMA engine to read, very slow for the CPU to read back: input frames only).
+ * No counterpart in the reference. */
+int orbx_host_alloc(size_t bytes, int write_combined, void** out);
+void orbx_host_free(void* p);
+
 /* ---- measurement hooks (bench.py) ---------------------------------------------------------------------------- */
 enum { ORBX_STAGE_PYRAMID = 0, ORBX_STAGE_FAST, ORBX_STAGE_SELECT, ORBX_STAGE_BLUR, ORBX_STAGE_DESCRIBE,
        ORBX_STAGE_COUNT };

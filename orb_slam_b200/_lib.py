@@ -55,6 +55,9 @@ def lib():
     L.orbx_debug_cell_candidates.argtypes = [vp, C.c_int, C.c_int, C.c_int, i32p, i32p, f32p, C.c_int, i32p]
     L.orbx_debug_level_cells.argtypes = [vp, C.c_int, C.c_int, i32p, i32p]
     L.orbx_debug_retain_best.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]
+    L.orbx_host_alloc.argtypes = [C.c_size_t, C.c_int, C.POINTER(vp)]
+    L.orbx_host_free.argtypes = [vp]
+    L.orbx_host_free.restype = None
     L.orbx_synth_frames_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_uint64, vp]
     _lib = L
     return L

@@ -579,6 +579,15 @@ extern "C" int orbx_extract(orbx_handle* h, const uint8_t* img, int w, int hgt, 
   return orbx_extract_batch(h, img, 1, w, hgt, stride, stride * (size_t)(hgt > 0 ? hgt : 0), kps, desc, n_out);
 }
 
+extern "C" int orbx_host_alloc(size_t bytes, int write_combined, void** out) {
+  if (!out || !bytes) return ORBX_ERR_ARG;
+  *out = nullptr;
+  const cudaError_t e = cudaHostAlloc(out, bytes, write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault);
+  if (e != cudaSuccess) { g_create_err = std::string("cudaHostAlloc: ") + cudaGetErrorString(e); return ORBX_ERR_CUDA; }
+  return ORBX_OK;
+}
+extern "C" void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 extern "C" int orbx_profile_enable(orbx_handle* h, int on) {
   if (!h) return ORBX_ERR_ARG;
   h->profiling = on != 0;
