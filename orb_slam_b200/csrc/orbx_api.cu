@@ -50,7 +50,7 @@ struct orbx_handle {
   } lane[kLanes];
   int plan_version = 0;
   int fast_mode = 0;                // 0 TMA kernel when the buffers allow it, 1 legacy kernel only (ORBX_FAST=legacy)
-  int resize_mode = 0;              // the same for the pyramid kernels (ORBX_RESIZE=legacy)
+  int resize_mode = 0;              // pyramid kernels: 0 TMA for chunks of > 16 frames, 1 legacy only, 2 TMA always (ORBX_RESIZE)
   int nlanes = kDefaultLanes;
   int select_mode = 0;              // 0 by chunk size, 1 global, 2 shared memory (ORBX_SELECT)
   int pdl_mode = 1;                 // 0 never, 1 chunks of <= kPdlMaxFrames frames, 2 always (ORBX_PDL)
@@ -293,7 +293,7 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
     if (const char* e = getenv("ORBX_PDL")) h->pdl_mode = std::min(2, std::max(0, atoi(e)));
     if (const char* e = getenv("ORBX_SELECT")) h->select_mode = e[0] == 'g' ? 1 : (e[0] == 's' ? 2 : 0);
     if (const char* e = getenv("ORBX_FAST")) h->fast_mode = e[0] == 'l' ? 1 : 0;
-    if (const char* e = getenv("ORBX_RESIZE")) h->resize_mode = e[0] == 'l' ? 1 : 0;
+    if (const char* e = getenv("ORBX_RESIZE")) h->resize_mode = e[0] == 'l' ? 1 : (e[0] == 't' ? 2 : 0);
     if (const char* e = getenv("ORBX_LANES")) h->nlanes = std::min(kLanes, std::max(1, atoi(e)));
     for (int li = 0; li < h->nlanes; li++) {
       orbx_handle::Lane& ln = h->lane[li];
@@ -398,8 +398,11 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   set_launch_pdl(h->pdl_mode == 2 || (h->pdl_mode == 1 && n <= kPdlMaxFrames));
   int st = 0;
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
+  // a chunk of a few frames is a chain of 7 latency-bound launches: there the register kernel, which starts computing
+  // with its first loads, beats waiting for a tensor copy per CTA (28 vs 42 us for one frame); ORBX_RESIZE=tma forces it
+  const bool resize_tma = h->resize_mode == 2 || n > kPdlMaxFrames;
   for (int l = 1; l < dp.nlevels; l++) {
-    if (ln.rtma_ok[l]) launch_resize_level_tma(b, dp, ln.rtma, l, n, s);
+    if (resize_tma && ln.rtma_ok[l]) launch_resize_level_tma(b, dp, ln.rtma, l, n, s);
     else launch_resize_level(b, dp, l, n, s);
   }
   if (prof) cudaEventRecord(h->ev_stage[st++], s);

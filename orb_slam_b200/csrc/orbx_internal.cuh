@@ -62,8 +62,8 @@ struct alignas(16) CellPlan {   // 16-byte aligned: a kernel reads its record wi
   int16_t wpr;           // bitmap words per shifted row = (rwt + 31) / 32
   int16_t nbw;           // bitmap words = wpr * rh
   int32_t ngrp;          // reject groups = g16 * rh
-  int32_t nz16;          // uint4 stores that clear score map + bitmaps A, B
-  int32_t off_sc, off_bm, off_q;   // shared-memory byte offsets (raw image at 0): score map, bitmaps A + B, lists
+  int32_t nz16;          // uint4 stores that clear the score map
+  int32_t off_sc, off_bm, off_q;   // shared-memory byte offsets: score map (0: it overlays the raw image), bitmaps A + B, lists
   uint32_t m_g16;        // fast_magic(g16)
   uint32_t m_wprt;       // fast_magic(wpr)
 };
@@ -124,7 +124,7 @@ inline __host__ __device__ int fast_cell_smem(int cw, int ch) {
 // fast_cells_tma_kernel: box width for a level whose widest scored region is rw (scored pixel x at byte 8 + x; the last
 // 8-pixel reject group reads 4 bytes beyond its 8), multiple of 16 as the tensor map wants
 inline __host__ __device__ int fast_tma_box_w(int rwt) { return 16 * ((rwt + 15) >> 4) + 32; }   // rwt = lead + rw; position xs at byte 16 + xs
-constexpr int kFastTmaListBytes = (1024 + 1024) * 4;   // kFastQ1 + kFastQ2 entries
+constexpr int kFastTmaListBytes = (1024 + 512) * 4;   // kFastQ1 + kFastQ2 entries
 // floor(i / d) == umulhi(i, fast_magic(d)) for i * d < 2^32; d == 1 gives 0, which magic_div() reads as "i itself"
 inline uint32_t fast_magic(uint32_t d) { return 0xffffffffu / d + 1u; }
 

@@ -13,6 +13,9 @@
 //             atomicAdd per thread that has any (sparse), then consumed thread = entry by full warps; the per-warp
 //             bit queues with their prefix scans over every bitmap word are gone.  A list that overflows (noise
 //             images) switches that phase to a dense walk over the cell - slower, same result.
+//   score map lives in the bytes of the image, which is dead once the (few) pixels above the threshold are known: they
+//             are kept as a list with their scores, scattered into the cleared map, and suppressed against it.  One
+//             14 KB array per cell instead of image + score map: nine CTAs per SM instead of six (+13 % on its own).
 //   emission  one warp: each lane owns a contiguous run of bitmap words, one shuffle scan gives its output offset.
 // ------------------------------------------------------------------------------------------------------------------
 // 128 threads: with one 35 KB copy of the cell per CTA six CTAs share an SM, and the sparse phases (few entries per
@@ -21,7 +24,7 @@
 #define ORBX_FAST_TMA_THREADS 128
 #endif
 constexpr int kFastTmaThreads = ORBX_FAST_TMA_THREADS;
-constexpr int kFastQ1 = 1024, kFastQ2 = 1024;   // list capacities (entries): flagged pairs / pixels with S >= tmin
+constexpr int kFastQ1 = 1024, kFastQ2 = 512;   // list capacities (entries): flagged pairs / pixels with S >= tmin
 
 __device__ __forceinline__ uint32_t ft_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -92,12 +95,14 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
   const int lead = c.lead, rw = c.rwt, rh = c.rh;
   const int scp = c.scp, wpr = c.wpr, nbw = c.nbw;
   uint8_t* s_raw = smem_tma;                                     // [box_h][rp] raw bytes
-  uint8_t* s_sc = s_raw + c.off_sc;                              // [rh + 2][scp] score map, position xs at byte 4 + xs
+  uint8_t* s_sc = s_raw;                                         // [rh + 2][scp] score map, position xs at byte 4 + xs:
+                                                                 // takes the image's place once the scores are known
   uint32_t* s_bmA = reinterpret_cast<uint32_t*>(s_raw + c.off_bm);   // survivors with S >= fastTh
   uint32_t* s_bmB = s_bmA + nbw;                                     // survivors with S >= 7
   uint32_t* s_q1 = reinterpret_cast<uint32_t*>(s_raw + c.off_q);     // flagged pairs  (y << 16 | xs)
   uint32_t* s_q2 = s_q1 + kFastQ1;                                   // pixels with S >= tmin
-  uint32_t* s_flag = s_q2;   // [rh][g16] reject result per 16-pixel group; dead before list 2 is written (same bytes)
+  uint8_t* s_flag = reinterpret_cast<uint8_t*>(s_q2);   // [rh][g16] one byte of pair flags per 16-pixel group (rounded up to
+                                                        // a word); dead before list 2 is written (same bytes)
   const uint32_t bar = ft_smem_u32(&s_bar);
 
   // ---- 0  one thread asks the TMA engine for the sub-image; everybody else clears the score map and bitmaps ------------
@@ -105,15 +110,16 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)c.off_sc) : "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)c.off_bm) : "memory");
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
         ::"r"(ft_smem_u32(s_raw)), "l"(reinterpret_cast<uint64_t>(&tm.map[level])), "r"((int)c.x0 - 16 - lead),
           "r"((int)c.y0 - 3), "r"(frame), "r"(bar)
         : "memory");
   }
-  const int nz = c.nz16;                                         // score map + bitmaps A, B (contiguous)
-  for (int i = tid; i < nz; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+  const int nz = c.nz16;                                         // uint4 stores that clear the score map
+  const int nzb0 = (8 * nbw + 15) >> 4;                          // ... and bitmaps A + B
+  for (int i = tid; i < nzb0; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_bmA)[i] = make_uint4(0, 0, 0, 0);
   if (tid < 4) s_cnt[tid] = 0;
   __syncthreads();                                               // barrier initialised before anybody polls it
   {
@@ -131,7 +137,7 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
   const int tB = kRetryTh;
   // searched at fastTh first, again at 7 only when <= 3 corners survive (:599-614); fastTh <= 7: one pass serves both
   int tmin = max(tA > tB ? tA : min(tA, tB), 1);
-  bool useA;
+  bool useA, dense = false;
   for (;;) {
     // ---- 1a  reject, 16 pixels per thread on the raw bytes, branch-free: one flag word per group ------------------------
     // An arc of 9 ring pixels holds one pixel of every opposite pair, so a corner at threshold t needs
@@ -139,6 +145,7 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
     // The four result words (bit 7 of byte k = pixel 4j + k of word j) are folded into one: bit 8k + j = pixel 4j + k.
     {
       const int G16 = c.g16, ng = c.ngrp;
+      if (tid < 3 && ng + tid < ((ng + 3) & ~3)) s_flag[ng + tid] = 0;      // the tail of the last flag word
       const uint32_t bias4 = (0x7fu - (uint32_t)tmin) * 0x01010101u;
       const int sy = magic_div(kFastTmaThreads, c.m_g16), sg = kFastTmaThreads - sy * G16;
       int y = magic_div(tid, c.m_g16), g = tid - y * G16;
@@ -162,53 +169,48 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
         ORBX_REJ(U.w, D.w, __byte_perm(C.z, C.w, 0x4321), __byte_perm(C.w, W5, 0x6543), C.w, m3)
 #undef ORBX_REJ
 #undef ORBX_GT
-        s_flag[i] = (m0 >> 7) | (m1 >> 6) | (m2 >> 5) | (m3 >> 4);
+        const uint32_t t = (m0 >> 7) | (m1 >> 6) | (m2 >> 5) | (m3 >> 4);
+        const uint32_t pr = (t | (t >> 8)) & 0x000f000fu;       // bit j: pair at 4j (pixels 4j, 4j+1); bit 16+j: pair at 4j+2
+        s_flag[i] = (uint8_t)(pr | (pr >> 12));                 // bit j / bit 4+j
         y += sy; g += sg;
         if (g >= G16) { g -= G16; y++; }
       }
     }
     __syncthreads();
-    // ---- 1b  flag words -> list 1 of pixel PAIRS (xs even) with either pixel flagged and inside the scored region ------
+    // ---- 1b  flag bytes -> list 1 of pixel PAIRS (xs even) with either pixel flagged; a thread takes four groups ---------
+    // (pairs outside [lead, rw) - padding / the neighbour cell - are dropped by the scorer: cheaper than masking here)
     {
-      const int G16 = c.g16, ng = c.ngrp;
-      for (int i = tid; i < ng; i += kFastTmaThreads) {
-        const uint32_t t = s_flag[i];
-        uint32_t pr = (t | (t >> 8)) & 0x000f000fu;             // bit j: pair at 4j (pixels 4j, 4j+1); bit 16+j: pair at 4j+2
+      const int G16 = c.g16, nw = (c.ngrp + 3) >> 2;
+      const uint32_t* fw = reinterpret_cast<const uint32_t*>(s_flag);
+      for (int i = tid; i < nw; i += kFastTmaThreads) {
+        uint32_t pr = fw[i];
         if (pr) {
-          const int y = magic_div(i, c.m_g16), x0g = 16 * (i - y * G16);
-          // (pairs outside [lead, rw) - padding / the neighbour cell - are dropped by the scorer: cheaper than masking here)
-          if (pr) {
-            int off = atomicAdd(&s_cnt[2], __popc(pr));
-            const uint32_t base = ((uint32_t)y << 16) | (uint32_t)x0g;
-            while (pr) {
-              const int bit = 31 - __clz(pr);
-              pr ^= 1u << bit;
-              if (off < kFastQ1) s_q1[off] = base + (uint32_t)(4 * (bit & 15) + ((bit >> 4) << 1));
-              off++;
-            }
+          int off = atomicAdd(&s_cnt[2], __popc(pr));
+          while (pr) {
+            const int bit = 31 - __clz(pr);
+            pr ^= 1u << bit;
+            const int gi = 4 * i + (bit >> 3), y = magic_div(gi, c.m_g16), g = gi - y * G16, bb = bit & 7;
+            if (off < kFastQ1) s_q1[off] = ((uint32_t)y << 16) | (uint32_t)(16 * g + 4 * (bb & 3) + 2 * (bb >> 2));
+            off++;
           }
         }
       }
     }
     __syncthreads();
 
-    // ---- 2  full score of the flagged pairs; pixels with S >= tmin go to list 2 ------------------------------------------
+    // ---- 2  full score of the flagged pairs; pixels with S >= tmin go to list 2 as (y << 16 | xs << 8 | S) -------------------
+    // Only those pixels matter to the NMS, as centres AND as neighbours: a neighbour below tmin cannot suppress anybody.
     {
       auto heavy = [&](int x, int y) {
         if (x + 1 < lead || x >= rw) return;                    // a pair of the padding / the neighbour cell
         const uint32_t s2 = fast_pair_score_u8(s_raw, rp, x, y);
-        uint32_t two = __byte_perm(s2, 0, 0x4420);               // (S(x), S(x+1)) as two bytes
-        if (x + 1 >= rw) two &= 0xff;
-        if (x < lead) two &= 0xff00;
-        if (two) {
-          *reinterpret_cast<uint16_t*>(s_sc + (y + 1) * scp + 4 + x) = (uint16_t)two;
-          const bool m0 = (int)(two & 0xff) >= tmin, m1 = (int)(two >> 8) >= tmin;
-          if (m0 | m1) {
-            int off = atomicAdd(&s_cnt[3], (int)m0 + (int)m1);
-            const uint32_t e = ((uint32_t)y << 16) | (uint32_t)x;
-            if (m0) { if (off < kFastQ2) s_q2[off] = e; off++; }
-            if (m1) { if (off < kFastQ2) s_q2[off] = e + 1; }
-          }
+        const int s0 = x >= lead ? (int)(s2 & 0xffff) : 0, s1 = x + 1 < rw ? (int)(s2 >> 16) : 0;
+        const bool m0 = s0 >= tmin, m1 = s1 >= tmin;
+        if (m0 | m1) {
+          int off = atomicAdd(&s_cnt[3], (int)m0 + (int)m1);
+          const uint32_t e = ((uint32_t)y << 16) | ((uint32_t)x << 8);
+          if (m0) { if (off < kFastQ2) s_q2[off] = e | (uint32_t)s0; off++; }
+          if (m1) { if (off < kFastQ2) s_q2[off] = (e + 0x100u) | (uint32_t)s1; }
         }
       };
       const int n1 = s_cnt[2];
@@ -223,26 +225,65 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
 
     // ---- 3  strict 3x3 NMS of the pixels with S >= tmin ---------------------------------------------------------------------
     int nA = 0, nB = 0;
-    {
-      auto nms = [&](int x, int y) {
+    const int n2 = s_cnt[3];
+    dense = n2 > kFastQ2;
+    if (!dense) {
+      // The raw image is dead now: the score map takes its place (cleared, then list 2 scattered into it).  Not keeping a
+      // second 11 KB array alive beside the image is what lets nine CTAs share an SM instead of six.
+      for (int i = tid; i < nz; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+      __syncthreads();
+      for (int i = tid; i < n2; i += kFastTmaThreads) {
+        const uint32_t e = s_q2[i];
+        s_sc[((e >> 16) + 1) * scp + 4 + ((e >> 8) & 0xff)] = (uint8_t)e;
+      }
+      __syncthreads();
+      for (int i = tid; i < n2; i += kFastTmaThreads) {
+        const uint32_t e = s_q2[i];
+        const int x = (e >> 8) & 0xff, y = e >> 16, sc = e & 0xff;
         const uint8_t* p = s_sc + (y + 1) * scp + 4 + x;
-        const int s = p[0];
         const int m = max(max(max(p[-1], p[1]), max(p[-scp - 1], p[-scp])),
                           max(max(p[-scp + 1], p[scp - 1]), max(p[scp], p[scp + 1])));
-        if (s > m) {
+        if (sc > m) {
           const int w = y * wpr + (x >> 5);
-          if (s >= tA) { atomicOr(&s_bmA[w], 1u << (x & 31)); nA++; }
-          if (s >= tB) { atomicOr(&s_bmB[w], 1u << (x & 31)); nB++; }
+          if (sc >= tA) { atomicOr(&s_bmA[w], 1u << (x & 31)); nA++; }
+          if (sc >= tB) { atomicOr(&s_bmB[w], 1u << (x & 31)); nB++; }
         }
-      };
-      const int n2 = s_cnt[3];
-      if (n2 <= kFastQ2) {
-        for (int i = tid; i < n2; i += kFastTmaThreads) { const uint32_t e = s_q2[i]; nms((int)(e & 0xffff), (int)(e >> 16)); }
-      } else {                                                   // list 2 overflowed: every pixel of the score map
-        for (int i = tid; i < rw * rh; i += kFastTmaThreads) {        // (columns < lead hold zeros)
-          const int y = i / rw, x = i - y * rw;
-          if ((int)s_sc[(y + 1) * scp + 4 + x] >= tmin) nms(x, y);
+      }
+    } else {
+      // List 2 overflowed (noise-like cells): dense walk in bands of rows whose score map fits the bytes of the two lists;
+      // the raw image stays intact (every score is recomputed from it, the band's halo rows included).  Slow, rare, exact.
+      uint8_t* s_band = reinterpret_cast<uint8_t*>(s_q1);
+      const int brows = (kFastQ1 + kFastQ2) * 4 / scp - 2;       // rows per band (the map has one halo row on either side)
+      const int hp = (rw + 1) >> 1;
+      for (int y0 = 0; y0 < rh; y0 += brows) {
+        const int y1 = min(y0 + brows, rh);                     // band rows [y0, y1), map rows y0 - 1 .. y1
+        const int nzb = ((y1 - y0 + 2) * scp + 15) >> 4;
+        for (int i = tid; i < nzb; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_band)[i] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+        const int ya = max(y0 - 1, 0), yb = min(y1 + 1, rh);
+        for (int i = tid; i < hp * (yb - ya); i += kFastTmaThreads) {
+          const int yy = i / hp, x = 2 * (i - yy * hp), y = ya + yy;
+          const uint32_t s2 = fast_pair_score_u8(s_raw, rp, x, y);
+          uint32_t two = __byte_perm(s2, 0, 0x4420);
+          if (x + 1 >= rw) two &= 0xff;
+          if (x < lead) two &= x + 1 < lead ? 0u : 0xff00u;
+          *reinterpret_cast<uint16_t*>(s_band + (y - y0 + 1) * scp + 4 + x) = (uint16_t)two;
         }
+        __syncthreads();
+        for (int i = tid; i < rw * (y1 - y0); i += kFastTmaThreads) {
+          const int yy = i / rw, x = i - yy * rw, y = y0 + yy;
+          const uint8_t* p = s_band + (yy + 1) * scp + 4 + x;
+          const int sc = p[0];
+          if (sc < tmin) continue;
+          const int m = max(max(max(p[-1], p[1]), max(p[-scp - 1], p[-scp])),
+                            max(max(p[-scp + 1], p[scp - 1]), max(p[scp], p[scp + 1])));
+          if (sc > m) {
+            const int w = y * wpr + (x >> 5);
+            if (sc >= tA) { atomicOr(&s_bmA[w], 1u << (x & 31)); nA++; }
+            if (sc >= tB) { atomicOr(&s_bmB[w], 1u << (x & 31)); nB++; }
+          }
+        }
+        __syncthreads();
       }
     }
     nA = __reduce_add_sync(0xffffffffu, nA);
@@ -251,11 +292,32 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
     __syncthreads();
     useA = s_cnt[0] > 3;                          // :609-614
     if (useA || tmin <= tB) break;
-    // retry at 7: forget this pass's scores, bitmaps and lists
-    __syncthreads();                              // everyone has read s_cnt
-    for (int i = tid; i < nz; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+    // retry at 7: forget this pass's bitmaps and lists; the score map may have overwritten the image: fetch it again
+    __syncthreads();                              // everyone has read s_cnt and is done with the score map
+    for (int i = tid; i < nzb0; i += kFastTmaThreads) reinterpret_cast<uint4*>(s_bmA)[i] = make_uint4(0, 0, 0, 0);
     if (tid < 4) s_cnt[tid] = 0;
     tmin = tB;
+    if (!dense) {
+      if (tid == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic writes (score map) before the async copy
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)c.off_bm) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"(ft_smem_u32(s_raw)), "l"(reinterpret_cast<uint64_t>(&tm.map[level])), "r"((int)c.x0 - 16 - lead),
+              "r"((int)c.y0 - 3), "r"(frame), "r"(bar)
+            : "memory");
+      }
+      uint32_t ok = 0;
+#pragma unroll 1
+      for (int spin = 0; spin < (1 << 22) && !ok; ++spin)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 1;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(bar) : "memory");
+      if (!ok) {
+        if (tid == 0) { atomicExch(b.err_flag, 3); *n_total = 0; }
+        return;
+      }
+    }
     __syncthreads();
   }
   const int total = useA ? s_cnt[0] : s_cnt[1];
@@ -298,7 +360,12 @@ fast_cells_tma_kernel(ChunkBuffers b, FastLevels fl, const __grid_constant__ Fas
                      ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
                      : harris_response_edge(img, pitch, lx, ly, LP.w, LP.h);
       } else {
-        r.resp = (float)s_sc[(y + 1) * scp + 4 + lead + x];
+        if (!dense) r.resp = (float)s_sc[(y + 1) * scp + 4 + lead + x];
+        else {                                  // the dense walk keeps no score map: recompute from the intact image
+          const int xs = lead + x;
+          const uint32_t s2 = fast_pair_score_u8(s_raw, rp, xs & ~1, y);
+          r.resp = (float)((xs & 1) ? (s2 >> 16) : (s2 & 0xffff));
+        }
       }
       r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
       *out++ = r;
@@ -315,5 +382,6 @@ void launch_fast_cells_tma(const ChunkBuffers& b, const DevicePlan& hp, const Fa
   fl.cand_per_frame = hp.cand_per_frame; fl.frame_bytes = hp.pyr_frame_bytes;
   for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
   dim3 grid(hp.total_cells, nframes);
-  launch_k(kern, grid, dim3(kFastTmaThreads), (size_t)tm.smem_bytes, s, b, fl, tm);
+  static const int pad = [] { const char* e = getenv("ORBX_FAST_SMEM_PAD"); return e ? atoi(e) : 0; }();   // occupancy experiments
+  launch_k(kern, grid, dim3(kFastTmaThreads), (size_t)(tm.smem_bytes + pad), s, b, fl, tm);
 }

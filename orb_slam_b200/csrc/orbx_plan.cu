@@ -232,10 +232,12 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
         CellPlan& c = hp.cells[k];
         if (c.rw <= 0) continue;
         const int sc = fast_sc_bytes(c.rwt, c.rh);
-        c.off_sc = bw * bh; c.off_bm = c.off_sc + sc;
+        if (sc > bw * bh) hp.fast_tma_ok = false;                // the score map takes the image's place
+        c.off_sc = 0; c.off_bm = bw * bh;
         c.off_q = (c.off_bm + 8 * c.nbw + 15) & ~15;
-        c.nz16 = (sc + 8 * c.nbw + 15) / 16;
-        if (4 * c.ngrp > 4 * 1024) hp.fast_tma_ok = false;        // the flag words share list 2's bytes (kFastQ2 entries)
+        c.nz16 = (sc + 15) / 16;
+        if (c.ngrp + 4 > 4 * 512) hp.fast_tma_ok = false;         // the flag bytes share list 2's bytes (kFastQ2 entries)
+        if ((1024 + 512) * 4 / c.scp < 3) hp.fast_tma_ok = false; // the dense walk needs a band of at least one row
         hp.fast_tma_smem_bytes = std::max(hp.fast_tma_smem_bytes, c.off_q + kFastTmaListBytes);
       }
     }
