@@ -299,7 +299,10 @@ extern "C" int orbx_create(const orbx_params* pp, orbx_handle** out) {
       orbx_handle::Lane& ln = h->lane[li];
       CK(cudaMalloc(&ln.d_pyr, B * h->cap_pyr));
       CK(cudaMalloc(&ln.d_blur, B * h->cap_pyr));
-      CK(cudaMalloc(&ln.d_cand, B * h->cap_cand * sizeof(Cand)));
+      // 4 pad records in front (cap_cand already leaves slack behind): the batched partition scans of select_kernel may
+      // read up to 3 records beyond either end of a cell's list
+      CK(cudaMalloc(&ln.d_cand, (B * h->cap_cand + 8) * sizeof(Cand)));
+      CK(cudaMemset(ln.d_cand, 0, (B * h->cap_cand + 8) * sizeof(Cand)));
       CK(cudaMalloc(&ln.d_list, B * h->cap_list * sizeof(Cand)));
       CK(cudaMalloc(&ln.d_kp, B * pp->nfeatures * sizeof(Cand)));
       CK(cudaMalloc(&ln.d_n_total, B * h->cap_cells_frame * sizeof(int32_t)));
@@ -385,7 +388,7 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   orbx_handle::Lane& ln = h->lane[li];
   ChunkBuffers b{};
   b.lv0 = d_imgs; b.lv0_frame_stride = (int64_t)frame_stride; b.lv0_pitch = (int)stride;
-  b.pyr = ln.d_pyr; b.blur = ln.d_blur; b.cand = ln.d_cand; b.n_total = ln.d_n_total; b.n_retain = ln.d_n_retain;
+  b.pyr = ln.d_pyr; b.blur = ln.d_blur; b.cand = ln.d_cand + 4; b.n_total = ln.d_n_total; b.n_retain = ln.d_n_retain;
   b.list = ln.d_list; b.kp = ln.d_kp; b.kp_count = ln.d_kp_count; b.err_flag = h->d_err;
   b.plan = h->d_plan; b.cells = h->d_cells; b.rx = h->d_rx; b.ry = h->d_ry;
   // this scratch set was last used on another stream (a caller's, or the lane's own): order behind that chunk

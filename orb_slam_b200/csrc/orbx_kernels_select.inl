@@ -149,8 +149,13 @@ __device__ __forceinline__ void retain_best_port(Cand* v, int size, int n, int r
 //   lanes    publish the level's keypoints into the frame's slots [kp_base, kp_base + count)
 // Serial sections are a few hundred steps; thousands of (level, frame) warps run concurrently.
 // ------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_total) {
+// kSmemList: the LEVEL list (survivors of the cells, <= list_cap records) lives in shared memory, `stride` records per
+// warp.  The level cap is one lane's chain of several hundred dependent steps (nth_element over ~240 records): ~30
+// cycles per step from shared memory instead of an L2 round trip, and it is the longest chain of the kernel.
+template <bool kSmemList>
+__global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_total, int stride) {
   ORBX_PDL_ENTRY();
+  extern __shared__ __align__(16) uint8_t sel_list_smem[];
   const DevicePlan* P = b.plan;
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (gw >= nwarps_total) return;
@@ -160,7 +165,8 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
   const int32_t* nTotal = b.n_total + (int64_t)frame * P->total_cells + L.cell_base;
   int32_t* nToRetain = b.n_retain + (int64_t)frame * P->total_cells + L.cell_base;
   Cand* cand = b.cand + (int64_t)frame * P->cand_per_frame;
-  Cand* list = b.list + (int64_t)frame * P->list_per_frame + L.list_base;
+  Cand* list = kSmemList ? reinterpret_cast<Cand*>(sel_list_smem) + (threadIdx.x >> 5) * stride + 4   // 4 pad records either side
+                         : b.list + (int64_t)frame * P->list_per_frame + L.list_base;
 
   if (lane == 0) {
     // bNoMore is kept in the sign bit of nToRetain while the loop runs (-(v)-1 encodes "no more")
@@ -190,7 +196,9 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
   __syncwarp();
   for (int c = lane; c < nCells; c += 32) {
     const CellPlan& cp = b.cells[L.cell_base + c];
-    retain_best_port(cand + cp.cand_off, nTotal[c], nToRetain[c], P->retain_mode);
+    // batched scans (four independent loads per trip): the over-read of <= 3 records lands in the neighbouring cell's
+    // block or in the pad records around the array; whatever it reads is ignored
+    retain_best_port<true>(cand + cp.cand_off, nTotal[c], nToRetain[c], P->retain_mode);
   }
   __syncwarp();
   // exclusive prefix of nToRetain over the cells (warp scan in chunks of 32)
@@ -218,7 +226,7 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
   __syncwarp();
   int count = run;
   if (run > L.nDesired) {
-    if (lane == 0) retain_best_port(list, run, L.nDesired, P->retain_mode);
+    if (lane == 0) retain_best_port<kSmemList>(list, run, L.nDesired, P->retain_mode);   // (padded: batched scans allowed)
     count = L.nDesired;
   }
   __syncwarp();
@@ -375,7 +383,14 @@ void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cud
     launch_k(select_smem_kernel, dim3(nwarps), dim3(32 * warps), (size_t)smem, s, b, nwarps, max_list, max_cells);
     return;
   }
-  launch_k(select_kernel, dim3((nwarps * 32 + 127) / 128), dim3(128), 0, s, b, nwarps);
+  const int stride = max_list + 8;                               // 4 pad records on either side
+  const size_t list_smem = (size_t)4 * stride * sizeof(Cand);
+  if (list_smem <= 96 * 1024) {
+    cudaFuncSetAttribute(select_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)list_smem);
+    launch_k(select_kernel<true>, dim3((nwarps * 32 + 127) / 128), dim3(128), list_smem, s, b, nwarps, stride);
+  } else {
+    launch_k(select_kernel<false>, dim3((nwarps * 32 + 127) / 128), dim3(128), 0, s, b, nwarps, 0);
+  }
 }
 
 // Unit-test hook (orbx_debug_retain_best): retain_best_port on caller-made lists, one thread per list.  Lists lie back
