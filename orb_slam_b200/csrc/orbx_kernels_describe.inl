@@ -372,6 +372,7 @@ void launch_describe(const ChunkBuffers& b, const DevicePlan& hp, int nframes, o
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, describe_kernel, 32 * kDescWarps, 0);
+    if (const char* e = getenv("ORBX_DESC_CTAS_PER_SM")) per_sm = std::max(1, std::min(per_sm, atoi(e)));   // co-residency experiments
     max_ctas = sms * (per_sm > 0 ? per_sm : 1);
   }
   const int ctas = (nslots + kDescWarps - 1) / kDescWarps;
