@@ -37,6 +37,8 @@ struct orbx_handle {
     bool used = false;
     // tensor maps of the TMA-staged FAST kernel: levels >= 1 point into d_pyr (valid for one plan), level 0 into the
     // caller's frames (re-encoded when pointer / strides change)
+    uint8_t* d_big = nullptr;           // scratch of fast_cells_big_kernel (plans with oversized cells only)
+    size_t big_cap = 0;
     FastTma tma;
     ResizeTma rtma;                     // source boxes of resize_tma_kernel; rtma_ok[l]: level l has a valid map
     bool rtma_ok[kMaxLevels] = {};
@@ -48,6 +50,8 @@ struct orbx_handle {
     size_t rtma_stride = 0, rtma_frame_stride = 0;
     bool rtma_lv0_valid = false;
   } lane[kLanes];
+  int32_t* d_big_cells = nullptr;   // indices of the oversized cells of the current plan
+  size_t big_cells_cap = 0;
   int plan_version = 0;
   int fast_mode = 0;                // 0 TMA kernel when the buffers allow it, 1 legacy kernel only (ORBX_FAST=legacy)
   int resize_mode = 0;              // pyramid kernels: 0 TMA for chunks of > 16 frames, 1 legacy only, 2 TMA always (ORBX_RESIZE)
@@ -227,10 +231,7 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     h->err = "image larger than the max_width x max_height the handle was created for";
     return ORBX_ERR_ARG;
   }
-  if (h->hp.fast_smem_bytes > 200 * 1024) {
-    h->err = "cell too large for the shared-memory FAST tile (cell area > ~100k px)";
-    return ORBX_ERR_UNSUPPORTED;
-  }
+  // (cells too large for the shared-memory FAST kernels are served by fast_cells_big_kernel: scratch below)
   // the tables below are read by kernels of earlier calls, which may still run on the lanes' streams or - single-chunk
   // device-API calls - on a caller's stream (ev_last): wait for all of them before overwriting
   for (int li = 0; li < h->nlanes; li++) {
@@ -238,6 +239,27 @@ static int upload_plan(orbx_handle* h, int w, int hgt) {
     if (h->lane[li].used) CK(cudaEventSynchronize(h->lane[li].ev_last));
   }
   h->plan_version++;
+  if (!h->hp.big_cells.empty()) {
+    // global scratch of the big-cell kernel (score map + bitmaps per big cell and frame), grown on demand: such plans
+    // are rare (few features on a large image), so the memory is not reserved at orbx_create
+    const size_t need = (size_t)h->hp.big_bytes_per_frame * h->p.max_batch;
+    for (int li = 0; li < h->nlanes; li++) {
+      orbx_handle::Lane& ln = h->lane[li];
+      if (ln.big_cap < need) {
+        if (ln.d_big) cudaFree(ln.d_big);
+        ln.d_big = nullptr; ln.big_cap = 0;
+        CK(cudaMalloc(&ln.d_big, need));
+        ln.big_cap = need;
+      }
+    }
+    if (h->big_cells_cap < h->hp.big_cells.size()) {
+      if (h->d_big_cells) cudaFree(h->d_big_cells);
+      h->d_big_cells = nullptr; h->big_cells_cap = 0;
+      CK(cudaMalloc(&h->d_big_cells, h->hp.big_cells.size() * sizeof(int32_t)));
+      h->big_cells_cap = h->hp.big_cells.size();
+    }
+    CK(cudaMemcpy(h->d_big_cells, h->hp.big_cells.data(), h->hp.big_cells.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  }
   CK(cudaMemcpy(h->d_plan, &dp, sizeof(dp), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(h->d_cells, h->hp.cells.data(), h->hp.cells.size() * sizeof(CellPlan), cudaMemcpyHostToDevice));
   if (!h->hp.rx.empty()) {
@@ -349,7 +371,7 @@ extern "C" void orbx_destroy(orbx_handle* h) {
   if (!h) return;
   cudaSetDevice(h->p.device);
   cudaDeviceSynchronize();
-  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry};
+  void* ptrs[] = {h->d_err, h->d_plan, h->d_cells, h->d_rx, h->d_ry, h->d_big_cells};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_err) cudaFreeHost(h->h_err);
   for (int i = 0; i < kLanes; i++) {
@@ -357,7 +379,7 @@ extern "C" void orbx_destroy(orbx_handle* h) {
     for (void* p : sp) if (p) cudaFree(p);
   }
   for (auto& ln : h->lane) {
-    void* lp[] = {ln.d_pyr, ln.d_blur, ln.d_cand, ln.d_list, ln.d_kp, ln.d_n_total, ln.d_n_retain, ln.d_kp_count};
+    void* lp[] = {ln.d_pyr, ln.d_blur, ln.d_cand, ln.d_list, ln.d_kp, ln.d_n_total, ln.d_n_retain, ln.d_kp_count, ln.d_big};
     for (void* p : lp) if (p) cudaFree(p);
     if (ln.s_main) cudaStreamDestroy(ln.s_main);
     if (ln.s_aux) cudaStreamDestroy(ln.s_aux);
@@ -411,6 +433,10 @@ static int run_chunk(orbx_handle* h, int li, const uint8_t* d_imgs, int n, size_
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   if (fast_tma) launch_fast_cells_tma(b, dp, ln.tma, n, s);
   else launch_fast_cells(b, dp, h->hp.fast_smem_bytes, n, s);
+  if (!h->hp.big_cells.empty()) {
+    launch_fast_cells_big(b, dp, h->d_big_cells, (int)h->hp.big_cells.size(), ln.d_big, h->hp.big_bytes_per_frame, n, s);
+    h->launches++;
+  }
   if (prof) cudaEventRecord(h->ev_stage[st++], s);
   if (prof) {                     // serial, so that the per-stage events mean something
     launch_select(b, dp, n, s, h->select_mode);

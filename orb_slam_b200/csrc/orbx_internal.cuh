@@ -45,7 +45,8 @@ struct alignas(16) CellPlan {   // 16-byte aligned: a kernel reads its record wi
   int16_t level;
   int16_t x0, y0;        // first scored pixel of the cell (= iniX + 3, iniY + 3) in level coordinates
   int16_t rw, rh;        // scored region size; 0 when the reference skips the cell (hX <= 0 / hY <= 0 / < 7 px)
-  int16_t skipped;       // 1: the reference `continue`s over this cell (hX <= 0 or hY <= 0)
+  int16_t skipped;       // bit 0: the reference `continue`s over this cell (hX <= 0 or hY <= 0); bit 1: "big" cell - its
+                         // sub-image does not fit the shared-memory kernels, fast_cells_big_kernel serves it
   int32_t cand_off;      // offset of the cell's candidate list in the per-frame candidate array
   int32_t cand_cap;      // ceil(rw/2)*ceil(rh/2): NMS survivors are pairwise non-adjacent, so this cannot overflow
   // reciprocal multipliers (fast_magic) of the three row lengths fast_cells_kernel splits flat indices by
@@ -66,6 +67,7 @@ struct alignas(16) CellPlan {   // 16-byte aligned: a kernel reads its record wi
   int32_t off_sc, off_bm, off_q;   // shared-memory byte offsets: score map (0: it overlays the raw image), bitmaps A + B, lists
   uint32_t m_g16;        // fast_magic(g16)
   uint32_t m_wprt;       // fast_magic(wpr)
+  int32_t big_off;       // big cells: byte offset of score map + bitmaps in the per-frame global scratch
 };
 
 struct ResizeX {  // per destination column: source column and the two 11-bit weights (cv::resize INTER_LINEAR)
@@ -101,6 +103,9 @@ struct HostPlan {
   bool fast_tma_ok;
   // TMA-staged resize (resize_tma_kernel): source box of a 128 x 64 destination tile of level l, 0 = not available
   int resize_box_w[kMaxLevels], resize_box_h[kMaxLevels];
+  // cells beyond the shared-memory kernels (few features on a large image): indices and global scratch per frame
+  std::vector<int32_t> big_cells;
+  int64_t big_bytes_per_frame;
 };
 
 // Shared-memory geometry of fast_cells_kernel for a cell sub-image of cw x ch pixels (scored region (cw-6) x (ch-6)):

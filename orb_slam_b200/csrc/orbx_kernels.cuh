@@ -63,6 +63,8 @@ void launch_resize_level_tma(const ChunkBuffers& b, const DevicePlan& hp, const 
                              cudaStream_t s);
 void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_bytes, int nframes, cudaStream_t s);
 void launch_fast_cells_tma(const ChunkBuffers& b, const DevicePlan& hp, const FastTma& tm, int nframes, cudaStream_t s);
+void launch_fast_cells_big(const ChunkBuffers& b, const DevicePlan& hp, const int32_t* d_big_cells, int nbig, uint8_t* d_scratch,
+                           int64_t scratch_per_frame, int nframes, cudaStream_t s);
 void launch_select(const ChunkBuffers& b, const DevicePlan& hp, int nframes, cudaStream_t s, int force);
 void launch_retain_best_debug(Cand* v, const int32_t* start, const int32_t* keep, int nlists, int retain_mode, int batch,
                               cudaStream_t s);

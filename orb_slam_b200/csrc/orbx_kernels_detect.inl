@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(kFastThreads, 1024 / kFastThreads) fast_cells_
   const CellPlan c = b.cells[cell];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int32_t* n_total = b.n_total + (int64_t)frame * fl.total_cells + cell;
+  if (c.skipped & 2) return;                       // a cell beyond shared memory: fast_cells_big_kernel's
   if (c.rw <= 0) {
     if (tid == 0) *n_total = 0;
     return;
@@ -457,6 +458,140 @@ void launch_fast_cells(const ChunkBuffers& b, const DevicePlan& hp, int smem_byt
   for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
   dim3 grid(hp.total_cells, nframes);
   launch_k(kern, grid, dim3(kFastThreads), (size_t)smem_bytes, s, b, fl);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Cells whose sub-image does not fit one CTA's shared memory (few features on a large image: e.g. 200 features at
+// 975 x 686 give 2 x 2 cells of 472 x 327 px).  Same per-cell semantics, worked in GLOBAL memory: the score of EVERY
+// pixel of the scored region straight from the level image (scalar ring walk, no reject), score map and survivor bitmaps
+// in a per-frame scratch block, NMS, retry at 7, ordered emission by one warp.  Rare and not tuned: a 150 k-pixel cell
+// takes a few hundred microseconds.
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int fast_score_scalar(const uint8_t* p, int pitch) {
+  const int v = p[0];
+  const int r[16] = {p[3 * pitch], p[3 * pitch + 1], p[2 * pitch + 2], p[pitch + 3], p[3], p[-pitch + 3], p[-2 * pitch + 2],
+                     p[-3 * pitch + 1], p[-3 * pitch], p[-3 * pitch - 1], p[-2 * pitch - 2], p[-pitch - 3], p[-3],
+                     p[pitch - 3], p[2 * pitch - 2], p[3 * pitch - 1]};
+  int bright = 0, dark = 255;                                 // max over arcs of min9(ring), min over arcs of max9(ring)
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    int mn = 255, mx = 0;
+#pragma unroll
+    for (int j = 0; j < 9; j++) { mn = min(mn, r[(k + j) & 15]); mx = max(mx, r[(k + j) & 15]); }
+    bright = max(bright, mn); dark = min(dark, mx);
+  }
+  return max(max(bright - v, v - dark) - 1, 0);               // as fast_pair_score
+}
+
+template <bool kHarris>
+__global__ void __launch_bounds__(1024) fast_cells_big_kernel(ChunkBuffers b, FastLevels fl, const int32_t* big_cells,
+                                                             uint8_t* scratch, int64_t scratch_per_frame) {
+  ORBX_PDL_ENTRY();
+  __shared__ int s_cnt[2];
+  const int cell = big_cells[blockIdx.x], frame = blockIdx.y;
+  const CellPlan c = b.cells[cell];
+  const int tid = threadIdx.x, lane = tid & 31, nthr = blockDim.x;
+  const int level = c.level, rw = c.rw, rh = c.rh;
+  const int pitch = level == 0 ? b.lv0_pitch : fl.pitch[level];
+  const uint8_t* img = level == 0 ? b.lv0 + (int64_t)frame * b.lv0_frame_stride
+                                  : b.pyr + (int64_t)frame * fl.frame_bytes + fl.off[level];
+  const int scp = fast_scp(rw), wpr = (rw + 31) >> 5, nbw = wpr * rh;
+  uint8_t* s_sc = scratch + (int64_t)frame * scratch_per_frame + c.big_off;      // [rh + 2][scp], pixel x at byte 4 + x
+  uint32_t* bmA = reinterpret_cast<uint32_t*>(s_sc + fast_sc_bytes(rw, rh));
+  uint32_t* bmB = bmA + nbw;
+  const int tA = fl.fast_th, tB = kRetryTh;
+  int tmin = max(tA > tB ? tA : min(tA, tB), 1);
+  const int nz = (fast_sc_bytes(rw, rh) + 8 * nbw) >> 2;
+  // the threshold-free score map is computed once; a retry at 7 only repeats the suppression
+  for (int i = tid; i < nz; i += nthr) reinterpret_cast<uint32_t*>(s_sc)[i] = 0;
+  if (tid < 2) s_cnt[tid] = 0;
+  __syncthreads();
+  for (int i = tid; i < rw * rh; i += nthr) {
+    const int y = i / rw, x = i - y * rw;
+    const int sc = fast_score_scalar(img + (int64_t)(c.y0 + y) * pitch + c.x0 + x, pitch);
+    if (sc) s_sc[(y + 1) * scp + 4 + x] = (uint8_t)sc;
+  }
+  __syncthreads();
+  bool useA;
+  for (;;) {
+    int nA = 0, nB = 0;
+    for (int i = tid; i < rw * rh; i += nthr) {
+      const int y = i / rw, x = i - y * rw;
+      const uint8_t* p = s_sc + (y + 1) * scp + 4 + x;
+      const int sc = p[0];
+      if (sc < tmin) continue;
+      const int m = max(max(max(p[-1], p[1]), max(p[-scp - 1], p[-scp])),
+                        max(max(p[-scp + 1], p[scp - 1]), max(p[scp], p[scp + 1])));
+      if (sc > m) {
+        const int w = y * wpr + (x >> 5);
+        if (sc >= tA) { atomicOr(&bmA[w], 1u << (x & 31)); nA++; }
+        if (sc >= tB) { atomicOr(&bmB[w], 1u << (x & 31)); nB++; }
+      }
+    }
+    nA = __reduce_add_sync(0xffffffffu, nA);
+    nB = __reduce_add_sync(0xffffffffu, nB);
+    if (lane == 0 && (nA | nB)) { atomicAdd(&s_cnt[0], nA); atomicAdd(&s_cnt[1], nB); }
+    __syncthreads();
+    useA = s_cnt[0] > 3;                          // :609-614
+    if (useA || tmin <= tB) break;
+    __syncthreads();
+    for (int i = tid; i < 2 * nbw; i += nthr) bmA[i] = 0;
+    if (tid < 2) s_cnt[tid] = 0;
+    tmin = tB;
+    __syncthreads();
+  }
+  const int total = useA ? s_cnt[0] : s_cnt[1];
+  int32_t* n_total = b.n_total + (int64_t)frame * fl.total_cells + cell;
+  if (tid == 0) *n_total = total;
+  if (total > c.cand_cap) {
+    if (tid == 0) atomicExch(b.err_flag, 1);
+    return;
+  }
+  if (total == 0 || tid >= 32) return;
+  const uint32_t* bm = useA ? bmA : bmB;
+  const int per = (nbw + 31) >> 5, w0 = min(lane * per, nbw), w1 = min(w0 + per, nbw);
+  int cnt = 0;
+  for (int i = w0; i < w1; i++) cnt += __popc(bm[i]);
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (cnt == 0) return;
+  Cand* out = b.cand + (int64_t)frame * fl.cand_per_frame + c.cand_off + (incl - cnt);
+  for (int i = w0; i < w1; i++) {
+    uint32_t bits = bm[i];
+    if (!bits) continue;
+    const int y = i / wpr, xb = 32 * (i - y * wpr);
+    const int ly = c.y0 + y;
+    while (bits) {
+      const int x = xb + __ffs(bits) - 1;
+      bits &= bits - 1;
+      const int lx = c.x0 + x;
+      Cand r;
+      if constexpr (kHarris) {
+        const LevelPlan& LP = b.plan->lv[level];
+        r.resp = (lx >= 4 && ly >= 4 && lx + 4 < LP.w && ly + 4 < LP.h)
+                     ? harris_response(img + (int64_t)ly * pitch + lx, pitch)
+                     : harris_response_edge(img, pitch, lx, ly, LP.w, LP.h);
+      } else {
+        r.resp = (float)s_sc[(y + 1) * scp + 4 + x];
+      }
+      r.xy = ((uint32_t)ly << 16) | (uint32_t)lx;
+      *out++ = r;
+    }
+  }
+}
+
+void launch_fast_cells_big(const ChunkBuffers& b, const DevicePlan& hp, const int32_t* d_big_cells, int nbig, uint8_t* d_scratch,
+                           int64_t scratch_per_frame, int nframes, cudaStream_t s) {
+  auto* kern = hp.score_type == ORBX_HARRIS_SCORE ? fast_cells_big_kernel<true> : fast_cells_big_kernel<false>;
+  FastLevels fl;
+  fl.fast_th = hp.fast_th; fl.score_type = hp.score_type; fl.total_cells = hp.total_cells;
+  fl.cand_per_frame = hp.cand_per_frame; fl.frame_bytes = hp.pyr_frame_bytes;
+  for (int l = 0; l < kMaxLevels; l++) { fl.pitch[l] = hp.lv[l].pitch; fl.off[l] = hp.lv[l].off; }
+  launch_k(kern, dim3(nbig, nframes), dim3(1024), 0, s, b, fl, d_big_cells, d_scratch, scratch_per_frame);
 }
 
 #include "orbx_kernels_detect_tma.inl"

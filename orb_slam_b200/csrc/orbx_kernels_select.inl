@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(128) select_kernel(ChunkBuffers b, int nwarps_
       const int nKeys = nTotal[c];
       // a cell the reference `continue`s over (:571, :595) keeps nToRetain = 0 / bNoMore = false and is NOT
       // counted in nNoMore; it still takes part in the redistribution below with nTotal = 0
-      if (cp.skipped) { nToRetain[c] = 0; continue; }
+      if (cp.skipped & 1) { nToRetain[c] = 0; continue; }
       if (nKeys > q) nToRetain[c] = q;
       else { nToRetain[c] = -nKeys - 1; nToDistribute += q - nKeys; nNoMore++; }
     }
@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(1024) select_smem_kernel(ChunkBuffers b, int n
 
   for (int c = tid; c < nCells; c += blockDim.x) {
     s_tot[c] = nTotal[c];
-    s_off[c] = cells[c].skipped;                       // borrowed until the prefix below
+    s_off[c] = cells[c].skipped & 1;                       // borrowed until the prefix below
   }
   __syncthreads();
   if (tid == 0) {                                      // quota + redistribution, :622-636 / :644-670 (see select_kernel)

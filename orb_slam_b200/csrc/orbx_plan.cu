@@ -99,6 +99,8 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
   int64_t pyr_off = 0, blur_off = 0, cand_off = 0;
   int cell_base = 0, kp_base = 0, list_base = 0;
   hp.fast_smem_bytes = 0;
+  hp.big_cells.clear();
+  hp.big_bytes_per_frame = 0;
   hp.fast_tma_smem_bytes = 0;
   hp.fast_tma_ok = true;
   for (int l = 0; l < kMaxLevels; l++) hp.fast_box_w[l] = hp.fast_box_h[l] = 0;
@@ -207,7 +209,16 @@ int build_plan(const orbx_params& p, int width, int height, HostPlan* out, std::
             c.m_grp = fast_magic(fast_ngrp(cw));
             c.m_g8 = fast_magic((c.rw + 7) / 8);
             c.m_wpr = fast_magic((c.rw + 31) / 32);
-            hp.fast_smem_bytes = std::max(hp.fast_smem_bytes, fast_cell_smem(cw, ch));
+            if (fast_cell_smem(cw, ch) > 200 * 1024) {
+              // too large for one CTA's shared memory: fast_cells_big_kernel works on it in global memory
+              c.skipped |= 2;
+              c.big_off = (int32_t)hp.big_bytes_per_frame;
+              hp.big_bytes_per_frame += (fast_sc_bytes(c.rw, c.rh) + 8 * fast_bm_words(c.rw, c.rh) + 255) & ~255;
+              hp.big_cells.push_back((int32_t)hp.cells.size());
+              hp.fast_tma_ok = false;
+            } else {
+              hp.fast_smem_bytes = std::max(hp.fast_smem_bytes, fast_cell_smem(cw, ch));
+            }
             c.lead = (int16_t)(c.x0 & 15);
             c.rwt = (int16_t)(c.lead + c.rw);
             c.g16 = (int16_t)((c.rwt + 15) / 16);

@@ -340,3 +340,28 @@ def test_device_api_with_unaligned_rows_takes_the_legacy_kernels(oracle):
     for f in range(3):
         ok, od = O(imgs[f])
         _cmp_final(k[f, :n[f]], dd[f, :n[f]], ok, od)
+
+
+@pytest.mark.parametrize("w,h,nf,nl,st,th", [(975, 686, 200, 8, 1, 20), (1200, 700, 150, 4, 0, 12), (900, 640, 100, 3, 1, 3)])
+def test_cells_beyond_shared_memory(oracle, w, h, nf, nl, st, th):
+    """Few features on a large image give cells of > 60 k pixels (2 x 2 cells of 472 x 327 at 975 x 686 / 200 features):
+    too large for the shared-memory FAST kernels, served by fast_cells_big_kernel in global memory.  Scene, noise (thousands
+    of corners per cell) and low-contrast (retry at 7) images, FAST and Harris scores, mixed with normal cells on the
+    smaller levels."""
+    rng = np.random.default_rng(3)
+    base = oracle.synth(h, w, 31)
+    imgs = [base, rng.integers(0, 256, (h, w), dtype=np.uint8), (base // 12 + 90).astype(np.uint8)]
+    O = oracle.OracleExtractor(nf, 1.2, nl, st, th)
+    ex = _ex(nfeatures=nf, nlevels=nl, scoreType=st, fastTh=th, max_width=w, max_height=h, max_batch=2)
+    big = 0
+    for l in range(nl):
+        i = ex.debug_level_info(l)
+        big += int((i["cellW"] + 6) * (i["cellH"] + 6) > 60_000)       # ~4.5 B of shared memory per pixel against 200 KB
+    assert big >= 1, "the configuration no longer has an oversized cell"
+    ref = [O(im) for im in imgs]
+    for im, (ok, od) in zip(imgs, ref):
+        k, d = ex(im)
+        _cmp_final(k, d, ok, od)
+    kps, desc, n = ex.extract_batch(np.stack(imgs))
+    for i in range(3):
+        _cmp_final(kps[i, :n[i]], desc[i, :n[i]], *ref[i])
