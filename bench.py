@@ -400,7 +400,7 @@ def main():
         if kclk and kclk.get("sm_mhz"):
             sms = torch.cuda.get_device_properties(dev).multi_processor_count
             peak = sms * BM.POPC_PER_CLK_PER_SM * kclk["sm_mhz"] * 1e6 * world
-            knn["roofline"].update({"peak": peak / 1e12, "frac": knn["value"] * 8 / peak, "clock_mhz_assumed": kclk["sm_mhz"]})
+            knn["roofline"]["popc_bound"].update({"peak": peak / 1e12, "frac": knn["value"] * 8 / peak, "clock_mhz_assumed": kclk["sm_mhz"]})
             knn["clocks"] = kclk
         init = BM.bench_init_search(args, rank, world, dev, local, mt)
         if rank == 0 and not args.no_cpu:
@@ -451,7 +451,7 @@ def main():
         if matching:
             k, i = matching["knn2_all_pairs"], matching["search_for_initialization"]
             sm.update({"knn2_pairs_s": float(f"{k['value']:.4g}"), "knn2_ms": round(k["ms_per_step"], 3),
-                       "knn2_frac_popc": round(k["roofline"]["frac"], 3), "knn2_nranks": world,
+                       "knn2_frac_tensor_fp8": round(k["roofline"]["frac"], 3), "knn2_x_popc_bound": round(k["roofline"]["popc_bound"]["frac"], 2), "knn2_nranks": world,
                        "sharded_equals_single": (k.get("check") or {}).get("sharded_equals_single"),
                        "knn2_accepted_frac": (k.get("check") or {}).get("accepted_frac"),
                        "init_pairs_s": round(i["value"]), "init_e2e_pairs_s": round(i["e2e"]["value"]),

@@ -52,6 +52,8 @@ struct orbm_handle {
   int num_sms = 148;
   int commit_mode = 0;       // 0 by job size, 1 in-order replay, 2 fixed point (ORBM_COMMIT, read at orbm_create)
   int knn_variant = 2;       // distance arithmetic of knn2_kernel (ORBM_KNN_VARIANT, read at orbm_create)
+  int knn_tc = -1;           // tensor-core 2-NN: -1 by job size, 0 never, 1 always (ORBM_KNN_TC, read at orbm_create)
+  bool knn_tc_ready = false; // knn2_tc_kernel's dynamic shared-memory limit has been raised on this device
   // workspaces
   orbm::DevBuf knn_part;     // per-chunk partial top-2 keys
   orbm::DevBuf stage_a, stage_b, stage_c;  // staging for host-pointer entry points

@@ -32,11 +32,13 @@ def _matcher_with(env):
 
 
 # every test of this file runs under the default commit choice (fixed point for <= 512 problems), under the in-order
-# replay (commit_kernel) and under the fixed point forced; the 2-NN tests under each distance-arithmetic variant
-@pytest.fixture(scope="module", params=["auto", "serial+knn0", "parallel+knn1"])
+# replay (commit_kernel) and under the fixed point forced; the 2-NN tests under each distance-arithmetic variant of the
+# POPC kernels (tensor-core kernel off) and with the tensor-core kernel forced for every size
+@pytest.fixture(scope="module", params=["auto", "serial+knn0", "parallel+knn1", "knn-tc"])
 def matcher(request):
-    env = {"auto": {}, "serial+knn0": {"ORBM_COMMIT": "serial", "ORBM_KNN_VARIANT": "0"},
-           "parallel+knn1": {"ORBM_COMMIT": "parallel", "ORBM_KNN_VARIANT": "1"}}[request.param]
+    env = {"auto": {}, "serial+knn0": {"ORBM_COMMIT": "serial", "ORBM_KNN_VARIANT": "0", "ORBM_KNN_TC": "0"},
+           "parallel+knn1": {"ORBM_COMMIT": "parallel", "ORBM_KNN_VARIANT": "1", "ORBM_KNN_TC": "0"},
+           "knn-tc": {"ORBM_KNN_TC": "1"}}[request.param]
     return _matcher_with(env)
 
 
@@ -210,6 +212,50 @@ def test_knn2(M, matcher):
         ref = M.knn2(q, db, idx_base=1000, threads=8)
         assert np.array_equal(got, ref), (nq, ndb)
     assert matcher.last_kernel_ms() > 0
+
+
+def test_knn2_tensor_core_kernel_edge_cases(M):
+    """knn2_tc_kernel (forced with ORBM_KNN_TC=1) against the oracle on the shapes and contents its schedule and its
+    filter have to survive: query counts around the 128 / 256 rows of a CTA / a pair, databases around the 256-descriptor
+    tile and smaller than one, one cluster range crossing several query-tile pairs (many queries, few tiles) and many
+    clusters sharing one pair (few queries, many tiles), a database of identical descriptors (every distance ties: the
+    lowest indices must win), a database far from every query (all distances > 128: the dot products are negative and
+    the integer-max shortcut must not be trusted), exact duplicates, an index base."""
+    tc = _matcher_with({"ORBM_KNN_TC": "1"})
+    pop = _matcher_with({"ORBM_KNN_TC": "0"})
+    rng = np.random.default_rng(2024)
+    shapes = [(1, 1), (1, 255), (127, 256), (128, 257), (129, 511), (255, 512), (256, 513), (257, 1000), (385, 3000),
+              (5000, 300), (3000, 40), (60, 70000), (2, 150000), (1000, 20011)]
+    for nq, ndb in shapes:
+        db = rng.integers(0, 256, (ndb, 32), dtype=np.uint8)
+        q = db[rng.integers(0, ndb, nq)].copy()
+        q ^= np.packbits(rng.random((nq, 256)) < 0.07, axis=1)
+        q[::5] = db[rng.integers(0, ndb, len(q[::5]))]           # exact copies: distance 0
+        ref = M.knn2(q, db, idx_base=37, threads=8)
+        got = tc.knn2(q, db, idx_base=37)
+        assert np.array_equal(got, ref), (nq, ndb)
+        assert np.array_equal(pop.knn2(q, db, idx_base=37), ref), (nq, ndb)
+    # every database descriptor identical: all distances tie, indices 0 and 1 win for every query
+    db = np.tile(rng.integers(0, 256, (1, 32), dtype=np.uint8), (3000, 1))
+    q = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    got = tc.knn2(q, db)
+    assert np.array_equal(got, M.knn2(q, db, threads=8))
+    assert np.all((got[:, 0] & 0x7FFFFF) == 0) and np.all((got[:, 1] & 0x7FFFFF) == 1)
+    # a database on the far side of EVERY query (queries: upper 128 bits clear; database: upper 128 bits set but for a
+    # few): every distance is above 128, every dot product negative
+    q = rng.integers(0, 256, (500, 32), dtype=np.uint8); q[:, 16:] = 0
+    far = rng.integers(0, 256, (20000, 32), dtype=np.uint8)
+    far[:, 16:] = 0xFF ^ np.packbits(rng.random((20000, 128)) < 0.04, axis=1)
+    far[123] = ~q[7]                                             # distance exactly 256 to query 7
+    ref = M.knn2(q, far, threads=8)
+    assert np.array_equal(tc.knn2(q, far), ref)
+    assert (ref[:, 0] >> 23).min() > 128
+    # mixed: half of the queries only have far neighbours, the others a near one late in the database - lanes of one
+    # warp with and without a usable threshold (a vote under that per-lane condition once hung the kernel)
+    mixed = far.copy(); mixed[15000:15250] = q[:250]
+    assert np.array_equal(tc.knn2(q, mixed), M.knn2(q, mixed, threads=8))
+    rng.shuffle(q)
+    assert np.array_equal(tc.knn2(q, mixed), M.knn2(q, mixed, threads=8))
 
 
 def test_knn2_sharded_merge_single_gpu(M, matcher):
