@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <climits>
+#include <cuda_fp16.h>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>

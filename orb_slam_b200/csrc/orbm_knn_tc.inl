@@ -160,37 +160,39 @@ constexpr long long kTcWaitClocks = 4000000000ll;
 __device__ __forceinline__ bool tc_wait(uint32_t bar, uint32_t parity) {
   long long t0 = 0;
 #pragma unroll 1
-  for (int spin = 0;; ++spin) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    if (ok) return true;
-    if ((spin & 63) == 63) {
-      const long long now = clock64();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > kTcWaitClocks) return false;
+  for (;;) {
+#pragma unroll 1
+    for (int spin = 0; spin < 64; ++spin) {                  // nothing but the try in the polling loop
+      uint32_t ok;
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+      if (ok) return true;
     }
+    const long long now = clock64();
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > kTcWaitClocks) return false;
   }
 }
 __device__ __forceinline__ bool tc_wait_cluster(uint32_t bar, uint32_t parity) {
   long long t0 = 0;
 #pragma unroll 1
-  for (int spin = 0;; ++spin) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    if (ok) return true;
-    if ((spin & 63) == 63) {
-      const long long now = clock64();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > kTcWaitClocks) return false;
+  for (;;) {
+#pragma unroll 1
+    for (int spin = 0; spin < 64; ++spin) {                  // nothing but the try in the polling loop
+      uint32_t ok;
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+      if (ok) return true;
     }
+    const long long now = clock64();
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > kTcWaitClocks) return false;
   }
 }
 
@@ -262,6 +264,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
     const int nseg = (int)min((int64_t)(ntiles - t0), lin1 - lin);
     const int qtile = 2 * pair + (int)rank;
     const int piece = (int)(cluster - ((int64_t)pair * ntiles) / per);
+    const int seg_rows = (int)(ndb - (int64_t)t0 * kTcN);   // database rows from the segment's first tile on (< 2^31)
 
     if (warp > kTcEpiWarps) {  // operand A: the CTA's 128 queries of this segment (rows past nq: +0.0 bytes)
       const int e = tid - 32 * (kTcEpiWarps + 1);
@@ -291,7 +294,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
         ok = tc_wait(smem_u32(&s_acc_full[a]), (uint32_t)(it >> 1) & 1u);
         if (!ok) break;
         tc_fence_after();
-        const int cnt = (int)min((int64_t)kTcN, ndb - (int64_t)t * kTcN) - half * kHalfCols;   // valid columns of this half
+        const int cnt = min(kTcN, seg_rows - i * kTcN) - half * kHalfCols;   // valid columns of this half
         const uint32_t kb = idx_base + (uint32_t)t * kTcN + (uint32_t)(half * kHalfCols);
 #pragma unroll 1
         for (int g = 0; g < kHalfCols / 64; g++) {
@@ -337,6 +340,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
     } else if (warp == kTcEpiWarps) {
       if (rank == 0) {
         // ================================ MMA issue: CTA 0 of the pair ===============================================
+        // (this one lane's instruction stream is the pace of the tensor pipe: keep it short)
+        const uint64_t adesc0 = tc_smem_desc(sA), bdesc0 = tc_smem_desc(sB);
         for (int i = 0; i < nseg && ok; ++i) {
           const int it = it0 + i, s = it % kTcStages, a = it & 1;
           const uint32_t ph = (uint32_t)(it / kTcStages) & 1u, pa = (uint32_t)(it >> 1) & 1u;
@@ -345,12 +350,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
           if (!ok) break;
           tc_fence_after();
           if (lane == 0) {
-            const uint32_t b0 = sB + (uint32_t)s * kTcBBytes, d = tmem + (uint32_t)(a * kTcN);
+            // descriptors differ in their start-address field only (16-byte units, low word): one add per operand
+            const uint32_t blo = (uint32_t)bdesc0 + (uint32_t)s * (kTcBBytes >> 4), d = tmem + (uint32_t)(a * kTcN);
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-              const uint64_t ad = tc_smem_desc(sA + (uint32_t)(k >> 2) * (kTcQ * 128u) + (uint32_t)(k & 3) * 32u);
-              const uint64_t bd = tc_smem_desc(b0 + (uint32_t)(k >> 2) * (kTcBRows * 128u) + (uint32_t)(k & 3) * 32u);
-              tc_mma(d, ad, bd, k > 0);
+              const uint32_t ka = ((uint32_t)(k >> 2) * (kTcQ * 128u) + (uint32_t)(k & 3) * 32u) >> 4;
+              const uint32_t kb = ((uint32_t)(k >> 2) * (kTcBRows * 128u) + (uint32_t)(k & 3) * 32u) >> 4;
+              tc_mma(d, (adesc0 & 0xFFFFFFFF00000000ull) | ((uint32_t)adesc0 + ka),
+                     (bdesc0 & 0xFFFFFFFF00000000ull) | (blo + kb), k > 0);
             }
             tc_commit(smem_u32(&s_free[s]));       // the stage may be refilled once these MMAs have read it
             tc_commit(smem_u32(&s_acc_full[a]));   // and the accumulator is complete
@@ -377,10 +384,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
       const int trow = (int)rank * kTcBRows + row;                // row of the whole 256-descriptor tile
       // packed descriptors are fetched two tile steps ahead into registers (a deeper register pipeline and L2 prefetch
       // instructions sixteen steps ahead were measured: no change, the expanders do not wait for memory)
+      const uint4* dbp = db + 2 * ((int64_t)t0 * kTcN + trow) + (e >> 7);   // this thread's 16 bytes of tile step 0
       auto fetch = [&](int i) {                                    // tile step i of the segment
         uint4 v = make_uint4(0, 0, 0, 0);
-        const int64_t j = (int64_t)(t0 + i) * kTcN + trow;
-        if (i < nseg && j < ndb) v = __ldg(db + 2 * j + (e >> 7));
+        if (i < nseg && trow < seg_rows - i * kTcN) v = __ldg(dbp + (size_t)i * (2 * kTcN));
         return v;
       };
       uint4 w0 = fetch(0), w1 = fetch(1);
@@ -390,7 +397,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
         if (it >= kTcStages) ok = tc_wait(smem_u32(&s_free[s]), (uint32_t)(it / kTcStages - 1) & 1u);
         if (!ok) break;
         const uint32_t b0 = sB + (uint32_t)s * kTcBBytes;
-        if ((int64_t)(t0 + i) * kTcN + trow < ndb) {
+        if (trow < seg_rows - i * kTcN) {
           const uint32_t w[4] = {w0.x, w0.y, w0.z, w0.w};
           tc_expand_words<4>(b0, kTcBRows, row, wbase, w);
         } else tc_zero_words<4>(b0, kTcBRows, row, wbase);        // past the end of the database: +0.0, ignored by the epilogue
