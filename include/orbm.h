@@ -292,7 +292,10 @@ int orbm_search_for_triangulation(orbm_handle* h, const orbm_frameset* set1, con
 /* ---- M8  all-pairs 2-NN over a descriptor database (BASELINE config 5) ---------------------------------------
  * Semantics of the reference's shared inner loop (src/ORBmatcher.cc:201-222) without exclusions: strict `<`, the
  * lowest index wins ties, the second best is the multiset second minimum.  top2[2 q], top2[2 q + 1] =
- * (dist << 23) | (idx_base + index) keys of the best and second best (0xFFFFFFFF = none); idx_base + ndb <= 2^23. */
+ * (dist << 23) | (idx_base + index) keys of the best and second best (0xFFFFFFFF = none); idx_base + ndb <= 2^23.
+ * Two implementations with bit-identical results, chosen by job size (ORBM_KNN_TC=0|1 at orbm_create forces one): jobs
+ * of 4 M query x database pairs and more run on the tensor cores (knn2_tc_kernel: every bit a +-1 FP8 value, distance =
+ * (256 - dot) / 2, sums exact), smaller ones on the XOR + POPC kernels. */
 #define ORBM_KEY_NONE 0xFFFFFFFFu
 #define ORBM_KEY_DIST(k) ((int)((k) >> 23))
 #define ORBM_KEY_INDEX(k) ((int)((k) & 0x7FFFFFu))

@@ -1,4 +1,4 @@
-"""Per-kernel SASS opcode histogram of liborbx.so (cuobjdump -sass), so that the UTMALDG / UBLKCP / SYNCS / IDP /
+"""Per-kernel SASS opcode histogram of liborbx.so (cuobjdump -sass), so that the UTCQMMA / LDTM (tcgen05, tensor memory) / UTMALDG / UBLKCP / SYNCS / IDP /
 VIMNMX3 / VABSDIFF4 claims of DESIGN.md can be checked without rebuilding.
     python tools/sass_opcodes.py > profiles/r2_sass_opcodes.txt"""
 import collections
@@ -18,9 +18,9 @@ for line in sass.splitlines():
         hist[cur][m.group(1)] += 1
 print("# per-kernel SASS opcode histogram of orb_slam_b200/liborbx.so (cuobjdump -sass, sm_100a), mnemonic without modifiers;")
 print("# top 14 per kernel + the Blackwell / Hopper data-movement and SIMD opcodes whatever their rank")
-key = ["UTMALDG", "UBLKCP", "SYNCS", "LDGSTS", "IDP", "VIMNMX3", "VIMNMX", "VABSDIFF4", "POPC", "REDUX", "ATOMS", "ACQBULK", "PREEXIT"]
+key = ["UTCQMMA", "UTCHMMA", "LDTM", "UTCBAR", "UTCATOMSWS", "UTMALDG", "UBLKCP", "SYNCS", "LDGSTS", "IDP", "VIMNMX3", "VIMNMX", "VABSDIFF4", "POPC", "REDUX", "ATOMS", "ACQBULK", "PREEXIT"]
 for k, c in hist.items():
-    name = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip().split("(")[0]
+    name = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip().replace("(anonymous namespace)::", "").split("(")[0]
     print(f"{name}  [{sum(c.values())} instr]")
     print("    top: " + ", ".join(f"{o} {n}" for o, n in c.most_common(14)))
     print("    key: " + ", ".join(f"{o} {c[o]}" for o in key if c[o]))
