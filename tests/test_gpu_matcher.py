@@ -258,6 +258,45 @@ def test_knn2_tensor_core_kernel_edge_cases(M):
     assert np.array_equal(tc.knn2(q, mixed), M.knn2(q, mixed, threads=8))
 
 
+def test_knn2_under_cuda_graph_capture(M):
+    """The device entry points only enqueue work, so they can be recorded into a CUDA graph once their scratch has been
+    reserved by a first call: the tensor-core kernel (a cluster launch + a memset), the POPC kernels and the
+    static-scratch entry point are captured in one graph, the graph is replayed on new data in the same buffers and
+    every result must equal the oracle."""
+    import torch
+    rng = np.random.default_rng(77)
+    nq, ndb = 700, 30000
+    tc, pop = _matcher_with({"ORBM_KNN_TC": "1"}), _matcher_with({"ORBM_KNN_TC": "0"})
+    d_q = torch.zeros((nq, 32), dtype=torch.uint8, device="cuda"); d_db = torch.zeros((ndb, 32), dtype=torch.uint8, device="cuda")
+    outs = [torch.zeros((nq, 2), dtype=torch.int32, device="cuda") for _ in range(3)]
+    st = torch.cuda.Stream()
+
+    def enqueue(sp):
+        tc.knn2_device(d_q.data_ptr(), nq, d_db.data_ptr(), ndb, 5, outs[0].data_ptr(), sp)
+        pop.knn2_device(d_q.data_ptr(), nq, d_db.data_ptr(), ndb, 5, outs[1].data_ptr(), sp)
+        pop.knn2_device_static(d_q.data_ptr(), nq, d_db.data_ptr(), ndb, 5, outs[2].data_ptr(), sp)
+
+    with torch.cuda.stream(st):
+        enqueue(st.cuda_stream)                                # warm-up: the handles reserve their scratch here
+    st.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=st):
+        enqueue(torch.cuda.current_stream().cuda_stream)
+    for seed in (1, 2):
+        db = rng.integers(0, 256, (ndb, 32), dtype=np.uint8)
+        q = db[rng.integers(0, ndb, nq)] ^ np.packbits(rng.random((nq, 256)) < 0.08, axis=1)
+        d_db.copy_(torch.from_numpy(db)); d_q.copy_(torch.from_numpy(q))
+        for o in outs:
+            o.zero_()
+        torch.cuda.synchronize()
+        g.replay()
+        torch.cuda.synchronize()
+        ref = M.knn2(q, db, idx_base=5, threads=8)
+        for k, o in enumerate(outs):
+            assert np.array_equal(o.cpu().numpy().view(np.uint32), ref), (seed, k)
+    tc.synchronize(); pop.synchronize()                        # raise on a deferred kernel error
+
+
 def test_knn2_sharded_merge_single_gpu(M, matcher):
     """The multi-GPU merge path on one device: 4 database shards searched separately, results laid out like the
     all-gather receive buffer, merged by orbm_merge_top2_device == one search over the whole database."""
