@@ -325,7 +325,7 @@ int orbm_knn2_device_static(orbm_handle* h, const uint8_t* d_q, int nq, const ui
 int orbm_knn2_device64(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int64_t idx_base,
                        uint64_t* d_top2, void* stream);
 /* Waits for the handle's stream and reports what the asynchronous entry points above and below could not return: a
- * database tile that never arrived in knn2_kernel (ORBM_ERR_CUDA; the affected queries hold ORBM_KEY_NONE keys) and an
+ * database tile or tensor-pipe signal that never arrived in knn2_kernel / knn2_tc_kernel (ORBM_ERR_CUDA; the affected queries hold ORBM_KEY_NONE keys) and an
  * asynchronous NCCL error on the communicator last used by orbm_knn2_sharded (ncclCommGetAsyncError, ORBM_ERR_COMM).
  * Work enqueued on a caller's stream must have been synchronised by the caller first.  The counterpart of
  * orbx_synchronize. */

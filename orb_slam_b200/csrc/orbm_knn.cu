@@ -126,7 +126,8 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
     return ORBM_ERR_UNSUPPORTED;
   }
   if (((uintptr_t)d_q | (uintptr_t)d_db) & 15) { h->err = "descriptor arrays must be 16-byte aligned"; return ORBM_ERR_ARG; }
-  // sticky: set by a CTA whose TMA tile never arrived, read and cleared by orbm_knn2 / orbm_synchronize
+  // sticky: set by a CTA whose mbarrier wait timed out (knn2_kernel: a TMA tile never arrived; knn2_tc_kernel: a stage /
+  // accumulator signal), read and cleared by orbm_knn2 / orbm_synchronize
   int* d_err = h->ws_misc.as<int>();
   if (nq == 0) return ORBM_OK;
   if (ndb == 0) { ORBM_CK(cudaMemsetAsync(d_top2, 0xFF, (size_t)nq * 8, s)); return ORBM_OK; }
@@ -207,7 +208,7 @@ int knn_check_err(orbm_handle* h) {  // call after the stream has been synchroni
   ORBM_CK(cudaMemcpy(&flag, h->ws_misc.p, sizeof(int), cudaMemcpyDeviceToHost));
   if (flag) {
     cudaMemset(h->ws_misc.p, 0, sizeof(int));
-    h->err = "knn2: TMA tile never arrived (mbarrier wait timed out); the affected queries hold 'none' keys";
+    h->err = "knn2: an mbarrier wait timed out (a TMA tile or a tensor-pipe signal never arrived); the affected queries hold 'none' keys";
     return ORBM_ERR_CUDA;
   }
   return ORBM_OK;
