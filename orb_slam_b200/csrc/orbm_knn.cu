@@ -158,14 +158,22 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    ORBM_CK(cudaLaunchKernelEx(&cfg, knn2_tc_kernel, reinterpret_cast<const uint4*>(d_q), nq,
-                               reinterpret_cast<const uint4*>(d_db), ndb, ntiles, per, total, (uint32_t)idx_base, part,
-                               d_err));
-    merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(part), pieces, nq, 0, 0.f,
-                                                      reinterpret_cast<uint2*>(d_top2), nullptr);
-    h->launches += 2;
-    ORBM_CK(cudaGetLastError());
-    return ORBM_OK;
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, knn2_tc_kernel, reinterpret_cast<const uint4*>(d_q), nq,
+                                              reinterpret_cast<const uint4*>(d_db), ndb, ntiles, per, total,
+                                              (uint32_t)idx_base, part, d_err);
+    if (le == cudaSuccess) {
+      merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(part), pieces, nq, 0, 0.f,
+                                                        reinterpret_cast<uint2*>(d_top2), nullptr);
+      h->launches += 2;
+      ORBM_CK(cudaGetLastError());
+      return ORBM_OK;
+    }
+    // A device or partition that cannot place the CTA pairs (cluster launch refused): when the tensor-core kernel was
+    // this handle's own choice, the POPC kernels below take the job - and every later one - instead; when it was forced
+    // (ORBM_KNN_TC=1) the refusal is the caller's to see.
+    (void)cudaGetLastError();
+    if (h->knn_tc == 1) { h->err = std::string("knn2_tc_kernel launch refused: ") + cudaGetErrorString(le); return ORBM_ERR_CUDA; }
+    h->knn_tc = 0;
   }
   // chunks: about 2 CTAs per SM over the whole grid; each chunk a whole number of tiles and >= 8 tiles (the TMA ring
   // needs a few tiles to reach its steady state).  A database too small to give every SM a CTA that way (frame-to-frame
