@@ -37,6 +37,13 @@ constexpr int kTcQ = 128, kTcN = 256;                       // queries per CTA, 
 constexpr int kTcEpiWarps = 8, kTcExpWarps = 8, kTcThreads = 32 * (kTcEpiWarps + 1 + kTcExpWarps);
 constexpr int kTcABytes = kTcQ * 256;
 
+// one lane of a converged warp, as a predicate ptxas keeps uniform: `if (lane == 0)` made it wrap every UTCQMMA in an
+// ELECT / BRA.U.ANY loop over the active lanes, ~100 clocks of dependent predicate logic per MMA on the issuing lane
+__device__ __forceinline__ bool tc_elect_one() {
+  uint32_t p;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+  return p != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // K-major SWIZZLE_128B shared-memory matrix descriptor: start address >> 4, LBO (unused for swizzled K-major) = 1,
@@ -69,13 +76,16 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 template <int NW>
 __device__ __forceinline__ void tc_expand_words(uint32_t tile, int nrows, int row, int wbase, const uint32_t (&w)[NW]) {
   const uint32_t rowbase = tile + (uint32_t)row * 128u, rx = ((uint32_t)row & 7u) << 4;
+  uint32_t c80 = 0x80808080u, c38 = 0x38383838u;
+  asm volatile("" : "+r"(c80), "+r"(c38));            // keep them in registers
 #pragma unroll
   for (int i = 0; i < NW; i++) {
 #pragma unroll
     for (int h = 0; h < 2; h++) {
       uint32_t o[4];
 #pragma unroll
-      for (int t = 0; t < 4; t++) o[t] = ((w[i] << (7 - (4 * h + t))) & 0x80808080u) | 0x38383838u;
+      for (int t = 0; t < 4; t++)   // (x & 0x80808080) | 0x38383838 as ONE lop3 (both constants in registers; ptxas emits two otherwise)
+        asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(o[t]) : "r"(w[i] << (7 - (4 * h + t))), "r"(c80), "r"(c38));
       const int chunk = 2 * (wbase + i) + h;               // wbase is a multiple of 4: the K block is uniform per call
       const uint32_t a = rowbase + (uint32_t)(chunk >> 3) * (uint32_t)nrows * 128u + ((((uint32_t)chunk & 7u) << 4) ^ rx);
       asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3])
@@ -142,6 +152,17 @@ __device__ __forceinline__ void tc_arrive_leader(uint32_t bar) {
       "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
       ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t tc_leader_addr(uint32_t bar) {   // the barrier at this offset in CTA 0, as a cluster address
+  uint32_t ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(ra) : "r"(bar));
+  return ra;
+}
+__device__ __forceinline__ void tc_arrive_remote(uint32_t ra) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
+}
+__device__ __forceinline__ void tc_arrive_remote_relaxed(uint32_t ra) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
 }
 // the same without release semantics: for the accumulator-free signal, whose only prior accesses are tcgen05.ld reads
 // already ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync
@@ -256,6 +277,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
   tc_cluster_sync();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
+  // barrier addresses once: taking them inside the tile loops cost a dozen instructions per use (S2UR of the cluster
+  // window, LEA, MAPA) on warps whose per-tile instruction count is the latency of the accumulator hand-back
+  const uint32_t b_full = smem_u32(&s_full[0]), b_peer = smem_u32(&s_peer_full[0]), b_free = smem_u32(&s_free[0]);
+  const uint32_t b_acc_full = smem_u32(&s_acc_full[0]), b_acc_free = smem_u32(&s_acc_free[0]);
+  const uint32_t r_acc_free = tc_leader_addr(b_acc_free), r_peer = tc_leader_addr(b_peer);
   bool ok = true;
   int it0 = 0;                                               // tile steps done so far: the barriers' phases run on
 
@@ -291,7 +317,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
       const uint32_t lane_addr = tmem + ((uint32_t)(32 * quarter) << 16) + (uint32_t)(half * kHalfCols);
       for (int i = 0; i < nseg && ok; ++i) {
         const int it = it0 + i, a = it & 1, t = t0 + i;
-        ok = tc_wait(smem_u32(&s_acc_full[a]), (uint32_t)(it >> 1) & 1u);
+        ok = tc_wait(b_acc_full + 8u * (uint32_t)a, (uint32_t)(it >> 1) & 1u);
         if (!ok) break;
         tc_fence_after();
         const int cnt = min(kTcN, seg_rows - i * kTcN) - half * kHalfCols;   // valid columns of this half
@@ -323,7 +349,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) tc_arrive_leader_relaxed(smem_u32(&s_acc_free[a]));
+        if (lane == 0) tc_arrive_remote_relaxed(r_acc_free + 8u * (uint32_t)a);
       }
       if (!ok) { atomicExch(err, 3); best = kNone; second = kNone; }
       // the two column halves of a query meet in shared memory
@@ -345,11 +371,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
         for (int i = 0; i < nseg && ok; ++i) {
           const int it = it0 + i, s = it % kTcStages, a = it & 1;
           const uint32_t ph = (uint32_t)(it / kTcStages) & 1u, pa = (uint32_t)(it >> 1) & 1u;
-          ok = tc_wait(smem_u32(&s_full[s]), ph) && tc_wait_cluster(smem_u32(&s_peer_full[s]), ph) &&
-               tc_wait_cluster(smem_u32(&s_acc_free[a]), pa ^ 1u);
+          // CTA-scope acquires on purpose: what the remote arrives order is shared memory read by the tensor core (async
+          // proxy, fenced by its writers), nothing this thread loads; a cluster-scope acquire costs a CCTL.IVALL - the
+          // whole L1 invalidated - on every successful wait (12 % of this warp's time in the ncu samples)
+          ok = tc_wait(b_full + 8u * (uint32_t)s, ph) && tc_wait(b_peer + 8u * (uint32_t)s, ph) &&
+               tc_wait(b_acc_free + 8u * (uint32_t)a, pa ^ 1u);
           if (!ok) break;
           tc_fence_after();
-          if (lane == 0) {
+          if (tc_elect_one()) {
             // descriptors differ in their start-address field only (16-byte units, low word): one add per operand
             const uint32_t blo = (uint32_t)bdesc0 + (uint32_t)s * (kTcBBytes >> 4), d = tmem + (uint32_t)(a * kTcN);
 #pragma unroll
@@ -359,8 +388,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
               tc_mma(d, (adesc0 & 0xFFFFFFFF00000000ull) | ((uint32_t)adesc0 + ka),
                      (bdesc0 & 0xFFFFFFFF00000000ull) | (blo + kb), k > 0);
             }
-            tc_commit(smem_u32(&s_free[s]));       // the stage may be refilled once these MMAs have read it
-            tc_commit(smem_u32(&s_acc_full[a]));   // and the accumulator is complete
+            tc_commit(b_free + 8u * (uint32_t)s);       // the stage may be refilled once these MMAs have read it
+            tc_commit(b_acc_full + 8u * (uint32_t)a);   // and the accumulator is complete
           }
           __syncwarp();
         }
@@ -370,9 +399,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
         // remotely cost it 700 clocks per tile and made the expanders the bottleneck.)
         for (int i = 0; i < nseg && ok; ++i) {
           const int it = it0 + i, s = it % kTcStages;
-          ok = tc_wait(smem_u32(&s_full[s]), (uint32_t)(it / kTcStages) & 1u);
+          ok = tc_wait(b_full + 8u * (uint32_t)s, (uint32_t)(it / kTcStages) & 1u);
           if (!ok) break;
-          if (lane == 0) tc_arrive_leader(smem_u32(&s_peer_full[s]));
+          if (lane == 0) tc_arrive_remote(r_peer + 8u * (uint32_t)s);
           __syncwarp();
         }
       }
@@ -394,7 +423,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
       for (int i = 0; i < nseg && ok; ++i) {
         const int it = it0 + i, s = it % kTcStages;
         const uint4 w2 = fetch(i + 2);
-        if (it >= kTcStages) ok = tc_wait(smem_u32(&s_free[s]), (uint32_t)(it / kTcStages - 1) & 1u);
+        if (it >= kTcStages) ok = tc_wait(b_free + 8u * (uint32_t)s, (uint32_t)(it / kTcStages - 1) & 1u);
         if (!ok) break;
         const uint32_t b0 = sB + (uint32_t)s * kTcBBytes;
         if (trow < seg_rows - i * kTcN) {
@@ -403,7 +432,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) knn2_tc_kernel(const uint4* __r
         } else tc_zero_words<4>(b0, kTcBRows, row, wbase);        // past the end of the database: +0.0, ignored by the epilogue
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&s_full[s]));
+        if (lane == 0) mbar_arrive(b_full + 8u * (uint32_t)s);
         w0 = w1; w1 = w2;
       }
       if (!ok && lane == 0) atomicExch(err, 3);

@@ -2,6 +2,7 @@
 // build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -I orb_slam_b200/csrc tools/scratch/tc_probe.cu -o gpurun_out/tc_probe
 #include <climits>
 #include <cuda_fp16.h>
+#include <cuda_fp16.h>
 #include <cstdio>
 #include <cstdlib>
 #include <algorithm>
