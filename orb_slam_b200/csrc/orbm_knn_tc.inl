@@ -145,14 +145,7 @@ __device__ __forceinline__ void tc_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// arrive on the barrier at the same shared-memory offset in CTA 0 of the cluster (the MMA-issuing CTA)
-__device__ __forceinline__ void tc_arrive_leader(uint32_t bar) {
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
-      ::"r"(bar) : "memory");
-}
+// remote arrives on barriers of CTA 0 (the MMA-issuing CTA)
 __device__ __forceinline__ uint32_t tc_leader_addr(uint32_t bar) {   // the barrier at this offset in CTA 0, as a cluster address
   uint32_t ra;
   asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(ra) : "r"(bar));
@@ -161,17 +154,10 @@ __device__ __forceinline__ uint32_t tc_leader_addr(uint32_t bar) {   // the barr
 __device__ __forceinline__ void tc_arrive_remote(uint32_t ra) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
 }
+// without release semantics: for the accumulator-free signal, whose only prior accesses are tcgen05.ld reads already
+// ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync (a release at cluster scope costs hundreds of clocks)
 __device__ __forceinline__ void tc_arrive_remote_relaxed(uint32_t ra) {
   asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
-}
-// the same without release semantics: for the accumulator-free signal, whose only prior accesses are tcgen05.ld reads
-// already ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync
-__device__ __forceinline__ void tc_arrive_leader_relaxed(uint32_t bar) {
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
-      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}"
-      ::"r"(bar) : "memory");
 }
 // Bounded waits: a lost signal must end as a reported error, never as a hung GPU.  The bound is TIME (about two
 // seconds of SM clock), not a try count: one try_wait may itself sleep for a system-defined while, and 2^20 of those
@@ -188,25 +174,6 @@ __device__ __forceinline__ bool tc_wait(uint32_t bar, uint32_t parity) {
       asm volatile(
           "{\n\t.reg .pred p;\n\t"
           "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-          "selp.u32 %0, 1, 0, p;\n\t}"
-          : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-      if (ok) return true;
-    }
-    const long long now = clock64();
-    if (t0 == 0) t0 = now;
-    else if (now - t0 > kTcWaitClocks) return false;
-  }
-}
-__device__ __forceinline__ bool tc_wait_cluster(uint32_t bar, uint32_t parity) {
-  long long t0 = 0;
-#pragma unroll 1
-  for (;;) {
-#pragma unroll 1
-    for (int spin = 0; spin < 64; ++spin) {                  // nothing but the try in the polling loop
-      uint32_t ok;
-      asm volatile(
-          "{\n\t.reg .pred p;\n\t"
-          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
           "selp.u32 %0, 1, 0, p;\n\t}"
           : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
       if (ok) return true;
