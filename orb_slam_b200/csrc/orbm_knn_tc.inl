@@ -159,11 +159,11 @@ __device__ __forceinline__ void tc_arrive_remote(uint32_t ra) {
 __device__ __forceinline__ void tc_arrive_remote_relaxed(uint32_t ra) {
   asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
 }
-// Bounded waits: a lost signal must end as a reported error, never as a hung GPU.  The bound is TIME (about two
-// seconds of SM clock), not a try count: one try_wait may itself sleep for a system-defined while, and 2^20 of those
+// Bounded waits: a lost signal must end as a reported error, never as a hung GPU.  The bound is TIME (about ten
+// seconds of SM clock - generous, so that a time-sliced or debugged GPU does not trip it), not a try count: one try_wait may itself sleep for a system-defined while, and 2^20 of those
 // was a twenty-minute "bounded" wait.  A suspend-time hint on try_wait was measured and dropped: the waiting warps wake
 // later (8.21 -> 8.45 ms on the 8,000 x 5 M job).
-constexpr long long kTcWaitClocks = 4000000000ll;
+constexpr long long kTcWaitClocks = 20000000000ll;
 __device__ __forceinline__ bool tc_wait(uint32_t bar, uint32_t parity) {
   long long t0 = 0;
 #pragma unroll 1
