@@ -316,6 +316,9 @@ int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* 
 #define ORBM_KNN2_STATIC_SCRATCH_BYTES (4u << 20)
 int orbm_knn2_device_static(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
                             int64_t idx_base, uint32_t* d_top2, void* stream);
+/* Test hook, no device needed: the work split of the tensor-core kernel for nq queries x ndb descriptors on num_sms SMs.
+ * out5 = {query-tile pairs, database tiles, clusters, tile steps per cluster, rows of the partial-result buffer}. */
+int orbm_debug_knn2_tc_plan(int nq, int64_t ndb, int num_sms, int64_t* out5);
 /* The same search for databases beyond the 2^23 indices of the 32-bit keys: d_top2 [nq][2] receives 64-bit keys
  * (dist << 40) | (idx_base + index), all ones = none; idx_base + ndb < 2^40.  The database is searched in segments of
  * 2^23 descriptors with the kernels above and merged on the device. */

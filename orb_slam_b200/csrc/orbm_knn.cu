@@ -115,6 +115,19 @@ extern "C" int orbm_descriptor_distance(orbm_handle* h, const uint8_t* a, const 
 
 namespace {
 
+// Work split of knn2_tc_kernel: (query-tile pairs) x (database tiles) tile steps, linearised pair-major, `per` consecutive
+// steps per cluster, one cluster per SM pair; `pieces` bounds how many clusters can share one query-tile pair (rows of the
+// partial-result buffer).  Host logic, covered without a GPU by tests/test_knn_tc_plan.py through orbm_debug_knn2_tc_plan.
+void knn_tc_plan(int nq, int64_t ndb, int num_sms, int* npairs, int* ntiles, int* clusters, int64_t* per, int* pieces) {
+  *npairs = ((nq + kTcQ - 1) / kTcQ + 1) / 2;
+  *ntiles = (int)((ndb + kTcN - 1) / kTcN);
+  const int64_t total = (int64_t)*npairs * *ntiles;          // tile steps, shared out evenly
+  int ncl = (int)std::max<int64_t>(1, std::min<int64_t>(num_sms / 2, total));
+  *per = (total + ncl - 1) / ncl;
+  *clusters = (int)((total + *per - 1) / *per);
+  *pieces = (int)((*ntiles + *per - 1) / *per) + 1;
+}
+
 int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int64_t idx_base,
                 uint32_t* d_top2, cudaStream_t s) {
   if (!d_q || !d_db || !d_top2 || nq < 0 || ndb < 0 || idx_base < 0) {
@@ -135,13 +148,10 @@ int knn2_launch(orbm_handle* h, const uint8_t* d_q, int nq, const uint8_t* d_db,
   // POPC kernels at 8,000 x 5 M; level at 1,000 x 1,000, where both are launch latency).  ORBM_KNN_TC=0|1 forces one.
   const bool tc = h->knn_tc < 0 ? (int64_t)nq * ndb >= (4ll << 20) : h->knn_tc == 1;
   if (tc) {
-    const int npairs = ((nq + kTcQ - 1) / kTcQ + 1) / 2;
-    const int ntiles = (int)((ndb + kTcN - 1) / kTcN);
-    const int64_t total = (int64_t)npairs * ntiles;          // tile steps, shared out evenly over one cluster per SM pair
-    int ncl = (int)std::max<int64_t>(1, std::min<int64_t>(h->num_sms / 2, total));
-    const int64_t per = (total + ncl - 1) / ncl;
-    ncl = (int)((total + per - 1) / per);
-    const int pieces = (int)((ntiles + per - 1) / per) + 1;  // clusters that can share one query-tile pair
+    int npairs, ntiles, ncl, pieces;
+    int64_t per;
+    knn_tc_plan(nq, ndb, h->num_sms, &npairs, &ntiles, &ncl, &per, &pieces);
+    const int64_t total = (int64_t)npairs * ntiles;
     ORBM_CK(h->knn_part.reserve((size_t)pieces * nq * 8 + 16));
     if (!h->knn_tc_ready) {
       ORBM_CK(cudaFuncSetAttribute(knn2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
@@ -231,6 +241,15 @@ extern "C" int orbm_knn2_device(orbm_handle* h, const uint8_t* d_q, int nq, cons
   if (!h) return ORBM_ERR_ARG;
   ORBM_CK(cudaSetDevice(h->device));
   return knn2_launch(h, d_q, nq, d_db, ndb, idx_base, d_top2, stream ? (cudaStream_t)stream : h->stream);
+}
+
+extern "C" int orbm_debug_knn2_tc_plan(int nq, int64_t ndb, int num_sms, int64_t* out5) {
+  if (nq < 1 || ndb < 1 || num_sms < 2 || !out5) return ORBM_ERR_ARG;
+  int npairs, ntiles, ncl, pieces;
+  int64_t per;
+  knn_tc_plan(nq, ndb, num_sms, &npairs, &ntiles, &ncl, &per, &pieces);
+  out5[0] = npairs; out5[1] = ntiles; out5[2] = ncl; out5[3] = per; out5[4] = pieces;
+  return ORBM_OK;
 }
 
 // ---- databases beyond the 2^23 indices of the packed 32-bit keys: 64-bit keys (dist << 40) | index ----------------------
